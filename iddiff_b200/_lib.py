@@ -1,0 +1,85 @@
+"""ctypes binding of libiddiff_b200.so (the C ABI declared in include/iddiff_b200.h).
+
+There is NO fallback: if the library is missing or a call is rejected, an exception is raised.
+The CPU implementation of this path is the reference itself (used only as oracle / baseline under
+oracle/, never from here).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libiddiff_b200.so")
+
+_lock = threading.Lock()
+_lib = None
+
+_vp = C.c_void_p
+_i = C.c_int
+_f = C.c_float
+_d = C.c_double
+_u64 = C.c_uint64
+_ll = C.c_longlong
+
+# name -> (restype, argtypes); must list every symbol of include/iddiff_b200.h
+SIGNATURES = {
+    "idb_abi_version": (_i, []),
+    "idb_last_error": (C.c_char_p, []),
+    "idb_perturb": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _f, _f, _u64, _u64, _vp, _vp, _vp, _vp]),
+    "idb_pack_weight": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
+    "idb_anchor_linear": (_i, [_vp, _i, _i, _f, _vp, _i, _vp, _vp, _i, _f, _vp, _i, _i, _i, _i, _vp]),
+    "idb_fcn_hidden_layer": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _i, _vp, _vp, _vp]),
+    "idb_fcn_output_layer": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp]),
+    "idb_fcn_scores": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _f, _vp, _vp]),
+    "idb_ksphere_gt_score": (_i, [_vp, _vp, _f, _i, _i, _i, _vp, _vp]),
+    "idb_center_gram": (_i, [_vp, _ll, _i, _i, _i, _i, _d, _vp, _vp, _vp]),
+    "idb_spectrum_workspace_bytes": (C.c_size_t, [_i, _i]),
+    "idb_spectrum": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
+    "idb_id_from_spectrum": (_i, [_vp, _i, _i, _i, _vp, _vp]),
+}
+
+
+class IdbError(RuntimeError):
+    pass
+
+
+def load():
+    """Loads the shared library (once).  Raises IdbError when it has not been built."""
+    global _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if not os.path.exists(LIB_PATH):
+            raise IdbError(f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(there is no CPU or PyTorch fallback for this path)")
+        lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+        return lib
+
+
+def call(name: str, *args):
+    """Calls an int-returning entry point and raises IdbError with idb_last_error() on failure."""
+    lib = load()
+    rc = getattr(lib, name)(*args)
+    if rc != 0:
+        raise IdbError(f"{name} failed ({rc}): {lib.idb_last_error().decode()}")
+
+
+def ptr(t):
+    """Device pointer of a CUDA tensor (or None)."""
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise IdbError("iddiff_b200 kernels take CUDA tensors only (no CPU path)")
+    return t.data_ptr()
+
+
+def stream_ptr():
+    import torch
+    return torch.cuda.current_stream().cuda_stream

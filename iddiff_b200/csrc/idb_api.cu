@@ -1,0 +1,149 @@
+// C ABI of libiddiff_b200.so -- see include/iddiff_b200.h for the contract of every entry point.
+#include "../../include/iddiff_b200.h"
+#include "idb_kernels.h"
+#include <stdio.h>
+
+namespace {
+thread_local char g_err[512] = "";
+
+int fail(const char* what) {
+    snprintf(g_err, sizeof(g_err), "%s", what);
+    return -1;
+}
+int check(cudaError_t e, const char* where) {
+    if (e == cudaSuccess) return 0;
+    snprintf(g_err, sizeof(g_err), "%s: %s", where, cudaGetErrorString(e));
+    return -2;
+}
+int num_sms() {
+    int dev = 0, n = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    return n;
+}
+bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+}  // namespace
+
+extern "C" {
+
+int idb_abi_version(void) { return 1; }
+const char* idb_last_error(void) { return g_err; }
+
+int idb_perturb(const float* x0, const float* z, int n_anchors, int K, int D, int Kp, int Dp, float mean_coeff,
+                float std, uint64_t seed, uint64_t anchor_id0, float* x_out, void* d_hi, void* d_lo, void* stream) {
+    if (!x0 || n_anchors < 0 || K <= 0 || D <= 0) return fail("idb_perturb: bad shape");
+    if ((d_hi == nullptr) != (d_lo == nullptr)) return fail("idb_perturb: d_hi and d_lo must both be set or both NULL");
+    if (d_hi && (Kp % 128 || Dp % 64 || Kp < K || Dp < D || !aligned16(d_hi) || !aligned16(d_lo)))
+        return fail("idb_perturb: need Kp % 128 == 0, Dp % 64 == 0, Kp >= K, Dp >= D, 16-byte aligned slabs");
+    if (!d_hi && !x_out) return fail("idb_perturb: no output requested");
+    idb::PerturbParams p;
+    p.x0 = x0; p.z = z; p.n_anchors = n_anchors; p.K = K; p.D = D;
+    p.Kp = d_hi ? Kp : K;
+    p.Dp = d_hi ? Dp : ((D + 7) & ~7);
+    p.mean_coeff = mean_coeff; p.std = std; p.seed = seed; p.anchor_id0 = anchor_id0;
+    p.x_out = x_out; p.d_hi = static_cast<uint8_t*>(d_hi); p.d_lo = static_cast<uint8_t*>(d_lo);
+    return check(idb::launch_perturb(p, static_cast<cudaStream_t>(stream)), "idb_perturb");
+}
+
+int idb_pack_weight(const float* w, int N, int K, int ldw, int Np, int Kc, void* hi, void* lo, void* stream) {
+    if (!w || !hi || !lo || N <= 0 || K <= 0 || ldw < K) return fail("idb_pack_weight: bad argument");
+    if (Np % 256 || Kc % 64 || Np < N || Kc < K || !aligned16(hi) || !aligned16(lo))
+        return fail("idb_pack_weight: need Np % 256 == 0, Kc % 64 == 0, Np >= N, Kc >= K, 16-byte aligned slabs");
+    return check(idb::launch_pack_weight(w, N, K, ldw, Np, Kc, static_cast<uint8_t*>(hi), static_cast<uint8_t*>(lo),
+                                         static_cast<cudaStream_t>(stream)),
+                 "idb_pack_weight");
+}
+
+int idb_anchor_linear(const float* in, int ld_in, int apply_elu, float in_scale, const float* w, int ldw,
+                      const float* bias, const float* extra_col, int extra_stride, float extra_scalar, float* out,
+                      int ld_out, int n_anchors, int N, int K, void* stream) {
+    if (!in || !w || !out || n_anchors < 0 || N <= 0 || K <= 0 || ld_in < K || ldw < K || ld_out < N)
+        return fail("idb_anchor_linear: bad argument");
+    return check(idb::launch_anchor_linear(in, ld_in, apply_elu, in_scale, w, ldw, bias, extra_col, extra_stride,
+                                           extra_scalar, out, ld_out, n_anchors, N, K,
+                                           static_cast<cudaStream_t>(stream)),
+                 "idb_anchor_linear");
+}
+
+static int gemm_common(int mode, const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, int M, int Np,
+                       int Kc, const float* a0, int rows_per_anchor, void* out_hi, void* out_lo, float* out_f32,
+                       void* stream, const char* name) {
+    if (!a_hi || !a_lo || !w_hi || !w_lo) return fail("idb_fcn_*_layer: NULL operand");
+    if (M < 0 || M % 128 || Np <= 0 || Np % 256 || Kc <= 0 || Kc % 64)
+        return fail("idb_fcn_*_layer: need M % 128 == 0, Np % 256 == 0, Kc % 64 == 0");
+    if (!aligned16(a_hi) || !aligned16(a_lo) || !aligned16(w_hi) || !aligned16(w_lo))
+        return fail("idb_fcn_*_layer: operands must be 16-byte aligned");
+    idb::GemmParams p;
+    p.a_hi = static_cast<const uint8_t*>(a_hi); p.a_lo = static_cast<const uint8_t*>(a_lo);
+    p.b_hi = static_cast<const uint8_t*>(w_hi); p.b_lo = static_cast<const uint8_t*>(w_lo);
+    p.M = M; p.Np = Np; p.Kc = Kc;
+    p.a0 = a0; p.rows_per_anchor = rows_per_anchor;
+    p.out_hi = static_cast<uint8_t*>(out_hi); p.out_lo = static_cast<uint8_t*>(out_lo);
+    p.out_f32 = out_f32;
+    return check(idb::launch_gemm_bf16x3(mode, p, num_sms(), static_cast<cudaStream_t>(stream)), name);
+}
+
+int idb_fcn_hidden_layer(const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, int M, int Np, int Kc,
+                         const float* a0, int rows_per_anchor, void* out_hi, void* out_lo, void* stream) {
+    if (!a0 || !out_hi || !out_lo || rows_per_anchor <= 0 || rows_per_anchor % 128 || M % rows_per_anchor)
+        return fail("idb_fcn_hidden_layer: need a0, outputs, rows_per_anchor % 128 == 0 and M % rows_per_anchor == 0");
+    if (!aligned16(out_hi) || !aligned16(out_lo)) return fail("idb_fcn_hidden_layer: outputs must be 16-byte aligned");
+    return gemm_common(0, a_hi, a_lo, w_hi, w_lo, M, Np, Kc, a0, rows_per_anchor, out_hi, out_lo, nullptr, stream,
+                       "idb_fcn_hidden_layer");
+}
+
+int idb_fcn_output_layer(const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, int M, int Np, int Kc,
+                         float* out_f32, void* stream) {
+    if (!out_f32 || !aligned16(out_f32)) return fail("idb_fcn_output_layer: out_f32 must be set and 16-byte aligned");
+    return gemm_common(1, a_hi, a_lo, w_hi, w_lo, M, Np, Kc, nullptr, 128, nullptr, nullptr, out_f32, stream,
+                       "idb_fcn_output_layer");
+}
+
+int idb_fcn_scores(const float* a_out, int ld_a, const float* d_out, int ld_d, int n_anchors, int K, int Kp, int D,
+                   float std, float* score, void* stream) {
+    if (!a_out || !d_out || !score || K <= 0 || Kp < K || D <= 0 || ld_a < D || ld_d < D || !(std > 0.f))
+        return fail("idb_fcn_scores: bad argument");
+    return check(idb::launch_fcn_scores(a_out, ld_a, d_out, ld_d, n_anchors, K, Kp, D, std, score,
+                                        static_cast<cudaStream_t>(stream)),
+                 "idb_fcn_scores");
+}
+
+int idb_ksphere_gt_score(const float* x, const float* sigma_rows, float sigma, int rows, int D, int manifold_dim,
+                         float* out, void* stream) {
+    if (!x || !out || rows < 0 || D <= 0 || manifold_dim < 2) return fail("idb_ksphere_gt_score: bad argument");
+    if (!sigma_rows && !(sigma > 0.f)) return fail("idb_ksphere_gt_score: sigma must be positive");
+    return check(idb::launch_ksphere_score(x, sigma_rows, sigma, rows, D, manifold_dim, out,
+                                           static_cast<cudaStream_t>(stream)),
+                 "idb_ksphere_gt_score");
+}
+
+int idb_center_gram(const float* X, long long anchor_stride, int ld, int n_anchors, int K, int D, double scale,
+                    double* colmean, double* G, void* stream) {
+    if (!X || !colmean || !G || n_anchors < 0 || K <= 0 || D <= 0 || ld < D)
+        return fail("idb_center_gram: bad argument");
+    return check(idb::launch_center_gram(X, anchor_stride, ld, n_anchors, K, D, scale, colmean, G,
+                                         static_cast<cudaStream_t>(stream)),
+                 "idb_center_gram");
+}
+
+size_t idb_spectrum_workspace_bytes(int n_anchors, int n) {
+    if (n_anchors <= 0 || n <= 0) return 256;
+    return idb::spectrum_workspace_bytes(n_anchors, n);
+}
+
+int idb_spectrum(const double* G, int n_anchors, int n, int n_out, float* sv, int* sweeps, void* workspace,
+                 void* stream) {
+    if (!G || !sv || !workspace || n_anchors < 0 || n <= 0 || n_out <= 0 || n_out > n)
+        return fail("idb_spectrum: bad argument");
+    if (!aligned16(workspace)) return fail("idb_spectrum: workspace must be 16-byte aligned");
+    return check(idb::launch_spectrum(G, n_anchors, n, n_out, sv, sweeps, workspace,
+                                      static_cast<cudaStream_t>(stream)),
+                 "idb_spectrum");
+}
+
+int idb_id_from_spectrum(const float* sv, int n_anchors, int n, int ld, int* dims, void* stream) {
+    if (!sv || !dims || n_anchors < 0 || n < 3 || ld < n) return fail("idb_id_from_spectrum: need n >= 3, ld >= n");
+    return check(idb::launch_id_readout(sv, n_anchors, n, ld, dims, static_cast<cudaStream_t>(stream)),
+                 "idb_id_from_spectrum");
+}
+
+}  // extern "C"

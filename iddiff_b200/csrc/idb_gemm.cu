@@ -1,0 +1,219 @@
+// Split-precision (bf16 x 3) tensor-core GEMM for the score-network "delta" chain.
+//
+//   acc[m, n] = sum_k (Ah + Al)[m, k] * (Bh + Bl)[n, k]   ~=  Ah.Bh + Al.Bh + Ah.Bl     (fp32 in TMEM)
+//
+// A = per-row deviations from the anchor activation (all K perturbations of an anchor share x0, so
+// the network is evaluated as anchor + deviation; see DESIGN.md "precision"), B = nn.Linear weight
+// [out, in] -- both K-major, both stored in HBM in the slab layout of idb_common.cuh, so every
+// operand tile is one contiguous bulk-TMA copy.
+//
+// Replaces, for models/fcn.py:20-30,38-39 (reference), the cuBLAS SGEMM + bias + ELU launches.
+//
+// Kernel shape: persistent, one CTA per SM, 192 threads:
+//   warp 0      : TMA producer   (cp.async.bulk -> 2-stage smem ring, 96 KB / stage)
+//   warp 1      : MMA issuer     (tcgen05.mma kind::f16, M=128 N=256 K=16, 12 per 64-wide k-block)
+//   warps 2..5  : epilogue       (tcgen05.ld 32x32b.x32; ELU-deviation + hi/lo split, or fp32 store)
+// TMEM: 2 x 256 fp32 columns, so the epilogue of tile i overlaps the MMAs of tile i+1.
+#include "idb_common.cuh"
+#include "idb_kernels.h"
+
+namespace idb {
+
+constexpr int BM = 128;
+constexpr int BN = 256;
+constexpr int BK = 64;
+constexpr int STAGES = 2;
+constexpr uint32_t A_TILE_BYTES = BM * 128;  // 16 KB (one of hi / lo)
+constexpr uint32_t B_TILE_BYTES = BN * 128;  // 32 KB
+constexpr uint32_t STAGE_BYTES = 2 * A_TILE_BYTES + 2 * B_TILE_BYTES;
+constexpr int GEMM_THREADS = 192;
+constexpr size_t GEMM_SMEM = 1024 /*align slack*/ + (size_t)STAGES * STAGE_BYTES + 2 * 2 * BN * sizeof(float) + 256;
+
+
+// ELU(a + d) - ELU(a) without cancellation; em1 = expm1(a) (only read when a <= 0).
+__device__ __forceinline__ float elu_deviation(float a, float em1, float d) {
+    const float s = a + d;
+    if (a > 0.f) return s > 0.f ? d : expm1f(s) - a;
+    return s > 0.f ? s - em1 : (em1 + 1.f) * expm1f(d);
+}
+
+template <int kMode>
+__global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_bf16x3_kernel(const GemmParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    float* s_a0 = reinterpret_cast<float*>(smem + (size_t)STAGES * STAGE_BYTES);  // [2][BN]
+    float* s_em1 = s_a0 + 2 * BN;                                                 // [2][BN]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(s_em1 + 2 * BN);
+    uint64_t* full = bars;                  // [STAGES]
+    uint64_t* empty = bars + STAGES;        // [STAGES]
+    uint64_t* tfull = bars + 2 * STAGES;    // [2]
+    uint64_t* tempty = bars + 2 * STAGES + 2;  // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int n_tiles_n = p.Np / BN;
+    const int n_tiles = (p.M / BM) * n_tiles_n;
+    const int n_kb = p.Kc / BK;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&tfull[s], 1);
+            mbar_init(&tempty[s], 128);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+                const size_t m0 = (size_t)(t / n_tiles_n) * BM;
+                const size_t n0 = (size_t)(t % n_tiles_n) * BN;
+                for (int kb = 0; kb < n_kb; ++kb) {
+                    mbar_wait(&empty[stage], phase ^ 1);
+                    uint8_t* st = smem + (size_t)stage * STAGE_BYTES;
+                    mbar_arrive_expect_tx(&full[stage], STAGE_BYTES);
+                    const size_t a_off = ((size_t)kb * p.M + m0) * 128;
+                    const size_t b_off = ((size_t)kb * p.Np + n0) * 128;
+                    tma_bulk_g2s(st, p.a_hi + a_off, A_TILE_BYTES, &full[stage]);
+                    tma_bulk_g2s(st + A_TILE_BYTES, p.a_lo + a_off, A_TILE_BYTES, &full[stage]);
+                    tma_bulk_g2s(st + 2 * A_TILE_BYTES, p.b_hi + b_off, B_TILE_BYTES, &full[stage]);
+                    tma_bulk_g2s(st + 2 * A_TILE_BYTES + B_TILE_BYTES, p.b_lo + b_off, B_TILE_BYTES, &full[stage]);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
+            int stage = 0;
+            uint32_t phase = 0;
+            int it = 0;
+            for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
+                const int as = it & 1;
+                const uint32_t aphase = (it >> 1) & 1;
+                mbar_wait(&tempty[as], aphase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + as * BN;
+                for (int kb = 0; kb < n_kb; ++kb) {
+                    mbar_wait(&full[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + (size_t)stage * STAGE_BYTES);
+                    const uint64_t ah = umma_desc_sw128(sa);
+                    const uint64_t al = umma_desc_sw128(sa + A_TILE_BYTES);
+                    const uint64_t bh = umma_desc_sw128(sa + 2 * A_TILE_BYTES);
+                    const uint64_t bl = umma_desc_sw128(sa + 2 * A_TILE_BYTES + B_TILE_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BK / 16; ++k) {
+                        const uint64_t adv = (uint64_t)((k * 32) >> 4);  // 16 bf16 = 32 B along K inside the swizzle atom
+                        umma_bf16(d_tmem, al + adv, bh + adv, idesc, (kb | k) != 0);
+                        umma_bf16(d_tmem, ah + adv, bl + adv, idesc, 1);
+                        umma_bf16(d_tmem, ah + adv, bh + adv, idesc, 1);
+                    }
+                    umma_commit(&empty[stage]);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(&tfull[as]);
+            }
+        }
+    } else {
+        const int et = threadIdx.x - 64;   // 0..127
+        const int quarter = warp & 3;      // TMEM lanes this warp may read: 32*quarter .. +31
+        const int row_in_tile = quarter * 32 + lane;
+        int it = 0;
+        for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
+            const int as = it & 1;
+            const uint32_t aphase = (it >> 1) & 1;
+            const size_t m0 = (size_t)(t / n_tiles_n) * BM;
+            const size_t n0 = (size_t)(t % n_tiles_n) * BN;
+            if (kMode == 0) {
+                const int anchor = (int)(m0 / (size_t)p.rows_per_anchor);
+                const float* a0 = p.a0 + (size_t)anchor * p.Np + n0;
+                for (int c = et; c < BN; c += 128) {
+                    const float a = __ldg(a0 + c);
+                    s_a0[as * BN + c] = a;
+                    s_em1[as * BN + c] = expm1f(fminf(a, 0.f));
+                }
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+            }
+            mbar_wait(&tfull[as], aphase);
+            tc_fence_after();
+            const size_t m = m0 + row_in_tile;
+            const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * BN;
+#pragma unroll 1
+            for (int cc = 0; cc < BN / 32; ++cc) {
+                uint32_t v[32];
+                tmem_ld32(t_row + cc * 32, v);
+                tmem_ld_wait();
+                if (kMode == 0) {
+                    const float* sa = s_a0 + as * BN + cc * 32;
+                    const float* se = s_em1 + as * BN + cc * 32;
+                    const size_t n = n0 + cc * 32;  // 32 columns = half of one 64-wide output slab
+                    uint8_t* row_hi = p.out_hi + ((n >> 6) * (size_t)p.M + m) * 128;
+                    uint8_t* row_lo = p.out_lo + ((n >> 6) * (size_t)p.M + m) * 128;
+                    const int chunk0 = (int)((n & 63) >> 3);
+#pragma unroll
+                    for (int ch = 0; ch < 4; ++ch) {
+                        uint32_t h[4], l[4];
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const int c = ch * 8 + j * 2;
+                            const float e0 = elu_deviation(sa[c], se[c], __uint_as_float(v[c]));
+                            const float e1 = elu_deviation(sa[c + 1], se[c + 1], __uint_as_float(v[c + 1]));
+                            __nv_bfloat16 h0, l0, h1, l1;
+                            split_bf16(e0, h0, l0);
+                            split_bf16(e1, h1, l1);
+                            h[j] = pack_bf16(h0, h1);
+                            l[j] = pack_bf16(l0, l1);
+                        }
+                        const int sw = ((chunk0 + ch) ^ (int)(m & 7)) << 4;
+                        *reinterpret_cast<uint4*>(row_hi + sw) = make_uint4(h[0], h[1], h[2], h[3]);
+                        *reinterpret_cast<uint4*>(row_lo + sw) = make_uint4(l[0], l[1], l[2], l[3]);
+                    }
+                } else {
+                    float4* dst = reinterpret_cast<float4*>(p.out_f32 + m * (size_t)p.Np + n0 + cc * 32);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        dst[j] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]),
+                                             __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+                }
+            }
+            tc_fence_before();
+            mbar_arrive(&tempty[as]);
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
+cudaError_t launch_gemm_bf16x3(int mode, const GemmParams& p, int num_sms, cudaStream_t stream) {
+    const int n_tiles = (p.M / BM) * (p.Np / BN);
+    const int grid = n_tiles < num_sms ? n_tiles : num_sms;
+    if (grid <= 0) return cudaSuccess;
+    cudaError_t e;
+    if (mode == 0) {
+        e = cudaFuncSetAttribute(gemm_bf16x3_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GEMM_SMEM);
+        if (e != cudaSuccess) return e;
+        gemm_bf16x3_kernel<0><<<grid, GEMM_THREADS, GEMM_SMEM, stream>>>(p);
+    } else {
+        e = cudaFuncSetAttribute(gemm_bf16x3_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GEMM_SMEM);
+        if (e != cudaSuccess) return e;
+        gemm_bf16x3_kernel<1><<<grid, GEMM_THREADS, GEMM_SMEM, stream>>>(p);
+    }
+    return cudaGetLastError();
+}
+
+}  // namespace idb

@@ -1,0 +1,65 @@
+// Internal launcher declarations shared by the .cu files and the C-ABI (idb_api.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace idb {
+
+struct GemmParams {
+    const uint8_t* a_hi;  // slab [Kc/64][M][128 B]
+    const uint8_t* a_lo;
+    const uint8_t* b_hi;  // slab [Kc/64][Np][128 B]
+    const uint8_t* b_lo;
+    int M, Np, Kc;
+    // mode 0 (hidden layer): anchor pre-activations in, slab-layout deviations out
+    const float* a0;  // [n_anchors][Np]
+    int rows_per_anchor;
+    uint8_t* out_hi;  // slab [Np/64][M][128 B]
+    uint8_t* out_lo;
+    // mode 1 (last layer): fp32 row-major [M][Np]
+    float* out_f32;
+};
+
+cudaError_t launch_gemm_bf16x3(int mode, const GemmParams& p, int num_sms, cudaStream_t stream);
+
+// fp32 [N][K] (row stride ldw) -> hi/lo bf16 slabs [Kc/64][Np][128 B], zero padded
+cudaError_t launch_pack_weight(const float* w, int N, int K, int ldw, int Np, int Kc, uint8_t* hi, uint8_t* lo,
+                               cudaStream_t stream);
+
+struct PerturbParams {
+    const float* x0;  // [n_anchors][D]
+    const float* z;   // [n_anchors][K][D] or null (Philox)
+    int n_anchors, K, D;
+    int Kp, Dp;       // padded rows per anchor / padded columns (slab outputs)
+    float mean_coeff, std;
+    uint64_t seed;
+    uint64_t anchor_id0;  // global id of anchor 0 of this call (Philox stream key)
+    float* x_out;     // optional fp32 [n_anchors][K][D] (perturbed points, reference arithmetic)
+    uint8_t* d_hi;    // optional slab [Dp/64][n_anchors*Kp][128 B]: deviation x - mean
+    uint8_t* d_lo;
+};
+cudaError_t launch_perturb(const PerturbParams& p, cudaStream_t stream);
+
+// out[a][n] = sum_k w[n][k] * act(in[a][k]) + bias[n] (+ extra_col[n] * extra_scalar);  act = identity or ELU
+cudaError_t launch_anchor_linear(const float* in, int ld_in, int apply_elu, float in_scale, const float* w, int ldw,
+                                 const float* bias, const float* extra_col, int extra_stride, float extra_scalar,
+                                 float* out, int ld_out, int n_anchors, int N, int K, cudaStream_t stream);
+
+// score[a][k][c] = -(a_out[a][c] + d_out[a*Kp + k][c]) / std   (models/utils.py:264-267)
+cudaError_t launch_fcn_scores(const float* a_out, int ld_a, const float* d_out, int ld_d, int n_anchors, int K, int Kp,
+                              int D, float std, float* score, cudaStream_t stream);
+
+cudaError_t launch_ksphere_score(const float* x, const float* sigma_or_null, float sigma, int rows, int D,
+                                 int manifold_dim, float* out, cudaStream_t stream);
+
+// column means (fp64) and centred Gram G = (scale (X - mean))^T (scale (X - mean)) in fp64
+cudaError_t launch_center_gram(const float* X, long long anchor_stride, int ld, int n_anchors, int K, int D,
+                               double scale, double* colmean, double* G, cudaStream_t stream);
+
+size_t spectrum_workspace_bytes(int n_anchors, int n);
+cudaError_t launch_spectrum(const double* G, int n_anchors, int n, int n_out, float* sv, int* sweeps, void* workspace,
+                            cudaStream_t stream);
+
+cudaError_t launch_id_readout(const float* sv, int n_anchors, int n, int ld, int* dims, cudaStream_t stream);
+
+}  // namespace idb

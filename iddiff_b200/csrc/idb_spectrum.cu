@@ -1,0 +1,354 @@
+// Spectrum stage: centre -> Gram (fp64) -> Cholesky (fp64) -> one-sided Jacobi on the triangular
+// factor (fp32, shared memory, one anchor per CTA, warp-shuffle rotations) -> singular values ->
+// spectral-gap read-out.  Replaces dim_reduction.py:190-199 (column centring + full LAPACK SVD
+// on the host) and plot_utils.py:224-229 (gap rule) of the reference.
+//
+// Why not an fp32 Gram + eigensolver: the spectra this path exists for have a cliff of 1e3 or more
+// between the tangent and normal singular values; squaring that in fp32 loses the tail.  The Gram
+// is therefore accumulated in fp64 (B200 has full-rate fp64 FMA; the stage is < 5 % of a step),
+// its Cholesky factor L (G = L L^T, so sv(L) = sv(centred scores)) is taken in fp64, and only
+// then rounded to fp32, where a one-sided Jacobi keeps high RELATIVE accuracy on graded columns.
+#include "idb_common.cuh"
+#include "idb_kernels.h"
+#include <math.h>
+
+namespace idb {
+
+// ---------------------------------- column means --------------------------------------------
+__global__ void __launch_bounds__(256) colmean_kernel(const float* __restrict__ X, long long anchor_stride, int ld,
+                                                      int K, int D, double* __restrict__ colmean) {
+    __shared__ double s_part[8][33];
+    const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+    const int rg = threadIdx.x >> 5;
+    const float* Xa = X + (size_t)blockIdx.y * anchor_stride;
+    double acc = 0.0;
+    if (c < D)
+        for (int k = rg; k < K; k += 8) acc += (double)Xa[(size_t)k * ld + c];
+    s_part[rg][threadIdx.x & 31] = acc;
+    __syncthreads();
+    if (rg == 0 && c < D) {
+        double t = 0.0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) t += s_part[i][threadIdx.x];
+        colmean[(size_t)blockIdx.y * D + c] = t / (double)K;
+    }
+}
+
+// ---------------------------------- centred Gram (fp64) -------------------------------------
+// One CTA = one 64 x 64 tile of G for one anchor (upper-triangular tile pairs only; mirrored on store).
+__global__ void __launch_bounds__(256) center_gram_kernel(const float* __restrict__ X, long long anchor_stride, int ld,
+                                                          int K, int D, double scale,
+                                                          const double* __restrict__ colmean, double* __restrict__ G) {
+    __shared__ double sA[16][64];
+    __shared__ double sB[16][64];
+    // decode (ti <= tj) from the linear pair index
+    const int T = (D + 63) >> 6;
+    int ti = 0, rem = blockIdx.x;
+    while (rem >= T - ti) { rem -= T - ti; ++ti; }
+    const int tj = ti + rem;
+    const int a = blockIdx.y;
+    const float* Xa = X + (size_t)a * anchor_stride;
+    const double* mu = colmean + (size_t)a * D;
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    double acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.0;
+
+    for (int k0 = 0; k0 < K; k0 += 16) {
+        for (int i = threadIdx.x; i < 16 * 64; i += 256) {
+            const int kk = i >> 6, c = i & 63;
+            const int k = k0 + kk;
+            const int ca = ti * 64 + c, cb = tj * 64 + c;
+            double va = 0.0, vb = 0.0;
+            if (k < K) {
+                if (ca < D) va = ((double)Xa[(size_t)k * ld + ca] - mu[ca]) * scale;
+                if (cb < D) vb = ((double)Xa[(size_t)k * ld + cb] - mu[cb]) * scale;
+            }
+            sA[kk][c] = va;
+            sB[kk][c] = vb;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < 16; ++kk) {
+            double av[4], bv[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) av[i] = sA[kk][ty * 4 + i];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) bv[j] = sB[kk][tx * 4 + j];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fma(av[i], bv[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+    double* Ga = G + (size_t)a * D * D;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int r = ti * 64 + ty * 4 + i;
+        if (r >= D) continue;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int c = tj * 64 + tx * 4 + j;
+            if (c >= D) continue;
+            Ga[(size_t)r * D + c] = acc[i][j];
+            if (ti != tj) Ga[(size_t)c * D + r] = acc[i][j];
+        }
+    }
+}
+
+cudaError_t launch_center_gram(const float* X, long long anchor_stride, int ld, int n_anchors, int K, int D,
+                               double scale, double* colmean, double* G, cudaStream_t stream) {
+    if (n_anchors <= 0 || D <= 0) return cudaSuccess;
+    colmean_kernel<<<dim3((D + 31) / 32, n_anchors), 256, 0, stream>>>(X, anchor_stride, ld, K, D, colmean);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    const int T = (D + 63) / 64;
+    center_gram_kernel<<<dim3(T * (T + 1) / 2, n_anchors), 256, 0, stream>>>(X, anchor_stride, ld, K, D, scale,
+                                                                             colmean, G);
+    return cudaGetLastError();
+}
+
+// ---------------------------------- Cholesky + one-sided Jacobi -----------------------------
+constexpr int SPEC_THREADS = 512;
+constexpr int SPEC_WARPS = SPEC_THREADS / 32;
+constexpr size_t SPEC_SMEM_MAX = 224 * 1024;
+
+__host__ __device__ inline size_t spec_ldb(int n) { return (size_t)((n + 1) & ~1) | 1; }  // odd stride >= n (+pad col room)
+__host__ __device__ inline size_t spec_packed_bytes(int n) { return (size_t)n * (n + 1) / 2 * sizeof(double); }
+__host__ __device__ inline size_t spec_square_bytes(int n) { return spec_ldb(n) * (size_t)((n + 1) & ~1) * sizeof(float); }
+
+size_t spectrum_workspace_bytes(int n_anchors, int n) {
+    // per anchor: packed fp64 factor (only used when it does not fit shared memory) + fp32 square factor
+    return (size_t)n_anchors * (spec_packed_bytes(n) + spec_square_bytes(n)) + 256;
+}
+
+// Tournament (circle-method) ordering: ne players (even), round r in [0, ne-1), slot i in [0, ne/2).
+__device__ __forceinline__ void rr_pair(int ne, int r, int i, int& p, int& q) {
+    const int m = ne - 1;
+    if (i == 0) {
+        p = m;
+        q = r;
+    } else {
+        p = (r + i) % m;
+        q = (r - i + m) % m;
+    }
+    if (p > q) { const int t = p; p = q; q = t; }
+}
+
+// L: packed lower triangle (row-major: L[i][j] at i(i+1)/2 + j), in shared or global memory.
+// B: fp32 column-major [ne columns][ldb], in shared or global memory.
+__global__ void __launch_bounds__(SPEC_THREADS, 1) spectrum_kernel(const double* __restrict__ G, int n, int n_out,
+                                                                   float* __restrict__ sv, int* __restrict__ sweeps,
+                                                                   uint8_t* __restrict__ workspace, int l_in_smem,
+                                                                   int b_in_smem) {
+    extern __shared__ __align__(16) uint8_t spec_smem[];
+    __shared__ double s_red[SPEC_WARPS];
+    __shared__ double s_pivot;
+    __shared__ int s_flag;
+    const int a = blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const size_t per_anchor = spec_packed_bytes(n) + spec_square_bytes(n);
+    uint8_t* ws = workspace + (size_t)a * per_anchor;
+    double* L = l_in_smem ? reinterpret_cast<double*>(spec_smem) : reinterpret_cast<double*>(ws);
+    float* Bg = reinterpret_cast<float*>(ws + spec_packed_bytes(n));
+    const double* Ga = G + (size_t)a * n * n;
+    const int ne = (n + 1) & ~1;
+    const size_t ldb = spec_ldb(n);
+
+    // ---- load the lower triangle, find max diagonal
+    double dmax = 0.0;
+    for (int idx = tid; idx < n * n; idx += SPEC_THREADS) {
+        const int i = idx / n, j = idx - i * n;
+        if (j <= i) {
+            const double v = Ga[idx];
+            L[(size_t)i * (i + 1) / 2 + j] = v;
+            if (i == j) dmax = fmax(dmax, v);
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) dmax = fmax(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
+    if (lane == 0) s_red[warp] = dmax;
+    __syncthreads();
+    dmax = 0.0;
+    for (int w = 0; w < SPEC_WARPS; ++w) dmax = fmax(dmax, s_red[w]);
+    const double thresh = dmax * (double)n * 2.3e-16;
+
+    // ---- right-looking Cholesky, positive semi-definite safe (a vanished pivot zeroes its column)
+    for (int j = 0; j < n; ++j) {
+        if (tid == 0) {
+            const double pv = L[(size_t)j * (j + 1) / 2 + j];
+            s_pivot = (pv > thresh && pv > 0.0) ? sqrt(pv) : 0.0;
+        }
+        __syncthreads();
+        const double d = s_pivot;
+        const double inv = d > 0.0 ? 1.0 / d : 0.0;
+        for (int i = j + tid; i < n; i += SPEC_THREADS) {
+            double* e = &L[(size_t)i * (i + 1) / 2 + j];
+            *e = (i == j) ? d : (*e) * inv;
+        }
+        __syncthreads();
+        if (d > 0.0) {
+            for (int i = j + 1 + warp; i < n; i += SPEC_WARPS) {
+                double* Li = &L[(size_t)i * (i + 1) / 2];
+                const double lij = Li[j];
+                for (int k = j + 1 + lane; k <= i; k += 32) Li[k] = fma(-lij, L[(size_t)k * (k + 1) / 2 + j], Li[k]);
+            }
+        }
+        __syncthreads();
+    }
+
+    // ---- B = L rounded to fp32, column-major with a zero pad column when n is odd
+    for (size_t idx = tid; idx < (size_t)ne * ldb; idx += SPEC_THREADS) {
+        const int j = (int)(idx / ldb), i = (int)(idx - (size_t)j * ldb);
+        float v = 0.f;
+        if (j < n && i < n && i >= j) v = (float)L[(size_t)i * (i + 1) / 2 + j];
+        Bg[idx] = v;
+    }
+    __syncthreads();
+    float* B = Bg;
+    if (b_in_smem) {
+        B = reinterpret_cast<float*>(spec_smem);
+        for (size_t idx = tid; idx < (size_t)ne * ldb; idx += SPEC_THREADS) B[idx] = Bg[idx];
+        __syncthreads();
+    }
+
+    // ---- one-sided Jacobi sweeps: orthogonalise the columns of B, one column pair per warp
+    const float tol = 2e-6f;
+    int sweep = 0;
+    for (; sweep < 40; ++sweep) {
+        int rotated = 0;
+        for (int r = 0; r < ne - 1; ++r) {
+            for (int i = warp; i < ne / 2; i += SPEC_WARPS) {
+                int p, q;
+                rr_pair(ne, r, i, p, q);
+                float* bp = B + (size_t)p * ldb;
+                float* bq = B + (size_t)q * ldb;
+                float al = 0.f, be = 0.f, ga = 0.f;
+                // columns of a lower-triangular start are zero above the diagonal only before the first
+                // rotation touches them, so always run the full length
+                for (int k = lane; k < n; k += 32) {
+                    const float x = bp[k], y = bq[k];
+                    al = fmaf(x, x, al);
+                    be = fmaf(y, y, be);
+                    ga = fmaf(x, y, ga);
+                }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    al += __shfl_xor_sync(0xffffffffu, al, o);
+                    be += __shfl_xor_sync(0xffffffffu, be, o);
+                    ga += __shfl_xor_sync(0xffffffffu, ga, o);
+                }
+                if (fabsf(ga) > tol * sqrtf(al * be) && al > 0.f && be > 0.f) {
+                    rotated = 1;
+                    const float zeta = (be - al) / (2.f * ga);
+                    const float tt = copysignf(1.f, zeta) / (fabsf(zeta) + sqrtf(fmaf(zeta, zeta, 1.f)));
+                    const float cs = rsqrtf(fmaf(tt, tt, 1.f));
+                    const float sn = cs * tt;
+                    for (int k = lane; k < n; k += 32) {
+                        const float x = bp[k], y = bq[k];
+                        bp[k] = fmaf(cs, x, -sn * y);
+                        bq[k] = fmaf(sn, x, cs * y);
+                    }
+                }
+            }
+            __syncthreads();
+        }
+        if (__syncthreads_or(rotated) == 0) break;
+    }
+
+    // ---- singular values = column norms (fp64 accumulate), sorted descending by rank
+    double* nrm = reinterpret_cast<double*>(ws);  // reuse the packed-L area of the workspace (n doubles)
+    __syncthreads();
+    for (int j = warp; j < n; j += SPEC_WARPS) {
+        const float* bj = B + (size_t)j * ldb;
+        double s = 0.0;
+        for (int k = lane; k < n; k += 32) s = fma((double)bj[k], (double)bj[k], s);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (lane == 0) nrm[j] = sqrt(s);
+    }
+    __threadfence_block();
+    __syncthreads();
+    for (int j = tid; j < n; j += SPEC_THREADS) {
+        const double v = nrm[j];
+        int rank = 0;
+        for (int i = 0; i < n; ++i) {
+            const double u = nrm[i];
+            rank += (u > v) || (u == v && i < j);
+        }
+        if (rank < n_out) sv[(size_t)a * n_out + rank] = (float)v;
+    }
+    if (tid == 0 && sweeps) sweeps[a] = sweep;
+    (void)s_flag;
+}
+
+cudaError_t launch_spectrum(const double* G, int n_anchors, int n, int n_out, float* sv, int* sweeps, void* workspace,
+                            cudaStream_t stream) {
+    if (n_anchors <= 0 || n <= 0) return cudaSuccess;
+    const int l_in_smem = spec_packed_bytes(n) <= SPEC_SMEM_MAX;
+    const int b_in_smem = spec_square_bytes(n) <= SPEC_SMEM_MAX;
+    size_t smem = 16;
+    if (l_in_smem) smem = spec_packed_bytes(n);
+    if (b_in_smem && spec_square_bytes(n) > smem) smem = spec_square_bytes(n);
+    cudaError_t e = cudaFuncSetAttribute(spectrum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    spectrum_kernel<<<n_anchors, SPEC_THREADS, smem, stream>>>(G, n, n_out, sv, sweeps,
+                                                               reinterpret_cast<uint8_t*>(workspace), l_in_smem,
+                                                               b_in_smem);
+    return cudaGetLastError();
+}
+
+// ---------------------------------- spectral-gap read-out -----------------------------------
+// plot_utils.py:224-229 in the reference's own arithmetic: Python floats (fp64) on the fp32 singular
+// values widened by s.tolist(); softmax as in plot_utils.py:211-214 (x - max, exp, / sum), first-occurrence
+// argmax with NumPy's NaN rule (the first NaN wins).  dims = -1 flags the reference's ZeroDivisionError.
+__global__ void __launch_bounds__(128) id_readout_kernel(const float* __restrict__ sv, int A, int n, int ld,
+                                                         int* __restrict__ dims) {
+    const int a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a >= A) return;
+    const float* s = sv + (size_t)a * ld;
+    const double nf = (double)s[1] - (double)s[2];
+    if (nf == 0.0) {
+        dims[a] = -1;
+        return;
+    }
+    const int m = n - 2;  // len(diff)
+    double mx = ((double)s[1] - (double)s[2]) / nf;
+    bool has_nan = mx != mx;
+    for (int i = 2; i < n - 1 && !has_nan; ++i) {
+        const double d = ((double)s[i] - (double)s[i + 1]) / nf;
+        if (d != d) has_nan = true;
+        else if (d > mx) mx = d;
+    }
+    if (has_nan) {
+        // np.max propagates NaN -> every soft entry is NaN -> argmax = 0
+        dims[a] = m;
+        return;
+    }
+    double sum = 0.0;
+    for (int i = 1; i < n - 1; ++i) sum += exp(((double)s[i] - (double)s[i + 1]) / nf - mx);
+    int best = 0;
+    double bv = -1.0;
+    bool nan_found = false;
+    for (int i = 1; i < n - 1; ++i) {
+        const double v = exp(((double)s[i] - (double)s[i + 1]) / nf - mx) / sum;
+        if (v != v) {
+            if (!nan_found) { best = i - 1; nan_found = true; }
+        } else if (!nan_found && v > bv) {
+            bv = v;
+            best = i - 1;
+        }
+    }
+    dims[a] = m - best;
+}
+
+cudaError_t launch_id_readout(const float* sv, int n_anchors, int n, int ld, int* dims, cudaStream_t stream) {
+    if (n_anchors <= 0) return cudaSuccess;
+    id_readout_kernel<<<(n_anchors + 127) / 128, 128, 0, stream>>>(sv, n_anchors, n, ld, dims);
+    return cudaGetLastError();
+}
+
+}  // namespace idb

@@ -1,0 +1,208 @@
+"""Device pipeline of the `manifold_dimension` hot path: thin Python over the C ABI.
+
+    anchors x0 --perturb--> deviations (bf16 hi/lo slabs) --tcgen05 GEMM chain--> d_out (fp32)
+            \\--fp32 anchor chain--> per-layer anchor pre-activations --^
+    d_out --centre + Gram (fp64)--> G --Cholesky + one-sided Jacobi--> singular values --gap rule--> ID
+
+Everything is batched over a chunk of anchors; nothing returns to the host until the spectra are
+done (the reference moves every score batch to the CPU, dim_reduction.py:183).  torch is used for
+device memory and streams only.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+from typing import List, Optional, Sequence
+
+import torch
+
+from . import _lib
+from ._lib import call, ptr, stream_ptr
+
+
+def _ceil(x: int, m: int) -> int:
+    return (x + m - 1) // m * m
+
+
+def _require_cuda(t: torch.Tensor, name: str):
+    if not (isinstance(t, torch.Tensor) and t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
+        raise _lib.IdbError(f"{name} must be a contiguous float32 CUDA tensor")
+
+
+@dataclass
+class SpectrumResult:
+    singular_values: torch.Tensor  # [A, n] fp32, descending (device)
+    dims: torch.Tensor             # [A] int32 (device); -1 where the reference raises ZeroDivisionError
+    sweeps: torch.Tensor           # [A] int32 Jacobi sweeps
+    scores: Optional[torch.Tensor] = None  # [A, K, D] fp32 raw scores when requested
+
+
+def spectrum_from_rows(X: torch.Tensor, K: int, D: int, scale: float, rows_per_anchor: Optional[int] = None
+                       ) -> SpectrumResult:
+    """dim_reduction.py:190-199 + plot_utils.py:224-229 on device.
+    X: [A, rows_per_anchor, ld] fp32 (rows >= K and columns >= D are ignored)."""
+    _require_cuda(X, "X")
+    A, R, ld = X.shape
+    if rows_per_anchor is not None and rows_per_anchor != R:
+        raise _lib.IdbError("rows_per_anchor mismatch")
+    if K < D:
+        raise NotImplementedError("K < D (row-side Gram) is not built yet; see DESIGN.md scope")
+    dev = X.device
+    colmean = torch.empty(A, D, dtype=torch.float64, device=dev)
+    G = torch.empty(A, D, D, dtype=torch.float64, device=dev)
+    st = stream_ptr()
+    call("idb_center_gram", ptr(X), R * ld, ld, A, K, D, float(scale), ptr(colmean), ptr(G), st)
+    n = D
+    n_out = min(K, D)
+    ws_bytes = _lib.load().idb_spectrum_workspace_bytes(A, n)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+    sv = torch.empty(A, n_out, dtype=torch.float32, device=dev)
+    sweeps = torch.empty(A, dtype=torch.int32, device=dev)
+    call("idb_spectrum", ptr(G), A, n, n_out, ptr(sv), ptr(sweeps), ptr(ws), st)
+    dims = torch.empty(A, dtype=torch.int32, device=dev)
+    if n_out >= 3:
+        call("idb_id_from_spectrum", ptr(sv), A, n_out, n_out, ptr(dims), st)
+    else:
+        dims.fill_(-2)
+    return SpectrumResult(sv, dims, sweeps)
+
+
+class FcnEngine:
+    """models/fcn.py FCN (Linear(D+1,H), L x Linear(H,H), Linear(H,D), ELU between) evaluated for all K
+    perturbations of a chunk of anchors.  Weights stay owned by the caller's module; this object keeps
+    packed bf16 hi/lo slab copies (tensor-core operands) and fp32 references (anchor chain)."""
+
+    def __init__(self, weights: Sequence[torch.Tensor], biases: Sequence[torch.Tensor]):
+        if len(weights) < 2 or len(weights) != len(biases):
+            raise _lib.IdbError("FCN needs >= 2 linear layers with biases")
+        self.w = [w.detach().contiguous() for w in weights]
+        self.b = [b.detach().contiguous() for b in biases]
+        for t in self.w + self.b:
+            _require_cuda(t, "FCN parameter")
+        self.dev = self.w[0].device
+        self.D = self.w[-1].shape[0]
+        if self.w[0].shape[1] != self.D + 1:
+            raise _lib.IdbError("first layer must take state_size + 1 inputs (time column, models/fcn.py:35-38)")
+        self.n_layers = len(self.w)
+        # padded dims: layer l maps Kc[l] -> Np[l]
+        self.in_real = [self.D] + [w.shape[0] for w in self.w[:-1]]
+        self.out_real = [w.shape[0] for w in self.w]
+        self.Np = [_ceil(n, 256) for n in self.out_real]
+        self.Kc = [_ceil(self.D, 64)] + self.Np[:-1]
+        st = stream_ptr()
+        self.w_hi, self.w_lo = [], []
+        for l, w in enumerate(self.w):
+            nbytes = self.Np[l] * self.Kc[l] * 2
+            hi = torch.empty(nbytes, dtype=torch.uint8, device=self.dev)
+            lo = torch.empty(nbytes, dtype=torch.uint8, device=self.dev)
+            call("idb_pack_weight", ptr(w), w.shape[0], self.in_real[l], w.shape[1], self.Np[l], self.Kc[l],
+                 ptr(hi), ptr(lo), st)
+            self.w_hi.append(hi)
+            self.w_lo.append(lo)
+
+    @classmethod
+    def from_module(cls, fcn_module: torch.nn.Module, device="cuda"):
+        """Ingests a reference `models.fcn.FCN` (or any module whose `.mlp` is the same Sequential)."""
+        lin = [m for m in fcn_module.mlp if isinstance(m, torch.nn.Linear)]
+        return cls([m.weight.detach().to(device, torch.float32) for m in lin],
+                   [m.bias.detach().to(device, torch.float32) for m in lin])
+
+    def rows_per_anchor(self, K: int) -> int:
+        return _ceil(K, 128)
+
+    def bytes_per_anchor(self, K: int) -> int:
+        Kp = self.rows_per_anchor(K)
+        act = max(self.Np[:-1]) * 2 * 2  # hi + lo, bf16
+        return Kp * (2 * act + self.Kc[0] * 4 + self.Np[-1] * 4) + self.D * self.D * 8 * 3
+
+    def anchor_chain(self, x0: torch.Tensor, mean_coeff: float, label: float) -> List[torch.Tensor]:
+        """Pre-activations of every layer at the un-perturbed anchors, fp32: list of [A, Np[l]]."""
+        A = x0.shape[0]
+        st = stream_ptr()
+        P = []
+        for l in range(self.n_layers):
+            out = torch.zeros(A, self.Np[l], dtype=torch.float32, device=self.dev)
+            if l == 0:
+                call("idb_anchor_linear", ptr(x0), self.D, 0, float(mean_coeff), ptr(self.w[0]), self.D + 1,
+                     ptr(self.b[0]), self.w[0].data_ptr() + 4 * self.D, self.D + 1, float(label), ptr(out),
+                     self.Np[0], A, self.out_real[0], self.D, st)
+            else:
+                call("idb_anchor_linear", ptr(P[-1]), self.Np[l - 1], 1, 1.0, ptr(self.w[l]), self.w[l].shape[1],
+                     ptr(self.b[l]), None, 0, 0.0, ptr(out), self.Np[l], A, self.out_real[l], self.in_real[l], st)
+            P.append(out)
+        return P
+
+    def deviations(self, x0: torch.Tensor, K: int, mean_coeff: float, std: float, label: float,
+                   z: Optional[torch.Tensor] = None, seed: int = 0, anchor_id0: int = 0):
+        """Runs perturb + anchor chain + GEMM chain.  Returns (d_out [A, Kp, Np_last] fp32, a_out [A, Np_last])."""
+        _require_cuda(x0, "x0")
+        A, D = x0.shape
+        if D != self.D:
+            raise _lib.IdbError(f"anchor dimension {D} != model state_size {self.D}")
+        if z is not None:
+            _require_cuda(z, "z")
+            if tuple(z.shape) != (A, K, D):
+                raise _lib.IdbError("z must be [A, K, D]")
+        Kp = self.rows_per_anchor(K)
+        M = A * Kp
+        st = stream_ptr()
+        dev = self.dev
+        e_hi = torch.empty(M * self.Kc[0] * 2, dtype=torch.uint8, device=dev)
+        e_lo = torch.empty(M * self.Kc[0] * 2, dtype=torch.uint8, device=dev)
+        call("idb_perturb", ptr(x0), ptr(z), A, K, D, Kp, self.Kc[0], float(mean_coeff), float(std), int(seed),
+             int(anchor_id0), None, ptr(e_hi), ptr(e_lo), st)
+        P = self.anchor_chain(x0, mean_coeff, label)
+        for l in range(self.n_layers - 1):
+            o_hi = torch.empty(M * self.Np[l] * 2, dtype=torch.uint8, device=dev)
+            o_lo = torch.empty(M * self.Np[l] * 2, dtype=torch.uint8, device=dev)
+            call("idb_fcn_hidden_layer", ptr(e_hi), ptr(e_lo), ptr(self.w_hi[l]), ptr(self.w_lo[l]), M, self.Np[l],
+                 self.Kc[l], ptr(P[l]), Kp, ptr(o_hi), ptr(o_lo), st)
+            e_hi, e_lo = o_hi, o_lo
+        l = self.n_layers - 1
+        d_out = torch.empty(A, Kp, self.Np[l], dtype=torch.float32, device=dev)
+        call("idb_fcn_output_layer", ptr(e_hi), ptr(e_lo), ptr(self.w_hi[l]), ptr(self.w_lo[l]), M, self.Np[l],
+             self.Kc[l], ptr(d_out), st)
+        return d_out, P[-1]
+
+    def estimate(self, x0: torch.Tensor, K: int, mean_coeff: float, std: float, label: float,
+                 z: Optional[torch.Tensor] = None, seed: int = 0, anchor_id0: int = 0,
+                 want_scores: bool = False) -> SpectrumResult:
+        d_out, a_out = self.deviations(x0, K, mean_coeff, std, label, z, seed, anchor_id0)
+        # centring removes the anchor part exactly: spectrum of (-(a + d)/std - mean) = spectrum of (d - mean(d))/std
+        res = spectrum_from_rows(d_out, K, self.D, 1.0 / std)
+        if want_scores:
+            A, Kp, ld = d_out.shape
+            sc = torch.empty(A, K, self.D, dtype=torch.float32, device=self.dev)
+            call("idb_fcn_scores", ptr(a_out), a_out.shape[1], ptr(d_out), ld, A, K, Kp, self.D, float(std), ptr(sc),
+                 stream_ptr())
+            res.scores = sc
+        return res
+
+
+class KSphereEngine:
+    """models/ksphere_gt.py analytic score + models/utils.py:169-175 wrapper."""
+
+    def __init__(self, manifold_dim: int, device="cuda"):
+        self.p = int(manifold_dim)
+        self.dev = torch.device(device)
+
+    def bytes_per_anchor(self, K: int, D: int) -> int:
+        return K * D * 8 + D * D * 24
+
+    def estimate(self, x0: torch.Tensor, K: int, mean_coeff: float, std: float, label: float = 0.0,
+                 z: Optional[torch.Tensor] = None, seed: int = 0, anchor_id0: int = 0,
+                 want_scores: bool = False) -> SpectrumResult:
+        _require_cuda(x0, "x0")
+        A, D = x0.shape
+        if z is not None:
+            _require_cuda(z, "z")
+        st = stream_ptr()
+        x = torch.empty(A, K, D, dtype=torch.float32, device=x0.device)
+        call("idb_perturb", ptr(x0), ptr(z), A, K, D, 0, 0, float(mean_coeff), float(std), int(seed), int(anchor_id0),
+             ptr(x), None, None, st)
+        sc = torch.empty_like(x)
+        call("idb_ksphere_gt_score", ptr(x), None, float(std), A * K, D, self.p, ptr(sc), st)
+        res = spectrum_from_rows(sc, K, D, 1.0)
+        if want_scores:
+            res.scores = sc
+        return res

@@ -1,0 +1,98 @@
+/* iddiff_b200 -- C ABI of the B200-native `manifold_dimension` hot path of GBATZOLIS/ID-diff.
+ *
+ * Conventions (all entry points):
+ *   - every pointer is a DEVICE pointer into caller-owned memory (torch tensors on the Python side);
+ *     nothing is allocated, freed or synchronised inside; the work is enqueued on `stream`
+ *     (a cudaStream_t passed as void*), mirroring the reference ops which launch on the current
+ *     ATen stream without syncing (op/upfirdn2d_kernel.cu:213-215 in the reference);
+ *   - return value 0 = enqueued, negative = rejected (bad argument or CUDA launch error);
+ *     idb_last_error() returns a thread-local description of the last failure;
+ *   - no global mutable state: callable from any host thread with its own stream.
+ *
+ * "slab layout": bf16 matrix [R rows][C cols], C % 64 == 0, R % 128 == 0, stored as C/64 k-slabs of
+ * R lines x 128 bytes, the eight 16-byte chunks of a line XOR-permuted by (row % 8): the
+ * SWIZZLE_128B K-major shared-memory image of tcgen05.mma, so an operand tile is one contiguous
+ * bulk-TMA copy.  byte offset of (r, c) = ((c/64)*R + r)*128 + ((((c%64)/8) ^ (r%8)) * 16) + (c%8)*2.
+ *
+ * Reference file:line citations are relative to the root of GBATZOLIS/ID-diff.
+ */
+#ifndef IDDIFF_B200_H
+#define IDDIFF_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+int idb_abi_version(void);
+const char* idb_last_error(void);
+
+/* Perturbation sampling: dim_reduction.py:178-182 (x.clone(); sde.marginal_prob; randn_like; mean + std*z)
+ * with sde_lib.py:342-347 / 250-254 / 300-304 / 181-186 folded into (mean_coeff, std) by the host
+ * (t is one constant for the whole run, dim_reduction.py:173-174).
+ *   x0 [n_anchors][D] fp32;  z [n_anchors][K][D] fp32 or NULL -> fused Philox4x32-10 + Box-Muller keyed by
+ *   (seed, anchor_id0 + a, row, column), so results do not depend on sharding or chunking.
+ * Outputs (either may be NULL): x_out [n_anchors][K][D] fp32 = fl(fl(mean_coeff*x0) + fl(std*z));
+ *   d_hi/d_lo slab layout [Dp/64][n_anchors*Kp][128B] = bf16 hi/lo split of (x - mean), rows >= K and
+ *   columns >= D zero.  Kp % 128 == 0, Dp % 64 == 0. */
+int idb_perturb(const float* x0, const float* z, int n_anchors, int K, int D, int Kp, int Dp, float mean_coeff,
+                float std, uint64_t seed, uint64_t anchor_id0, float* x_out, void* d_hi, void* d_lo, void* stream);
+
+/* nn.Linear weight [N][K] fp32 (row stride ldw) -> bf16 hi/lo slabs [Kc/64][Np][128B], zero padded.
+ * Np % 256 == 0, Kc % 64 == 0.  Done once per model (models/fcn.py:16-30 holds the weights). */
+int idb_pack_weight(const float* w, int N, int K, int ldw, int Np, int Kc, void* hi, void* lo, void* stream);
+
+/* One nn.Linear of models/fcn.py:20-30 evaluated in fp32 at the un-perturbed anchors:
+ *   out[a][n] = sum_k w[n][k] * f(in_scale*in[a][k]) + bias[n] + extra_col[n*extra_stride]*extra_scalar,
+ * f = ELU when apply_elu else identity; extra_col/extra_scalar carry the time column of
+ * torch.cat([x, t]) (models/fcn.py:35-38).  bias / extra_col may be NULL. */
+int idb_anchor_linear(const float* in, int ld_in, int apply_elu, float in_scale, const float* w, int ldw,
+                      const float* bias, const float* extra_col, int extra_stride, float extra_scalar, float* out,
+                      int ld_out, int n_anchors, int N, int K, void* stream);
+
+/* Hidden nn.Linear + ELU on the deviations (tcgen05, bf16x3 split precision, fp32 accumulate in TMEM):
+ *   acc = A (hi+lo) . W^T (hi+lo);  out = ELU(a0 + acc) - ELU(a0), re-split to bf16 hi/lo slabs [Np/64][M][128B].
+ * a0 [M/rows_per_anchor][Np] fp32 = anchor pre-activations of this layer.  M % 128 == 0, Np % 256 == 0,
+ * Kc % 64 == 0, rows_per_anchor % 128 == 0. */
+int idb_fcn_hidden_layer(const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, int M, int Np, int Kc,
+                         const float* a0, int rows_per_anchor, void* out_hi, void* out_lo, void* stream);
+
+/* Last nn.Linear on the deviations: out_f32 [M][Np] fp32 row-major = A (hi+lo) . W^T (hi+lo). */
+int idb_fcn_output_layer(const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, int M, int Np, int Kc,
+                         float* out_f32, void* stream);
+
+/* Raw scores as the reference's score_fn returns them (models/utils.py:264-267):
+ *   score[a][k][c] = -(a_out[a][c] + d_out[a*Kp + k][c]) / std,  score [n_anchors][K][D] fp32. */
+int idb_fcn_scores(const float* a_out, int ld_a, const float* d_out, int ld_d, int n_anchors, int K, int Kp, int D,
+                   float std, float* score, void* stream);
+
+/* Analytic k-sphere score, models/ksphere_gt.py:14-26 (+ models/utils.py:169-175: std passed, output
+ * returned unchanged).  x/out [rows][D] fp32; sigma_rows [rows] or NULL -> scalar sigma. */
+int idb_ksphere_gt_score(const float* x, const float* sigma_rows, float sigma, int rows, int D, int manifold_dim,
+                         float* out, void* stream);
+
+/* dim_reduction.py:190-194 + the Gram side of the SVD (:197): per anchor a, over rows k < K of
+ * X + a*anchor_stride (row stride ld, fp32): colmean[a][D] (fp64) and
+ * G[a][D][D] = sum_k (scale (X[k]-mean))^T (scale (X[k]-mean)) accumulated in fp64. */
+int idb_center_gram(const float* X, long long anchor_stride, int ld, int n_anchors, int K, int D, double scale,
+                    double* colmean, double* G, void* stream);
+
+/* Singular values of the centred score matrix from its Gram matrix (replaces torch.linalg.svd at
+ * dim_reduction.py:197-198): fp64 Cholesky G = L L^T, one-sided Jacobi on L in fp32, one anchor per CTA.
+ * sv [n_anchors][n_out] fp32 descending (n_out <= n: the reference returns min(K, D) values);
+ * sweeps [n_anchors] (may be NULL) = Jacobi sweeps used.  workspace: idb_spectrum_workspace_bytes. */
+size_t idb_spectrum_workspace_bytes(int n_anchors, int n);
+int idb_spectrum(const double* G, int n_anchors, int n, int n_out, float* sv, int* sweeps, void* workspace,
+                 void* stream);
+
+/* Spectral-gap read-out, plot_utils.py:224-229 (dup :173-182) with softmax :211-214:
+ * dims[a] = (n-2) - argmax softmax((s[i]-s[i+1])/(s[1]-s[2]), i=1..n-2); -1 where the reference raises
+ * ZeroDivisionError (s[1]==s[2]).  sv [n_anchors][ld] fp32, n >= 3. */
+int idb_id_from_spectrum(const float* sv, int n_anchors, int n, int ld, int* dims, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
