@@ -23,15 +23,17 @@ _d = C.c_double
 _u64 = C.c_uint64
 _ll = C.c_longlong
 
+FMT_BF16, FMT_FP16 = 0, 1
+
 # name -> (restype, argtypes); must list every symbol of include/iddiff_b200.h
 SIGNATURES = {
     "idb_abi_version": (_i, []),
     "idb_last_error": (C.c_char_p, []),
-    "idb_perturb": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _f, _f, _u64, _u64, _vp, _vp, _vp, _vp]),
-    "idb_pack_weight": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
+    "idb_perturb": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _f, _f, _u64, _u64, _vp, _i, _f, _vp, _vp, _vp]),
+    "idb_pack_weight": (_i, [_vp, _i, _i, _i, _i, _i, _i, _f, _vp, _vp, _vp]),
     "idb_anchor_linear": (_i, [_vp, _i, _i, _f, _vp, _i, _vp, _vp, _i, _f, _vp, _i, _i, _i, _i, _vp]),
-    "idb_fcn_hidden_layer": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _i, _vp, _vp, _vp]),
-    "idb_fcn_output_layer": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp]),
+    "idb_fcn_hidden_layer": (_i, [_vp, _vp, _vp, _vp, _i, _f, _f, _i, _i, _i, _vp, _i, _vp, _vp, _vp]),
+    "idb_fcn_output_layer": (_i, [_vp, _vp, _vp, _vp, _i, _f, _i, _i, _i, _vp, _vp]),
     "idb_fcn_scores": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _f, _vp, _vp]),
     "idb_ksphere_gt_score": (_i, [_vp, _vp, _f, _i, _i, _i, _vp, _vp]),
     "idb_center_gram": (_i, [_vp, _ll, _i, _i, _i, _i, _d, _vp, _vp, _vp]),

@@ -29,8 +29,11 @@ int idb_abi_version(void) { return 1; }
 const char* idb_last_error(void) { return g_err; }
 
 int idb_perturb(const float* x0, const float* z, int n_anchors, int K, int D, int Kp, int Dp, float mean_coeff,
-                float std, uint64_t seed, uint64_t anchor_id0, float* x_out, void* d_hi, void* d_lo, void* stream) {
+                float std, uint64_t seed, uint64_t anchor_id0, float* x_out, int fmt, float d_scale, void* d_hi,
+                void* d_lo, void* stream) {
     if (!x0 || n_anchors < 0 || K <= 0 || D <= 0) return fail("idb_perturb: bad shape");
+    if (d_hi && fmt != IDB_FMT_BF16 && fmt != IDB_FMT_FP16) return fail("idb_perturb: unknown fmt");
+    if (d_hi && !(d_scale > 0.f)) return fail("idb_perturb: d_scale must be positive");
     if ((d_hi == nullptr) != (d_lo == nullptr)) return fail("idb_perturb: d_hi and d_lo must both be set or both NULL");
     if (d_hi && (Kp % 128 || Dp % 64 || Kp < K || Dp < D || !aligned16(d_hi) || !aligned16(d_lo)))
         return fail("idb_perturb: need Kp % 128 == 0, Dp % 64 == 0, Kp >= K, Dp >= D, 16-byte aligned slabs");
@@ -40,15 +43,21 @@ int idb_perturb(const float* x0, const float* z, int n_anchors, int K, int D, in
     p.Kp = d_hi ? Kp : K;
     p.Dp = d_hi ? Dp : ((D + 7) & ~7);
     p.mean_coeff = mean_coeff; p.std = std; p.seed = seed; p.anchor_id0 = anchor_id0;
+    p.fmt = fmt; p.d_scale = d_scale;
     p.x_out = x_out; p.d_hi = static_cast<uint8_t*>(d_hi); p.d_lo = static_cast<uint8_t*>(d_lo);
     return check(idb::launch_perturb(p, static_cast<cudaStream_t>(stream)), "idb_perturb");
 }
 
-int idb_pack_weight(const float* w, int N, int K, int ldw, int Np, int Kc, void* hi, void* lo, void* stream) {
+int idb_pack_weight(const float* w, int N, int K, int ldw, int Np, int Kc, int w_fmt, float scale, void* hi, void* lo,
+                    void* stream) {
+    const int IDB_W_BF16 = IDB_FMT_BF16, IDB_W_FP16 = IDB_FMT_FP16;
     if (!w || !hi || !lo || N <= 0 || K <= 0 || ldw < K) return fail("idb_pack_weight: bad argument");
+    if (w_fmt != IDB_W_BF16 && w_fmt != IDB_W_FP16) return fail("idb_pack_weight: unknown w_fmt");
+    if (w_fmt == IDB_W_BF16 && scale != 1.0f) return fail("idb_pack_weight: scale must be 1 for IDB_W_BF16");
+    if (!(scale > 0.f)) return fail("idb_pack_weight: scale must be positive");
     if (Np % 256 || Kc % 64 || Np < N || Kc < K || !aligned16(hi) || !aligned16(lo))
         return fail("idb_pack_weight: need Np % 256 == 0, Kc % 64 == 0, Np >= N, Kc >= K, 16-byte aligned slabs");
-    return check(idb::launch_pack_weight(w, N, K, ldw, Np, Kc, static_cast<uint8_t*>(hi), static_cast<uint8_t*>(lo),
+    return check(idb::launch_pack_weight(w, N, K, ldw, Np, Kc, w_fmt, scale, static_cast<uint8_t*>(hi), static_cast<uint8_t*>(lo),
                                          static_cast<cudaStream_t>(stream)),
                  "idb_pack_weight");
 }
@@ -64,10 +73,12 @@ int idb_anchor_linear(const float* in, int ld_in, int apply_elu, float in_scale,
                  "idb_anchor_linear");
 }
 
-static int gemm_common(int mode, const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, int M, int Np,
-                       int Kc, const float* a0, int rows_per_anchor, void* out_hi, void* out_lo, float* out_f32,
+static int gemm_common(int mode, const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, int w_fmt,
+                       float w_inv_scale, float out_scale, int M, int Np, int Kc, const float* a0, int rows_per_anchor, void* out_hi, void* out_lo, float* out_f32,
                        void* stream, const char* name) {
     if (!a_hi || !a_lo || !w_hi || !w_lo) return fail("idb_fcn_*_layer: NULL operand");
+    if (w_fmt != IDB_FMT_BF16 && w_fmt != IDB_FMT_FP16) return fail("idb_fcn_*_layer: unknown fmt");
+    if (!(w_inv_scale > 0.f) || !(out_scale > 0.f)) return fail("idb_fcn_*_layer: scales must be positive");
     if (M < 0 || M % 128 || Np <= 0 || Np % 256 || Kc <= 0 || Kc % 64)
         return fail("idb_fcn_*_layer: need M % 128 == 0, Np % 256 == 0, Kc % 64 == 0");
     if (!aligned16(a_hi) || !aligned16(a_lo) || !aligned16(w_hi) || !aligned16(w_lo))
@@ -76,25 +87,27 @@ static int gemm_common(int mode, const void* a_hi, const void* a_lo, const void*
     p.a_hi = static_cast<const uint8_t*>(a_hi); p.a_lo = static_cast<const uint8_t*>(a_lo);
     p.b_hi = static_cast<const uint8_t*>(w_hi); p.b_lo = static_cast<const uint8_t*>(w_lo);
     p.M = M; p.Np = Np; p.Kc = Kc;
+    p.fmt = w_fmt; p.acc_scale = w_inv_scale; p.out_scale = out_scale;
     p.a0 = a0; p.rows_per_anchor = rows_per_anchor;
     p.out_hi = static_cast<uint8_t*>(out_hi); p.out_lo = static_cast<uint8_t*>(out_lo);
     p.out_f32 = out_f32;
     return check(idb::launch_gemm_bf16x3(mode, p, num_sms(), static_cast<cudaStream_t>(stream)), name);
 }
 
-int idb_fcn_hidden_layer(const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, int M, int Np, int Kc,
-                         const float* a0, int rows_per_anchor, void* out_hi, void* out_lo, void* stream) {
+int idb_fcn_hidden_layer(const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, int w_fmt,
+                         float w_inv_scale, float out_scale, int M, int Np, int Kc, const float* a0,
+                         int rows_per_anchor, void* out_hi, void* out_lo, void* stream) {
     if (!a0 || !out_hi || !out_lo || rows_per_anchor <= 0 || rows_per_anchor % 128 || M % rows_per_anchor)
         return fail("idb_fcn_hidden_layer: need a0, outputs, rows_per_anchor % 128 == 0 and M % rows_per_anchor == 0");
     if (!aligned16(out_hi) || !aligned16(out_lo)) return fail("idb_fcn_hidden_layer: outputs must be 16-byte aligned");
-    return gemm_common(0, a_hi, a_lo, w_hi, w_lo, M, Np, Kc, a0, rows_per_anchor, out_hi, out_lo, nullptr, stream,
+    return gemm_common(0, a_hi, a_lo, w_hi, w_lo, w_fmt, w_inv_scale, out_scale, M, Np, Kc, a0, rows_per_anchor, out_hi, out_lo, nullptr, stream,
                        "idb_fcn_hidden_layer");
 }
 
-int idb_fcn_output_layer(const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, int M, int Np, int Kc,
-                         float* out_f32, void* stream) {
+int idb_fcn_output_layer(const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, int w_fmt,
+                         float w_inv_scale, int M, int Np, int Kc, float* out_f32, void* stream) {
     if (!out_f32 || !aligned16(out_f32)) return fail("idb_fcn_output_layer: out_f32 must be set and 16-byte aligned");
-    return gemm_common(1, a_hi, a_lo, w_hi, w_lo, M, Np, Kc, nullptr, 128, nullptr, nullptr, out_f32, stream,
+    return gemm_common(1, a_hi, a_lo, w_hi, w_lo, w_fmt, w_inv_scale, 1.0f, M, Np, Kc, nullptr, 128, nullptr, nullptr, out_f32, stream,
                        "idb_fcn_output_layer");
 }
 

@@ -6,6 +6,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <stdint.h>
 
 namespace idb {
@@ -99,8 +100,10 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
 // Instruction descriptor for kind::f16 with bf16 A/B (both K-major) and fp32 accumulate
 // (cute::UMMA::InstrDescriptor: c_format [4,6)=1, a_format [7,10)=1, b_format [10,13)=1,
 //  n>>3 at [17,23), m>>4 at [24,29)).
-__host__ __device__ constexpr uint32_t umma_idesc_bf16(uint32_t M, uint32_t N) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((N >> 3) << 17) | ((M >> 4) << 24);
+// a_fmt / b_fmt: 0 = fp16, 1 = bf16.  The two fields must be EQUAL: bf16 x fp16 raises an illegal-instruction
+// fault on sm_100a (measured, round 1).
+__host__ __device__ constexpr uint32_t umma_idesc_f16(uint32_t M, uint32_t N, uint32_t a_fmt, uint32_t b_fmt) {
+    return (1u << 4) | (a_fmt << 7) | (b_fmt << 10) | ((N >> 3) << 17) | ((M >> 4) << 24);
 }
 
 // D[tmem] (+)= A[smem] * B[smem]; one thread issues for the CTA.
@@ -142,6 +145,30 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 __device__ __forceinline__ void split_bf16(float v, __nv_bfloat16& hi, __nv_bfloat16& lo) {
     hi = __float2bfloat16_rn(v);
     lo = __float2bfloat16_rn(v - __bfloat162float(hi));
+}
+// fp16 pair of v (caller pre-scales so that hi and lo are normal numbers): 22 significand bits.
+__device__ __forceinline__ void split_fp16(float v, __half& hi, __half& lo) {
+    hi = __float2half_rn(v);
+    lo = __float2half_rn(v - __half2float(hi));
+}
+__device__ __forceinline__ uint32_t pack_fp16(__half a, __half b) {
+    return (uint32_t)__half_as_ushort(a) | ((uint32_t)__half_as_ushort(b) << 16);
+}
+// Two consecutive values -> (hi pair, lo pair) 32-bit words in the operand format fmt (0 = bf16, 1 = fp16).
+__device__ __forceinline__ void split_pair16(float v0, float v1, int fmt, uint32_t& hi, uint32_t& lo) {
+    if (fmt) {
+        __half h0, l0, h1, l1;
+        split_fp16(v0, h0, l0);
+        split_fp16(v1, h1, l1);
+        hi = pack_fp16(h0, h1);
+        lo = pack_fp16(l0, l1);
+    } else {
+        const __nv_bfloat16 h0 = __float2bfloat16_rn(v0), h1 = __float2bfloat16_rn(v1);
+        const __nv_bfloat16 l0 = __float2bfloat16_rn(v0 - __bfloat162float(h0));
+        const __nv_bfloat16 l1 = __float2bfloat16_rn(v1 - __bfloat162float(h1));
+        hi = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+        lo = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
+    }
 }
 __device__ __forceinline__ uint32_t pack_bf16(__nv_bfloat16 a, __nv_bfloat16 b) {
     return (uint32_t)__bfloat16_as_ushort(a) | ((uint32_t)__bfloat16_as_ushort(b) << 16);

@@ -78,13 +78,8 @@ __global__ void __launch_bounds__(256) perturb_kernel(const PerturbParams p) {
         if (p.d_hi) {
             uint32_t h[4], l[4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                __nv_bfloat16 h0, l0, h1, l1;
-                split_bf16(dev[2 * j], h0, l0);
-                split_bf16(dev[2 * j + 1], h1, l1);
-                h[j] = pack_bf16(h0, h1);
-                l[j] = pack_bf16(l0, l1);
-            }
+            for (int j = 0; j < 4; ++j)
+                split_pair16(dev[2 * j] * p.d_scale, dev[2 * j + 1] * p.d_scale, p.fmt, h[j], l[j]);
             const size_t off = slab_offset_bytes((size_t)Mtot, (size_t)m, (size_t)c0);
             *reinterpret_cast<uint4*>(p.d_hi + off) = make_uint4(h[0], h[1], h[2], h[3]);
             *reinterpret_cast<uint4*>(p.d_lo + off) = make_uint4(l[0], l[1], l[2], l[3]);
@@ -103,7 +98,8 @@ cudaError_t launch_perturb(const PerturbParams& p, cudaStream_t stream) {
 
 // ---------------------------------- weight packing ------------------------------------------
 __global__ void __launch_bounds__(256) pack_weight_kernel(const float* __restrict__ w, int N, int K, int ldw, int Np,
-                                                          int Kc, uint8_t* __restrict__ hi, uint8_t* __restrict__ lo) {
+                                                          int Kc, int fp16, float scale, uint8_t* __restrict__ hi,
+                                                          uint8_t* __restrict__ lo) {
     const int chunks = Kc >> 3;
     const long long total = (long long)Np * chunks;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
@@ -119,11 +115,7 @@ __global__ void __launch_bounds__(256) pack_weight_kernel(const float* __restric
                 if (k0 + 2 * j < K) v0 = w[(size_t)n * ldw + k0 + 2 * j];
                 if (k0 + 2 * j + 1 < K) v1 = w[(size_t)n * ldw + k0 + 2 * j + 1];
             }
-            __nv_bfloat16 h0, l0, h1, l1;
-            split_bf16(v0, h0, l0);
-            split_bf16(v1, h1, l1);
-            h[j] = pack_bf16(h0, h1);
-            l[j] = pack_bf16(l0, l1);
+            split_pair16(v0 * scale, v1 * scale, fp16, h[j], l[j]);  // scale is a power of two: exact
         }
         const size_t off = slab_offset_bytes((size_t)Np, (size_t)n, (size_t)k0);
         *reinterpret_cast<uint4*>(hi + off) = make_uint4(h[0], h[1], h[2], h[3]);
@@ -131,11 +123,11 @@ __global__ void __launch_bounds__(256) pack_weight_kernel(const float* __restric
     }
 }
 
-cudaError_t launch_pack_weight(const float* w, int N, int K, int ldw, int Np, int Kc, uint8_t* hi, uint8_t* lo,
-                               cudaStream_t stream) {
+cudaError_t launch_pack_weight(const float* w, int N, int K, int ldw, int Np, int Kc, int fp16, float scale,
+                               uint8_t* hi, uint8_t* lo, cudaStream_t stream) {
     const long long total = (long long)Np * (Kc >> 3);
     if (total <= 0) return cudaSuccess;
-    pack_weight_kernel<<<(int)((total + 255) / 256), 256, 0, stream>>>(w, N, K, ldw, Np, Kc, hi, lo);
+    pack_weight_kernel<<<(int)((total + 255) / 256), 256, 0, stream>>>(w, N, K, ldw, Np, Kc, fp16, scale, hi, lo);
     return cudaGetLastError();
 }
 

@@ -96,7 +96,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_bf16x3_kernel(const Gemm
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
+            const uint32_t ofmt = p.fmt ? 0u : 1u;  // descriptor code: 0 = fp16, 1 = bf16
+            const uint32_t idesc = umma_idesc_f16(BM, BN, ofmt, ofmt);
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
@@ -156,6 +157,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_bf16x3_kernel(const Gemm
                 uint32_t v[32];
                 tmem_ld32(t_row + cc * 32, v);
                 tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) * p.acc_scale);
                 if (kMode == 0) {
                     const float* sa = s_a0 + as * BN + cc * 32;
                     const float* se = s_em1 + as * BN + cc * 32;
@@ -171,11 +174,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_bf16x3_kernel(const Gemm
                             const int c = ch * 8 + j * 2;
                             const float e0 = elu_deviation(sa[c], se[c], __uint_as_float(v[c]));
                             const float e1 = elu_deviation(sa[c + 1], se[c + 1], __uint_as_float(v[c + 1]));
-                            __nv_bfloat16 h0, l0, h1, l1;
-                            split_bf16(e0, h0, l0);
-                            split_bf16(e1, h1, l1);
-                            h[j] = pack_bf16(h0, h1);
-                            l[j] = pack_bf16(l0, l1);
+                            split_pair16(e0 * p.out_scale, e1 * p.out_scale, p.fmt, h[j], l[j]);
                         }
                         const int sw = ((chunk0 + ch) ^ (int)(m & 7)) << 4;
                         *reinterpret_cast<uint4*>(row_hi + sw) = make_uint4(h[0], h[1], h[2], h[3]);

@@ -11,6 +11,9 @@ struct GemmParams {
     const uint8_t* b_hi;  // slab [Kc/64][Np][128 B]
     const uint8_t* b_lo;
     int M, Np, Kc;
+    int fmt;          // operand format of A, B and the mode-0 output: 0 = bf16 hi/lo pairs, 1 = fp16 hi/lo pairs
+    float acc_scale;  // accumulator * acc_scale = un-scaled product (1 / (a_scale * w_scale), exact power of two)
+    float out_scale;  // mode 0: deviations are multiplied by this before the hi/lo split (a_scale of the next layer)
     // mode 0 (hidden layer): anchor pre-activations in, slab-layout deviations out
     const float* a0;  // [n_anchors][Np]
     int rows_per_anchor;
@@ -23,8 +26,8 @@ struct GemmParams {
 cudaError_t launch_gemm_bf16x3(int mode, const GemmParams& p, int num_sms, cudaStream_t stream);
 
 // fp32 [N][K] (row stride ldw) -> hi/lo bf16 slabs [Kc/64][Np][128 B], zero padded
-cudaError_t launch_pack_weight(const float* w, int N, int K, int ldw, int Np, int Kc, uint8_t* hi, uint8_t* lo,
-                               cudaStream_t stream);
+cudaError_t launch_pack_weight(const float* w, int N, int K, int ldw, int Np, int Kc, int fp16, float scale,
+                               uint8_t* hi, uint8_t* lo, cudaStream_t stream);
 
 struct PerturbParams {
     const float* x0;  // [n_anchors][D]
@@ -34,6 +37,8 @@ struct PerturbParams {
     float mean_coeff, std;
     uint64_t seed;
     uint64_t anchor_id0;  // global id of anchor 0 of this call (Philox stream key)
+    int fmt;          // operand format of d_hi/d_lo (0 = bf16 pair, 1 = fp16 pair)
+    float d_scale;    // deviations are multiplied by this (power of two) before the split
     float* x_out;     // optional fp32 [n_anchors][K][D] (perturbed points, reference arithmetic)
     uint8_t* d_hi;    // optional slab [Dp/64][n_anchors*Kp][128 B]: deviation x - mean
     uint8_t* d_lo;

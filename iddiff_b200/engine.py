@@ -72,7 +72,11 @@ class FcnEngine:
     perturbations of a chunk of anchors.  Weights stay owned by the caller's module; this object keeps
     packed bf16 hi/lo slab copies (tensor-core operands) and fp32 references (anchor chain)."""
 
-    def __init__(self, weights: Sequence[torch.Tensor], biases: Sequence[torch.Tensor]):
+    # Deviations are sigma-sized; in the fp16-pair format they are multiplied by 2^6 so that the lo halves of
+    # typical values stay normal fp16 numbers (absolute resolution 2^-24 / 2^6 ~ 9e-10, overflow at |e| > 1023).
+    A_SCALE_FP16 = 64.0
+
+    def __init__(self, weights: Sequence[torch.Tensor], biases: Sequence[torch.Tensor], fmt: int = _lib.FMT_FP16):
         if len(weights) < 2 or len(weights) != len(biases):
             raise _lib.IdbError("FCN needs >= 2 linear layers with biases")
         self.w = [w.detach().contiguous() for w in weights]
@@ -90,13 +94,21 @@ class FcnEngine:
         self.Np = [_ceil(n, 256) for n in self.out_real]
         self.Kc = [_ceil(self.D, 64)] + self.Np[:-1]
         st = stream_ptr()
-        self.w_hi, self.w_lo = [], []
+        self.fmt = int(fmt)
+        self.a_scale = self.A_SCALE_FP16 if self.fmt == _lib.FMT_FP16 else 1.0
+        self.w_hi, self.w_lo, self.w_inv_scale = [], [], []
         for l, w in enumerate(self.w):
+            scale = 1.0
+            if self.fmt == _lib.FMT_FP16:
+                # power of two that puts max|w| in [2^13, 2^14): hi and lo are normal fp16 numbers, products exact
+                wmax = float(w.abs().max())
+                scale = 2.0 ** (13 - math.frexp(wmax)[1] + 1) if wmax > 0 else 1.0
+            self.w_inv_scale.append(1.0 / scale)
             nbytes = self.Np[l] * self.Kc[l] * 2
             hi = torch.empty(nbytes, dtype=torch.uint8, device=self.dev)
             lo = torch.empty(nbytes, dtype=torch.uint8, device=self.dev)
             call("idb_pack_weight", ptr(w), w.shape[0], self.in_real[l], w.shape[1], self.Np[l], self.Kc[l],
-                 ptr(hi), ptr(lo), st)
+                 self.fmt, scale, ptr(hi), ptr(lo), st)
             self.w_hi.append(hi)
             self.w_lo.append(lo)
 
@@ -150,18 +162,18 @@ class FcnEngine:
         e_hi = torch.empty(M * self.Kc[0] * 2, dtype=torch.uint8, device=dev)
         e_lo = torch.empty(M * self.Kc[0] * 2, dtype=torch.uint8, device=dev)
         call("idb_perturb", ptr(x0), ptr(z), A, K, D, Kp, self.Kc[0], float(mean_coeff), float(std), int(seed),
-             int(anchor_id0), None, ptr(e_hi), ptr(e_lo), st)
+             int(anchor_id0), None, self.fmt, self.a_scale, ptr(e_hi), ptr(e_lo), st)
         P = self.anchor_chain(x0, mean_coeff, label)
         for l in range(self.n_layers - 1):
             o_hi = torch.empty(M * self.Np[l] * 2, dtype=torch.uint8, device=dev)
             o_lo = torch.empty(M * self.Np[l] * 2, dtype=torch.uint8, device=dev)
-            call("idb_fcn_hidden_layer", ptr(e_hi), ptr(e_lo), ptr(self.w_hi[l]), ptr(self.w_lo[l]), M, self.Np[l],
-                 self.Kc[l], ptr(P[l]), Kp, ptr(o_hi), ptr(o_lo), st)
+            call("idb_fcn_hidden_layer", ptr(e_hi), ptr(e_lo), ptr(self.w_hi[l]), ptr(self.w_lo[l]), self.fmt,
+                 self.w_inv_scale[l] / self.a_scale, self.a_scale, M, self.Np[l], self.Kc[l], ptr(P[l]), Kp, ptr(o_hi), ptr(o_lo), st)
             e_hi, e_lo = o_hi, o_lo
         l = self.n_layers - 1
         d_out = torch.empty(A, Kp, self.Np[l], dtype=torch.float32, device=dev)
-        call("idb_fcn_output_layer", ptr(e_hi), ptr(e_lo), ptr(self.w_hi[l]), ptr(self.w_lo[l]), M, self.Np[l],
-             self.Kc[l], ptr(d_out), st)
+        call("idb_fcn_output_layer", ptr(e_hi), ptr(e_lo), ptr(self.w_hi[l]), ptr(self.w_lo[l]), self.fmt,
+             self.w_inv_scale[l] / self.a_scale, M, self.Np[l], self.Kc[l], ptr(d_out), st)
         return d_out, P[-1]
 
     def estimate(self, x0: torch.Tensor, K: int, mean_coeff: float, std: float, label: float,
@@ -199,7 +211,7 @@ class KSphereEngine:
         st = stream_ptr()
         x = torch.empty(A, K, D, dtype=torch.float32, device=x0.device)
         call("idb_perturb", ptr(x0), ptr(z), A, K, D, 0, 0, float(mean_coeff), float(std), int(seed), int(anchor_id0),
-             ptr(x), None, None, st)
+             ptr(x), 0, 1.0, None, None, st)
         sc = torch.empty_like(x)
         call("idb_ksphere_gt_score", ptr(x), None, float(std), A * K, D, self.p, ptr(sc), st)
         res = spectrum_from_rows(sc, K, D, 1.0)

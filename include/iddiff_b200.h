@@ -35,14 +35,26 @@ const char* idb_last_error(void);
  *   x0 [n_anchors][D] fp32;  z [n_anchors][K][D] fp32 or NULL -> fused Philox4x32-10 + Box-Muller keyed by
  *   (seed, anchor_id0 + a, row, column), so results do not depend on sharding or chunking.
  * Outputs (either may be NULL): x_out [n_anchors][K][D] fp32 = fl(fl(mean_coeff*x0) + fl(std*z));
- *   d_hi/d_lo slab layout [Dp/64][n_anchors*Kp][128B] = bf16 hi/lo split of (x - mean), rows >= K and
- *   columns >= D zero.  Kp % 128 == 0, Dp % 64 == 0. */
+ *   d_hi/d_lo slab layout [Dp/64][n_anchors*Kp][128B] = hi/lo pair (format fmt) of d_scale*(x - mean), rows >= K
+ *   and columns >= D zero.  Kp % 128 == 0, Dp % 64 == 0. */
 int idb_perturb(const float* x0, const float* z, int n_anchors, int K, int D, int Kp, int Dp, float mean_coeff,
-                float std, uint64_t seed, uint64_t anchor_id0, float* x_out, void* d_hi, void* d_lo, void* stream);
+                float std, uint64_t seed, uint64_t anchor_id0, float* x_out, int fmt, float d_scale, void* d_hi,
+                void* d_lo, void* stream);
 
-/* nn.Linear weight [N][K] fp32 (row stride ldw) -> bf16 hi/lo slabs [Kc/64][Np][128B], zero padded.
- * Np % 256 == 0, Kc % 64 == 0.  Done once per model (models/fcn.py:16-30 holds the weights). */
-int idb_pack_weight(const float* w, int N, int K, int ldw, int Np, int Kc, void* hi, void* lo, void* stream);
+/* Operand formats of the tensor-core chain.  Every operand is a hi/lo PAIR of 16-bit numbers (v ~= hi + lo) so
+ * that three tcgen05.mma (hi.hi + lo.hi + hi.lo) reproduce an fp32-accurate product:
+ *   IDB_FMT_BF16  bf16 pairs, 16 significand bits, fp32 exponent range, no scaling needed (scales must be 1);
+ *   IDB_FMT_FP16  fp16 pairs, 22 significand bits; values are pre-multiplied by a power-of-two scale so that hi
+ *                 and lo are normal fp16 numbers, and the fp32 accumulator is multiplied by the exact inverse.
+ * A and B of one layer must use the SAME format (kind::f16 faults on bf16 x fp16). */
+#define IDB_FMT_BF16 0
+#define IDB_FMT_FP16 1
+
+/* nn.Linear weight [N][K] fp32 (row stride ldw) -> hi/lo slabs [Kc/64][Np][128B] of (w * scale), zero padded.
+ * Np % 256 == 0, Kc % 64 == 0.  Done once per model (models/fcn.py:16-30 holds the weights).  For IDB_FMT_FP16
+ * choose scale = 2^k with max|w|*scale in [2^13, 2^14). */
+int idb_pack_weight(const float* w, int N, int K, int ldw, int Np, int Kc, int fmt, float scale, void* hi, void* lo,
+                    void* stream);
 
 /* One nn.Linear of models/fcn.py:20-30 evaluated in fp32 at the un-perturbed anchors:
  *   out[a][n] = sum_k w[n][k] * f(in_scale*in[a][k]) + bias[n] + extra_col[n*extra_stride]*extra_scalar,
@@ -52,16 +64,18 @@ int idb_anchor_linear(const float* in, int ld_in, int apply_elu, float in_scale,
                       const float* bias, const float* extra_col, int extra_stride, float extra_scalar, float* out,
                       int ld_out, int n_anchors, int N, int K, void* stream);
 
-/* Hidden nn.Linear + ELU on the deviations (tcgen05, bf16x3 split precision, fp32 accumulate in TMEM):
- *   acc = A (hi+lo) . W^T (hi+lo);  out = ELU(a0 + acc) - ELU(a0), re-split to bf16 hi/lo slabs [Np/64][M][128B].
+/* Hidden nn.Linear + ELU on the deviations (tcgen05 kind::f16, 3 MMAs per product, fp32 accumulate in TMEM):
+ *   acc = acc_scale * A (hi+lo) . W^T (hi+lo);  e = ELU(a0 + acc) - ELU(a0);  out = hi/lo pair of out_scale * e in
+ *   slabs [Np/64][M][128B].  acc_scale = 1 / (scale of A * scale of W); out_scale = scale the next layer expects.
  * a0 [M/rows_per_anchor][Np] fp32 = anchor pre-activations of this layer.  M % 128 == 0, Np % 256 == 0,
  * Kc % 64 == 0, rows_per_anchor % 128 == 0. */
-int idb_fcn_hidden_layer(const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, int M, int Np, int Kc,
-                         const float* a0, int rows_per_anchor, void* out_hi, void* out_lo, void* stream);
+int idb_fcn_hidden_layer(const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, int fmt,
+                         float acc_scale, float out_scale, int M, int Np, int Kc, const float* a0,
+                         int rows_per_anchor, void* out_hi, void* out_lo, void* stream);
 
-/* Last nn.Linear on the deviations: out_f32 [M][Np] fp32 row-major = A (hi+lo) . W^T (hi+lo). */
-int idb_fcn_output_layer(const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, int M, int Np, int Kc,
-                         float* out_f32, void* stream);
+/* Last nn.Linear on the deviations: out_f32 [M][Np] fp32 row-major = acc_scale * A (hi+lo) . W^T (hi+lo). */
+int idb_fcn_output_layer(const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, int fmt,
+                         float acc_scale, int M, int Np, int Kc, float* out_f32, void* stream);
 
 /* Raw scores as the reference's score_fn returns them (models/utils.py:264-267):
  *   score[a][k][c] = -(a_out[a][c] + d_out[a*Kp + k][c]) / std,  score [n_anchors][K][D] fp32. */

@@ -293,3 +293,37 @@ def ksphere_data(n_samples: int, n_spheres: int, ambient_dim: int, manifold_dim,
         new = new + noise_std * torch.randn_like(new)
         data.append(new)
     return torch.cat(data, dim=0)
+
+
+# --------------------------------------------------------------------------------------
+# fp64 evaluation of the same restatement -- measures the reference's own fp32 noise floor
+# --------------------------------------------------------------------------------------
+
+
+def fcn_centred_spectrum_fp64(weights, biases, x0: torch.Tensor, z: torch.Tensor, sde: str, sde_params: Dict,
+                              N: int = 1000) -> np.ndarray:
+    """Singular values of the centred FCN score matrix with every operation AFTER the perturbation draw
+    in float64.  The perturbed points x = mean + std*z are formed in float32 exactly as
+    dim_reduction.py:178-182 does (they are the network INPUT, identical for every implementation);
+    fcn.py:32-40, the -1/std scaling (models/utils.py:264-267), centring and the SVD
+    (dim_reduction.py:190-199) then run in float64.  |reference - this| is the rounding noise of the
+    reference's fp32 arithmetic for that input, the floor below which 'matching the reference' is
+    not defined.  x0 [n, D], z [n, K, D] float32 -> [n, D] float64."""
+    t_eps = SAMPLING_EPS[sde.lower()]
+    n, K, D = z.shape
+    out = []
+    for a in range(n):
+        vec_t = torch.ones(K) * t_eps
+        batch = x0[a].repeat(K, 1)
+        mean, std = marginal(sde, batch, vec_t, **sde_params)
+        x = mean + std[:, None] * z[a]
+        labels = vec_t * (N - 1)
+        h = torch.cat([x.double(), labels.double().unsqueeze(-1)], dim=1)
+        for i, (w, b) in enumerate(zip(weights, biases)):
+            h = h @ w.double().T + b.double()
+            if i < len(weights) - 1:
+                h = torch.where(h > 0, h, torch.expm1(h))
+        score = -h / std.double()[:, None]
+        c = score - score.mean(dim=0, keepdim=True)
+        out.append(torch.linalg.svdvals(c).numpy())
+    return np.stack(out)

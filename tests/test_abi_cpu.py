@@ -32,7 +32,7 @@ def test_argument_validation_without_a_gpu():
     """Rejected calls return before touching CUDA, so this runs on the CPU box."""
     from iddiff_b200 import _lib
     with pytest.raises(_lib.IdbError, match="NULL operand"):
-        _lib.call("idb_fcn_output_layer", None, None, None, None, 128, 256, 64, 16, None)
+        _lib.call("idb_fcn_output_layer", None, None, None, None, 0, 1.0, 128, 256, 64, 16, None)
     with pytest.raises(_lib.IdbError, match="n >= 3"):
         _lib.call("idb_id_from_spectrum", 16, 1, 2, 2, 16, None)
     import torch
