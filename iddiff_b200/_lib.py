@@ -65,12 +65,21 @@ def load():
         return lib
 
 
+# CUDA kernels each entry point enqueues (for bench.py's `gpu_launches` claim)
+KERNELS_PER_CALL = {"idb_perturb": 1, "idb_pack_weight": 1, "idb_anchor_linear": 1, "idb_fcn_hidden_layer": 1,
+                    "idb_fcn_output_layer": 1, "idb_fcn_scores": 1, "idb_ksphere_gt_score": 1, "idb_center_gram": 2,
+                    "idb_spectrum": 1, "idb_id_from_spectrum": 1}
+launch_count = 0
+
+
 def call(name: str, *args):
     """Calls an int-returning entry point and raises IdbError with idb_last_error() on failure."""
+    global launch_count
     lib = load()
     rc = getattr(lib, name)(*args)
     if rc != 0:
         raise IdbError(f"{name} failed ({rc}): {lib.idb_last_error().decode()}")
+    launch_count += KERNELS_PER_CALL.get(name, 0)
 
 
 def ptr(t):

@@ -1,0 +1,147 @@
+"""Drop-in for the reference's `dim_reduction.get_manifold_dimension` (dim_reduction.py:116-211).
+
+Same signature, same config keys, same output (`{'singular_values': list[list[float]]}` returned or pickled
+to {log_path}/{log_name}/svd/{name}.pkl), same quirks (N-1 anchors, K from the loader batch size, file
+'None.pkl' when name is None).  The body is different: anchors are gathered from the loader, moved to the
+device once, and every stage -- perturbation, score network, centring, spectrum, gap read-out -- runs on
+the GPU for a whole chunk of anchors; only the spectra come back.
+"""
+from __future__ import annotations
+
+import math
+import os
+import pickle
+from pathlib import Path
+from typing import Dict, List, Optional, Sequence
+
+import torch
+
+from . import _lib, sde_lib
+from .config import lookup
+from .engine import FcnEngine, KSphereEngine, SpectrumResult
+
+
+def k_schedule(anchor_shape: Sequence[int], batchsize: int):
+    """(num_batches, extra_in_last_batch, K) with the reference's integer arithmetic, dim_reduction.py:166-171,
+    185-188: `x` is ONE sample there, so `x.shape[1:]` drops the first DATA axis."""
+    ambient_dim = math.prod(tuple(anchor_shape)[1:])
+    num_batches = ambient_dim // batchsize + 1
+    extra = ambient_dim - (ambient_dim // batchsize) * batchsize
+    num_batches *= 4
+    return num_batches, extra, (num_batches - 1) * batchsize + extra
+
+
+def gather_anchors(loader, num_datapoints: int):
+    """The anchors the reference's two loops visit (dim_reduction.py:154-164): idx+1 >= num_datapoints breaks,
+    so num_datapoints-1 anchors are used.  Returns [(anchor tensor, loader batch size B)], B decides K."""
+    out, idx = [], 0
+    for orig_batch in loader:
+        batchsize = orig_batch.size(0)
+        if idx + 1 >= num_datapoints:
+            break
+        for x in orig_batch:
+            if idx + 1 >= num_datapoints:
+                break
+            out.append((x, batchsize))
+            idx += 1
+    return out
+
+
+def build_engine(config, score_model: Optional[torch.nn.Module] = None, device="cuda"):
+    """Recognises the model class by config.model.name and ingests its weights into a device engine."""
+    name = config.model.name
+    if name == "ksphere_gt":
+        return KSphereEngine(config.data.manifold_dim, device=device)
+    if name == "fcn":
+        if score_model is None:
+            from . import models
+            score_model = models.create_model(config)
+            path = lookup(config, "model.checkpoint_path")
+            if path:
+                models.load_checkpoint_into(score_model, path)
+        return FcnEngine.from_module(score_model, device=device)
+    raise NotImplementedError(f"model.name={name!r}: only 'fcn' and 'ksphere_gt' are built so far (DESIGN.md scope)")
+
+
+def estimate_anchors(engine, anchors: torch.Tensor, K: int, sde, t: float, *, seed: int = 0,
+                     z: Optional[torch.Tensor] = None, chunk: Optional[int] = None, anchor_id0: int = 0,
+                     mem_budget_bytes: int = 24 << 30) -> Dict[str, torch.Tensor]:
+    """anchors [N, D] (host or device) -> {'singular_values': [N, n] fp32, 'dims': [N] int32, 'sweeps'} on the
+    HOST.  Host anchors are copied to the device chunk by chunk (pinned staging), results copied back once."""
+    dev = engine.dev
+    N, D = anchors.shape
+    mc, std = sde.coefficients(t)
+    label = float((torch.ones(1, dtype=torch.float32) * t * (sde.N - 1))[0])
+    if chunk is None:
+        per = engine.bytes_per_anchor(K) if isinstance(engine, FcnEngine) else engine.bytes_per_anchor(K, D)
+        chunk = max(1, min(N, mem_budget_bytes // max(per, 1)))
+    svs, dims, sweeps = [], [], []
+    for s in range(0, N, chunk):
+        x0 = anchors[s:s + chunk]
+        if not x0.is_cuda:
+            x0 = x0.contiguous().float()
+            x0 = (x0 if x0.is_pinned() else x0.pin_memory()).to(dev, non_blocking=True)
+        zc = None if z is None else z[s:s + chunk].to(dev, non_blocking=True).contiguous()
+        r: SpectrumResult = engine.estimate(x0.contiguous(), K, mc, std, label, z=zc, seed=seed,
+                                            anchor_id0=anchor_id0 + s)
+        svs.append(r.singular_values)
+        dims.append(r.dims)
+        sweeps.append(r.sweeps)
+    out = {"singular_values": torch.cat(svs), "dims": torch.cat(dims), "sweeps": torch.cat(sweeps)}
+    host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True) for k, v in out.items()}
+    for k in out:
+        host[k].copy_(out[k], non_blocking=True)
+    torch.cuda.current_stream().synchronize()
+    return host
+
+
+def get_manifold_dimension(config, name=None, return_svd=False, *, score_model=None, loader=None, seed=None,
+                           noise=None):
+    """Reference signature `get_manifold_dimension(config, name=None, return_svd=False)`; the keyword-only extras
+    let a caller pass live weights (the training callback, callbacks.py:403-432), an existing loader, a Philox
+    seed, or recorded noise `noise[i]` = [K, D] per anchor (parity runs)."""
+    save_path = os.path.join(config.logging.log_path, config.logging.log_name, "svd")
+    Path(save_path).mkdir(parents=True, exist_ok=True)
+
+    if loader is None:
+        from .data import create_lightning_datamodule
+        dm = create_lightning_datamodule(config)
+        dm.setup()
+        loader = dm.train_dataloader()
+    sde, sampling_eps = sde_lib.configure_sde(config)
+    device = torch.device(lookup(config, "device", "cuda"))
+    if device.type != "cuda":
+        raise _lib.IdbError("iddiff_b200 runs on CUDA devices only; the CPU path is the reference itself")
+    engine = build_engine(config, score_model, device)
+
+    num_datapoints = lookup(config, "dim_estimation.num_datapoints")
+    if num_datapoints is None:
+        num_datapoints = lookup(config, "logging.svd_points")
+    if num_datapoints is None:  # the reference leaves the name unbound here (appendix A.8)
+        raise NameError("name 'num_datapoints' is not defined")
+
+    picked = gather_anchors(loader, num_datapoints)
+    singular_values: List[List[float]] = [None] * len(picked)
+    dims: List[int] = [None] * len(picked)
+    # anchors that share a loader batch size share K: run each group as one device batch
+    groups: Dict[int, List[int]] = {}
+    for i, (_, B) in enumerate(picked):
+        groups.setdefault(B, []).append(i)
+    for B, idxs in groups.items():
+        x = torch.stack([picked[i][0] for i in idxs]).float()
+        if x.dim() != 2:
+            raise NotImplementedError("image-shaped anchors need the U-Net engines (DESIGN.md: next rows)")
+        _, _, K = k_schedule(picked[idxs[0]][0].shape, B)
+        z = None if noise is None else torch.stack([torch.as_tensor(noise[i]) for i in idxs]).float()
+        res = estimate_anchors(engine, x, K, sde, sampling_eps, seed=0 if seed is None else seed, z=z,
+                               anchor_id0=idxs[0])
+        sv = res["singular_values"].double().tolist()  # fp32 values widened, like s.tolist() at dim_reduction.py:198
+        for j, i in enumerate(idxs):
+            singular_values[i] = sv[j]
+            dims[i] = int(res["dims"][j])
+    info = {"singular_values": singular_values}
+    get_manifold_dimension.last_dims = dims  # device read-out (plot_utils.py:224-229), for callers that want it
+    if return_svd:
+        return info
+    with open(os.path.join(save_path, f"{name}.pkl"), "wb") as f:
+        pickle.dump(info, f)

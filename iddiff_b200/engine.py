@@ -20,6 +20,28 @@ from . import _lib
 from ._lib import call, ptr, stream_ptr
 
 
+# Set to a dict to collect (start event, end event, algorithmic work) per stage -- bench.py reads it after a sync.
+EVENT_LOG = None
+
+
+class _stage:
+    def __init__(self, name: str, work: float = 0.0):
+        self.name, self.work = name, work
+
+    def __enter__(self):
+        self.start = None
+        if EVENT_LOG is not None:
+            self.start = torch.cuda.Event(enable_timing=True)
+            self.start.record()
+
+    def __exit__(self, *exc):
+        if self.start is not None:
+            end = torch.cuda.Event(enable_timing=True)
+            end.record()
+            EVENT_LOG.setdefault(self.name, []).append((self.start, end, self.work))
+        return False
+
+
 def _ceil(x: int, m: int) -> int:
     return (x + m - 1) // m * m
 
@@ -51,14 +73,16 @@ def spectrum_from_rows(X: torch.Tensor, K: int, D: int, scale: float, rows_per_a
     colmean = torch.empty(A, D, dtype=torch.float64, device=dev)
     G = torch.empty(A, D, D, dtype=torch.float64, device=dev)
     st = stream_ptr()
-    call("idb_center_gram", ptr(X), R * ld, ld, A, K, D, float(scale), ptr(colmean), ptr(G), st)
+    with _stage("center_gram", A * (K * D * 4.0 + D * D * 8.0)):
+        call("idb_center_gram", ptr(X), R * ld, ld, A, K, D, float(scale), ptr(colmean), ptr(G), st)
     n = D
     n_out = min(K, D)
     ws_bytes = _lib.load().idb_spectrum_workspace_bytes(A, n)
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
     sv = torch.empty(A, n_out, dtype=torch.float32, device=dev)
     sweeps = torch.empty(A, dtype=torch.int32, device=dev)
-    call("idb_spectrum", ptr(G), A, n, n_out, ptr(sv), ptr(sweeps), ptr(ws), st)
+    with _stage("spectrum", A * (n * n * 8.0 + n_out * 4.0)):
+        call("idb_spectrum", ptr(G), A, n, n_out, ptr(sv), ptr(sweeps), ptr(ws), st)
     dims = torch.empty(A, dtype=torch.int32, device=dev)
     if n_out >= 3:
         call("idb_id_from_spectrum", ptr(sv), A, n_out, n_out, ptr(dims), st)
@@ -161,19 +185,24 @@ class FcnEngine:
         dev = self.dev
         e_hi = torch.empty(M * self.Kc[0] * 2, dtype=torch.uint8, device=dev)
         e_lo = torch.empty(M * self.Kc[0] * 2, dtype=torch.uint8, device=dev)
-        call("idb_perturb", ptr(x0), ptr(z), A, K, D, Kp, self.Kc[0], float(mean_coeff), float(std), int(seed),
-             int(anchor_id0), None, self.fmt, self.a_scale, ptr(e_hi), ptr(e_lo), st)
-        P = self.anchor_chain(x0, mean_coeff, label)
+        with _stage("perturb", 2.0 * M * self.Kc[0] * 2):
+            call("idb_perturb", ptr(x0), ptr(z), A, K, D, Kp, self.Kc[0], float(mean_coeff), float(std), int(seed),
+                 int(anchor_id0), None, self.fmt, self.a_scale, ptr(e_hi), ptr(e_lo), st)
+        with _stage("anchor_chain", sum(2.0 * A * i * o for i, o in zip(self.in_real, self.out_real))):
+            P = self.anchor_chain(x0, mean_coeff, label)
         for l in range(self.n_layers - 1):
             o_hi = torch.empty(M * self.Np[l] * 2, dtype=torch.uint8, device=dev)
             o_lo = torch.empty(M * self.Np[l] * 2, dtype=torch.uint8, device=dev)
-            call("idb_fcn_hidden_layer", ptr(e_hi), ptr(e_lo), ptr(self.w_hi[l]), ptr(self.w_lo[l]), self.fmt,
-                 self.w_inv_scale[l] / self.a_scale, self.a_scale, M, self.Np[l], self.Kc[l], ptr(P[l]), Kp, ptr(o_hi), ptr(o_lo), st)
+            with _stage("hidden_first" if l == 0 else "hidden", 2.0 * A * K * self.in_real[l] * self.out_real[l]):
+                call("idb_fcn_hidden_layer", ptr(e_hi), ptr(e_lo), ptr(self.w_hi[l]), ptr(self.w_lo[l]), self.fmt,
+                     self.w_inv_scale[l] / self.a_scale, self.a_scale, M, self.Np[l], self.Kc[l], ptr(P[l]), Kp,
+                     ptr(o_hi), ptr(o_lo), st)
             e_hi, e_lo = o_hi, o_lo
         l = self.n_layers - 1
         d_out = torch.empty(A, Kp, self.Np[l], dtype=torch.float32, device=dev)
-        call("idb_fcn_output_layer", ptr(e_hi), ptr(e_lo), ptr(self.w_hi[l]), ptr(self.w_lo[l]), self.fmt,
-             self.w_inv_scale[l] / self.a_scale, M, self.Np[l], self.Kc[l], ptr(d_out), st)
+        with _stage("output", 2.0 * A * K * self.in_real[l] * self.out_real[l]):
+            call("idb_fcn_output_layer", ptr(e_hi), ptr(e_lo), ptr(self.w_hi[l]), ptr(self.w_lo[l]), self.fmt,
+                 self.w_inv_scale[l] / self.a_scale, M, self.Np[l], self.Kc[l], ptr(d_out), st)
         return d_out, P[-1]
 
     def estimate(self, x0: torch.Tensor, K: int, mean_coeff: float, std: float, label: float,
