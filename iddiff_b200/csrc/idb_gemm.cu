@@ -12,7 +12,7 @@
 // Kernel shape: persistent, one CTA per SM, 192 threads:
 //   warp 0      : TMA producer   (cp.async.bulk -> 2-stage smem ring, 96 KB / stage)
 //   warp 1      : MMA issuer     (tcgen05.mma kind::f16, M=128 N=256 K=16, 12 per 64-wide k-block)
-//   warps 2..5  : epilogue       (tcgen05.ld 32x32b.x32; ELU-deviation + hi/lo split, or fp32 store)
+//   warps 2..17 : epilogue       (tcgen05.ld 32x32b.x32; ELU-deviation + hi/lo split, or fp32 store)
 // TMEM: 2 x 256 fp32 columns, so the epilogue of tile i overlaps the MMAs of tile i+1.
 #include "idb_common.cuh"
 #include "idb_kernels.h"
@@ -26,7 +26,9 @@ constexpr int STAGES = 2;
 constexpr uint32_t A_TILE_BYTES = BM * 128;  // 16 KB (one of hi / lo)
 constexpr uint32_t B_TILE_BYTES = BN * 128;  // 32 KB
 constexpr uint32_t STAGE_BYTES = 2 * A_TILE_BYTES + 2 * B_TILE_BYTES;
-constexpr int GEMM_THREADS = 192;
+constexpr int EPI_WARPS = 16;  // 4 per scheduler: the epilogue is issue-latency bound with fewer
+constexpr int EPI_THREADS = EPI_WARPS * 32;
+constexpr int GEMM_THREADS = 64 + EPI_THREADS;
 constexpr size_t GEMM_SMEM = 1024 /*align slack*/ + (size_t)STAGES * STAGE_BYTES + 2 * 2 * BN * sizeof(float) + 256;
 
 
@@ -63,7 +65,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_bf16x3_kernel(const Gemm
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(&tfull[s], 1);
-            mbar_init(&tempty[s], 128);
+            mbar_init(&tempty[s], EPI_THREADS);
         }
         fence_barrier_init();
     }
@@ -129,8 +131,9 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_bf16x3_kernel(const Gemm
             }
         }
     } else {
-        const int et = threadIdx.x - 64;   // 0..127
+        const int et = threadIdx.x - 64;   // 0..EPI_THREADS-1
         const int quarter = warp & 3;      // TMEM lanes this warp may read: 32*quarter .. +31
+        const int cgroup = (warp - 2) >> 2;  // which 32-column chunks of the tile this warp converts
         const int row_in_tile = quarter * 32 + lane;
         int it = 0;
         for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
@@ -141,19 +144,19 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_bf16x3_kernel(const Gemm
             if (kMode == 0) {
                 const int anchor = (int)(m0 / (size_t)p.rows_per_anchor);
                 const float* a0 = p.a0 + (size_t)anchor * p.Np + n0;
-                for (int c = et; c < BN; c += 128) {
+                for (int c = et; c < BN; c += EPI_THREADS) {
                     const float a = __ldg(a0 + c);
                     s_a0[as * BN + c] = a;
                     s_em1[as * BN + c] = expm1f(fminf(a, 0.f));
                 }
-                asm volatile("bar.sync 1, 128;" ::: "memory");
+                asm volatile("bar.sync 1, %0;" ::"n"(EPI_THREADS) : "memory");
             }
             mbar_wait(&tfull[as], aphase);
             tc_fence_after();
             const size_t m = m0 + row_in_tile;
             const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * BN;
 #pragma unroll 1
-            for (int cc = 0; cc < BN / 32; ++cc) {
+            for (int cc = cgroup; cc < BN / 32; cc += EPI_WARPS / 4) {
                 uint32_t v[32];
                 tmem_ld32(t_row + cc * 32, v);
                 tmem_ld_wait();
