@@ -24,6 +24,7 @@ _u64 = C.c_uint64
 _ll = C.c_longlong
 
 FMT_BF16, FMT_FP16 = 0, 1
+SPECTRUM_JACOBI, SPECTRUM_TRIDIAG = 0, 1
 
 # name -> (restype, argtypes); must list every symbol of include/iddiff_b200.h
 SIGNATURES = {
@@ -38,7 +39,7 @@ SIGNATURES = {
     "idb_ksphere_gt_score": (_i, [_vp, _vp, _f, _i, _i, _i, _vp, _vp]),
     "idb_center_gram": (_i, [_vp, _ll, _i, _i, _i, _i, _d, _vp, _vp, _vp]),
     "idb_spectrum_workspace_bytes": (C.c_size_t, [_i, _i]),
-    "idb_spectrum": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
+    "idb_spectrum": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "idb_id_from_spectrum": (_i, [_vp, _i, _i, _i, _vp, _vp]),
 }
 
@@ -68,7 +69,7 @@ def load():
 # CUDA kernels each entry point enqueues (for bench.py's `gpu_launches` claim)
 KERNELS_PER_CALL = {"idb_perturb": 1, "idb_pack_weight": 1, "idb_anchor_linear": 1, "idb_fcn_hidden_layer": 1,
                     "idb_fcn_output_layer": 1, "idb_fcn_scores": 1, "idb_ksphere_gt_score": 1, "idb_center_gram": 2,
-                    "idb_spectrum": 1, "idb_id_from_spectrum": 1}
+                    "idb_spectrum": 2, "idb_id_from_spectrum": 1}
 launch_count = 0
 
 

@@ -140,11 +140,21 @@ int idb_center_gram(const float* X, long long anchor_stride, int ld, int n_ancho
 
 size_t idb_spectrum_workspace_bytes(int n_anchors, int n) {
     if (n_anchors <= 0 || n <= 0) return 256;
-    return idb::spectrum_workspace_bytes(n_anchors, n);
+    const size_t a = idb::spectrum_workspace_bytes(n_anchors, n), b = idb::tridiag_workspace_bytes(n_anchors, n);
+    return a > b ? a : b;
 }
 
-int idb_spectrum(const double* G, int n_anchors, int n, int n_out, float* sv, int* sweeps, void* workspace,
+int idb_spectrum(const double* G, int n_anchors, int n, int n_out, int method, float* sv, int* sweeps, void* workspace,
                  void* stream) {
+    if (method == IDB_SPECTRUM_TRIDIAG) {
+        if (!G || !sv || !workspace || n_anchors < 0 || n <= 0 || n_out <= 0 || n_out > n)
+            return fail("idb_spectrum: bad argument");
+        if (!aligned16(workspace)) return fail("idb_spectrum: workspace must be 16-byte aligned");
+        return check(idb::launch_spectrum_tridiag(G, n_anchors, n, n_out, sv, sweeps, workspace,
+                                                  static_cast<cudaStream_t>(stream)),
+                     "idb_spectrum(tridiag)");
+    }
+    if (method != IDB_SPECTRUM_JACOBI) return fail("idb_spectrum: unknown method");
     if (!G || !sv || !workspace || n_anchors < 0 || n <= 0 || n_out <= 0 || n_out > n)
         return fail("idb_spectrum: bad argument");
     if (!aligned16(workspace)) return fail("idb_spectrum: workspace must be 16-byte aligned");

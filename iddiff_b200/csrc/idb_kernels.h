@@ -65,6 +65,10 @@ size_t spectrum_workspace_bytes(int n_anchors, int n);
 cudaError_t launch_spectrum(const double* G, int n_anchors, int n, int n_out, float* sv, int* sweeps, void* workspace,
                             cudaStream_t stream);
 
+size_t tridiag_workspace_bytes(int n_anchors, int n);
+cudaError_t launch_spectrum_tridiag(const double* G, int n_anchors, int n, int n_out, float* sv, int* iters,
+                                    void* workspace, cudaStream_t stream);
+
 cudaError_t launch_id_readout(const float* sv, int n_anchors, int n, int ld, int* dims, cudaStream_t stream);
 
 }  // namespace idb

@@ -1,0 +1,234 @@
+// Spectrum of the centred score matrix from its fp64 Gram matrix, method 1 (default):
+//   Householder tridiagonalisation of G (fp64, packed lower triangle resident in shared memory, one
+//   anchor per CTA)  ->  Sturm-sequence bisection of the tridiagonal (fp64, one thread per eigenvalue)
+//   ->  sigma_i = sqrt(lambda_i), descending.
+// Replaces torch.linalg.svd at dim_reduction.py:197-198 of the reference (LAPACK gesdd on the host).
+//
+// Why next to the one-sided Jacobi of idb_spectrum.cu (method 0): Jacobi on a 200 x 200 factor re-reads
+// both columns of every pair from shared memory in every rotation -- 12 n^3 bytes of smem traffic per
+// sweep, ~9 sweeps -- and measured 63 ms per 512 anchors; the two-stage solver touches the packed matrix
+// ~3 times per eliminated column (n^3 bytes in total) and has no convergence loop.  Backward error is
+// n * eps64 * |G|, i.e. relative 1e-16 * n * (s_max / s_i)^2 on singular value s_i: 2e-8 at a 1e3 cliff.
+#include "idb_common.cuh"
+#include "idb_kernels.h"
+#include <math.h>
+
+namespace idb {
+
+constexpr int TRI_THREADS = 1024;
+constexpr int TRI_WARPS = TRI_THREADS / 32;
+constexpr int TRI_GROUPS = TRI_THREADS / 256;
+constexpr size_t TRI_SMEM_MAX = 226 * 1024;
+
+__host__ __device__ inline size_t tri_packed_bytes(int n) { return (size_t)n * (n + 1) / 2 * sizeof(double); }
+// v, p and TRI_GROUPS partial-sum vectors
+__host__ __device__ inline size_t tri_vec_bytes(int n) { return (size_t)(2 + TRI_GROUPS) * ((n + 1) & ~1) * sizeof(double); }
+
+size_t tridiag_workspace_bytes(int n_anchors, int n) {
+    // per anchor: packed fp64 matrix (used only when it does not fit shared memory) + d[n] + e[n]
+    return (size_t)n_anchors * (tri_packed_bytes(n) + 2 * (size_t)n * sizeof(double)) + 256;
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// block-wide sum; every thread gets the result.  red: TRI_WARPS doubles of shared memory.
+__device__ __forceinline__ double block_sum(double v, double* red) {
+    v = warp_sum(v);
+    __syncthreads();  // red may still be read from the previous reduction
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    double t = 0.0;
+#pragma unroll
+    for (int w = 0; w < TRI_WARPS; ++w) t += red[w];
+    return t;
+}
+
+// A: packed lower triangle, row-major (A[i][j], j <= i, at i(i+1)/2 + j).
+__global__ void __launch_bounds__(TRI_THREADS, 1) tridiag_kernel(const double* __restrict__ G, int n,
+                                                                 uint8_t* __restrict__ workspace, int a_in_smem) {
+    extern __shared__ __align__(16) uint8_t tri_smem[];
+    __shared__ double red[TRI_WARPS];
+    const int a = blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const size_t per_anchor = tri_packed_bytes(n) + 2 * (size_t)n * sizeof(double);
+    uint8_t* ws = workspace + (size_t)a * per_anchor;
+    double* vec = reinterpret_cast<double*>(tri_smem);
+    double* v = vec;                      // Householder vector (indexed by absolute row)
+    const int nv = (n + 1) & ~1;
+    double* p = vec + nv;                 // p = tau A v, then w
+    double* cpart = vec + 2 * nv;         // [TRI_GROUPS][nv]
+    double* A = a_in_smem ? reinterpret_cast<double*>(tri_smem + tri_vec_bytes(n)) : reinterpret_cast<double*>(ws);
+    double* d_out = reinterpret_cast<double*>(ws + tri_packed_bytes(n));
+    double* e_out = d_out + n;
+    const double* Ga = G + (size_t)a * n * n;
+
+    for (int idx = tid; idx < n * n; idx += TRI_THREADS) {
+        const int i = idx / n, j = idx - i * n;
+        if (j <= i) A[(size_t)i * (i + 1) / 2 + j] = Ga[idx];
+    }
+    __syncthreads();
+
+    for (int k = 0; k + 2 < n; ++k) {
+        const int r0 = k + 1;  // first row of the trailing block
+        // ---- Householder reflector for x = A[r0:n, k]  (LAPACK dlarfg)
+        double part = 0.0;
+        for (int r = r0 + 1 + tid; r < n; r += TRI_THREADS) {
+            const double x = A[r * (r + 1) / 2 + k];
+            part = fma(x, x, part);
+        }
+        const double xnorm2 = block_sum(part, red);
+        const double alpha = A[(size_t)r0 * (r0 + 1) / 2 + k];
+        if (tid == 0) d_out[k] = A[(size_t)k * (k + 1) / 2 + k];
+        if (xnorm2 == 0.0) {  // already tridiagonal in this column
+            if (tid == 0) e_out[k] = alpha;
+            continue;
+        }
+        const double beta = -copysign(sqrt(alpha * alpha + xnorm2), alpha);
+        const double tau = (beta - alpha) / beta;
+        const double inv = 1.0 / (alpha - beta);
+        if (tid == 0) e_out[k] = beta;
+        for (int r = r0 + tid; r < n; r += TRI_THREADS) v[r] = (r == r0) ? 1.0 : A[r * (r + 1) / 2 + k] * inv;
+        __syncthreads();
+        // ---- p = tau * A22 v: row part (warp per row, lanes along the contiguous row) ...
+        for (int i = r0 + warp; i < n; i += TRI_WARPS) {
+            const double* Ai = A + i * (i + 1) / 2;
+            double s = 0.0;
+            for (int j = r0 + lane; j <= i; j += 32) s = fma(Ai[j], v[j], s);
+            s = warp_sum(s);
+            if (lane == 0) p[i] = s;
+        }
+        __syncthreads();
+        // ... column part: p_j += sum_{i > j} A[i][j] v_i.  Lanes own consecutive columns j and walk the SAME row i
+        // together (consecutive addresses, conflict-free); the rows are dealt round-robin to TRI_GROUPS groups of
+        // 256 threads whose partial sums meet in `cpart`.
+        {
+            const int m = n - r0;
+            const int jj0 = tid & 255, grp = tid >> 8;
+            for (int jj = jj0; jj < m; jj += 256) {
+                const int j = r0 + jj;
+                double s = 0.0;
+                for (int i = r0 + 1 + grp; i < n; i += TRI_GROUPS)
+                    if (i > j) s = fma(A[i * (i + 1) / 2 + j], v[i], s);
+                cpart[grp * nv + j] = s;
+            }
+        }
+        __syncthreads();
+        for (int r = r0 + tid; r < n; r += TRI_THREADS) {
+            double s = p[r];
+#pragma unroll
+            for (int g = 0; g < TRI_GROUPS; ++g) s += cpart[g * nv + r];
+            p[r] = s;
+        }
+        __syncthreads();
+        // ---- w = tau p - (tau^2/2)(p.v) v
+        double pv = 0.0;
+        for (int r = r0 + tid; r < n; r += TRI_THREADS) pv = fma(p[r], v[r], pv);
+        pv = block_sum(pv, red);
+        const double c = 0.5 * tau * tau * pv;
+        for (int r = r0 + tid; r < n; r += TRI_THREADS) p[r] = tau * p[r] - c * v[r];
+        __syncthreads();
+        // ---- A22 -= v w^T + w v^T  (lower triangle)
+        for (int i = r0 + warp; i < n; i += TRI_WARPS) {
+            double* Ai = A + i * (i + 1) / 2;
+            const double vi = v[i], wi = p[i];
+            for (int j = r0 + lane; j <= i; j += 32) Ai[j] -= vi * p[j] + wi * v[j];
+        }
+        __syncthreads();
+    }
+    if (tid == 0) {
+        if (n >= 2) {
+            d_out[n - 2] = A[(size_t)(n - 2) * (n - 1) / 2 + (n - 2)];
+            e_out[n - 2] = A[(size_t)(n - 1) * n / 2 + (n - 2)];
+        }
+        d_out[n - 1] = A[(size_t)(n - 1) * n / 2 + (n - 1)];
+        e_out[n - 1] = 0.0;
+    }
+}
+
+// ---------------------------------- Sturm bisection -----------------------------------------
+// One CTA per anchor, one thread per eigenvalue (index k = k-th smallest).  d, e^2 live in shared memory and
+// are read as warp broadcasts.  count(x) = #eigenvalues < x by the LAPACK dlaebz recurrence
+//   q_0 = d_0 - x,  q_i = d_i - x - e_{i-1}^2 / q_{i-1}   (|q| < pivmin -> -pivmin),   count = #{q_i < 0}.
+__global__ void __launch_bounds__(256) bisect_kernel(const uint8_t* __restrict__ workspace, int n, int n_out,
+                                                     float* __restrict__ sv, int* __restrict__ iters_out) {
+    extern __shared__ __align__(16) uint8_t bis_smem[];
+    double* d = reinterpret_cast<double*>(bis_smem);
+    double* e2 = d + n;
+    __shared__ double s_lo, s_hi, s_pivmin;
+    const int a = blockIdx.x;
+    const size_t per_anchor = tri_packed_bytes(n) + 2 * (size_t)n * sizeof(double);
+    const double* dg = reinterpret_cast<const double*>(workspace + (size_t)a * per_anchor + tri_packed_bytes(n));
+    const double* eg = dg + n;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        d[i] = dg[i];
+        const double e = eg[i];
+        e2[i] = e * e;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {  // Gershgorin interval and pivmin
+        double lo = d[0], hi = d[0], emax = 0.0;
+        for (int i = 0; i < n; ++i) {
+            const double el = i > 0 ? sqrt(e2[i - 1]) : 0.0, er = i + 1 < n ? sqrt(e2[i]) : 0.0;
+            lo = fmin(lo, d[i] - el - er);
+            hi = fmax(hi, d[i] + el + er);
+            emax = fmax(emax, e2[i]);
+        }
+        const double span = fmax(fabs(lo), fabs(hi));
+        s_lo = lo - 1e-14 * span - 1e-300;
+        s_hi = hi + 1e-14 * span + 1e-300;
+        s_pivmin = 2.2250738585072014e-308 * fmax(1.0, emax);
+    }
+    __syncthreads();
+    int it = 0;
+    for (int k = threadIdx.x; k < n; k += blockDim.x) {
+        double lo = s_lo, hi = s_hi;
+        const double pivmin = s_pivmin;
+        const double atol = 1e-17 * fmax(fabs(lo), fabs(hi));
+        for (it = 0; it < 200; ++it) {
+            const double mid = 0.5 * (lo + hi);
+            if (hi - lo <= fmax(atol, 4.4e-16 * fmax(fabs(lo), fabs(hi))) || mid <= lo || mid >= hi) break;
+            double q = d[0] - mid;
+            int cnt = q < 0.0;
+            for (int i = 1; i < n; ++i) {
+                if (fabs(q) < pivmin) q = -pivmin;
+                q = d[i] - mid - e2[i - 1] / q;
+                cnt += q < 0.0;
+            }
+            if (cnt > k) hi = mid; else lo = mid;  // the k-th smallest (0-based) is < mid iff count(mid) > k
+        }
+        const double lam = 0.5 * (lo + hi);
+        const int pos = n - 1 - k;  // descending order
+        if (pos < n_out) sv[(size_t)a * n_out + pos] = (float)sqrt(fmax(lam, 0.0));
+    }
+    if (threadIdx.x == 0 && iters_out) iters_out[a] = it;
+}
+
+cudaError_t launch_spectrum_tridiag(const double* G, int n_anchors, int n, int n_out, float* sv, int* iters,
+                                    void* workspace, cudaStream_t stream) {
+    if (n_anchors <= 0 || n <= 0) return cudaSuccess;
+    const size_t need = tri_vec_bytes(n) + tri_packed_bytes(n);
+    const int a_in_smem = need <= TRI_SMEM_MAX;
+    const size_t smem = a_in_smem ? need : tri_vec_bytes(n);
+    if (smem > TRI_SMEM_MAX) return cudaErrorInvalidValue;
+    cudaError_t e = cudaFuncSetAttribute(tridiag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    tridiag_kernel<<<n_anchors, TRI_THREADS, smem, stream>>>(G, n, reinterpret_cast<uint8_t*>(workspace), a_in_smem);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    const size_t bsmem = 2 * (size_t)n * sizeof(double);
+    if (bsmem > 48 * 1024) {
+        e = cudaFuncSetAttribute(bisect_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bsmem);
+        if (e != cudaSuccess) return e;
+    }
+    int threads = ((n + 31) / 32) * 32;
+    if (threads > 256) threads = 256;
+    bisect_kernel<<<n_anchors, threads, bsmem, stream>>>(reinterpret_cast<const uint8_t*>(workspace), n, n_out, sv,
+                                                        iters);
+    return cudaGetLastError();
+}
+
+}  // namespace idb

@@ -59,8 +59,11 @@ class SpectrumResult:
     scores: Optional[torch.Tensor] = None  # [A, K, D] fp32 raw scores when requested
 
 
-def spectrum_from_rows(X: torch.Tensor, K: int, D: int, scale: float, rows_per_anchor: Optional[int] = None
-                       ) -> SpectrumResult:
+SPECTRUM_METHOD = _lib.SPECTRUM_TRIDIAG  # default solver; _lib.SPECTRUM_JACOBI selects the one-sided Jacobi
+
+
+def spectrum_from_rows(X: torch.Tensor, K: int, D: int, scale: float, rows_per_anchor: Optional[int] = None,
+                       method: Optional[int] = None) -> SpectrumResult:
     """dim_reduction.py:190-199 + plot_utils.py:224-229 on device.
     X: [A, rows_per_anchor, ld] fp32 (rows >= K and columns >= D are ignored)."""
     _require_cuda(X, "X")
@@ -82,7 +85,8 @@ def spectrum_from_rows(X: torch.Tensor, K: int, D: int, scale: float, rows_per_a
     sv = torch.empty(A, n_out, dtype=torch.float32, device=dev)
     sweeps = torch.empty(A, dtype=torch.int32, device=dev)
     with _stage("spectrum", A * (n * n * 8.0 + n_out * 4.0)):
-        call("idb_spectrum", ptr(G), A, n, n_out, ptr(sv), ptr(sweeps), ptr(ws), st)
+        call("idb_spectrum", ptr(G), A, n, n_out, SPECTRUM_METHOD if method is None else method, ptr(sv),
+                 ptr(sweeps), ptr(ws), st)
     dims = torch.empty(A, dtype=torch.int32, device=dev)
     if n_out >= 3:
         call("idb_id_from_spectrum", ptr(sv), A, n_out, n_out, ptr(dims), st)

@@ -94,11 +94,15 @@ int idb_center_gram(const float* X, long long anchor_stride, int ld, int n_ancho
                     double* colmean, double* G, void* stream);
 
 /* Singular values of the centred score matrix from its Gram matrix (replaces torch.linalg.svd at
- * dim_reduction.py:197-198): fp64 Cholesky G = L L^T, one-sided Jacobi on L in fp32, one anchor per CTA.
+ * dim_reduction.py:197-198), one anchor per CTA, matrix resident in shared memory while it fits:
+ *   IDB_SPECTRUM_TRIDIAG  fp64 Householder tridiagonalisation + Sturm bisection (one thread per eigenvalue);
+ *   IDB_SPECTRUM_JACOBI   fp64 Cholesky G = L L^T, then one-sided Jacobi on L in fp32 with warp-shuffle rotations.
  * sv [n_anchors][n_out] fp32 descending (n_out <= n: the reference returns min(K, D) values);
- * sweeps [n_anchors] (may be NULL) = Jacobi sweeps used.  workspace: idb_spectrum_workspace_bytes. */
+ * sweeps [n_anchors] (may be NULL) = Jacobi sweeps / bisection steps used.  workspace: idb_spectrum_workspace_bytes. */
+#define IDB_SPECTRUM_JACOBI 0
+#define IDB_SPECTRUM_TRIDIAG 1
 size_t idb_spectrum_workspace_bytes(int n_anchors, int n);
-int idb_spectrum(const double* G, int n_anchors, int n, int n_out, float* sv, int* sweeps, void* workspace,
+int idb_spectrum(const double* G, int n_anchors, int n, int n_out, int method, float* sv, int* sweeps, void* workspace,
                  void* stream);
 
 /* Spectral-gap read-out, plot_utils.py:224-229 (dup :173-182) with softmax :211-214:
