@@ -35,6 +35,7 @@ SIGNATURES = {
     "idb_anchor_linear": (_i, [_vp, _i, _i, _f, _vp, _i, _vp, _vp, _i, _f, _vp, _i, _i, _i, _i, _vp]),
     "idb_fcn_hidden_layer": (_i, [_vp, _vp, _vp, _vp, _i, _f, _f, _i, _i, _i, _vp, _i, _vp, _vp, _vp]),
     "idb_fcn_output_layer": (_i, [_vp, _vp, _vp, _vp, _i, _f, _i, _i, _i, _vp, _vp]),
+    "idb_fcn_anchor_layer": (_i, [_vp, _vp, _vp, _vp, _i, _f, _f, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "idb_fcn_scores": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _f, _vp, _vp]),
     "idb_ksphere_gt_score": (_i, [_vp, _vp, _f, _i, _i, _i, _vp, _vp]),
     "idb_center_gram": (_i, [_vp, _ll, _i, _i, _i, _i, _d, _vp, _vp, _vp]),
@@ -68,7 +69,7 @@ def load():
 
 # CUDA kernels each entry point enqueues (for bench.py's `gpu_launches` claim)
 KERNELS_PER_CALL = {"idb_perturb": 1, "idb_pack_weight": 1, "idb_anchor_linear": 1, "idb_fcn_hidden_layer": 1,
-                    "idb_fcn_output_layer": 1, "idb_fcn_scores": 1, "idb_ksphere_gt_score": 1, "idb_center_gram": 2,
+                    "idb_fcn_output_layer": 1, "idb_fcn_anchor_layer": 1, "idb_fcn_scores": 1, "idb_ksphere_gt_score": 1, "idb_center_gram": 2,
                     "idb_spectrum": 2, "idb_id_from_spectrum": 1}
 launch_count = 0
 

@@ -53,10 +53,9 @@ int idb_pack_weight(const float* w, int N, int K, int ldw, int Np, int Kc, int w
     const int IDB_W_BF16 = IDB_FMT_BF16, IDB_W_FP16 = IDB_FMT_FP16;
     if (!w || !hi || !lo || N <= 0 || K <= 0 || ldw < K) return fail("idb_pack_weight: bad argument");
     if (w_fmt != IDB_W_BF16 && w_fmt != IDB_W_FP16) return fail("idb_pack_weight: unknown w_fmt");
-    if (w_fmt == IDB_W_BF16 && scale != 1.0f) return fail("idb_pack_weight: scale must be 1 for IDB_W_BF16");
     if (!(scale > 0.f)) return fail("idb_pack_weight: scale must be positive");
-    if (Np % 256 || Kc % 64 || Np < N || Kc < K || !aligned16(hi) || !aligned16(lo))
-        return fail("idb_pack_weight: need Np % 256 == 0, Kc % 64 == 0, Np >= N, Kc >= K, 16-byte aligned slabs");
+    if (Np % 128 || Kc % 64 || Np < N || Kc < K || !aligned16(hi) || !aligned16(lo))
+        return fail("idb_pack_weight: need Np % 128 == 0, Kc % 64 == 0, Np >= N, Kc >= K, 16-byte aligned slabs");
     return check(idb::launch_pack_weight(w, N, K, ldw, Np, Kc, w_fmt, scale, static_cast<uint8_t*>(hi), static_cast<uint8_t*>(lo),
                                          static_cast<cudaStream_t>(stream)),
                  "idb_pack_weight");
@@ -109,6 +108,16 @@ int idb_fcn_output_layer(const void* a_hi, const void* a_lo, const void* w_hi, c
     if (!out_f32 || !aligned16(out_f32)) return fail("idb_fcn_output_layer: out_f32 must be set and 16-byte aligned");
     return gemm_common(1, a_hi, a_lo, w_hi, w_lo, w_fmt, w_inv_scale, 1.0f, M, Np, Kc, nullptr, 128, nullptr, nullptr, out_f32, stream,
                        "idb_fcn_output_layer");
+}
+
+int idb_fcn_anchor_layer(const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, int fmt,
+                         float acc_scale, float out_scale, int M, int Np, int Kc, const float* bias, float* out_f32,
+                         void* out_hi, void* out_lo, void* stream) {
+    if (!out_f32 || !aligned16(out_f32)) return fail("idb_fcn_anchor_layer: out_f32 must be set and 16-byte aligned");
+    if ((out_hi == nullptr) != (out_lo == nullptr) || !aligned16(out_hi) || !aligned16(out_lo))
+        return fail("idb_fcn_anchor_layer: out_hi/out_lo must both be set (16-byte aligned) or both NULL");
+    return gemm_common(2, a_hi, a_lo, w_hi, w_lo, fmt, acc_scale, out_scale, M, Np, Kc, bias, 128, out_hi, out_lo,
+                       out_f32, stream, "idb_fcn_anchor_layer");
 }
 
 int idb_fcn_scores(const float* a_out, int ld_a, const float* d_out, int ld_d, int n_anchors, int K, int Kp, int D,

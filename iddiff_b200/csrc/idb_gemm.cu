@@ -150,6 +150,9 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_bf16x3_kernel(const Gemm
                     s_em1[as * BN + c] = expm1f(fminf(a, 0.f));
                 }
                 asm volatile("bar.sync 1, %0;" ::"n"(EPI_THREADS) : "memory");
+            } else if (kMode == 2) {  // anchor layer: p.a0 is the bias vector [Np] (may be null)
+                for (int c = et; c < BN; c += EPI_THREADS) s_a0[as * BN + c] = p.a0 ? __ldg(p.a0 + n0 + c) : 0.f;
+                asm volatile("bar.sync 1, %0;" ::"n"(EPI_THREADS) : "memory");
             }
             mbar_wait(&tfull[as], aphase);
             tc_fence_after();
@@ -162,7 +165,19 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_bf16x3_kernel(const Gemm
                 tmem_ld_wait();
 #pragma unroll
                 for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) * p.acc_scale);
-                if (kMode == 0) {
+                if (kMode == 2) {  // pre-activation = acc + bias, kept in fp32 for the hidden-layer epilogues
+                    const float* sb = s_a0 + as * BN + cc * 32;
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + sb[j]);
+                }
+                if (kMode == 1 || kMode == 2) {
+                    float4* dst = reinterpret_cast<float4*>(p.out_f32 + m * (size_t)p.Np + n0 + cc * 32);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        dst[j] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]),
+                                             __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+                }
+                if (kMode == 0 || (kMode == 2 && p.out_hi != nullptr)) {
                     const float* sa = s_a0 + as * BN + cc * 32;
                     const float* se = s_em1 + as * BN + cc * 32;
                     const size_t n = n0 + cc * 32;  // 32 columns = half of one 64-wide output slab
@@ -175,20 +190,21 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_bf16x3_kernel(const Gemm
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
                             const int c = ch * 8 + j * 2;
-                            const float e0 = elu_deviation(sa[c], se[c], __uint_as_float(v[c]));
-                            const float e1 = elu_deviation(sa[c + 1], se[c + 1], __uint_as_float(v[c + 1]));
+                            float e0, e1;
+                            if (kMode == 0) {
+                                e0 = elu_deviation(sa[c], se[c], __uint_as_float(v[c]));
+                                e1 = elu_deviation(sa[c + 1], se[c + 1], __uint_as_float(v[c + 1]));
+                            } else {  // next layer's anchor input: ELU of the pre-activation
+                                const float x0 = __uint_as_float(v[c]), x1 = __uint_as_float(v[c + 1]);
+                                e0 = x0 > 0.f ? x0 : expm1f(x0);
+                                e1 = x1 > 0.f ? x1 : expm1f(x1);
+                            }
                             split_pair16(e0 * p.out_scale, e1 * p.out_scale, p.fmt, h[j], l[j]);
                         }
                         const int sw = ((chunk0 + ch) ^ (int)(m & 7)) << 4;
                         *reinterpret_cast<uint4*>(row_hi + sw) = make_uint4(h[0], h[1], h[2], h[3]);
                         *reinterpret_cast<uint4*>(row_lo + sw) = make_uint4(l[0], l[1], l[2], l[3]);
                     }
-                } else {
-                    float4* dst = reinterpret_cast<float4*>(p.out_f32 + m * (size_t)p.Np + n0 + cc * 32);
-#pragma unroll
-                    for (int j = 0; j < 8; ++j)
-                        dst[j] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]),
-                                             __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
                 }
             }
             tc_fence_before();
@@ -210,10 +226,14 @@ cudaError_t launch_gemm_bf16x3(int mode, const GemmParams& p, int num_sms, cudaS
         e = cudaFuncSetAttribute(gemm_bf16x3_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GEMM_SMEM);
         if (e != cudaSuccess) return e;
         gemm_bf16x3_kernel<0><<<grid, GEMM_THREADS, GEMM_SMEM, stream>>>(p);
-    } else {
+    } else if (mode == 1) {
         e = cudaFuncSetAttribute(gemm_bf16x3_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GEMM_SMEM);
         if (e != cudaSuccess) return e;
         gemm_bf16x3_kernel<1><<<grid, GEMM_THREADS, GEMM_SMEM, stream>>>(p);
+    } else {
+        e = cudaFuncSetAttribute(gemm_bf16x3_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GEMM_SMEM);
+        if (e != cudaSuccess) return e;
+        gemm_bf16x3_kernel<2><<<grid, GEMM_THREADS, GEMM_SMEM, stream>>>(p);
     }
     return cudaGetLastError();
 }

@@ -124,6 +124,11 @@ class FcnEngine:
         st = stream_ptr()
         self.fmt = int(fmt)
         self.a_scale = self.A_SCALE_FP16 if self.fmt == _lib.FMT_FP16 else 1.0
+        self.b_pad = []
+        for l, b in enumerate(self.b):
+            bp = torch.zeros(self.Np[l], dtype=torch.float32, device=self.dev)
+            bp[:b.numel()] = b
+            self.b_pad.append(bp)
         self.w_hi, self.w_lo, self.w_inv_scale = [], [], []
         for l, w in enumerate(self.w):
             scale = 1.0
@@ -156,7 +161,36 @@ class FcnEngine:
         return Kp * (2 * act + self.Kc[0] * 4 + self.Np[-1] * 4) + self.D * self.D * 8 * 3
 
     def anchor_chain(self, x0: torch.Tensor, mean_coeff: float, label: float) -> List[torch.Tensor]:
-        """Pre-activations of every layer at the un-perturbed anchors, fp32: list of [A, Np[l]]."""
+        """Pre-activations of every layer at the un-perturbed anchors, fp32: list of [>= A, Np[l]].
+        Tensor-core version: the anchors are one more (small) batch through the same split-precision GEMM."""
+        A = x0.shape[0]
+        Mp = _ceil(A, 128)
+        st = stream_ptr()
+        dev = self.dev
+        a_hi = torch.empty(Mp * self.Kc[0] * 2, dtype=torch.uint8, device=dev)
+        a_lo = torch.empty_like(a_hi)
+        # anchor activations are O(1): no scaling needed to keep fp16 hi/lo normal (scale 1)
+        call("idb_pack_weight", ptr(x0), A, self.D, self.D, Mp, self.Kc[0], self.fmt, float(mean_coeff), ptr(a_hi),
+             ptr(a_lo), st)
+        P = []
+        for l in range(self.n_layers):
+            if l == 0:  # time column of cat([x, t]) folded into the bias (t is one constant, dim_reduction.py:173-174)
+                bias = torch.zeros(self.Np[0], dtype=torch.float32, device=dev)
+                bias[:self.out_real[0]] = self.b[0] + self.w[0][:, self.D] * label
+            else:
+                bias = self.b_pad[l]
+            out = torch.empty(Mp, self.Np[l], dtype=torch.float32, device=dev)
+            last = l == self.n_layers - 1
+            o_hi = None if last else torch.empty(Mp * self.Np[l] * 2, dtype=torch.uint8, device=dev)
+            o_lo = None if last else torch.empty_like(o_hi)
+            call("idb_fcn_anchor_layer", ptr(a_hi), ptr(a_lo), ptr(self.w_hi[l]), ptr(self.w_lo[l]), self.fmt,
+                 self.w_inv_scale[l], 1.0, Mp, self.Np[l], self.Kc[l], ptr(bias), ptr(out), ptr(o_hi), ptr(o_lo), st)
+            P.append(out)
+            a_hi, a_lo = o_hi, o_lo
+        return P
+
+    def anchor_chain_fp32(self, x0: torch.Tensor, mean_coeff: float, label: float) -> List[torch.Tensor]:
+        """Plain-fp32 SIMT version of anchor_chain (cross-check)."""
         A = x0.shape[0]
         st = stream_ptr()
         P = []

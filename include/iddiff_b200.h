@@ -51,7 +51,8 @@ int idb_perturb(const float* x0, const float* z, int n_anchors, int K, int D, in
 #define IDB_FMT_FP16 1
 
 /* nn.Linear weight [N][K] fp32 (row stride ldw) -> hi/lo slabs [Kc/64][Np][128B] of (w * scale), zero padded.
- * Np % 256 == 0, Kc % 64 == 0.  Done once per model (models/fcn.py:16-30 holds the weights).  For IDB_FMT_FP16
+ * Np % 128 == 0 (% 256 when used as a W operand), Kc % 64 == 0; also packs anchor rows [A][D] into an A operand.
+ * Done once per model (models/fcn.py:16-30 holds the weights).  For IDB_FMT_FP16
  * choose scale = 2^k with max|w|*scale in [2^13, 2^14). */
 int idb_pack_weight(const float* w, int N, int K, int ldw, int Np, int Kc, int fmt, float scale, void* hi, void* lo,
                     void* stream);
@@ -76,6 +77,16 @@ int idb_fcn_hidden_layer(const void* a_hi, const void* a_lo, const void* w_hi, c
 /* Last nn.Linear on the deviations: out_f32 [M][Np] fp32 row-major = acc_scale * A (hi+lo) . W^T (hi+lo). */
 int idb_fcn_output_layer(const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, int fmt,
                          float acc_scale, int M, int Np, int Kc, float* out_f32, void* stream);
+
+/* One nn.Linear of models/fcn.py:20-30 evaluated at the un-perturbed anchors on the tensor cores (same kernel,
+ * third epilogue): pre[m][n] = acc_scale * A (hi+lo) . W^T (hi+lo) + bias[n] -> out_f32 [M][Np] fp32, and, when
+ * out_hi/out_lo are set, hi/lo pairs of out_scale * ELU(pre) in slabs [Np/64][M][128B] = the next layer's anchor
+ * operand.  A rows are anchors (M % 128 == 0, rows past the last anchor are padding); bias [Np] may be NULL.
+ * The time column of torch.cat([x, t]) (models/fcn.py:35-38) is folded into the first layer's bias by the host.
+ * idb_anchor_linear above is the plain-fp32 SIMT version of the same op, kept as its unit-test cross-check. */
+int idb_fcn_anchor_layer(const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, int fmt,
+                         float acc_scale, float out_scale, int M, int Np, int Kc, const float* bias, float* out_f32,
+                         void* out_hi, void* out_lo, void* stream);
 
 /* Raw scores as the reference's score_fn returns them (models/utils.py:264-267):
  *   score[a][k][c] = -(a_out[a][c] + d_out[a*Kp + k][c]) / std,  score [n_anchors][K][D] fp32. */

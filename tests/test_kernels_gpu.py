@@ -290,6 +290,31 @@ def test_ksphere_score_matches_oracle():
         assert err < 2e-4 * ref.abs().max().item(), (sigma, err, ref.abs().max().item())
 
 
+@pytest.mark.parametrize("fmt", [_lib.FMT_BF16, _lib.FMT_FP16])
+def test_anchor_chain_tensor_core_matches_fp32_and_fp64(fmt):
+    from iddiff_b200.engine import FcnEngine
+    D, H, L, A = 100, 320, 2, 37
+    g = torch.Generator().manual_seed(21)
+    dims = [(H, D + 1)] + [(H, H)] * L + [(D, H)]
+    ws = [((torch.rand(o, i, generator=g) * 2 - 1) / math.sqrt(i)).to(dev()) for o, i in dims]
+    bs = [((torch.rand(o, generator=g) * 2 - 1) * 0.5).to(dev()) for o, _ in dims]
+    eng = FcnEngine(ws, bs, fmt=fmt)
+    x0 = _rand(A, D, seed=22)
+    mc, label = 0.9995, 0.999
+    P = eng.anchor_chain(x0, mc, label)
+    Q = eng.anchor_chain_fp32(x0, mc, label)
+    torch.cuda.synchronize()
+    h = torch.cat([(torch.tensor(mc, device=dev()) * x0).double(), torch.full((A, 1), label, dtype=torch.float64, device=dev())], 1)
+    for l in range(L + 2):
+        ref = h @ ws[l].double().T + bs[l].double()
+        n = ref.shape[1]
+        tol = (2e-5 if fmt == _lib.FMT_FP16 else 1e-4) * ref.abs().max().item()
+        assert (P[l][:A, :n].double() - ref).abs().max().item() < tol
+        assert (Q[l][:A, :n].double() - ref).abs().max().item() < 2e-5 * ref.abs().max().item()
+        assert P[l][:A, n:].abs().max().item() == 0 if P[l].shape[1] > n else True
+        h = _elu(ref)
+
+
 def test_bad_arguments_are_rejected_loudly():
     with pytest.raises(_lib.IdbError):
         call("idb_fcn_output_layer", None, None, None, None, 0, 1.0, 128, 256, 64, None, None)
