@@ -63,6 +63,40 @@ def build_engine(config, score_model: Optional[torch.nn.Module] = None, device="
     raise NotImplementedError(f"model.name={name!r}: only 'fcn' and 'ksphere_gt' are built so far (DESIGN.md scope)")
 
 
+def sde_coefficients(sde, t: float):
+    """(mean_coeff, std) as exact float32 values for x -> mean_coeff*x + std*z, from ANY object with the
+    reference's `marginal_prob(x, t)` (sde_lib.py): evaluated on a ones tensor with the same float32 torch ops."""
+    if hasattr(sde, "coefficients"):
+        return sde.coefficients(t)
+    tt = torch.ones(1, dtype=torch.float32) * t
+    mean, std = sde.marginal_prob(torch.ones(1, 1, dtype=torch.float32), tt)
+    return float(mean.reshape(-1)[0]), float(std.reshape(-1)[0])
+
+
+def shard_range(n_anchors: int, rank: int, world: int):
+    """Contiguous anchor shard [lo, hi) of this rank; the last ranks take the remainder-free tail."""
+    per = (n_anchors + world - 1) // world
+    lo = min(rank * per, n_anchors)
+    return lo, min(lo + per, n_anchors)
+
+
+def all_gather_spectra(sv: torch.Tensor, dims: torch.Tensor, n_total: int, group=None):
+    """The path's only collective: every rank contributes its [n_local, n] spectra and [n_local] IDs (shards
+    padded to the common size), everyone receives [n_total, n] / [n_total] in global anchor order."""
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    per = (n_total + world - 1) // world
+    pad = per - sv.shape[0]
+    if pad:
+        sv = torch.cat([sv, sv.new_zeros(pad, sv.shape[1])])
+        dims = torch.cat([dims, dims.new_zeros(pad)])
+    out_sv = sv.new_empty(world * per, sv.shape[1])
+    out_dims = dims.new_empty(world * per)
+    dist.all_gather_into_tensor(out_sv, sv.contiguous(), group=group)
+    dist.all_gather_into_tensor(out_dims, dims.contiguous(), group=group)
+    return out_sv[:n_total], out_dims[:n_total]
+
+
 def estimate_anchors(engine, anchors: torch.Tensor, K: int, sde, t: float, *, seed: int = 0,
                      z: Optional[torch.Tensor] = None, chunk: Optional[int] = None, anchor_id0: int = 0,
                      mem_budget_bytes: int = 24 << 30) -> Dict[str, torch.Tensor]:
@@ -70,7 +104,7 @@ def estimate_anchors(engine, anchors: torch.Tensor, K: int, sde, t: float, *, se
     HOST.  Host anchors are copied to the device chunk by chunk (pinned staging), results copied back once."""
     dev = engine.dev
     N, D = anchors.shape
-    mc, std = sde.coefficients(t)
+    mc, std = sde_coefficients(sde, t)
     label = float((torch.ones(1, dtype=torch.float32) * t * (sde.N - 1))[0])
     if chunk is None:
         per = engine.bytes_per_anchor(K) if isinstance(engine, FcnEngine) else engine.bytes_per_anchor(K, D)

@@ -1,0 +1,55 @@
+"""CPU, gloo, world_size 2: the anchor sharding and the single all-gather of the path."""
+import os
+import socket
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, n_total, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from iddiff_b200.dim_reduction import all_gather_spectra, shard_range
+    lo, hi = shard_range(n_total, rank, world)
+    # a rank's "spectra": row a holds the global anchor id, so order and ownership are checkable
+    sv = torch.arange(lo, hi, dtype=torch.float32)[:, None] * torch.ones(1, 5)
+    dims = torch.arange(lo, hi, dtype=torch.int32) + 100
+    g_sv, g_dims = all_gather_spectra(sv, dims, n_total)
+    q.put((rank, lo, hi, g_sv[:, 0].tolist(), g_dims.tolist()))
+    dist.destroy_process_group()
+
+
+def test_shard_and_all_gather_world2():
+    for n_total in (7, 8):
+        ctx = mp.get_context("spawn")
+        q = ctx.Queue()
+        port = _free_port()
+        procs = [ctx.Process(target=_worker, args=(r, 2, port, n_total, q)) for r in range(2)]
+        for p in procs:
+            p.start()
+        res = sorted(q.get(timeout=120) for _ in procs)
+        for p in procs:
+            p.join(timeout=60)
+            assert p.exitcode == 0
+        covered = []
+        for rank, lo, hi, sv0, dims in res:
+            covered += list(range(lo, hi))
+            assert sv0 == [float(i) for i in range(n_total)]          # global order, nothing lost or duplicated
+            assert dims == [100 + i for i in range(n_total)]
+        assert covered == list(range(n_total))                          # shards tile the anchors exactly
+
+
+def test_shard_range_edges():
+    from iddiff_b200.dim_reduction import shard_range
+    assert [shard_range(4096, r, 8) for r in (0, 7)] == [(0, 512), (3584, 4096)]
+    assert [shard_range(3, r, 4) for r in range(4)] == [(0, 1), (1, 2), (2, 3), (3, 3)]
+    assert shard_range(0, 0, 2) == (0, 0)

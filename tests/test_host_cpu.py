@@ -1,0 +1,122 @@
+"""CPU: the host-side mirror of the reference interface (no kernels are launched)."""
+import os
+import tempfile
+
+import numpy as np
+import pytest
+import torch
+
+from iddiff_b200 import data, models, plot_utils, sde_lib
+from iddiff_b200 import dim_reduction as DR
+from iddiff_b200.config import ConfigDict, lookup
+from oracle import fixtures as FX
+from oracle import id_oracle as O
+
+
+def test_k_schedule_matches_oracle_and_reference_fixture():
+    g = FX.golden("k_schedule")
+    for shape, nd, B, K, nb in zip(g["shape"], g["ndim"], g["B"], g["K"], g["num_batches"]):
+        assert DR.k_schedule(list(shape[:nd]), int(B)) == O.k_schedule(list(shape[:nd]), int(B))
+        assert DR.k_schedule(list(shape[:nd]), int(B))[2] == int(K)
+    assert DR.k_schedule([200], 500)[2] == 1501 and DR.k_schedule([3, 64, 64], 128)[2] == 16768
+
+
+def test_gather_anchors_keeps_the_n_minus_one_quirk():
+    batches = [torch.arange(12.).reshape(4, 3), torch.arange(12., 18.).reshape(2, 3)]
+    got = DR.gather_anchors(batches, 6)
+    assert len(got) == 5 and [b for _, b in got] == [4, 4, 4, 4, 2]       # last loader batch is smaller -> other K
+    assert len(DR.gather_anchors(batches, 3)) == 2 and DR.gather_anchors(batches, 1) == []
+    assert len(DR.gather_anchors(batches, 100)) == 6
+
+
+def test_sde_marginals_match_reference_fixture():
+    g = FX.golden("sde_marginals")
+    t, x = torch.from_numpy(g["t"]), torch.from_numpy(g["x"])
+    cases = {"ve_ksphere": sde_lib.VESDE(1e-2, 4, 1000), "ve_image": sde_lib.VESDE(0.009, 50, 1000),
+             "vp": sde_lib.VPSDE(0.1, 20, 1000), "subvp": sde_lib.subVPSDE(0.1, 20, 1000), "snr": sde_lib.SNRSDE(1000)}
+    for name, sde in cases.items():
+        mean, std = sde.marginal_prob(x, t)
+        assert np.array_equal(mean.numpy(), g[name + "_mean"]) and np.array_equal(std.numpy(), g[name + "_std"]), name
+        for ti in (1e-5, 1e-3):   # the two scalars the kernels get are the per-row fp32 values of marginal_prob
+            mc, sd = sde.coefficients(ti)
+            m2, s2 = sde.marginal_prob(torch.full((2, 3), 0.7), torch.ones(2) * ti)
+            assert np.float32(sd) == s2[0].item() and torch.equal(torch.tensor(mc) * torch.full((3,), 0.7), m2[0])
+            assert DR.sde_coefficients(sde, ti) == (mc, sd)
+
+    class RefLike:  # an object with only the reference's surface
+        N = 1000
+        marginal_prob = staticmethod(cases["vp"].marginal_prob)
+    assert DR.sde_coefficients(RefLike(), 1e-3) == cases["vp"].coefficients(1e-3)
+
+
+def test_configure_sde_picks_eps_like_the_reference():
+    base = dict(sigma_min=0.01, sigma_max=4.0, beta_min=0.1, beta_max=20.0, num_scales=1000)
+    for name, eps in [("vesde", 1e-5), ("VPSDE", 1e-3), ("subvpsde", 1e-3), ("snrsde", 1e-3)]:
+        cfg = ConfigDict(training=dict(sde=name), model=base, data=dict(use_data_mean=False))
+        sde, e = sde_lib.configure_sde(cfg)
+        assert e == eps and sde.N == 1000
+    with pytest.raises(NotImplementedError):
+        sde_lib.configure_sde(ConfigDict(training=dict(sde="foo"), model=base, data={}))
+
+
+def test_readout_matches_reference_fixture():
+    g = FX.golden("readout")
+    for s, n, d in zip(g["spectra"], g["lens"], g["dims"]):
+        assert plot_utils.dim_from_spectrum(s[:n].tolist()) == int(d) == O.id_from_spectrum(s[:n].tolist())
+    svd = {"singular_values": [g["spectra"][0][: g["lens"][0]].tolist(), g["spectra"][0][: g["lens"][0]][::-1].tolist()]}
+    assert np.array_equal(np.asarray(plot_utils.extract_sing_vals(svd, "mean")[0]), g["mean_mode"])
+    assert plot_utils.dims_from_spectra(svd, "first") == [int(g["dims"][0])]
+    with pytest.raises(ZeroDivisionError):
+        plot_utils.dim_from_spectrum([3.0, 1.0, 1.0, 0.5])
+
+
+def test_ksphere_generator_matches_oracle():
+    for kw in [dict(embedding_type="random_isometry"), dict(embedding_type="first", angle_std=0.5),
+               dict(embedding_type="separating"), dict(embedding_type="along_axis", radii=[1.0, 2.5])]:
+        torch.manual_seed(5)
+        a = data.ksphere_points(20, 2, 40, [3, 6] if "radii" not in kw else 6, 0.01, **kw)
+        torch.manual_seed(5)
+        b = O.ksphere_data(20, 2, 40, [3, 6] if "radii" not in kw else 6, 0.01, **kw)
+        assert a.shape == b.shape == (40, 40) and (a - b).abs().max().item() < 1e-6
+    g = FX.golden("ksphere_c1")   # and against the reference's own KSphereDataset output
+    torch.manual_seed(int(g["seed"]))
+    d = data.ksphere_points(int(g["B"]), 1, int(g["D"]), int(g["manifold_dim"]), 0.0, "random_isometry")
+    np.testing.assert_allclose(d[:8].numpy(), g["data_head"], rtol=1e-5, atol=1e-6)
+
+
+def test_config_lookup_and_registries():
+    cfg = ConfigDict(logging=dict(svd_points=5), dim_estimation={}, model=dict(name="fcn"))
+    assert lookup(cfg, "logging.svd_points") == 5 and lookup(cfg, "dim_estimation.num_datapoints") is None
+    assert cfg.logging.svd_points == 5 and cfg["model"]["name"] == "fcn"
+    assert models.get_model("fcn") is models.FCN and models.get_model("ksphere_gt") is models.KSphereGT
+    with pytest.raises(ValueError):
+        models.register_model("fcn")(object)
+
+
+def test_fcn_holder_has_reference_state_dict_layout_and_loads_lightning_ckpt():
+    g = FX.golden("fcn_small_ve")
+    D, H, L = int(g["D"]), int(g["H"]), int(g["L"])
+    cfg = ConfigDict(model=dict(name="fcn", state_size=D, hidden_layers=L, hidden_nodes=H, dropout=0.0))
+    m = models.create_model(cfg)
+    state = FX.golden_fcn_state(g)
+    assert set(m.state_dict()) == set(state)                      # mlp.0.weight, mlp.3.weight, ... like models/fcn.py
+    with tempfile.TemporaryDirectory() as td:
+        path = os.path.join(td, "last.ckpt")
+        torch.save({"state_dict": {"score_model." + k: v for k, v in state.items()}, "hyper_parameters": {}}, path)
+        models.load_checkpoint_into(m, path)
+    for k, v in state.items():
+        assert torch.equal(m.state_dict()[k], v)
+    with pytest.raises(RuntimeError, match="holds weights only"):
+        m(torch.zeros(1, D), torch.zeros(1))
+
+
+def test_drop_in_rejects_cpu_device_and_missing_num_datapoints():
+    from iddiff_b200._lib import IdbError
+    with tempfile.TemporaryDirectory() as td:
+        cfg = ConfigDict(logging=dict(log_path=td, log_name="x", svd_points=3), device="cpu",
+                         training=dict(sde="vesde", batch_size=4), data=dict(datamodule="Tensor", anchors=torch.zeros(4, 3),
+                                                                            use_data_mean=False, manifold_dim=2),
+                         model=dict(name="ksphere_gt", sigma_min=0.01, sigma_max=4.0, num_scales=1000))
+        with pytest.raises(IdbError, match="CUDA devices only"):
+            DR.get_manifold_dimension(cfg, return_svd=True)
+        assert os.path.isdir(os.path.join(td, "x", "svd"))        # the reference creates the directory first

@@ -166,3 +166,55 @@ def test_linearity_property_full_size():
     torch.cuda.synchronize()
     np.testing.assert_allclose(r2.singular_values.cpu().numpy(), 4.0 * r1.singular_values.cpu().numpy(), rtol=1e-5)
     assert r1.dims.cpu().tolist() == r2.dims.cpu().tolist() == [51] * 4
+
+
+def test_drop_in_get_manifold_dimension_against_reference_outputs(tmp_path):
+    """The reference entry point's signature end to end: config -> Lightning-style checkpoint -> anchors from a
+    loader batch of B rows -> {'singular_values': ...} + pickle, compared with what the REAL reference returned."""
+    import pickle
+    from iddiff_b200 import dim_reduction as DR, plot_utils
+    from iddiff_b200.config import ConfigDict
+    g = FX.golden("fcn_small_ve")
+    D, H, L, B, K = int(g["D"]), int(g["H"]), int(g["L"]), int(g["B"]), int(g["K"])
+    state = FX.golden_fcn_state(g)
+    ckpt = tmp_path / "last.ckpt"
+    torch.save({"state_dict": {"score_model." + k: v for k, v in state.items()}}, ckpt)
+    x0 = torch.from_numpy(g["x0"])
+    n = x0.shape[0]
+    batch = x0[torch.arange(B) % n]                      # the loader batch the reference run saw
+    cfg = ConfigDict(logging=dict(log_path=str(tmp_path), log_name="run", svd_points=int(g["svd_points"])),
+                     dim_estimation={}, device="cuda:0",
+                     training=dict(sde="vesde", batch_size=B, lightning_module="base"),
+                     data=dict(datamodule="Tensor", anchors=batch, shape=[D], use_data_mean=False),
+                     model=dict(name="fcn", checkpoint_path=str(ckpt), state_size=D, hidden_layers=L, hidden_nodes=H,
+                                dropout=0.0, sigma_min=1e-2, sigma_max=4.0, beta_min=0.1, beta_max=20.0,
+                                num_scales=1000))
+    noise = torch.from_numpy(g["z"]).reshape(n, -1, D)[:, :K]
+    info = DR.get_manifold_dimension(cfg, name=None, return_svd=True, noise=[noise[i] for i in range(n)])
+    sv = np.asarray(info["singular_values"])
+    assert sv.shape == g["singular_values"].shape        # svd_points - 1 anchors, min(K, D) values each
+    truth = O.fcn_centred_spectrum_fp64(*FX.fcn_state_to_lists(state, L), x0, noise, "vesde", SDE_PARAMS)
+    np.testing.assert_allclose(sv, truth, rtol=SV_RTOL)
+    assert plot_utils.dims_from_spectra(info) == g["dims"].tolist() == DR.get_manifold_dimension.last_dims
+    assert plot_utils.dims_on_device(info) == g["dims"].tolist()
+    assert all(isinstance(v, float) for v in info["singular_values"][0])
+    # pickle branch: name=None -> 'None.pkl' like the reference (run_lib.py:324-325, dim_reduction.py:210)
+    assert DR.get_manifold_dimension(cfg, noise=[noise[i] for i in range(n)]) is None
+    with open(tmp_path / "run" / "svd" / "None.pkl", "rb") as f:
+        assert pickle.load(f) == info
+
+
+def test_ksphere_drop_in_runs_from_config(tmp_path):
+    from iddiff_b200 import dim_reduction as DR
+    from iddiff_b200.config import ConfigDict
+    cfg = ConfigDict(logging=dict(log_path=str(tmp_path), log_name="ks", svd_points=4), device="cuda:0",
+                     training=dict(sde="vesde", batch_size=133, workers=0),
+                     data=dict(datamodule="KSphere", data_samples=266, n_spheres=1, ambient_dim=100, manifold_dim=10,
+                               noise_std=0.0, embedding_type="random_isometry", split=[0.5, 0.25, 0.25],
+                               use_data_mean=False),
+                     model=dict(name="ksphere_gt", sigma_min=1e-2, sigma_max=4.0, num_scales=1000))
+    torch.manual_seed(0)
+    info = DR.get_manifold_dimension(cfg, return_svd=True, seed=5)
+    sv = np.asarray(info["singular_values"])
+    assert sv.shape == (3, 100) and np.all(np.diff(sv, axis=1) <= 0) and np.isfinite(sv).all()
+    assert sv[:, 0].min() > 20 * sv[:, 1].max()          # radial-only field: one dominant direction (appendix A.10)
