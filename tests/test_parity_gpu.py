@@ -209,7 +209,7 @@ def test_ksphere_drop_in_runs_from_config(tmp_path):
     from iddiff_b200.config import ConfigDict
     cfg = ConfigDict(logging=dict(log_path=str(tmp_path), log_name="ks", svd_points=4), device="cuda:0",
                      training=dict(sde="vesde", batch_size=133, workers=0),
-                     data=dict(datamodule="KSphere", data_samples=266, n_spheres=1, ambient_dim=100, manifold_dim=10,
+                     data=dict(datamodule="KSphere", data_samples=268, n_spheres=1, ambient_dim=100, manifold_dim=10,
                                noise_std=0.0, embedding_type="random_isometry", split=[0.5, 0.25, 0.25],
                                use_data_mean=False),
                      model=dict(name="ksphere_gt", sigma_min=1e-2, sigma_max=4.0, num_scales=1000))
