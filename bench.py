@@ -60,6 +60,17 @@ def measured_peaks():
         return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
 
 
+def ncu_traffic_bytes(chunk):
+    """DRAM bytes of one hidden-layer launch from the committed ncu --set full capture (taken at chunk=128)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_gemm_hidden_full.json")) as f:
+            k = json.load(f)[0]
+        gb = float(k["dram__bytes_read.sum"]["value"]) + float(k["dram__bytes_write.sum"]["value"])
+        return gb * 1e9 * chunk / 128.0
+    except Exception:
+        return None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -273,7 +284,9 @@ def run_ours(args):
                 "mma_issue_frac": 3 * ach_tf / peak_tf,
                 "note": "achieved = ALGORITHMIC FLOPs (2*A*K*H*H per launch); the split-precision scheme issues 3 "
                         "tcgen05.mma per algorithmic product, so tensor-pipe occupancy is mma_issue_frac",
-                "traffic": None, "share_of_step": hid["ms_total"] / ms_total}
+                "traffic": ncu_traffic_bytes(chunk), "traffic_source": "profiles/r1_gemm_hidden_full.json (ncu --set full, "
+                "dram__bytes_read.sum + dram__bytes_write.sum of one launch over a 128-anchor chunk)",
+                "algorithmic_bytes": 2.0 * (2 * chunk * 1536 * H * 2) , "share_of_step": hid["ms_total"] / ms_total}
     line = {"metric": "ID-estimates/sec", "value": value, "unit": "anchors/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "fp16x2 split operands (22-bit), fp32 accumulate; fp64 Gram",
