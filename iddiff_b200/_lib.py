@@ -42,6 +42,8 @@ SIGNATURES = {
     "idb_spectrum_workspace_bytes": (C.c_size_t, [_i, _i]),
     "idb_spectrum": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "idb_id_from_spectrum": (_i, [_vp, _i, _i, _i, _vp, _vp]),
+    "idb_upfirdn2d": (_i, [_vp, _vp] + [_i] * 14 + [_vp, _vp]),
+    "idb_fused_bias_act": (_i, [_vp, _vp, _vp, _i, _i, _f, _f, _ll, _i, _i, _vp, _vp]),
 }
 
 
@@ -70,7 +72,7 @@ def load():
 # CUDA kernels each entry point enqueues (for bench.py's `gpu_launches` claim)
 KERNELS_PER_CALL = {"idb_perturb": 1, "idb_pack_weight": 1, "idb_anchor_linear": 1, "idb_fcn_hidden_layer": 1,
                     "idb_fcn_output_layer": 1, "idb_fcn_anchor_layer": 1, "idb_fcn_scores": 1, "idb_ksphere_gt_score": 1, "idb_center_gram": 2,
-                    "idb_spectrum": 2, "idb_id_from_spectrum": 1}
+                    "idb_spectrum": 2, "idb_id_from_spectrum": 1, "idb_upfirdn2d": 1, "idb_fused_bias_act": 1}
 launch_count = 0
 
 

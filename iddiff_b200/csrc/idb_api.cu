@@ -23,6 +23,12 @@ int num_sms() {
 bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 }  // namespace
 
+namespace idb {
+int api_fail(const char* what) { return fail(what); }
+int api_check(cudaError_t e, const char* where) { return check(e, where); }
+int api_num_sms() { return num_sms(); }
+}  // namespace idb
+
 extern "C" {
 
 int idb_abi_version(void) { return 1; }

@@ -71,4 +71,22 @@ cudaError_t launch_spectrum_tridiag(const double* G, int n_anchors, int n, int n
 
 cudaError_t launch_id_readout(const float* sv, int n_anchors, int n, int ld, int* dims, cudaStream_t stream);
 
+struct UpFirDnParams {
+    const float* in;      // [major][in_h][in_w][minor]
+    const float* kernel;  // [kh][kw]
+    float* out;           // [major][out_h][out_w][minor]
+    int major, in_h, in_w, minor, kh, kw;
+    int up_x, up_y, down_x, down_y, pad_x0, pad_x1, pad_y0, pad_y1;
+    int out_h, out_w, minor_tile;  // filled by the launcher
+};
+cudaError_t launch_upfirdn2d(UpFirDnParams p, int num_sms, cudaStream_t stream);
+cudaError_t launch_fused_bias_act(const float* x, const float* b, const float* ref, int act, int grad, float alpha,
+                                  float scale, long long size_x, int step_b, int size_b, float* out, int num_sms,
+                                  cudaStream_t stream);
+
+// helpers of the C-ABI translation units (thread-local error string lives in idb_api.cu)
+int api_fail(const char* what);
+int api_check(cudaError_t e, const char* where);
+int api_num_sms();
+
 }  // namespace idb

@@ -121,6 +121,26 @@ int idb_spectrum(const double* G, int n_anchors, int n, int n_out, int method, f
  * ZeroDivisionError (s[1]==s[2]).  sv [n_anchors][ld] fp32, n >= 3. */
 int idb_id_from_spectrum(const float* sv, int n_anchors, int n, int ld, int* dims, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Image score networks.
+ * ------------------------------------------------------------------------------------------------ */
+
+/* Replaces the reference extension op `upfirdn2d(input[major,in_h,in_w,minor], kernel[kh,kw], up_x, up_y, down_x,
+ * down_y, pad_x0, pad_x1, pad_y0, pad_y1) -> [major,out_h,out_w,minor]` (op/upfirdn2d.cpp:12-22; kernels
+ * op/upfirdn2d_kernel.cu:49-369; semantics = upfirdn2d_native, op/upfirdn2d.py:162-200): zero-stuff by up, pad (negative
+ * pad crops), correlate with the flipped FIR kernel, keep every down-th sample.  fp32, contiguous.
+ * out_h = (in_h*up_y + pad_y0 + pad_y1 - kh)/down_y + 1 (same for w); the caller allocates `out`. */
+int idb_upfirdn2d(const float* input, const float* kernel, int major, int in_h, int in_w, int minor, int kernel_h,
+                  int kernel_w, int up_x, int up_y, int down_x, int down_y, int pad_x0, int pad_x1, int pad_y0,
+                  int pad_y1, float* out, void* stream);
+
+/* Replaces the reference extension op `fused_bias_act(input, bias, refer, act, grad, alpha, scale)`
+ * (op/fused_bias_act.cpp:11-20, op/fused_bias_act_kernel.cu:19-99): out[i] = f(x[i] + bias[(i/step_b) % size_b]) * scale,
+ * f by (act, grad): act 1 linear, 3 leaky ReLU(alpha); grad 0 forward, 1 gradient (sign from refer), 2 -> 0.
+ * bias / refer may be NULL.  The reference passes step_b = prod(shape[2:]), size_b = shape[1] (fused_bias_act_kernel.cu:80-84). */
+int idb_fused_bias_act(const float* input, const float* bias, const float* refer, int act, int grad, float alpha,
+                       float scale, long long size_x, int step_b, int size_b, float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
