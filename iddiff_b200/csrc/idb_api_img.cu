@@ -35,4 +35,111 @@ int idb_fused_bias_act(const float* input, const float* bias, const float* refer
                      "idb_fused_bias_act");
 }
 
+int idb_groupnorm_stats(const float* src0, int C0, const float* src1, int C1, int N, int HW, int groups, double eps,
+                        double* sums, float* mean_rstd, void* stream) {
+    if (!src0 || !sums || !mean_rstd || C0 <= 0 || C1 < 0 || (C1 > 0 && !src1) || N < 0 || HW <= 0 || groups <= 0)
+        return api_fail("idb_groupnorm_stats: bad argument");
+    if ((C0 + C1) % groups) return api_fail("idb_groupnorm_stats: channels must divide into groups");
+    if (groups > 1024) return api_fail("idb_groupnorm_stats: at most 1024 groups");
+    return api_check(idb::launch_gn_stats(src0, C0, src1, C1, N, HW, groups, eps, sums, mean_rstd, idb::api_num_sms(),
+                                          static_cast<cudaStream_t>(stream)),
+                     "idb_groupnorm_stats");
+}
+
+int idb_conv_prep(const float* src0, int C0, const float* src1, int C1, int N, int Hs, int Ws, int src_nchw, int mode,
+                  const float* mean_rstd, int groups, const float* gamma, const float* beta, int act, float scale,
+                  void* out_hi, void* out_lo, int Cp, float* out_f32, void* stream) {
+    if (!src0 || C0 <= 0 || C1 < 0 || (C1 > 0 && !src1) || N < 0 || Hs <= 0 || Ws <= 0)
+        return api_fail("idb_conv_prep: bad argument");
+    if (mode < 0 || mode > 3) return api_fail("idb_conv_prep: mode must be 0..3");
+    if (src_nchw && C1) return api_fail("idb_conv_prep: NCHW source cannot be concatenated");
+    if ((out_hi == nullptr) != (out_lo == nullptr)) return api_fail("idb_conv_prep: out_hi/out_lo both or neither");
+    if (!out_hi && !out_f32) return api_fail("idb_conv_prep: no output requested");
+    const int C = C0 + C1;
+    if (out_hi && (Cp % 64 || Cp < C)) return api_fail("idb_conv_prep: Cp must be a multiple of 64 and >= C");
+    if (mean_rstd && (groups <= 0 || C % groups)) return api_fail("idb_conv_prep: bad groups");
+    if (mode == 3 && ((Hs | Ws) & 1)) return api_fail("idb_conv_prep: average pool needs even H, W");
+    if (act < 0 || act > 1) return api_fail("idb_conv_prep: act must be 0 or 1");
+    if (out_hi && !(scale > 0.f)) return api_fail("idb_conv_prep: scale must be positive");
+    idb::PrepParams p;
+    p.src0 = src0; p.src1 = src1; p.C0 = C0; p.C1 = C1; p.N = N; p.Hs = Hs; p.Ws = Ws; p.src_nchw = src_nchw;
+    p.mode = mode;
+    p.planes = mode == 2 ? 4 : 1;
+    p.Ho = mode == 1 ? 2 * Hs : (mode == 0 ? Hs : (mode == 2 ? (Hs + 1) / 2 : Hs / 2));
+    p.Wo = mode == 1 ? 2 * Ws : (mode == 0 ? Ws : (mode == 2 ? (Ws + 1) / 2 : Ws / 2));
+    p.mean_rstd = mean_rstd; p.groups = mean_rstd ? groups : 1; p.cg = mean_rstd ? C / groups : C;
+    p.gamma = gamma; p.beta = beta; p.act = act; p.scale = scale;
+    p.out_hi = static_cast<uint8_t*>(out_hi); p.out_lo = static_cast<uint8_t*>(out_lo);
+    p.Cp = out_hi ? Cp : ((C + 7) & ~7);
+    p.out_f32 = out_f32;
+    return api_check(idb::launch_conv_prep(p, idb::api_num_sms(), static_cast<cudaStream_t>(stream)), "idb_conv_prep");
+}
+
+namespace {
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn encode_tiled() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* sym = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(sym);
+    }
+    return fn;
+}
+}  // namespace
+
+int idb_conv2d(const void* a_hi, const void* a_lo, int planes, int N, int H, int W, int Cp, const void* w_hi,
+               const void* w_lo, int n_taps, const int* taps_host, int Np, int Cout, float acc_scale, float out_scale,
+               const float* bias, const float* residual, int ld_res, float* out, int ldo, void* stream) {
+    if (!a_hi || !a_lo || !w_hi || !w_lo || !out || !taps_host) return api_fail("idb_conv2d: null pointer");
+    if (planes <= 0 || N <= 0 || H <= 0 || W <= 0 || Cp <= 0 || Cp % 64) return api_fail("idb_conv2d: bad shape (Cp % 64)");
+    if (n_taps <= 0 || n_taps > 16) return api_fail("idb_conv2d: 1..16 taps");
+    if (Np % 128 || Cout <= 0 || Cout > Np || ldo < Cout) return api_fail("idb_conv2d: need Np % 128 == 0, Cout <= Np, ldo >= Cout");
+    if (residual && ld_res < Cout) return api_fail("idb_conv2d: ld_res < Cout");
+    idb::ConvParams p;
+    p.BW = W < 128 ? W : 128;
+    if (128 % p.BW || W % p.BW) return api_fail("idb_conv2d: W must be a power of two <= 128 or a multiple of 128");
+    p.BH = 128 / p.BW < H ? 128 / p.BW : H;
+    if ((128 / p.BW) % p.BH || H % p.BH) return api_fail("idb_conv2d: H must be a power of two or a multiple of 128/W");
+    p.BI = 128 / (p.BW * p.BH);
+    EncodeTiledFn enc = encode_tiled();
+    if (!enc) return api_fail("idb_conv2d: cuTensorMapEncodeTiled not available from the driver");
+    const cuuint64_t dims[5] = {(cuuint64_t)Cp, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N, (cuuint64_t)planes};
+    const cuuint64_t strides[4] = {(cuuint64_t)Cp * 2, (cuuint64_t)W * Cp * 2, (cuuint64_t)H * W * Cp * 2,
+                                   (cuuint64_t)N * H * W * Cp * 2};
+    const cuuint32_t box[5] = {64, (cuuint32_t)p.BW, (cuuint32_t)p.BH, (cuuint32_t)p.BI, 1};
+    const cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+    for (int which = 0; which < 2; ++which) {
+        CUresult r = enc(which ? &p.tm_lo : &p.tm_hi, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 5,
+                         const_cast<void*>(which ? a_lo : a_hi), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                         CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return api_fail("idb_conv2d: cuTensorMapEncodeTiled rejected the activation tensor");
+    }
+    p.w_hi = static_cast<const uint8_t*>(w_hi); p.w_lo = static_cast<const uint8_t*>(w_lo);
+    p.N = N; p.H = H; p.W = W; p.Cp = Cp; p.n_taps = n_taps;
+    for (int t = 0; t < n_taps; ++t) {
+        p.tap_plane[t] = taps_host[3 * t]; p.tap_dy[t] = taps_host[3 * t + 1]; p.tap_dx[t] = taps_host[3 * t + 2];
+        if (p.tap_plane[t] < 0 || p.tap_plane[t] >= planes) return api_fail("idb_conv2d: tap plane out of range");
+    }
+    p.Np = Np; p.Cout = Cout; p.acc_scale = acc_scale; p.out_scale = out_scale;
+    p.bias = bias; p.residual = residual; p.ld_res = ld_res; p.out = out; p.ldo = ldo;
+    return api_check(idb::launch_conv(p, idb::api_num_sms(), static_cast<cudaStream_t>(stream)), "idb_conv2d");
+}
+
+int idb_attention(const float* qkv, int N, int T, int ld, int heads, int dh, int q0, int k0, int v0, int head_stride,
+                  float scale, float* out, int ld_out, void* stream) {
+    if (!qkv || !out || N < 0 || T <= 0 || heads <= 0 || dh <= 0 || ld_out < heads * dh)
+        return api_fail("idb_attention: bad argument");
+    if (T > 1536) return api_fail("idb_attention: at most 1536 tokens (scores are kept in shared memory)");
+    idb::AttnParams p;
+    p.qkv = qkv; p.N = N; p.T = T; p.ld = ld; p.heads = heads; p.dh = dh; p.q0 = q0; p.k0 = k0; p.v0 = v0;
+    p.head_stride = head_stride; p.scale = scale; p.out = out; p.ld_out = ld_out;
+    return api_check(idb::launch_attention(p, static_cast<cudaStream_t>(stream)), "idb_attention");
+}
+
 }  // extern "C"

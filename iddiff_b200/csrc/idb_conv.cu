@@ -1,0 +1,232 @@
+// Implicit-GEMM convolution on the 5th-gen tensor cores for the U-Net score networks
+// (reference: every nn.Conv2d 3x3 / 1x1 and NIN of models/ddpm.py, models/ncsnpp.py, models/BeatGANsUNET.py --
+//  layers.py:93-100 ddpm_conv3x3, layers.py:555-564 NIN, layerspp.py conv3x3/conv1x1; cuDNN in the reference).
+//
+//   out[n,h,w,co] = out_scale * ( acc_scale * sum_{tap,ci} A[plane(tap)][n, h+dy(tap), w+dx(tap), ci] * Wt[co][tap][ci]
+//                                 + bias[co] + residual[n,h,w,co] )
+//
+// A is the activation in NHWC as hi/lo fp16 pairs (written by the operand-preparation pass, idb_unet.cu, which has
+// already applied GroupNorm + activation + up/down-sampling), so the M dimension of the GEMM is "output pixels" and
+// each filter tap is the SAME tensor shifted by (dy, dx): one 5-D TMA tensor map (C, W, H, N, plane) with
+// SWIZZLE_128B delivers the [128 pixels x 64 channels] operand tile of a tap straight into the K-major shared-memory
+// image tcgen05.mma reads, and the hardware's out-of-bounds zero fill IS the convolution's zero padding.  No im2col
+// buffer exists anywhere.  Stride-2 convolutions read four parity planes (space-to-depth done by the producer).
+//
+// Same split-precision scheme as the FCN chain (idb_gemm.cu): 3 tcgen05.mma (lo.hi + hi.lo + hi.hi) per product,
+// fp32 accumulation in TMEM, power-of-two operand scales undone exactly on the accumulator.
+//
+// Kernel shape: persistent, one CTA per SM, 64 + 512 threads: warp 0 TMA producer, warp 1 MMA issuer, 16 epilogue
+// warps; TMEM double-buffered (2 x BN fp32 columns) so the epilogue of tile i overlaps the MMAs of tile i+1.
+#include "idb_common.cuh"
+#include "idb_kernels.h"
+
+namespace idb {
+
+namespace {
+constexpr int CBM = 128;
+constexpr int CBK = 64;
+constexpr uint32_t CA_TILE = CBM * 128;  // 16 KB: 128 pixels x 64 fp16 channels
+constexpr int C_EPI_WARPS = 16;
+constexpr int C_EPI_THREADS = C_EPI_WARPS * 32;
+constexpr int C_THREADS = 64 + C_EPI_THREADS;
+
+template <int BN> struct ConvCfg {
+    static constexpr uint32_t B_TILE = BN * 128;
+    static constexpr uint32_t STAGE = 2 * CA_TILE + 2 * B_TILE;
+    static constexpr int STAGES = BN == 256 ? 2 : 3;
+    static constexpr size_t SMEM = 1024 + (size_t)STAGES * STAGE + 256;
+};
+
+__device__ __forceinline__ void tma_tensor5d_g2s(void* smem_dst, const CUtensorMap* tm, int c0, int c1, int c2, int c3,
+                                                 int c4, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.5d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], [%2];" ::
+            "r"(smem_u32(smem_dst)),
+        "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+        : "memory");
+}
+}  // namespace
+
+template <int BN>
+__global__ void __launch_bounds__(C_THREADS, 1) conv_fp16x3_kernel(const __grid_constant__ ConvParams p) {
+    using Cfg = ConvCfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)Cfg::STAGES * Cfg::STAGE);
+    uint64_t* full = bars;
+    uint64_t* empty = bars + Cfg::STAGES;
+    uint64_t* tfull = bars + 2 * Cfg::STAGES;
+    uint64_t* tempty = bars + 2 * Cfg::STAGES + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * Cfg::STAGES + 4);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int tiles_w = p.W / p.BW, tiles_h = p.H / p.BH;
+    const int tiles_img = (p.N + p.BI - 1) / p.BI;
+    const int m_tiles = tiles_w * tiles_h * tiles_img;
+    const int n_tiles_n = p.Np / BN;
+    const int n_tiles = m_tiles * n_tiles_n;
+    const int kc = p.Cp / CBK;          // 64-channel chunks per tap
+    const int n_kb = p.n_taps * kc;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < Cfg::STAGES; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&tfull[s], 1);
+            mbar_init(&tempty[s], C_EPI_THREADS);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, 2 * BN);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+                const int mt = t / n_tiles_n;
+                const size_t n0 = (size_t)(t % n_tiles_n) * BN;
+                const int w0 = (mt % tiles_w) * p.BW;
+                const int h0 = ((mt / tiles_w) % tiles_h) * p.BH;
+                const int i0 = (mt / (tiles_w * tiles_h)) * p.BI;
+                for (int kb = 0; kb < n_kb; ++kb) {
+                    const int tap = kb / kc, c0 = (kb % kc) * CBK;
+                    mbar_wait(&empty[stage], phase ^ 1);
+                    uint8_t* st = smem + (size_t)stage * Cfg::STAGE;
+                    mbar_arrive_expect_tx(&full[stage], Cfg::STAGE);
+                    const int cw = w0 + p.tap_dx[tap], ch = h0 + p.tap_dy[tap], cp = p.tap_plane[tap];
+                    tma_tensor5d_g2s(st, &p.tm_hi, c0, cw, ch, i0, cp, &full[stage]);
+                    tma_tensor5d_g2s(st + CA_TILE, &p.tm_lo, c0, cw, ch, i0, cp, &full[stage]);
+                    const size_t b_off = ((size_t)kb * p.Np + n0) * 128;
+                    tma_bulk_g2s(st + 2 * CA_TILE, p.w_hi + b_off, Cfg::B_TILE, &full[stage]);
+                    tma_bulk_g2s(st + 2 * CA_TILE + Cfg::B_TILE, p.w_lo + b_off, Cfg::B_TILE, &full[stage]);
+                    if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = umma_idesc_f16(CBM, BN, 0u, 0u);  // fp16 x fp16 -> fp32
+            int stage = 0;
+            uint32_t phase = 0;
+            int it = 0;
+            for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
+                const int as = it & 1;
+                const uint32_t aphase = (it >> 1) & 1;
+                mbar_wait(&tempty[as], aphase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + as * BN;
+                for (int kb = 0; kb < n_kb; ++kb) {
+                    mbar_wait(&full[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + (size_t)stage * Cfg::STAGE);
+                    const uint64_t ah = umma_desc_sw128(sa);
+                    const uint64_t al = umma_desc_sw128(sa + CA_TILE);
+                    const uint64_t bh = umma_desc_sw128(sa + 2 * CA_TILE);
+                    const uint64_t bl = umma_desc_sw128(sa + 2 * CA_TILE + Cfg::B_TILE);
+#pragma unroll
+                    for (int k = 0; k < CBK / 16; ++k) {
+                        const uint64_t adv = (uint64_t)((k * 32) >> 4);
+                        umma_bf16(d_tmem, al + adv, bh + adv, idesc, (kb | k) != 0);
+                        umma_bf16(d_tmem, ah + adv, bl + adv, idesc, 1);
+                        umma_bf16(d_tmem, ah + adv, bh + adv, idesc, 1);
+                    }
+                    umma_commit(&empty[stage]);
+                    if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(&tfull[as]);
+            }
+        }
+    } else {
+        const int quarter = warp & 3;
+        const int cgroup = (warp - 2) >> 2;
+        const int r = quarter * 32 + lane;  // row of the tile = TMEM lane = output pixel
+        int it = 0;
+        for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
+            const int as = it & 1;
+            const uint32_t aphase = (it >> 1) & 1;
+            const int mt = t / n_tiles_n;
+            const int n0 = (t % n_tiles_n) * BN;
+            const int w = (mt % tiles_w) * p.BW + r % p.BW;
+            const int h = ((mt / tiles_w) % tiles_h) * p.BH + (r / p.BW) % p.BH;
+            const int img = (mt / (tiles_w * tiles_h)) * p.BI + r / (p.BW * p.BH);
+            const bool row_ok = img < p.N;
+            const size_t pix = ((size_t)img * p.H + h) * p.W + w;
+            mbar_wait(&tfull[as], aphase);
+            tc_fence_after();
+            const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * BN;
+#pragma unroll 1
+            for (int cc = cgroup; cc < BN / 32; cc += C_EPI_WARPS / 4) {
+                const int c0 = n0 + cc * 32;
+                if (c0 >= p.Cout) continue;  // warp-uniform: padded output channels
+                uint32_t v[32];
+                tmem_ld32(t_row + cc * 32, v);
+                tmem_ld_wait();
+                if (!row_ok) continue;
+                float* dst = p.out + pix * p.ldo + c0;
+                const float* res = p.residual ? p.residual + pix * p.ld_res + c0 : nullptr;
+                if (c0 + 32 <= p.Cout && (p.ldo & 3) == 0 && (!res || (p.ld_res & 3) == 0)) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        float4 o;
+                        float4 b = p.bias ? __ldg(reinterpret_cast<const float4*>(p.bias + c0) + j)
+                                          : make_float4(0.f, 0.f, 0.f, 0.f);
+                        o.x = __uint_as_float(v[4 * j]) * p.acc_scale + b.x;
+                        o.y = __uint_as_float(v[4 * j + 1]) * p.acc_scale + b.y;
+                        o.z = __uint_as_float(v[4 * j + 2]) * p.acc_scale + b.z;
+                        o.w = __uint_as_float(v[4 * j + 3]) * p.acc_scale + b.w;
+                        if (res) {
+                            const float4 q = __ldg(reinterpret_cast<const float4*>(res) + j);
+                            o.x += q.x; o.y += q.y; o.z += q.z; o.w += q.w;
+                        }
+                        o.x *= p.out_scale; o.y *= p.out_scale; o.z *= p.out_scale; o.w *= p.out_scale;
+                        reinterpret_cast<float4*>(dst)[j] = o;
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        if (c0 + j < p.Cout) {
+                            float o = __uint_as_float(v[j]) * p.acc_scale + (p.bias ? __ldg(p.bias + c0 + j) : 0.f);
+                            if (res) o += __ldg(res + j);
+                            dst[j] = o * p.out_scale;
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            mbar_arrive(&tempty[as]);
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, 2 * BN);
+}
+
+template <int BN>
+static cudaError_t launch_conv_bn(const ConvParams& p, int num_sms, cudaStream_t stream) {
+    using Cfg = ConvCfg<BN>;
+    const int m_tiles = (p.W / p.BW) * (p.H / p.BH) * ((p.N + p.BI - 1) / p.BI);
+    const int n_tiles = m_tiles * (p.Np / BN);
+    const int grid = n_tiles < num_sms ? n_tiles : num_sms;
+    if (grid <= 0) return cudaSuccess;
+    cudaError_t e =
+        cudaFuncSetAttribute(conv_fp16x3_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM);
+    if (e != cudaSuccess) return e;
+    conv_fp16x3_kernel<BN><<<grid, C_THREADS, Cfg::SMEM, stream>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_conv(const ConvParams& p, int num_sms, cudaStream_t stream) {
+    if (p.Np % 256 == 0) return launch_conv_bn<256>(p, num_sms, stream);
+    return launch_conv_bn<128>(p, num_sms, stream);
+}
+
+}  // namespace idb

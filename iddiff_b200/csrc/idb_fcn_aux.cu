@@ -155,7 +155,8 @@ __global__ void __launch_bounds__(256) anchor_linear_kernel(const float* __restr
             float v = 0.f;
             if (a0 + r < A && k0 + kk < K) {
                 v = __fmul_rn(in_scale, in[(size_t)(a0 + r) * ld_in + k0 + kk]);
-                if (apply_elu) v = v > 0.f ? v : expm1f(v);
+                if (apply_elu == 1) v = v > 0.f ? v : expm1f(v);
+                else if (apply_elu == 2) v = v / (1.f + expf(-v));  // SiLU (time-embedding path of the U-Nets)
             }
             s_in[kk][r] = v;
             float wv = 0.f;

@@ -1,5 +1,6 @@
 // Internal launcher declarations shared by the .cu files and the C-ABI (idb_api.cu).
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -83,6 +84,55 @@ cudaError_t launch_upfirdn2d(UpFirDnParams p, int num_sms, cudaStream_t stream);
 cudaError_t launch_fused_bias_act(const float* x, const float* b, const float* ref, int act, int grad, float alpha,
                                   float scale, long long size_x, int step_b, int size_b, float* out, int num_sms,
                                   cudaStream_t stream);
+
+struct alignas(64) ConvParams {
+    CUtensorMap tm_hi, tm_lo;  // A operand: 5-D (Cp, W, H, N, planes) fp16, box (64, BW, BH, BI, 1), SWIZZLE_128B
+    const uint8_t* w_hi;       // slab [n_taps * Cp/64][Np][128 B]
+    const uint8_t* w_lo;
+    int N, H, W, Cp, n_taps;
+    int tap_plane[16], tap_dy[16], tap_dx[16];
+    int Np, Cout;
+    int BW, BH, BI;            // BW * BH * BI == 128 output pixels per tile
+    float acc_scale, out_scale;
+    const float* bias;         // [Cout] or null
+    const float* residual;     // [N][H][W][ld_res] or null
+    int ld_res;
+    float* out;                // [N][H][W][ldo]
+    int ldo;
+};
+cudaError_t launch_conv(const ConvParams& p, int num_sms, cudaStream_t stream);
+
+struct PrepParams {
+    const float* src0;  // NHWC [N][Hs][Ws][C0]  (NCHW [N][C0][Hs][Ws] when src_nchw)
+    const float* src1;  // optional second tensor concatenated along C: [N][Hs][Ws][C1]
+    int C0, C1, N, Hs, Ws, src_nchw;
+    int mode;           // 0 same size, 1 nearest x2 up, 2 stride-2 parity planes, 3 2x2 average pool
+    int planes, Ho, Wo;
+    const float* mean_rstd;  // [N][groups][2] or null
+    int groups, cg;
+    const float* gamma;      // [C] or null
+    const float* beta;
+    int act;                 // 0 none, 1 SiLU
+    float scale;             // power of two applied before the fp16 hi/lo split
+    uint8_t* out_hi;         // [planes][N][Ho][Wo][Cp] fp16 (may be null)
+    uint8_t* out_lo;
+    int Cp;
+    float* out_f32;          // optional fp32 [planes][N][Ho][Wo][C] copy of the transformed tensor
+};
+cudaError_t launch_conv_prep(const PrepParams& p, int num_sms, cudaStream_t stream);
+
+cudaError_t launch_gn_stats(const float* s0, int C0, const float* s1, int C1, int N, int HW, int groups, double eps,
+                            double* sums, float* mean_rstd, int num_sms, cudaStream_t stream);
+
+struct AttnParams {
+    const float* qkv;  // [N][T][ld]
+    int N, T, ld, heads, dh;
+    int q0, k0, v0, head_stride;  // channel offset of q / k / v of head h = x0 + h * head_stride
+    float scale;
+    float* out;        // [N][T][ld_out], channel h * dh + c
+    int ld_out;
+};
+cudaError_t launch_attention(const AttnParams& p, cudaStream_t stream);
 
 // helpers of the C-ABI translation units (thread-local error string lives in idb_api.cu)
 int api_fail(const char* what);

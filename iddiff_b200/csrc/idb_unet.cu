@@ -1,0 +1,270 @@
+// HBM-bound passes of the U-Net score networks (reference: models/ddpm.py, models/layers.py, models/ncsnpp.py,
+// models/BeatGANsblocks.py).  Activations live in HBM as fp32 NHWC; every convolution operand is produced by ONE
+// "operand preparation" pass that fuses everything the reference runs as separate elementwise / resampling kernels
+// between two convolutions:
+//
+//   concat of the skip tensor (ddpm.py:198) -> GroupNorm apply (layers.py:638,648) -> SiLU (:660,666)
+//   -> nearest x2 up-sampling (layers.py:600) | stride-2 parity split (layers.py:621-623) | 2x2 average pool
+//   -> hi/lo fp16 split (x 2^k) in the NHWC layout the implicit-GEMM convolution reads through TMA.
+//
+// GroupNorm statistics are one extra read of the tensor (fp64 accumulation).  Attention at 16 x 16 (layers.py:567-590)
+// is < 1 % of the network's FLOPs and is done in fp32 on the CUDA cores, scores resident in shared memory.
+#include "idb_common.cuh"
+#include "idb_kernels.h"
+
+namespace idb {
+
+// ---------------------------------- GroupNorm statistics -------------------------------------
+// sums[n][g] = (sum x, sum x^2) over the group's channels and all pixels, x = concat(src0, src1) along C.
+__global__ void __launch_bounds__(256) gn_stats_kernel(const float* __restrict__ s0, int C0,
+                                                       const float* __restrict__ s1, int C1, int HW, int groups,
+                                                       int CL, double* __restrict__ sums) {
+    extern __shared__ double gs[];  // [groups][2]
+    const int C = C0 + C1, cg = C / groups;
+    const int n = blockIdx.x;
+    for (int i = threadIdx.x; i < 2 * groups; i += blockDim.x) gs[i] = 0.0;
+    __syncthreads();
+    const int cl = threadIdx.x % CL, pl = threadIdx.x / CL, PL = blockDim.x / CL;
+    const int per = (HW + gridDim.y - 1) / gridDim.y;
+    const int p0 = blockIdx.y * per, p1 = min(HW, p0 + per);
+    for (int c = cl; c < C; c += CL) {
+        const float* src = c < C0 ? s0 + (size_t)n * HW * C0 + c : s1 + (size_t)n * HW * C1 + (c - C0);
+        const int ld = c < C0 ? C0 : C1;
+        double a = 0.0, b = 0.0;
+        for (int px = p0 + pl; px < p1; px += PL) {
+            const double v = (double)__ldg(src + (size_t)px * ld);
+            a += v;
+            b += v * v;
+        }
+        atomicAdd(&gs[2 * (c / cg)], a);
+        atomicAdd(&gs[2 * (c / cg) + 1], b);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 2 * groups; i += blockDim.x) atomicAdd(&sums[(size_t)n * 2 * groups + i], gs[i]);
+}
+
+// (mean, rstd) in fp32 from the fp64 sums: var = E[x^2] - mean^2 (biased, as torch GroupNorm), rstd = 1/sqrt(var+eps)
+__global__ void gn_finalize_kernel(const double* __restrict__ sums, int total, double count, double eps,
+                                   float* __restrict__ mr) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    const double m = sums[2 * i] / count;
+    double var = sums[2 * i + 1] / count - m * m;
+    if (var < 0.0) var = 0.0;
+    mr[2 * i] = (float)m;
+    mr[2 * i + 1] = (float)(1.0 / sqrt(var + eps));
+}
+
+cudaError_t launch_gn_stats(const float* s0, int C0, const float* s1, int C1, int N, int HW, int groups, double eps,
+                            double* sums, float* mean_rstd, int num_sms, cudaStream_t stream) {
+    if (N <= 0) return cudaSuccess;
+    const int C = C0 + C1;
+    cudaError_t e = cudaMemsetAsync(sums, 0, (size_t)N * groups * 2 * sizeof(double), stream);
+    if (e != cudaSuccess) return e;
+    int CL = 32;
+    while (CL < C && CL < 256) CL <<= 1;
+    int slices = (4 * num_sms + N - 1) / N;
+    const int max_slices = (HW + 15) / 16;
+    if (slices > max_slices) slices = max_slices;
+    if (slices < 1) slices = 1;
+    gn_stats_kernel<<<dim3(N, slices), 256, 2 * groups * sizeof(double), stream>>>(s0, C0, s1, C1, HW, groups, CL, sums);
+    const int total = N * groups;
+    gn_finalize_kernel<<<(total + 255) / 256, 256, 0, stream>>>(sums, total, (double)(C / groups) * HW, eps, mean_rstd);
+    return cudaGetLastError();
+}
+
+// ---------------------------------- operand preparation --------------------------------------
+__device__ __forceinline__ float prep_fetch(const PrepParams& p, int n, int y, int x, int c) {
+    // transformed source value at SOURCE pixel (y, x), channel c of the concat
+    float v;
+    if (p.src_nchw) {
+        v = __ldg(p.src0 + (((size_t)n * p.C0 + c) * p.Hs + y) * p.Ws + x);
+    } else if (c < p.C0) {
+        v = __ldg(p.src0 + (((size_t)n * p.Hs + y) * p.Ws + x) * p.C0 + c);
+    } else {
+        v = __ldg(p.src1 + (((size_t)n * p.Hs + y) * p.Ws + x) * p.C1 + (c - p.C0));
+    }
+    if (p.mean_rstd) {
+        const int g = c / p.cg;
+        const float2 mr = __ldg(reinterpret_cast<const float2*>(p.mean_rstd) + (size_t)n * p.groups + g);
+        v = (v - mr.x) * mr.y;
+    }
+    if (p.gamma) v = fmaf(v, __ldg(p.gamma + c), p.beta ? __ldg(p.beta + c) : 0.f);
+    if (p.act == 1) v = v / (1.f + expf(-v));
+    return v;
+}
+
+// one thread = one output pixel x one 8-channel chunk (16 B of hi and 16 B of lo)
+__global__ void __launch_bounds__(256) conv_prep_kernel(const PrepParams p) {
+    const int chunks = p.Cp >> 3;
+    const int C = p.C0 + p.C1;
+    const long long total = (long long)p.planes * p.N * p.Ho * p.Wo * chunks;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int ch = (int)(i % chunks);
+        long long r = i / chunks;
+        const int xo = (int)(r % p.Wo); r /= p.Wo;
+        const int yo = (int)(r % p.Ho); r /= p.Ho;
+        const int n = (int)(r % p.N);
+        const int plane = (int)(r / p.N);
+        float v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int c = ch * 8 + j;
+            float o = 0.f;
+            if (c < C) {
+                if (p.mode == 0) {
+                    o = prep_fetch(p, n, yo, xo, c);
+                } else if (p.mode == 1) {  // nearest-neighbour x2 (F.interpolate 'nearest', layers.py:600)
+                    o = prep_fetch(p, n, yo >> 1, xo >> 1, c);
+                } else if (p.mode == 2) {  // parity plane (py, px) of a stride-2 read: src[2*yo + py][2*xo + px]
+                    const int y = 2 * yo + (plane >> 1), x = 2 * xo + (plane & 1);
+                    o = (y < p.Hs && x < p.Ws) ? prep_fetch(p, n, y, x, c) : 0.f;
+                } else {  // 2 x 2 average pool (BeatGANs_nn.py avg_pool_nd)
+                    const float a = prep_fetch(p, n, 2 * yo, 2 * xo, c), b = prep_fetch(p, n, 2 * yo, 2 * xo + 1, c);
+                    const float d = prep_fetch(p, n, 2 * yo + 1, 2 * xo, c), e = prep_fetch(p, n, 2 * yo + 1, 2 * xo + 1, c);
+                    o = ((a + b) + (d + e)) * 0.25f;
+                }
+            }
+            v[j] = o;
+        }
+        const size_t pix = (((size_t)plane * p.N + n) * p.Ho + yo) * p.Wo + xo;
+        if (p.out_hi) {
+            uint32_t h[4], l[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) split_pair16(v[2 * j] * p.scale, v[2 * j + 1] * p.scale, 1, h[j], l[j]);
+            *reinterpret_cast<uint4*>(p.out_hi + (pix * p.Cp + ch * 8) * 2) = make_uint4(h[0], h[1], h[2], h[3]);
+            *reinterpret_cast<uint4*>(p.out_lo + (pix * p.Cp + ch * 8) * 2) = make_uint4(l[0], l[1], l[2], l[3]);
+        }
+        if (p.out_f32) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                if (ch * 8 + j < C) p.out_f32[pix * C + ch * 8 + j] = v[j];
+        }
+    }
+}
+
+cudaError_t launch_conv_prep(const PrepParams& p, int num_sms, cudaStream_t stream) {
+    const long long total = (long long)p.planes * p.N * p.Ho * p.Wo * (p.Cp >> 3);
+    if (total <= 0) return cudaSuccess;
+    long long grid = (total + 255) / 256;
+    const long long cap = (long long)num_sms * 16;
+    if (grid > cap) grid = cap;
+    conv_prep_kernel<<<(unsigned)grid, 256, 0, stream>>>(p);
+    return cudaGetLastError();
+}
+
+// ---------------------------------- attention -------------------------------------------------
+// out[n][i][h*dh + c] = sum_j softmax_j( scale * <q_i, k_j> ) v[j][c]     (layers.py:581-587; heads for BeatGANs)
+// CTA = 32 queries of one (image, head); scores for all T keys live in shared memory.
+constexpr int AT_Q = 32;
+
+__global__ void __launch_bounds__(256) attention_kernel(const AttnParams p) {
+    extern __shared__ float at_smem[];
+    float* Sm = at_smem;                    // [T][32]   scores, then probabilities (transposed: key-major)
+    float* Qc = Sm + (size_t)p.T * AT_Q;    // [32 c][32 i]
+    float* Kc = Qc + 32 * AT_Q;             // [256 j][33]
+    float* red = Kc + 256 * 33;             // [8][32] x 2
+    const int t = threadIdx.x;
+    const int i0 = blockIdx.x * AT_Q, head = blockIdx.y, n = blockIdx.z;
+    const float* base = p.qkv + (size_t)n * p.T * p.ld;
+    const int qo = p.q0 + head * p.head_stride, ko = p.k0 + head * p.head_stride, vo = p.v0 + head * p.head_stride;
+
+    // phase 1: S[i][j] = scale * <q_i, k_j>
+    for (int j0 = 0; j0 < p.T; j0 += 256) {
+        float acc[AT_Q];
+#pragma unroll
+        for (int i = 0; i < AT_Q; ++i) acc[i] = 0.f;
+        for (int c0 = 0; c0 < p.dh; c0 += 32) {
+            __syncthreads();
+            for (int e = t; e < 32 * AT_Q; e += 256) {  // Qc[c][i]
+                const int i = e >> 5, c = e & 31;
+                Qc[c * AT_Q + i] = (i0 + i < p.T && c0 + c < p.dh) ? __ldg(base + (size_t)(i0 + i) * p.ld + qo + c0 + c) : 0.f;
+            }
+            for (int e = t; e < 256 * 32; e += 256) {  // Kc[j][c]
+                const int j = e >> 5, c = e & 31;
+                Kc[j * 33 + c] = (j0 + j < p.T && c0 + c < p.dh) ? __ldg(base + (size_t)(j0 + j) * p.ld + ko + c0 + c) : 0.f;
+            }
+            __syncthreads();
+#pragma unroll 4
+            for (int c = 0; c < 32; ++c) {
+                const float kv = Kc[t * 33 + c];
+                const float4* q4 = reinterpret_cast<const float4*>(Qc + c * AT_Q);
+#pragma unroll
+                for (int i4 = 0; i4 < AT_Q / 4; ++i4) {
+                    const float4 q = q4[i4];
+                    acc[4 * i4] = fmaf(q.x, kv, acc[4 * i4]);
+                    acc[4 * i4 + 1] = fmaf(q.y, kv, acc[4 * i4 + 1]);
+                    acc[4 * i4 + 2] = fmaf(q.z, kv, acc[4 * i4 + 2]);
+                    acc[4 * i4 + 3] = fmaf(q.w, kv, acc[4 * i4 + 3]);
+                }
+            }
+        }
+        if (j0 + t < p.T) {
+            float4* dst = reinterpret_cast<float4*>(Sm + (size_t)(j0 + t) * AT_Q);
+#pragma unroll
+            for (int i4 = 0; i4 < AT_Q / 4; ++i4)
+                dst[i4] = make_float4(acc[4 * i4] * p.scale, acc[4 * i4 + 1] * p.scale, acc[4 * i4 + 2] * p.scale,
+                                      acc[4 * i4 + 3] * p.scale);
+        }
+    }
+    __syncthreads();
+    // phase 2: softmax over keys for each of the 32 queries (F.softmax, layers.py:584)
+    {
+        const int i = t & 31, part = t >> 5;
+        float m = -INFINITY;
+        for (int j = part; j < p.T; j += 8) m = fmaxf(m, Sm[(size_t)j * AT_Q + i]);
+        red[part * 32 + i] = m;
+        __syncthreads();
+        m = red[i];
+#pragma unroll
+        for (int q = 1; q < 8; ++q) m = fmaxf(m, red[q * 32 + i]);
+        float s = 0.f;
+        for (int j = part; j < p.T; j += 8) {
+            const float e = expf(Sm[(size_t)j * AT_Q + i] - m);
+            Sm[(size_t)j * AT_Q + i] = e;
+            s += e;
+        }
+        red[256 + part * 32 + i] = s;
+        __syncthreads();
+        s = 0.f;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) s += red[256 + q * 32 + i];
+        const float inv = 1.f / s;
+        for (int j = part; j < p.T; j += 8) Sm[(size_t)j * AT_Q + i] *= inv;
+    }
+    __syncthreads();
+    // phase 3: O[i][c] = sum_j P[i][j] v[j][c]
+    for (int c = t; c < p.dh; c += 256) {
+        float acc[AT_Q];
+#pragma unroll
+        for (int i = 0; i < AT_Q; ++i) acc[i] = 0.f;
+        for (int j = 0; j < p.T; ++j) {
+            const float vv = __ldg(base + (size_t)j * p.ld + vo + c);
+            const float4* p4 = reinterpret_cast<const float4*>(Sm + (size_t)j * AT_Q);
+#pragma unroll
+            for (int i4 = 0; i4 < AT_Q / 4; ++i4) {
+                const float4 q = p4[i4];
+                acc[4 * i4] = fmaf(q.x, vv, acc[4 * i4]);
+                acc[4 * i4 + 1] = fmaf(q.y, vv, acc[4 * i4 + 1]);
+                acc[4 * i4 + 2] = fmaf(q.z, vv, acc[4 * i4 + 2]);
+                acc[4 * i4 + 3] = fmaf(q.w, vv, acc[4 * i4 + 3]);
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < AT_Q; ++i)
+            if (i0 + i < p.T) p.out[((size_t)n * p.T + i0 + i) * p.ld_out + head * p.dh + c] = acc[i];
+    }
+}
+
+cudaError_t launch_attention(const AttnParams& p, cudaStream_t stream) {
+    if (p.N <= 0 || p.T <= 0) return cudaSuccess;
+    const size_t smem = ((size_t)p.T * AT_Q + 32 * AT_Q + 256 * 33 + 512) * sizeof(float);
+    if (smem > 220 * 1024) return cudaErrorInvalidValue;
+    cudaError_t e = cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    attention_kernel<<<dim3((p.T + AT_Q - 1) / AT_Q, p.heads, p.N), 256, smem, stream>>>(p);
+    return cudaGetLastError();
+}
+
+}  // namespace idb

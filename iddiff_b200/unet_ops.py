@@ -1,0 +1,163 @@
+"""Host-side handles of the U-Net kernels (C ABI: idb_groupnorm_stats, idb_conv_prep, idb_conv2d, idb_attention).
+
+Activations are fp32 NHWC torch tensors on the device; torch only owns the memory and the stream.  Weight packing
+(once per model) turns an nn.Conv2d / NIN / nn.Linear weight into the hi/lo fp16 slab operand of the tensor-core
+kernel.  No CPU path: every function raises IdbError on a CPU tensor.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from dataclasses import dataclass
+from typing import Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+
+ACT_SCALE = 64.0  # activations are multiplied by 2^6 before the fp16 hi/lo split (|v| < 1023 stays finite)
+PREP_SAME, PREP_UP2, PREP_STRIDE2, PREP_AVGPOOL2 = 0, 1, 2, 3
+
+TAPS_3x3 = [(0, ky - 1, kx - 1) for ky in range(3) for kx in range(3)]
+TAPS_3x3_S2 = [(2 * (ky & 1) + (kx & 1), ky >> 1, kx >> 1) for ky in range(3) for kx in range(3)]
+TAPS_1x1 = [(0, 0, 0)]
+
+
+def _ceil(a: int, b: int) -> int:
+    return (a + b - 1) // b * b
+
+
+@dataclass
+class PackedConv:
+    """One convolution's weights in tensor-core operand form."""
+    w_hi: torch.Tensor
+    w_lo: torch.Tensor
+    bias: Optional[torch.Tensor]
+    cin: int
+    cp: int
+    cout: int
+    np_: int
+    taps: Sequence[Tuple[int, int, int]]
+    w_scale: float
+    planes: int
+
+    @property
+    def taps_c(self):
+        flat = [v for t in self.taps for v in t]
+        return (C.c_int * len(flat))(*flat)
+
+
+def pack_conv(weight: torch.Tensor, bias: Optional[torch.Tensor], taps=None, planes: int = 1) -> PackedConv:
+    """weight: nn.Conv2d layout [Cout][Cin][kh][kw] (or [Cout][Cin] for 1x1 / Linear / NIN^T), fp32, on the device.
+    The GEMM B operand is the matrix [Cout][n_taps * Cp], tap-major (ky, kx row-major), channel-minor, zero padded."""
+    if not weight.is_cuda:
+        raise _lib.IdbError("pack_conv: CUDA tensor required")
+    w = weight.detach().float()
+    if w.dim() == 2:
+        w = w[:, :, None, None]
+    cout, cin, kh, kw = w.shape
+    n_taps = kh * kw
+    if taps is None:
+        taps = TAPS_3x3 if n_taps == 9 else TAPS_1x1
+    assert len(taps) == n_taps
+    cp = _ceil(cin, 64)
+    np_ = _ceil(cout, 128)
+    mat = torch.zeros(cout, n_taps, cp, device=w.device, dtype=torch.float32)
+    mat[:, :, :cin] = w.permute(0, 2, 3, 1).reshape(cout, n_taps, cin)
+    mat = mat.reshape(cout, n_taps * cp).contiguous()
+    amax = float(mat.abs().max())
+    # power-of-two scale with max|w| * scale in [2^13, 2^14)
+    w_scale = 2.0 ** (13 - math.floor(math.log2(amax))) if amax > 0 else 1.0
+    kc = n_taps * cp
+    hi = torch.empty(kc // 64 * np_ * 128, dtype=torch.uint8, device=w.device)
+    lo = torch.empty_like(hi)
+    _lib.call("idb_pack_weight", _lib.ptr(mat), cout, kc, kc, np_, kc, _lib.FMT_FP16, w_scale, _lib.ptr(hi), _lib.ptr(lo),
+              _lib.stream_ptr())
+    b = bias.detach().float().contiguous() if bias is not None else None
+    return PackedConv(hi, lo, b, cin, cp, cout, np_, list(taps), w_scale, planes)
+
+
+def gn_stats(x0: torch.Tensor, x1: Optional[torch.Tensor], groups: int, eps: float) -> torch.Tensor:
+    """x0 [N,H,W,C0] (+ x1 [N,H,W,C1] concatenated along C) -> mean_rstd [N, groups, 2] fp32."""
+    n, h, w, c0 = x0.shape
+    c1 = x1.shape[3] if x1 is not None else 0
+    sums = torch.empty(n, groups, 2, dtype=torch.float64, device=x0.device)
+    mr = torch.empty(n, groups, 2, dtype=torch.float32, device=x0.device)
+    _lib.call("idb_groupnorm_stats", _lib.ptr(x0), c0, _lib.ptr(x1), c1, n, h * w, groups, float(eps), _lib.ptr(sums),
+              _lib.ptr(mr), _lib.stream_ptr())
+    return mr
+
+
+@dataclass
+class Operand:
+    hi: torch.Tensor
+    lo: torch.Tensor
+    planes: int
+    n: int
+    h: int
+    w: int
+    cp: int
+
+
+def prep(x0: torch.Tensor, x1: Optional[torch.Tensor] = None, *, mode: int = PREP_SAME, mean_rstd=None, groups: int = 0,
+         gamma=None, beta=None, act: int = 0, nchw: bool = False, want_operand: bool = True, want_f32: bool = False):
+    """One pass: concat -> GroupNorm apply -> SiLU -> resample -> fp16 hi/lo operand (and / or fp32 NHWC copy)."""
+    if nchw:
+        n, c0, hs, ws = x0.shape
+    else:
+        n, hs, ws, c0 = x0.shape
+    c1 = x1.shape[3] if x1 is not None else 0
+    c = c0 + c1
+    planes = 4 if mode == PREP_STRIDE2 else 1
+    ho = {PREP_SAME: hs, PREP_UP2: 2 * hs, PREP_STRIDE2: (hs + 1) // 2, PREP_AVGPOOL2: hs // 2}[mode]
+    wo = {PREP_SAME: ws, PREP_UP2: 2 * ws, PREP_STRIDE2: (ws + 1) // 2, PREP_AVGPOOL2: ws // 2}[mode]
+    cp = _ceil(c, 64)
+    dev = x0.device
+    hi = lo = None
+    if want_operand:
+        hi = torch.empty(planes, n, ho, wo, cp, dtype=torch.float16, device=dev)
+        lo = torch.empty_like(hi)
+    f32 = torch.empty(planes, n, ho, wo, c, dtype=torch.float32, device=dev) if want_f32 else None
+    _lib.call("idb_conv_prep", _lib.ptr(x0), c0, _lib.ptr(x1), c1, n, hs, ws, int(nchw), mode, _lib.ptr(mean_rstd),
+              groups, _lib.ptr(gamma), _lib.ptr(beta), act, ACT_SCALE, _lib.ptr(hi), _lib.ptr(lo), cp, _lib.ptr(f32),
+              _lib.stream_ptr())
+    op = Operand(hi, lo, planes, n, ho, wo, cp) if want_operand else None
+    if want_f32:
+        return op, (f32[0] if planes == 1 else f32)
+    return op
+
+
+def conv(a: Operand, pc: PackedConv, *, bias: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None,
+         out_scale: float = 1.0, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """out [N,H,W,Cout] fp32 = out_scale * (conv(a, W) + bias + residual).  `bias` overrides pc.bias (the host folds
+    the time-embedding projection into it)."""
+    if a.cp != pc.cp or a.planes != pc.planes:
+        raise _lib.IdbError(f"conv: operand (Cp={a.cp}, planes={a.planes}) does not match weights (Cp={pc.cp}, planes={pc.planes})")
+    if out is None:
+        out = torch.empty(a.n, a.h, a.w, pc.cout, dtype=torch.float32, device=a.hi.device)
+    b = bias if bias is not None else pc.bias
+    ld_res = residual.shape[-1] if residual is not None else 0
+    _lib.call("idb_conv2d", _lib.ptr(a.hi), _lib.ptr(a.lo), a.planes, a.n, a.h, a.w, a.cp, _lib.ptr(pc.w_hi),
+              _lib.ptr(pc.w_lo), len(pc.taps), pc.taps_c, pc.np_, pc.cout, 1.0 / (ACT_SCALE * pc.w_scale), float(out_scale),
+              _lib.ptr(b), _lib.ptr(residual), ld_res, _lib.ptr(out), out.shape[-1], _lib.stream_ptr())
+    return out
+
+
+def attention(qkv: torch.Tensor, heads: int, dh: int, q0: int, k0: int, v0: int, head_stride: int,
+              scale: float) -> torch.Tensor:
+    """qkv [N,H,W,ld] fp32 -> [N,H,W,heads*dh] fp32."""
+    n, h, w, ld = qkv.shape
+    out = torch.empty(n, h, w, heads * dh, dtype=torch.float32, device=qkv.device)
+    _lib.call("idb_attention", _lib.ptr(qkv), n, h * w, ld, heads, dh, q0, k0, v0, head_stride, float(scale),
+              _lib.ptr(out), heads * dh, _lib.stream_ptr())
+    return out
+
+
+def dense(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], act_in: int = 0) -> torch.Tensor:
+    """fp32 nn.Linear on a few rows (time-embedding path): out = W f(x) + b, f = identity (0) / ELU (1) / SiLU (2)."""
+    a, k = x.shape
+    n = weight.shape[0]
+    out = torch.empty(a, n, dtype=torch.float32, device=x.device)
+    _lib.call("idb_anchor_linear", _lib.ptr(x), k, act_in, 1.0, _lib.ptr(weight), weight.stride(0), _lib.ptr(bias), None,
+              0, 0.0, _lib.ptr(out), n, a, n, k, _lib.stream_ptr())
+    return out

@@ -141,6 +141,52 @@ int idb_upfirdn2d(const float* input, const float* kernel, int major, int in_h, 
 int idb_fused_bias_act(const float* input, const float* bias, const float* refer, int act, int grad, float alpha,
                        float scale, long long size_x, int step_b, int size_b, float* out, void* stream);
 
+/* U-Net activations are fp32 NHWC [N][H][W][C] in HBM.  A convolution is three calls: idb_groupnorm_stats (when the
+ * conv input is normalised), idb_conv_prep (writes the tensor-core operand), idb_conv2d. */
+
+/* nn.GroupNorm statistics (layers.py:638,648; ddpm.py:143; BeatGANs_nn.py:23-25 GroupNorm32): per (image, group)
+ * mean and 1/sqrt(biased var + eps) of x = concat(src0 [N][HW][C0], src1 [N][HW][C1]) along C (src1 NULL / C1 = 0:
+ * no concat -- the concat of ddpm.py:198 is never materialised).  sums [N][groups][2] fp64 is scratch,
+ * mean_rstd [N][groups][2] fp32 the result. */
+int idb_groupnorm_stats(const float* src0, int C0, const float* src1, int C1, int N, int HW, int groups, double eps,
+                        double* sums, float* mean_rstd, void* stream);
+
+/* Operand preparation = everything between two convolutions in ONE pass over the activation:
+ *   v = concat(src0, src1)[n, y, x, c];  v = (v - mean) * rstd (if mean_rstd);  v = v * gamma[c] + beta[c] (if gamma);
+ *   v = SiLU(v) (act 1);  then by mode: 0 same size | 1 nearest x2 up (layers.py:600 F.interpolate) | 2 the four
+ *   stride-2 parity planes src[2y+py][2x+px], plane = 2 py + px, zero beyond the edge (layers.py:621-623 pad (0,1,0,1) +
+ *   stride-2 conv) | 3 2x2 average pool of the transformed values (BeatGANsblocks.py Downsample, avg_pool_nd).
+ * Outputs: out_hi/out_lo fp16 [planes][N][Ho][Wo][Cp] = hi/lo pair of scale * v (channels >= C zero), Cp % 64 == 0;
+ *          out_f32 [planes][N][Ho][Wo][C] (optional).  src_nchw: src0 is [N][C0][Hs][Ws] (the network input). */
+#define IDB_PREP_SAME 0
+#define IDB_PREP_UP2 1
+#define IDB_PREP_STRIDE2 2
+#define IDB_PREP_AVGPOOL2 3
+int idb_conv_prep(const float* src0, int C0, const float* src1, int C1, int N, int Hs, int Ws, int src_nchw, int mode,
+                  const float* mean_rstd, int groups, const float* gamma, const float* beta, int act, float scale,
+                  void* out_hi, void* out_lo, int Cp, float* out_f32, void* stream);
+
+/* nn.Conv2d / NIN as an implicit GEMM on tcgen05 (3 MMAs per product on fp16 hi/lo pairs, fp32 accumulate in TMEM):
+ *   out[n,h,w,co] = out_scale * (acc_scale * sum_{t,ci} A[plane_t][n, h+dy_t, w+dx_t, ci] * Wt[co][t][ci]
+ *                                + bias[co] + residual[n,h,w,co])
+ * A = idb_conv_prep output [planes][N][H][W][Cp]; reads outside the image are zero (TMA out-of-bounds fill = the
+ * convolution's zero padding).  Wt = idb_pack_weight of the matrix [Cout][n_taps*Cp] (tap-major, channel-minor).
+ * taps_host: HOST array [n_taps][3] = (plane, dy, dx).  3x3 pad 1: plane 0, dy,dx in {-1,0,1};  3x3 stride 2 after
+ * pad (0,1,0,1): tap (ky,kx) -> plane 2(ky&1)+(kx&1), dy = ky>>1, dx = kx>>1;  1x1 / NIN: one tap (0,0,0).
+ * bias [Cout] / residual [N][H][W][ld_res] may be NULL.  H, W powers of two (<= 128) so that 128-pixel tiles are boxes.
+ * Replaces cuDNN conv + bias add + temb add (layers.py:662-664; t is constant on this path so Dense_0(act(temb)) is
+ * folded into `bias` by the host) + residual add (:675) + skip rescale (layerspp.py:271-274). */
+int idb_conv2d(const void* a_hi, const void* a_lo, int planes, int N, int H, int W, int Cp, const void* w_hi,
+               const void* w_lo, int n_taps, const int* taps_host, int Np, int Cout, float acc_scale, float out_scale,
+               const float* bias, const float* residual, int ld_res, float* out, int ldo, void* stream);
+
+/* Self-attention over the T = H*W pixels of each image (layers.py:567-590 AttnBlock: 1 head, scale C^-1/2;
+ * BeatGANsblocks.py:434-491 QKVAttentionLegacy: heads, scale dh^-1/2): out[n][i][h*dh+c] =
+ * sum_j softmax_j(scale <q_i,k_j>) v[j][c], q/k/v of head h at channels q0/k0/v0 + h*head_stride of qkv [N][T][ld].
+ * fp32 on the CUDA cores (< 1 % of the network FLOPs), scores resident in shared memory. */
+int idb_attention(const float* qkv, int N, int T, int ld, int heads, int dh, int q0, int k0, int v0, int head_stride,
+                  float scale, float* out, int ld_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,122 @@
+"""GPU numerics of the U-Net kernels (through the C ABI) against plain PyTorch fp64 references of the same ops.
+Tolerances: the split-precision convolution carries 22-bit operands and fp32 accumulation, so it is compared with the
+fp64 result at 2e-6 of the output scale (the fp32 cuDNN/ATen result of the reference has the same order of error)."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def nhwc(x):
+    return x.permute(0, 2, 3, 1).contiguous()
+
+
+def rel_err(a, b):
+    return float((a.double().cpu() - b.double().cpu()).abs().max() / b.double().abs().max())
+
+
+@pytest.mark.parametrize("n,c,h,w,groups", [(3, 32, 8, 8, 32), (2, 128, 16, 16, 32), (5, 96, 4, 4, 32), (2, 384, 8, 8, 32)])
+def test_groupnorm_stats(n, c, h, w, groups):
+    from iddiff_b200 import unet_ops as U
+    torch.manual_seed(0)
+    x = torch.randn(n, c, h, w) * 3 + 1.5
+    c0 = c // 4 * 3
+    mr = U.gn_stats(nhwc(x[:, :c0]).cuda(), nhwc(x[:, c0:]).cuda(), groups, 1e-6).cpu()
+    xd = x.double().reshape(n, groups, -1)
+    mean, var = xd.mean(-1), xd.var(-1, unbiased=False)
+    np.testing.assert_allclose(mr[..., 0].numpy(), mean.numpy(), rtol=1e-6, atol=1e-6)
+    np.testing.assert_allclose(mr[..., 1].numpy(), (1 / torch.sqrt(var + 1e-6)).numpy(), rtol=1e-6)
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2, 3])
+def test_prep_modes_f32(mode):
+    """GroupNorm + SiLU + resampling of a concatenated pair, fp32 output and the hi+lo operand."""
+    from iddiff_b200 import unet_ops as U
+    torch.manual_seed(1)
+    n, c0, c1, h, w = 2, 40, 16, 8, 8
+    x = torch.randn(n, c0 + c1, h, w)
+    gamma, beta = torch.randn(c0 + c1), torch.randn(c0 + c1)
+    a, b = nhwc(x[:, :c0]).cuda(), nhwc(x[:, c0:]).cuda()
+    mr = U.gn_stats(a, b, 8, 1e-6)
+    op, f32 = U.prep(a, b, mode=mode, mean_rstd=mr, groups=8, gamma=gamma.cuda(), beta=beta.cuda(), act=1, want_f32=True)
+    ref = F.silu(F.group_norm(x.double(), 8, gamma.double(), beta.double(), eps=1e-6))
+    if mode == 1:
+        ref = F.interpolate(ref, scale_factor=2, mode="nearest")
+    elif mode == 3:
+        ref = F.avg_pool2d(ref, 2)
+    if mode == 2:
+        refp = F.pad(ref, (0, 1, 0, 1))
+        planes = [nhwc(refp[:, :, py::2, px::2][:, :, :h // 2, :w // 2]) for py in (0, 1) for px in (0, 1)]
+        ref_nhwc = torch.stack(planes)
+    else:
+        ref_nhwc = nhwc(ref)[None]
+    got = f32 if mode == 2 else f32[None]
+    np.testing.assert_allclose(got.cpu().numpy(), ref_nhwc.numpy(), rtol=2e-5, atol=2e-6)
+    rec = (op.hi.double() + op.lo.double()) / U.ACT_SCALE
+    assert rec.shape[-1] == 64 and float(rec[..., c0 + c1:].abs().max()) == 0.0
+    np.testing.assert_allclose(rec[..., :c0 + c1].cpu().numpy(), got.double().cpu().numpy(), rtol=1e-6, atol=1e-8)
+
+
+@pytest.mark.parametrize("n,cin,cout,h,w", [(2, 3, 128, 16, 16), (3, 128, 128, 16, 16), (5, 192, 256, 8, 8),
+                                            (9, 64, 96, 4, 4), (1, 320, 3, 32, 32), (2, 128, 384, 64, 64)])
+def test_conv3x3_vs_torch_fp64(n, cin, cout, h, w):
+    from iddiff_b200 import unet_ops as U
+    torch.manual_seed(2)
+    x = torch.randn(n, cin, h, w)
+    wt = torch.randn(cout, cin, 3, 3) / np.sqrt(9 * cin)
+    bias = torch.randn(cout)
+    res = torch.randn(n, cout, h, w)
+    pc = U.pack_conv(wt.cuda(), bias.cuda())
+    op = U.prep(nhwc(x).cuda())
+    out = U.conv(op, pc, residual=nhwc(res).cuda(), out_scale=0.5)
+    ref = nhwc((F.conv2d(x.double(), wt.double(), bias.double(), padding=1) + res.double()) * 0.5)
+    assert rel_err(out, ref) < 1e-5  # fp32 accumulation over up to 9*Cin products
+
+
+def test_conv3x3_stride2_ddpm_downsample():
+    """layers.py:607-629: F.pad(x, (0,1,0,1)) then 3x3 stride-2 conv, padding 0."""
+    from iddiff_b200 import unet_ops as U
+    torch.manual_seed(3)
+    n, c, h, w = 3, 128, 16, 16
+    x, wt, bias = torch.randn(n, c, h, w), torch.randn(c, c, 3, 3) / 30, torch.randn(c)
+    pc = U.pack_conv(wt.cuda(), bias.cuda(), taps=U.TAPS_3x3_S2, planes=4)
+    out = U.conv(U.prep(nhwc(x).cuda(), mode=U.PREP_STRIDE2), pc)
+    ref = nhwc(F.conv2d(F.pad(x.double(), (0, 1, 0, 1)), wt.double(), bias.double(), stride=2))
+    assert tuple(out.shape) == (n, h // 2, w // 2, c)
+    assert rel_err(out, ref) < 1e-5  # fp32 accumulation over up to 9*Cin products
+
+
+def test_nin_1x1_and_nchw_input():
+    from iddiff_b200 import unet_ops as U
+    torch.manual_seed(4)
+    n, cin, cout, h, w = 4, 3, 64, 8, 8
+    x, wt = torch.rand(n, cin, h, w), torch.randn(cout, cin)
+    pc = U.pack_conv(wt.cuda(), None)
+    two, m1 = torch.full((cin,), 2.0).cuda(), torch.full((cin,), -1.0).cuda()
+    out = U.conv(U.prep(x.cuda(), nchw=True, gamma=two, beta=m1), pc)   # 2x - 1 of ddpm.py:168 folded into the prep
+    ref = torch.einsum("nchw,oc->nhwo", 2 * x.double() - 1, wt.double())
+    assert rel_err(out, ref) < 1e-5  # fp32 accumulation over up to 9*Cin products
+
+
+@pytest.mark.parametrize("n,t_hw,c,heads", [(3, 8, 64, 1), (2, 16, 256, 1), (2, 16, 128, 4), (1, 4, 32, 2)])
+def test_attention_vs_torch(n, t_hw, c, heads):
+    from iddiff_b200 import unet_ops as U
+    torch.manual_seed(5)
+    T, dh = t_hw * t_hw, c // heads
+    qkv = torch.randn(n, T, 3 * c)
+    # layout A (DDPM): q | k | v blocks of C channels, head h at h*dh inside each block
+    out = U.attention(qkv.reshape(n, t_hw, t_hw, 3 * c).cuda(), heads, dh, 0, c, 2 * c, dh, dh ** -0.5)
+    q, k, v = (qkv[..., i * c:(i + 1) * c].double().reshape(n, T, heads, dh).transpose(1, 2) for i in range(3))
+    ref = (torch.softmax(q @ k.transpose(-1, -2) * dh ** -0.5, -1) @ v).transpose(1, 2).reshape(n, T, c)
+    np.testing.assert_allclose(out.reshape(n, T, c).cpu().numpy(), ref.numpy(), rtol=1e-4, atol=2e-6)
+
+
+def test_dense_silu():
+    from iddiff_b200 import unet_ops as U
+    torch.manual_seed(6)
+    x, w, b = torch.randn(1, 512), torch.randn(256, 512) / 20, torch.randn(256)
+    out = U.dense(x.cuda(), w.cuda(), b.cuda(), act_in=2)
+    ref = F.linear(F.silu(x.double()), w.double(), b.double())
+    np.testing.assert_allclose(out.cpu().numpy(), ref.numpy(), rtol=1e-5, atol=1e-6)
