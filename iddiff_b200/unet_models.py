@@ -1,0 +1,168 @@
+"""Weight holders for the image score networks, registered under the reference's model names.
+
+Like models.FCN they only OWN parameters, in exactly the reference's state_dict layout (so its Lightning
+checkpoints load with strict=True), plus a `plan` -- the ordered list of blocks the CUDA engine walks
+(unet_engine.py).  The forward pass itself is not here: calling the module raises.
+
+'ddpm' mirrors models/ddpm.py:82-147 (constructor order defines the `all_modules.<i>` indices) with the blocks of
+models/layers.py: ResnetBlockDDPM :632-675, AttnBlock :567-590, NIN :555-564, Downsample :607-629, Upsample :593-604,
+ddpm_conv3x3 :93-100, default_init :80-83.
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+import torch.nn as nn
+
+from .models import register_model
+
+
+def fan_avg_uniform_(t: torch.Tensor, scale: float = 1.0, in_axis: int = 1, out_axis: int = 0) -> torch.Tensor:
+    """layers.py:56-83 `default_init(scale)` = variance_scaling(scale, 'fan_avg', 'uniform'); scale 0 -> 1e-10."""
+    scale = 1e-10 if scale == 0 else scale
+    shape = t.shape
+    receptive = t.numel() / shape[in_axis] / shape[out_axis]
+    fan_in, fan_out = shape[in_axis] * receptive, shape[out_axis] * receptive
+    bound = math.sqrt(3.0 * scale / ((fan_in + fan_out) / 2.0))
+    with torch.no_grad():
+        return t.uniform_(-bound, bound)
+
+
+def _conv3x3(cin, cout, init_scale=1.0, stride=1, padding=1):
+    conv = nn.Conv2d(cin, cout, 3, stride=stride, padding=padding)
+    fan_avg_uniform_(conv.weight, init_scale)
+    nn.init.zeros_(conv.bias)
+    return conv
+
+
+def _dense(cin, cout):
+    lin = nn.Linear(cin, cout)
+    fan_avg_uniform_(lin.weight)
+    nn.init.zeros_(lin.bias)
+    return lin
+
+
+def _gn(ch):
+    return nn.GroupNorm(num_groups=32, num_channels=ch, eps=1e-6)
+
+
+class _Holder(nn.Module):
+    def forward(self, *a, **k):
+        raise RuntimeError(f"{type(self).__name__} holds weights only; the forward pass runs in unet_engine.UNetEngine "
+                           "(no PyTorch/CPU path for this network here)")
+
+
+class NIN(_Holder):
+    def __init__(self, cin, cout, init_scale=0.1):
+        super().__init__()
+        self.W = nn.Parameter(fan_avg_uniform_(torch.empty(cin, cout), init_scale))
+        self.b = nn.Parameter(torch.zeros(cout))
+
+
+class ResnetBlockDDPM(_Holder):
+    def __init__(self, in_ch, out_ch=None, temb_dim=None, conv_shortcut=False, dropout=0.1):
+        super().__init__()
+        out_ch = out_ch or in_ch
+        self.in_ch, self.out_ch, self.conv_shortcut = in_ch, out_ch, conv_shortcut
+        self.GroupNorm_0 = _gn(in_ch)
+        self.Conv_0 = _conv3x3(in_ch, out_ch)
+        if temb_dim is not None:
+            self.Dense_0 = _dense(temb_dim, out_ch)
+        self.GroupNorm_1 = _gn(out_ch)
+        self.Dropout_0 = nn.Dropout(dropout)
+        self.Conv_1 = _conv3x3(out_ch, out_ch, init_scale=0.0)
+        if in_ch != out_ch:
+            if conv_shortcut:
+                self.Conv_2 = _conv3x3(in_ch, out_ch)
+            else:
+                self.NIN_0 = NIN(in_ch, out_ch)
+
+
+class AttnBlock(_Holder):
+    def __init__(self, channels):
+        super().__init__()
+        self.channels = channels
+        self.GroupNorm_0 = _gn(channels)
+        self.NIN_0, self.NIN_1, self.NIN_2 = NIN(channels, channels), NIN(channels, channels), NIN(channels, channels)
+        self.NIN_3 = NIN(channels, channels, init_scale=0.0)
+
+
+class Downsample(_Holder):
+    def __init__(self, channels, with_conv=False):
+        super().__init__()
+        self.with_conv = with_conv
+        if with_conv:
+            self.Conv_0 = _conv3x3(channels, channels, stride=2, padding=0)
+
+
+class Upsample(_Holder):
+    def __init__(self, channels, with_conv=False):
+        super().__init__()
+        self.with_conv = with_conv
+        if with_conv:
+            self.Conv_0 = _conv3x3(channels, channels)
+
+
+@register_model("ddpm")
+class DDPM(_Holder):
+    """models/ddpm.py:82-147.  `plan` entries: (kind, module index, extra) in execution order (ddpm.py:149-213)."""
+
+    def __init__(self, config):
+        super().__init__()
+        m = config.model
+        if m.nonlinearity.lower() != "swish":
+            raise NotImplementedError("iddiff_b200 DDPM engine: only nonlinearity='swish' (every shipped config) is built")
+        self.nf = nf = m.nf
+        ch_mult = tuple(m.ch_mult)
+        self.num_res_blocks = nrb = m.num_res_blocks
+        self.attn_resolutions = tuple(m.attn_resolutions)
+        self.num_resolutions = nres = len(ch_mult)
+        self.all_resolutions = [config.data.effective_image_size // (2 ** i) for i in range(nres)]
+        self.conditional = m.conditional
+        self.centered = config.data.centered
+        if not self.conditional:
+            raise NotImplementedError("DDPM with conditional=False (no time embedding) is not built")
+        temb_dim = 4 * nf
+        mods, plan = [], []
+
+        def add(kind, mod, **extra):
+            plan.append((kind, len(mods), extra))
+            mods.append(mod)
+
+        mods.append(_dense(nf, temb_dim))
+        mods.append(_dense(temb_dim, temb_dim))
+        add("conv_in", _conv3x3(m.input_channels, nf))
+        plan.append(("push", -1, {}))
+        hs_c, in_ch = [nf], nf
+        for lvl in range(nres):
+            for _ in range(nrb):
+                out_ch = nf * ch_mult[lvl]
+                add("res", ResnetBlockDDPM(in_ch, out_ch, temb_dim, dropout=m.dropout))
+                in_ch = out_ch
+                if self.all_resolutions[lvl] in self.attn_resolutions:
+                    add("attn", AttnBlock(in_ch))
+                plan.append(("push", -1, {}))
+                hs_c.append(in_ch)
+            if lvl != nres - 1:
+                add("down", Downsample(in_ch, m.resamp_with_conv))
+                plan.append(("push", -1, {}))
+                hs_c.append(in_ch)
+        in_ch = hs_c[-1]
+        add("res", ResnetBlockDDPM(in_ch, None, temb_dim, dropout=m.dropout))
+        add("attn", AttnBlock(in_ch))
+        add("res", ResnetBlockDDPM(in_ch, None, temb_dim, dropout=m.dropout))
+        for lvl in reversed(range(nres)):
+            for _ in range(nrb + 1):
+                out_ch = nf * ch_mult[lvl]
+                add("res", ResnetBlockDDPM(in_ch + hs_c.pop(), out_ch, temb_dim, dropout=m.dropout), skip=True)
+                in_ch = out_ch
+            if self.all_resolutions[lvl] in self.attn_resolutions:
+                add("attn", AttnBlock(in_ch))
+            if lvl != 0:
+                add("up", Upsample(in_ch, m.resamp_with_conv))
+        assert not hs_c
+        add("gn_out", _gn(in_ch))
+        add("conv_out", _conv3x3(in_ch, m.output_channels, init_scale=0.0))
+        self.all_modules = nn.ModuleList(mods)
+        self.plan = plan

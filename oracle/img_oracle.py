@@ -55,3 +55,115 @@ def fused_bias_act_np(x, b, ref, act, grad, alpha, scale):
 def fused_leaky_relu_cpu_np(x, b, scale):
     """op/fused_act.py:87-94, the reference's CPU branch: slope hard-coded to 0.2 whatever `negative_slope` is."""
     return fused_bias_act_np(x, b, None, 3, 0, 0.2, scale)
+
+
+# ------------------------------------------------------------------------------------------------
+# DDPM U-Net (models/ddpm.py:149-213) as a function of a state_dict -- torch CPU, dtype follows the inputs
+# (float32 = the reference's arithmetic; float64 = "truth" for measuring the reference's own rounding floor).
+# ------------------------------------------------------------------------------------------------
+def _silu(x):
+    import torch
+    return x * torch.sigmoid(x)
+
+
+def ddpm_forward(state, cfg, x, labels):
+    """state: {'all_modules.<i>....': tensor}; cfg: dict(nf, ch_mult, num_res_blocks, attn_resolutions, image_size,
+    resamp_with_conv, centered); x [B,C,H,W]; labels [B].  Follows ddpm.py:149-213 block by block."""
+    import math
+    import torch
+    import torch.nn.functional as F
+    dt = x.dtype
+    P = lambda i, name: state[f"all_modules.{i}.{name}"].to(dt)
+    nf, ch_mult, nrb = cfg["nf"], cfg["ch_mult"], cfg["num_res_blocks"]
+    nres = len(ch_mult)
+    idx = [0]
+
+    def nxt():
+        idx[0] += 1
+        return idx[0] - 1
+
+    def gn(i, name, h):
+        return F.group_norm(h, 32, P(i, name + ".weight"), P(i, name + ".bias"), eps=1e-6)
+
+    def nin(i, name, h):  # layers.py:555-564
+        return torch.einsum("bchw,co->bohw", h, P(i, name + ".W")) + P(i, name + ".b")[None, :, None, None]
+
+    def res(h, temb):  # layers.py:654-675
+        i = nxt()
+        out = F.conv2d(_silu(gn(i, "GroupNorm_0", h)), P(i, "Conv_0.weight"), P(i, "Conv_0.bias"), padding=1)
+        out = out + F.linear(_silu(temb), P(i, "Dense_0.weight"), P(i, "Dense_0.bias"))[:, :, None, None]
+        out = F.conv2d(_silu(gn(i, "GroupNorm_1", out)), P(i, "Conv_1.weight"), P(i, "Conv_1.bias"), padding=1)
+        if f"all_modules.{i}.NIN_0.W" in state:
+            h = nin(i, "NIN_0", h)
+        elif f"all_modules.{i}.Conv_2.weight" in state:
+            h = F.conv2d(h, P(i, "Conv_2.weight"), P(i, "Conv_2.bias"), padding=1)
+        return h + out
+
+    def attn(h):  # layers.py:576-590
+        i = nxt()
+        B, C, H, W = h.shape
+        g = gn(i, "GroupNorm_0", h)
+        q, k, v = nin(i, "NIN_0", g), nin(i, "NIN_1", g), nin(i, "NIN_2", g)
+        w = torch.einsum("bchw,bcij->bhwij", q, k) * (int(C) ** (-0.5))
+        w = F.softmax(w.reshape(B, H, W, H * W), dim=-1).reshape(B, H, W, H, W)
+        o = torch.einsum("bhwij,bcij->bchw", w, v)
+        return h + nin(i, "NIN_3", o)
+
+    # time embedding, layers.py:524-538 + ddpm.py:152-159
+    half = nf // 2
+    freqs = torch.exp(torch.arange(half, dtype=torch.float32) * -(math.log(10000) / (half - 1))).to(dt)
+    arg = labels.to(dt)[:, None] * freqs[None, :]
+    temb = torch.cat([torch.sin(arg), torch.cos(arg)], dim=1)
+    i = nxt()
+    temb = F.linear(temb, P(i, "weight"), P(i, "bias"))
+    i = nxt()
+    temb = F.linear(_silu(temb), P(i, "weight"), P(i, "bias"))
+
+    h = x if cfg["centered"] else 2 * x - 1.0
+    i = nxt()
+    hs = [F.conv2d(h, P(i, "weight"), P(i, "bias"), padding=1)]
+    for lvl in range(nres):
+        for _ in range(nrb):
+            h = res(hs[-1], temb)
+            if h.shape[-1] in cfg["attn_resolutions"]:
+                h = attn(h)
+            hs.append(h)
+        if lvl != nres - 1:
+            i = nxt()
+            if cfg["resamp_with_conv"]:  # layers.py:621-623
+                hs.append(F.conv2d(F.pad(hs[-1], (0, 1, 0, 1)), P(i, "Conv_0.weight"), P(i, "Conv_0.bias"), stride=2))
+            else:
+                hs.append(F.avg_pool2d(hs[-1], 2))
+    h = hs[-1]
+    h = res(h, temb)
+    h = attn(h)
+    h = res(h, temb)
+    for lvl in reversed(range(nres)):
+        for _ in range(nrb + 1):
+            h = res(torch.cat([h, hs.pop()], dim=1), temb)
+        if h.shape[-1] in cfg["attn_resolutions"]:
+            h = attn(h)
+        if lvl != 0:
+            i = nxt()
+            h = F.interpolate(h, scale_factor=2, mode="nearest")  # layers.py:600
+            if cfg["resamp_with_conv"]:
+                h = F.conv2d(h, P(i, "Conv_0.weight"), P(i, "Conv_0.bias"), padding=1)
+    i = nxt()
+    h = _silu(F.group_norm(h, 32, P(i, "weight"), P(i, "bias"), eps=1e-6))
+    i = nxt()
+    return F.conv2d(h, P(i, "weight"), P(i, "bias"), padding=1)
+
+
+def unet_score_matrix(forward, state, cfg, x0, z, mean_coeff, std, label, batch=64):
+    """dim_reduction.py:177-194 + models/utils.py:264-267 for one anchor: x = mean_coeff*x0 + std*z, score = -net(x)/std,
+    flatten NCHW, centre.  x0 [C,H,W], z [K,C,H,W]; dtype follows z."""
+    import torch
+    rows = []
+    with torch.no_grad():
+        for s in range(0, z.shape[0], batch):
+            zz = z[s:s + batch]
+            x = mean_coeff * x0[None].to(zz.dtype) + std * zz
+            lab = torch.full((zz.shape[0],), label, dtype=zz.dtype)
+            rows.append(-forward(state, cfg, x, lab) / std)
+    S = torch.cat(rows).flatten(1)
+    return S - S.mean(0, keepdim=True)

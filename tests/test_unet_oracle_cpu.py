@@ -1,0 +1,57 @@
+"""CPU: the torch restatement of the DDPM U-Net path (oracle/img_oracle.py) against the goldens the REAL reference
+produced (tests/golden/unet_ddpm_small.npz via oracle/gen_golden_unet.py), and the weight holder's state_dict layout."""
+import numpy as np
+import torch
+
+from oracle import fixtures as FX
+from oracle import img_oracle as IO
+from oracle import id_oracle as O
+
+
+def _setup():
+    from iddiff_b200 import unet_models
+    g = FX.golden("unet_ddpm_small")
+    holder = unet_models.DDPM(FX.unet_config(FX.DDPM_SMALL))
+    state = FX.make_unet_state(holder, int(g["seed"]))
+    wsum = sum(v.double().abs().sum().item() for v in state.values())
+    assert abs(wsum - float(g["w_checksum"])) < 1e-6 * wsum, "fixture weights drifted from the ones the reference ran"
+    return g, holder, state
+
+
+def test_holder_state_dict_layout_and_plan():
+    g, holder, state = _setup()
+    holder.load_state_dict(state, strict=True)
+    kinds = [k for k, _, _ in holder.plan]
+    assert kinds.count("res") == 8 and kinds.count("attn") == 3 and kinds[0] == "conv_in" and kinds[-1] == "conv_out"
+    try:
+        holder(torch.zeros(1, 3, 16, 16), torch.zeros(1))
+    except RuntimeError as e:
+        assert "holds weights only" in str(e)
+    else:
+        raise AssertionError("the holder must not have a PyTorch forward path")
+
+
+def test_ddpm_forward_oracle_matches_reference():
+    g, _, state = _setup()
+    x = torch.from_numpy(g["x"])
+    lab = torch.full((x.shape[0],), float(g["label"]))
+    with torch.no_grad():
+        y = IO.ddpm_forward(state, FX.DDPM_SMALL, x, lab)
+    scale = np.abs(g["y"]).max()
+    assert np.abs(y.numpy() - g["y"]).max() < 1e-5 * scale
+
+
+def test_ddpm_path_oracle_matches_reference_spectrum():
+    g, _, state = _setup()
+    B, K, nb = int(g["B"]), int(g["K"]), int(g["nb"])
+    x0 = torch.from_numpy(g["x0"])
+    z = FX.seeded_noise(int(g["seed"]) + 3, x0.shape[0], nb, B, x0.shape[1:])
+    assert abs(FX.seeded_noise_checksum(z) - float(g["z_checksum"])) < 1e-6 * abs(float(g["z_checksum"])) + 1e-3
+    t = torch.ones(1) * 1e-5
+    std = float(O.ve_marginal(torch.zeros(1, 1), t, 1e-2, 4.0)[1][0])
+    a = 0
+    za = z[a].reshape(nb * B, *x0.shape[1:])[:K]
+    S = IO.unet_score_matrix(IO.ddpm_forward, state, FX.DDPM_SMALL, x0[a], za, 1.0, std, float(g["label"]))
+    s = torch.linalg.svdvals(S).double().numpy()
+    np.testing.assert_allclose(s, g["singular_values"][a], rtol=1e-3)
+    assert O.id_from_spectrum(s.tolist()) == int(g["dims"][a])

@@ -1,0 +1,83 @@
+"""GPU parity of the DDPM U-Net path (UNetEngine, through the C ABI) against the REAL reference's goldens
+(tests/golden/unet_ddpm_small.npz) and the fp64 oracle.
+
+Tolerances (BASELINE.json north_star): integer ID bit-exact; singular values rtol 1e-3 per value (tail included)
+against the fp32 reference plus the reference's own rounding floor max_i |s_ref - s_fp64| measured with the fp64
+oracle; raw network output 2e-5 of its largest magnitude (fp32 reference arithmetic has the same order of error)."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import fixtures as FX  # noqa: E402
+from oracle import id_oracle as O  # noqa: E402
+from oracle import img_oracle as IO  # noqa: E402
+
+
+def _engine():
+    from iddiff_b200 import unet_models
+    from iddiff_b200.unet_engine import UNetEngine
+    g = FX.golden("unet_ddpm_small")
+    holder = unet_models.DDPM(FX.unet_config(FX.DDPM_SMALL))
+    state = FX.make_unet_state(holder, int(g["seed"]))
+    holder.load_state_dict(state, strict=True)
+    eng = UNetEngine.from_module(holder, "cuda:0")
+    eng.image_shape = (3, 16, 16)
+    return g, state, eng
+
+
+def test_ddpm_forward_vs_reference_golden():
+    g, state, eng = _engine()
+    x = torch.from_numpy(g["x"]).cuda()
+    y = eng.forward(x, float(g["label"]))           # NHWC
+    got = y.permute(0, 3, 1, 2).cpu().numpy()
+    scale = np.abs(g["y"]).max()
+    assert np.abs(got - g["y"]).max() < 2e-5 * scale
+    # and against the fp64 evaluation of the oracle: the engine must be at least as close to the truth as 5x the
+    # fp32 reference is
+    with torch.no_grad():
+        y64 = IO.ddpm_forward(state, FX.DDPM_SMALL, torch.from_numpy(g["x"]).double(),
+                              torch.full((x.shape[0],), float(g["label"]), dtype=torch.float64)).numpy()
+    ref_err = np.abs(g["y"] - y64).max()
+    eng_err = np.abs(got - y64).max()
+    assert eng_err < max(5 * ref_err, 2e-6 * scale), (eng_err, ref_err)
+
+
+def test_ddpm_forward_batch_sizes_and_chunking():
+    """Ragged image counts (1, 7, 130: partial 128-pixel tiles at the 8x8 level pack 2 images per tile)."""
+    g, state, eng = _engine()
+    gen = torch.Generator().manual_seed(3)
+    x = torch.rand(130, 3, 16, 16, generator=gen)
+    full = eng.forward(x.cuda(), float(g["label"])).cpu()
+    for n in (1, 7):
+        part = eng.forward(x[:n].contiguous().cuda(), float(g["label"])).cpu()
+        assert torch.equal(part, full[:n])
+
+
+def test_ddpm_manifold_dimension_vs_reference_golden():
+    g, state, eng = _engine()
+    from iddiff_b200 import sde_lib
+    B, K, nb = int(g["B"]), int(g["K"]), int(g["nb"])
+    x0 = torch.from_numpy(g["x0"])
+    A = x0.shape[0]
+    z = FX.seeded_noise(int(g["seed"]) + 3, A, nb, B, x0.shape[1:]).reshape(A, nb * B, -1)[:, :K].contiguous()
+    sde = sde_lib.VESDE(sigma_min=1e-2, sigma_max=4.0, N=1000)
+    mc, std = sde.coefficients(1e-5)
+    res = eng.estimate(x0.reshape(A, -1).cuda(), K, mc, std, float(g["label"]), z=z.cuda(), want_scores=True)
+    torch.cuda.synchronize()
+    sv = res.singular_values.cpu().numpy().astype(np.float64)
+    want = g["singular_values"]
+    # the reference's own rounding floor from the fp64 oracle on anchor 0
+    za = z[0].reshape(K, *x0.shape[1:]).double()
+    S64 = IO.unet_score_matrix(IO.ddpm_forward, state, FX.DDPM_SMALL, x0[0].double(), za, mc, std, float(g["label"]))
+    s64 = torch.linalg.svdvals(S64).numpy()
+    floor = np.abs(want[0] - s64).max()
+    assert np.all(np.abs(sv[0] - s64) <= 1e-3 * s64 + floor), np.abs(sv[0] / s64 - 1).max()
+    for a in range(A):
+        assert np.all(np.abs(sv[a] - want[a]) <= 1e-3 * want[a] + floor), (a, np.abs(sv[a] / want[a] - 1).max())
+    assert res.dims.cpu().tolist() == g["dims"].tolist() == [O.id_from_spectrum(s) for s in want.tolist()]
+    head = res.scores[:, :8].reshape(A, 8, 3, 16, 16).cpu().numpy()
+    for a in range(A):
+        scale = np.abs(g["scores_head"][a]).max()
+        assert np.abs(head[a] - g["scores_head"][a]).max() < 2e-4 * scale
