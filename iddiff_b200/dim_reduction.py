@@ -60,7 +60,18 @@ def build_engine(config, score_model: Optional[torch.nn.Module] = None, device="
             if path:
                 models.load_checkpoint_into(score_model, path)
         return FcnEngine.from_module(score_model, device=device)
-    raise NotImplementedError(f"model.name={name!r}: only 'fcn' and 'ksphere_gt' are built so far (DESIGN.md scope)")
+    if name == "ddpm":
+        from . import models, unet_models  # noqa: F401  (registers 'ddpm')
+        from .unet_engine import UNetEngine
+        if score_model is None:
+            score_model = models.create_model(config)
+            path = lookup(config, "model.checkpoint_path")
+            if path:
+                models.load_checkpoint_into(score_model, path)
+        eng = UNetEngine.from_module(score_model, device=device)
+        eng.image_shape = tuple(config.data.shape)
+        return eng
+    raise NotImplementedError(f"model.name={name!r}: 'fcn', 'ksphere_gt' and 'ddpm' are built so far (DESIGN.md scope)")
 
 
 def sde_coefficients(sde, t: float):
@@ -108,6 +119,8 @@ def estimate_anchors(engine, anchors: torch.Tensor, K: int, sde, t: float, *, se
     label = float((torch.ones(1, dtype=torch.float32) * t * (sde.N - 1))[0])
     if chunk is None:
         per = engine.bytes_per_anchor(K) if isinstance(engine, FcnEngine) else engine.bytes_per_anchor(K, D)
+        if not isinstance(engine, (FcnEngine, KSphereEngine)):
+            mem_budget_bytes = max(mem_budget_bytes, 96 << 30)  # image score matrices: size chunks for 180 GB HBM3e
         chunk = max(1, min(N, mem_budget_bytes // max(per, 1)))
     svs, dims, sweeps = [], [], []
     for s in range(0, N, chunk):
@@ -163,8 +176,8 @@ def get_manifold_dimension(config, name=None, return_svd=False, *, score_model=N
         groups.setdefault(B, []).append(i)
     for B, idxs in groups.items():
         x = torch.stack([picked[i][0] for i in idxs]).float()
-        if x.dim() != 2:
-            raise NotImplementedError("image-shaped anchors need the U-Net engines (DESIGN.md: next rows)")
+        if x.dim() > 2:  # image anchors [C, H, W]: rows of the score matrix are the NCHW flatten (dim_reduction.py:191)
+            x = x.flatten(1)
         _, _, K = k_schedule(picked[idxs[0]][0].shape, B)
         z = None if noise is None else torch.stack([torch.as_tensor(noise[i]) for i in idxs]).float()
         res = estimate_anchors(engine, x, K, sde, sampling_eps, seed=0 if seed is None else seed, z=z,

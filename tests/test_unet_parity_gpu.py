@@ -81,3 +81,36 @@ def test_ddpm_manifold_dimension_vs_reference_golden():
     for a in range(A):
         scale = np.abs(g["scores_head"][a]).max()
         assert np.abs(head[a] - g["scores_head"][a]).max() < 2e-4 * scale
+
+
+def test_ddpm_drop_in_get_manifold_dimension(tmp_path):
+    """The reference entry point end to end for an image model: config (model.name='ddpm') -> Lightning-style
+    checkpoint -> image anchors from a loader batch -> {'singular_values': ...}, against the REAL reference's output."""
+    from iddiff_b200 import dim_reduction as DR, plot_utils
+    from iddiff_b200 import unet_models
+    g = FX.golden("unet_ddpm_small")
+    holder = unet_models.DDPM(FX.unet_config(FX.DDPM_SMALL))
+    state = FX.make_unet_state(holder, int(g["seed"]))
+    ckpt = tmp_path / "last.ckpt"
+    torch.save({"state_dict": {"score_model." + k: v for k, v in state.items()}}, ckpt)
+    B, K, nb = int(g["B"]), int(g["K"]), int(g["nb"])
+    x0 = torch.from_numpy(g["x0"])
+    n_used, svd_points = x0.shape[0], int(g["svd_points"])
+    imgs = FX.smooth_images(svd_points, 3, 16, int(g["seed"]) + 2)
+    assert torch.equal(imgs[:n_used], x0)
+    cfg = FX.unet_config(FX.DDPM_SMALL)
+    cfg.logging = dict(log_path=str(tmp_path), log_name="run", svd_points=svd_points)
+    cfg.dim_estimation = {}
+    cfg.device = "cuda:0"
+    cfg.training.batch_size = B
+    cfg.training.lightning_module = "base"
+    cfg.data.datamodule = "Tensor"
+    cfg.data.anchors = imgs[torch.arange(B) % svd_points]
+    cfg.model.checkpoint_path = str(ckpt)
+    assert DR.k_schedule(x0.shape[1:], B)[2] == K
+    z = FX.seeded_noise(int(g["seed"]) + 3, n_used, nb, B, x0.shape[1:]).reshape(n_used, nb * B, -1)[:, :K]
+    info = DR.get_manifold_dimension(cfg, name="img", return_svd=True, noise=[z[i] for i in range(n_used)])
+    sv = np.asarray(info["singular_values"])
+    assert sv.shape == g["singular_values"].shape
+    np.testing.assert_allclose(sv, g["singular_values"], rtol=1e-3)
+    assert plot_utils.dims_from_spectra(info) == g["dims"].tolist() == DR.get_manifold_dimension.last_dims
