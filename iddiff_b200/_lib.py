@@ -46,7 +46,7 @@ SIGNATURES = {
     "idb_fused_bias_act": (_i, [_vp, _vp, _vp, _i, _i, _f, _f, _ll, _i, _i, _vp, _vp]),
     "idb_groupnorm_stats": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _d, _vp, _vp, _vp]),
     "idb_conv_prep": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _i, _vp, _vp, _i, _f, _vp, _vp, _i, _vp, _vp]),
-    "idb_conv2d": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _i, C.POINTER(C.c_int), _i, _i, _f, _f, _vp, _vp, _i,
+    "idb_conv2d": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, C.POINTER(C.c_int), _i, _i, _f, _f, _vp, _vp, _i,
                         _vp, _i, _vp]),
     "idb_attention": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _f, _vp, _i, _vp]),
 }

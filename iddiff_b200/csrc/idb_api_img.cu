@@ -92,11 +92,12 @@ EncodeTiledFn encode_tiled() {
 }
 }  // namespace
 
-int idb_conv2d(const void* a_hi, const void* a_lo, int planes, int N, int H, int W, int Cp, const void* w_hi,
+int idb_conv2d(const void* a_hi, const void* a_lo, int planes, int N, int Ha, int Wa, int H, int W, int Cp, const void* w_hi,
                const void* w_lo, int n_taps, const int* taps_host, int Np, int Cout, float acc_scale, float out_scale,
                const float* bias, const float* residual, int ld_res, float* out, int ldo, void* stream) {
     if (!a_hi || !a_lo || !w_hi || !w_lo || !out || !taps_host) return api_fail("idb_conv2d: null pointer");
     if (planes <= 0 || N <= 0 || H <= 0 || W <= 0 || Cp <= 0 || Cp % 64) return api_fail("idb_conv2d: bad shape (Cp % 64)");
+    if (Ha < H || Wa < W) return api_fail("idb_conv2d: operand planes must be at least as large as the output (Ha >= H, Wa >= W)");
     if (n_taps <= 0 || n_taps > 16) return api_fail("idb_conv2d: 1..16 taps");
     if (Np % 128 || Cout <= 0 || Cout > Np || ldo < Cout) return api_fail("idb_conv2d: need Np % 128 == 0, Cout <= Np, ldo >= Cout");
     if (residual && ld_res < Cout) return api_fail("idb_conv2d: ld_res < Cout");
@@ -108,9 +109,9 @@ int idb_conv2d(const void* a_hi, const void* a_lo, int planes, int N, int H, int
     p.BI = 128 / (p.BW * p.BH);
     EncodeTiledFn enc = encode_tiled();
     if (!enc) return api_fail("idb_conv2d: cuTensorMapEncodeTiled not available from the driver");
-    const cuuint64_t dims[5] = {(cuuint64_t)Cp, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N, (cuuint64_t)planes};
-    const cuuint64_t strides[4] = {(cuuint64_t)Cp * 2, (cuuint64_t)W * Cp * 2, (cuuint64_t)H * W * Cp * 2,
-                                   (cuuint64_t)N * H * W * Cp * 2};
+    const cuuint64_t dims[5] = {(cuuint64_t)Cp, (cuuint64_t)Wa, (cuuint64_t)Ha, (cuuint64_t)N, (cuuint64_t)planes};
+    const cuuint64_t strides[4] = {(cuuint64_t)Cp * 2, (cuuint64_t)Wa * Cp * 2, (cuuint64_t)Ha * Wa * Cp * 2,
+                                   (cuuint64_t)N * Ha * Wa * Cp * 2};
     const cuuint32_t box[5] = {64, (cuuint32_t)p.BW, (cuuint32_t)p.BH, (cuuint32_t)p.BI, 1};
     const cuuint32_t estr[5] = {1, 1, 1, 1, 1};
     for (int which = 0; which < 2; ++which) {

@@ -108,6 +108,7 @@ struct PrepParams {
     int C0, C1, N, Hs, Ws, src_nchw;
     int mode;           // 0 same size, 1 nearest x2 up, 2 stride-2 parity planes, 3 2x2 average pool
     int planes, Ho, Wo;
+    int wo_shift, ho_shift;  // log2 when Wo / Ho are powers of two, else -1 (filled by the launcher)
     const float* mean_rstd;  // [N][groups][2] or null
     int groups, cg;
     const float* gamma;      // [C] or null

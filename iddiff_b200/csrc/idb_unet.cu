@@ -43,6 +43,46 @@ __global__ void __launch_bounds__(256) gn_stats_kernel(const float* __restrict__
     for (int i = threadIdx.x; i < 2 * groups; i += blockDim.x) atomicAdd(&sums[(size_t)n * 2 * groups + i], gs[i]);
 }
 
+// float4 variant (C0 % 4 == 0 and C1 % 4 == 0): one thread = 4 channels, pixels strided over the block
+__global__ void __launch_bounds__(256) gn_stats_vec_kernel(const float* __restrict__ s0, int C0,
+                                                           const float* __restrict__ s1, int C1, int HW, int groups,
+                                                           int QL, double* __restrict__ sums) {
+    extern __shared__ double gs[];  // [groups][2]
+    const int C = C0 + C1, cg = C / groups;
+    const int n = blockIdx.x;
+    for (int i = threadIdx.x; i < 2 * groups; i += blockDim.x) gs[i] = 0.0;
+    __syncthreads();
+    const int ql = threadIdx.x % QL, pl = threadIdx.x / QL, PL = blockDim.x / QL;
+    const int per = (HW + gridDim.y - 1) / gridDim.y;
+    const int p0 = blockIdx.y * per, p1 = min(HW, p0 + per);
+    for (int q = ql; q < (C >> 2); q += QL) {
+        const int c = q << 2;
+        const float* src = c < C0 ? s0 + (size_t)n * HW * C0 + c : s1 + (size_t)n * HW * C1 + (c - C0);
+        const int ld = c < C0 ? C0 : C1;
+        double a[4] = {0.0, 0.0, 0.0, 0.0}, b[4] = {0.0, 0.0, 0.0, 0.0};
+        for (int px = p0 + pl; px < p1; px += PL) {
+            const float4 f = __ldg(reinterpret_cast<const float4*>(src + (size_t)px * ld));
+            const double v0 = f.x, v1 = f.y, v2 = f.z, v3 = f.w;
+            a[0] += v0; b[0] = fma(v0, v0, b[0]);
+            a[1] += v1; b[1] = fma(v1, v1, b[1]);
+            a[2] += v2; b[2] = fma(v2, v2, b[2]);
+            a[3] += v3; b[3] = fma(v3, v3, b[3]);
+        }
+        if ((cg & 3) == 0) {  // the four channels share a group
+            atomicAdd(&gs[2 * (c / cg)], (a[0] + a[1]) + (a[2] + a[3]));
+            atomicAdd(&gs[2 * (c / cg) + 1], (b[0] + b[1]) + (b[2] + b[3]));
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                atomicAdd(&gs[2 * ((c + j) / cg)], a[j]);
+                atomicAdd(&gs[2 * ((c + j) / cg) + 1], b[j]);
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 2 * groups; i += blockDim.x) atomicAdd(&sums[(size_t)n * 2 * groups + i], gs[i]);
+}
+
 // (mean, rstd) in fp32 from the fp64 sums: var = E[x^2] - mean^2 (biased, as torch GroupNorm), rstd = 1/sqrt(var+eps)
 __global__ void gn_finalize_kernel(const double* __restrict__ sums, int total, double count, double eps,
                                    float* __restrict__ mr) {
@@ -67,90 +107,203 @@ cudaError_t launch_gn_stats(const float* s0, int C0, const float* s1, int C1, in
     const int max_slices = (HW + 15) / 16;
     if (slices > max_slices) slices = max_slices;
     if (slices < 1) slices = 1;
-    gn_stats_kernel<<<dim3(N, slices), 256, 2 * groups * sizeof(double), stream>>>(s0, C0, s1, C1, HW, groups, CL, sums);
+    auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+    if (C0 % 4 == 0 && C1 % 4 == 0 && al16(s0) && (!s1 || al16(s1))) {
+        int QL = 8;
+        while (QL < (C >> 2) && QL < 256) QL <<= 1;
+        gn_stats_vec_kernel<<<dim3(N, slices), 256, 2 * groups * sizeof(double), stream>>>(s0, C0, s1, C1, HW, groups, QL,
+                                                                                          sums);
+    } else {
+        gn_stats_kernel<<<dim3(N, slices), 256, 2 * groups * sizeof(double), stream>>>(s0, C0, s1, C1, HW, groups, CL,
+                                                                                      sums);
+    }
     const int total = N * groups;
     gn_finalize_kernel<<<(total + 255) / 256, 256, 0, stream>>>(sums, total, (double)(C / groups) * HW, eps, mean_rstd);
     return cudaGetLastError();
 }
 
 // ---------------------------------- operand preparation --------------------------------------
-__device__ __forceinline__ float prep_fetch(const PrepParams& p, int n, int y, int x, int c) {
-    // transformed source value at SOURCE pixel (y, x), channel c of the concat
-    float v;
-    if (p.src_nchw) {
-        v = __ldg(p.src0 + (((size_t)n * p.C0 + c) * p.Hs + y) * p.Ws + x);
-    } else if (c < p.C0) {
-        v = __ldg(p.src0 + (((size_t)n * p.Hs + y) * p.Ws + x) * p.C0 + c);
-    } else {
-        v = __ldg(p.src1 + (((size_t)n * p.Hs + y) * p.Ws + x) * p.C1 + (c - p.C0));
-    }
-    if (p.mean_rstd) {
-        const int g = c / p.cg;
-        const float2 mr = __ldg(reinterpret_cast<const float2*>(p.mean_rstd) + (size_t)n * p.groups + g);
-        v = (v - mr.x) * mr.y;
-    }
-    if (p.gamma) v = fmaf(v, __ldg(p.gamma + c), p.beta ? __ldg(p.beta + c) : 0.f);
-    if (p.act == 1) v = v / (1.f + expf(-v));
-    return v;
-}
+// one thread = one output pixel x one 8-channel chunk (16 B of hi and 16 B of lo).  VEC: the chunk lies inside one NHWC
+// source and is 32-byte aligned -> two float4 loads; otherwise a scalar gather (NCHW network input, odd channel counts).
+struct PrepChunk {
+    float g[8], b[8];   // GroupNorm / affine scale and shift of the 8 channels
+    float m[8], r[8];   // mean and rstd of the 8 channels' groups
+};
 
-// one thread = one output pixel x one 8-channel chunk (16 B of hi and 16 B of lo)
-__global__ void __launch_bounds__(256) conv_prep_kernel(const PrepParams p) {
-    const int chunks = p.Cp >> 3;
-    const int C = p.C0 + p.C1;
-    const long long total = (long long)p.planes * p.N * p.Ho * p.Wo * chunks;
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
-         i += (long long)gridDim.x * blockDim.x) {
-        const int ch = (int)(i % chunks);
-        long long r = i / chunks;
-        const int xo = (int)(r % p.Wo); r /= p.Wo;
-        const int yo = (int)(r % p.Ho); r /= p.Ho;
-        const int n = (int)(r % p.N);
-        const int plane = (int)(r / p.N);
-        float v[8];
+template <bool VEC>
+__device__ __forceinline__ void prep_load8(const PrepParams& p, int n, int y, int x, int c0, int C, float (&v)[8]) {
+    if (VEC) {
+        const float* src = c0 < p.C0 ? p.src0 + (((size_t)n * p.Hs + y) * p.Ws + x) * p.C0 + c0
+                                     : p.src1 + (((size_t)n * p.Hs + y) * p.Ws + x) * p.C1 + (c0 - p.C0);
+        const float4 a = __ldg(reinterpret_cast<const float4*>(src));
+        const float4 b = __ldg(reinterpret_cast<const float4*>(src) + 1);
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    } else {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            const int c = ch * 8 + j;
+            const int c = c0 + j;
             float o = 0.f;
             if (c < C) {
-                if (p.mode == 0) {
-                    o = prep_fetch(p, n, yo, xo, c);
-                } else if (p.mode == 1) {  // nearest-neighbour x2 (F.interpolate 'nearest', layers.py:600)
-                    o = prep_fetch(p, n, yo >> 1, xo >> 1, c);
-                } else if (p.mode == 2) {  // parity plane (py, px) of a stride-2 read: src[2*yo + py][2*xo + px]
-                    const int y = 2 * yo + (plane >> 1), x = 2 * xo + (plane & 1);
-                    o = (y < p.Hs && x < p.Ws) ? prep_fetch(p, n, y, x, c) : 0.f;
-                } else {  // 2 x 2 average pool (BeatGANs_nn.py avg_pool_nd)
-                    const float a = prep_fetch(p, n, 2 * yo, 2 * xo, c), b = prep_fetch(p, n, 2 * yo, 2 * xo + 1, c);
-                    const float d = prep_fetch(p, n, 2 * yo + 1, 2 * xo, c), e = prep_fetch(p, n, 2 * yo + 1, 2 * xo + 1, c);
-                    o = ((a + b) + (d + e)) * 0.25f;
-                }
+                if (p.src_nchw) o = __ldg(p.src0 + (((size_t)n * p.C0 + c) * p.Hs + y) * p.Ws + x);
+                else if (c < p.C0) o = __ldg(p.src0 + (((size_t)n * p.Hs + y) * p.Ws + x) * p.C0 + c);
+                else o = __ldg(p.src1 + (((size_t)n * p.Hs + y) * p.Ws + x) * p.C1 + (c - p.C0));
             }
             v[j] = o;
         }
-        const size_t pix = (((size_t)plane * p.N + n) * p.Ho + yo) * p.Wo + xo;
+    }
+}
+
+// ((x - mean) * rstd) * gamma + beta, then SiLU: the reference's order of operations (F.group_norm, then act)
+__device__ __forceinline__ void prep_transform8(const PrepParams& p, const PrepChunk& k, int c0, int C, float (&v)[8]) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        float o = v[j];
+        if (p.mean_rstd) o = (o - k.m[j]) * k.r[j];
+        if (p.gamma) o = fmaf(o, k.g[j], k.b[j]);
+        if (p.act == 1) o = __fdividef(o, 1.f + expf(-o));
+        v[j] = (c0 + j < C) ? o : 0.f;
+    }
+}
+
+template <bool VEC, bool POOL>
+__global__ void __launch_bounds__(256, POOL ? 2 : 4) conv_prep_kernel(const PrepParams p) {
+    // The launcher sizes the grid so that (gridDim.x * 256) % chunks == 0: a thread keeps ONE 8-channel chunk for its
+    // whole grid-stride loop (per-channel parameters live in registers) and only the pixel index advances; all index
+    // arithmetic is 32-bit, spatial sizes that are powers of two use shifts.
+    const unsigned chunks = (unsigned)(p.Cp >> 3);
+    const int C = p.C0 + p.C1;
+    const unsigned n_pix = (unsigned)p.planes * p.N * p.Ho * p.Wo;
+    const unsigned gtid = blockIdx.x * 256u + threadIdx.x;
+    const unsigned ch = gtid % chunks;
+    const unsigned pix_stride = (gridDim.x * 256u) / chunks;
+    const int c0 = (int)ch * 8;
+    const bool live = c0 < C;
+    float kg[8], kb[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int c = min(c0 + j, C - 1);
+        kg[j] = (live && p.gamma) ? __ldg(p.gamma + c) : 1.f;
+        kb[j] = (live && p.gamma && p.beta) ? __ldg(p.beta + c) : 0.f;
+    }
+    const int g_first = live ? c0 / p.cg : 0;
+    for (unsigned pix = gtid / chunks; pix < n_pix; pix += pix_stride) {
+        unsigned r = pix;
+        int xo, yo;
+        if (p.wo_shift >= 0) { xo = (int)(r & (unsigned)(p.Wo - 1)); r >>= p.wo_shift; } else { xo = (int)(r % (unsigned)p.Wo); r /= (unsigned)p.Wo; }
+        if (p.ho_shift >= 0) { yo = (int)(r & (unsigned)(p.Ho - 1)); r >>= p.ho_shift; } else { yo = (int)(r % (unsigned)p.Ho); r /= (unsigned)p.Ho; }
+        int n = (int)r, plane = 0;
+        if (p.planes > 1) { n = (int)(r % (unsigned)p.N); plane = (int)(r / (unsigned)p.N); }
+        float v[8];
+        if (!live) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = 0.f;
+        } else {
+            PrepChunk k;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { k.g[j] = kg[j]; k.b[j] = kb[j]; k.m[j] = 0.f; k.r[j] = 1.f; }
+            if (p.mean_rstd) {
+                const float2* mrp = reinterpret_cast<const float2*>(p.mean_rstd) + (size_t)n * p.groups;
+                if ((p.cg & 7) == 0) {            // the chunk lies in one group
+                    const float2 mr = __ldg(mrp + g_first);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) { k.m[j] = mr.x; k.r[j] = mr.y; }
+                } else if ((p.cg & 3) == 0) {     // two groups per chunk (cg = 4, 12, ...)
+                    const float2 a = __ldg(mrp + g_first), b = __ldg(mrp + (c0 + 4) / p.cg);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) { k.m[j] = a.x; k.r[j] = a.y; k.m[j + 4] = b.x; k.r[j + 4] = b.y; }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const float2 mr = __ldg(mrp + min(c0 + j, C - 1) / p.cg);
+                        k.m[j] = mr.x; k.r[j] = mr.y;
+                    }
+                }
+            }
+            if (POOL) {  // 2 x 2 average pool of the transformed values (BeatGANs_nn.py avg_pool_nd)
+                float a[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] = 0.f;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    prep_load8<VEC>(p, n, 2 * yo + (q >> 1), 2 * xo + (q & 1), c0, C, a);
+                    prep_transform8(p, k, c0, C, a);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) v[j] += a[j];
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] *= 0.25f;
+            } else if (p.mode == 0) {
+                prep_load8<VEC>(p, n, yo, xo, c0, C, v);
+                prep_transform8(p, k, c0, C, v);
+            } else if (p.mode == 1) {  // nearest-neighbour x2 (F.interpolate 'nearest', layers.py:600)
+                prep_load8<VEC>(p, n, yo >> 1, xo >> 1, c0, C, v);
+                prep_transform8(p, k, c0, C, v);
+            } else if (p.mode == 2) {  // parity plane (py, px) of a stride-2 read: src[2*yo + py][2*xo + px]
+                const int y = 2 * yo + (plane >> 1), x = 2 * xo + (plane & 1);
+                if (y < p.Hs && x < p.Ws) {
+                    prep_load8<VEC>(p, n, y, x, c0, C, v);
+                    prep_transform8(p, k, c0, C, v);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) v[j] = 0.f;
+                }
+            }
+        }
         if (p.out_hi) {
             uint32_t h[4], l[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) split_pair16(v[2 * j] * p.scale, v[2 * j + 1] * p.scale, 1, h[j], l[j]);
-            *reinterpret_cast<uint4*>(p.out_hi + (pix * p.Cp + ch * 8) * 2) = make_uint4(h[0], h[1], h[2], h[3]);
-            *reinterpret_cast<uint4*>(p.out_lo + (pix * p.Cp + ch * 8) * 2) = make_uint4(l[0], l[1], l[2], l[3]);
+            *reinterpret_cast<uint4*>(p.out_hi + ((size_t)pix * p.Cp + c0) * 2) = make_uint4(h[0], h[1], h[2], h[3]);
+            *reinterpret_cast<uint4*>(p.out_lo + ((size_t)pix * p.Cp + c0) * 2) = make_uint4(l[0], l[1], l[2], l[3]);
         }
-        if (p.out_f32) {
+        if (p.out_f32 && live) {
+            if (VEC) {
+                float4* dst = reinterpret_cast<float4*>(p.out_f32 + (size_t)pix * C + c0);
+                dst[0] = make_float4(v[0], v[1], v[2], v[3]);
+                dst[1] = make_float4(v[4], v[5], v[6], v[7]);
+            } else {
 #pragma unroll
-            for (int j = 0; j < 8; ++j)
-                if (ch * 8 + j < C) p.out_f32[pix * C + ch * 8 + j] = v[j];
+                for (int j = 0; j < 8; ++j)
+                    if (c0 + j < C) p.out_f32[(size_t)pix * C + c0 + j] = v[j];
+            }
         }
     }
 }
 
-cudaError_t launch_conv_prep(const PrepParams& p, int num_sms, cudaStream_t stream) {
-    const long long total = (long long)p.planes * p.N * p.Ho * p.Wo * (p.Cp >> 3);
+static int ilog2_exact(int v) {
+    if (v <= 0 || (v & (v - 1))) return -1;
+    int s = 0;
+    while ((1 << s) < v) ++s;
+    return s;
+}
+
+cudaError_t launch_conv_prep(const PrepParams& p_in, int num_sms, cudaStream_t stream) {
+    PrepParams p = p_in;
+    const long long n_pix = (long long)p.planes * p.N * p.Ho * p.Wo;
+    const long long chunks = p.Cp >> 3;
+    const long long total = n_pix * chunks;
     if (total <= 0) return cudaSuccess;
+    if (n_pix >= (1ll << 31)) return cudaErrorInvalidValue;
+    p.wo_shift = ilog2_exact(p.Wo);
+    p.ho_shift = ilog2_exact(p.Ho);
+    // grid * 256 must be a multiple of chunks: grid = multiple of chunks / gcd(chunks, 256)
+    long long g = chunks, b = 256;
+    while (b) { const long long t = g % b; g = b; b = t; }
+    const long long unit = chunks / g;
     long long grid = (total + 255) / 256;
     const long long cap = (long long)num_sms * 16;
     if (grid > cap) grid = cap;
-    conv_prep_kernel<<<(unsigned)grid, 256, 0, stream>>>(p);
+    grid = (grid + unit - 1) / unit * unit;
+    auto al32 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+    const bool vec = !p.src_nchw && p.C0 % 8 == 0 && p.C1 % 8 == 0 && al32(p.src0) && (!p.src1 || al32(p.src1)) &&
+                     (!p.out_f32 || al32(p.out_f32));
+    if (p.mode == 3) {
+        if (vec) conv_prep_kernel<true, true><<<(unsigned)grid, 256, 0, stream>>>(p);
+        else conv_prep_kernel<false, true><<<(unsigned)grid, 256, 0, stream>>>(p);
+    } else {
+        if (vec) conv_prep_kernel<true, false><<<(unsigned)grid, 256, 0, stream>>>(p);
+        else conv_prep_kernel<false, false><<<(unsigned)grid, 256, 0, stream>>>(p);
+    }
     return cudaGetLastError();
 }
 

@@ -60,7 +60,7 @@ def build_engine(config, score_model: Optional[torch.nn.Module] = None, device="
             if path:
                 models.load_checkpoint_into(score_model, path)
         return FcnEngine.from_module(score_model, device=device)
-    if name == "ddpm":
+    if name in ("ddpm", "ncsnpp"):
         from . import models, unet_models  # noqa: F401  (registers 'ddpm')
         from .unet_engine import UNetEngine
         if score_model is None:
@@ -71,7 +71,7 @@ def build_engine(config, score_model: Optional[torch.nn.Module] = None, device="
         eng = UNetEngine.from_module(score_model, device=device)
         eng.image_shape = tuple(config.data.shape)
         return eng
-    raise NotImplementedError(f"model.name={name!r}: 'fcn', 'ksphere_gt' and 'ddpm' are built so far (DESIGN.md scope)")
+    raise NotImplementedError(f"model.name={name!r}: 'fcn', 'ksphere_gt', 'ddpm' and 'ncsnpp' are built so far (DESIGN.md scope)")
 
 
 def sde_coefficients(sde, t: float):

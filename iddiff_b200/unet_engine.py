@@ -34,29 +34,44 @@ def timestep_embedding(label: float, dim: int, max_positions: int = 10000) -> to
     return emb
 
 
+def _f32(t, dev):
+    return t.detach().to(dev, torch.float32).contiguous()
+
+
 class _Res:
-    """ResnetBlockDDPM weights in kernel form."""
+    """ResnetBlockDDPM (layers.py:632-675) / ResnetBlockBigGANpp (layerspp.py:212-274) weights in kernel form."""
 
     def __init__(self, m, dev):
-        g = lambda t: t.detach().to(dev, torch.float32).contiguous()
+        g = lambda t: _f32(t, dev)
         self.in_ch, self.out_ch = m.in_ch, m.out_ch
+        self.up, self.down = bool(getattr(m, "up", False)), bool(getattr(m, "down", False))
+        self.groups0, self.groups1 = m.GroupNorm_0.num_groups, m.GroupNorm_1.num_groups
+        self.out_scale = float(1.0 / math.sqrt(2.0)) if getattr(m, "skip_rescale", False) else 1.0
         self.gn0 = (g(m.GroupNorm_0.weight), g(m.GroupNorm_0.bias))
         self.gn1 = (g(m.GroupNorm_1.weight), g(m.GroupNorm_1.bias))
         self.conv0 = U.pack_conv(g(m.Conv_0.weight), g(m.Conv_0.bias))
         self.conv1 = U.pack_conv(g(m.Conv_1.weight), g(m.Conv_1.bias))
         self.dense = (g(m.Dense_0.weight), g(m.Dense_0.bias)) if hasattr(m, "Dense_0") else None
         self.short = None
-        if m.in_ch != m.out_ch:
-            if m.conv_shortcut:
-                self.short = U.pack_conv(g(m.Conv_2.weight), g(m.Conv_2.bias))
-            else:
-                self.short = U.pack_conv(g(m.NIN_0.W).t().contiguous(), g(m.NIN_0.b))
+        if hasattr(m, "Conv_2"):      # 3x3 (DDPM conv_shortcut) or 1x1 (BigGAN++)
+            self.short = U.pack_conv(g(m.Conv_2.weight), g(m.Conv_2.bias))
+        elif hasattr(m, "NIN_0"):
+            self.short = U.pack_conv(g(m.NIN_0.W).t().contiguous(), g(m.NIN_0.b))
+        if self.up or self.down:
+            if not m.fir:
+                raise NotImplementedError("BigGAN res-block resampling without FIR (naive_up/downsample) is not built")
+            # upsample_2d: k * factor^2, up 2, pad (2, 1); downsample_2d: k, down 2, pad (1, 1)  (up_or_down_sampling.py:181-257)
+            self.fir = U.fir_kernel(m.fir_kernel, 4.0 if self.up else 1.0, dev)
 
 
 class _Attn:
+    """AttnBlock (layers.py:567-590) / AttnBlockpp (layerspp.py:62-91)."""
+
     def __init__(self, m, dev):
-        g = lambda t: t.detach().to(dev, torch.float32).contiguous()
+        g = lambda t: _f32(t, dev)
         self.c = m.channels
+        self.groups = m.GroupNorm_0.num_groups
+        self.out_scale = float(1.0 / math.sqrt(2.0)) if getattr(m, "skip_rescale", False) else 1.0
         self.gn = (g(m.GroupNorm_0.weight), g(m.GroupNorm_0.bias))
         wqkv = torch.cat([g(m.NIN_0.W).t(), g(m.NIN_1.W).t(), g(m.NIN_2.W).t()], dim=0).contiguous()  # [3C, C]
         bqkv = torch.cat([g(m.NIN_0.b), g(m.NIN_1.b), g(m.NIN_2.b)]).contiguous()
@@ -64,17 +79,29 @@ class _Attn:
         self.proj = U.pack_conv(g(m.NIN_3.W).t().contiguous(), g(m.NIN_3.b))
 
 
+class _PyrDown:
+    """layerspp.Downsample(fir, with_conv) on the input pyramid (ncsnpp.py:297-304): FIR pad (2, 2) then 3x3 stride 2."""
+
+    def __init__(self, m, dev):
+        self.conv = U.pack_conv(_f32(m.Conv2d_0.weight, dev), _f32(m.Conv2d_0.bias, dev), taps=U.TAPS_3x3_S2, planes=4)
+        self.fir = U.fir_kernel(m.fir_kernel, 1.0, dev)
+
+
 class UNetEngine:
     """DDPM U-Net (models/ddpm.py) on the sm_100a kernels.  Build with `UNetEngine.from_module(holder, device)`."""
 
-    GROUPS, EPS = 32, 1e-6
+    EPS = 1e-6
 
     def __init__(self, holder, device):
         self.dev = torch.device(device)
         self.h = holder
         g = lambda t: t.detach().to(self.dev, torch.float32).contiguous()
         mods = holder.all_modules
-        self.temb_w = [(g(mods[0].weight), g(mods[0].bias)), (g(mods[1].weight), g(mods[1].bias))]
+        self.fourier = getattr(holder, "embedding_type", "positional") == "fourier"
+        t0 = 1 if self.fourier else 0
+        self.fourier_w = mods[0].W.detach().float().cpu() if self.fourier else None
+        self.temb_w = [(g(mods[t0].weight), g(mods[t0].bias)), (g(mods[t0 + 1].weight), g(mods[t0 + 1].bias))]
+        self.rescale = float(1.0 / math.sqrt(2.0)) if getattr(holder, "skip_rescale", False) else 1.0
         self.blocks: Dict[int, object] = {}
         for kind, idx, _ in holder.plan:
             m = mods[idx] if idx >= 0 else None
@@ -89,8 +116,10 @@ class UNetEngine:
                     if m.with_conv else None
             elif kind == "up":
                 self.blocks[idx] = U.pack_conv(g(m.Conv_0.weight), g(m.Conv_0.bias)) if m.with_conv else None
+            elif kind == "pyr_down":
+                self.blocks[idx] = _PyrDown(m, self.dev)
             elif kind == "gn_out":
-                self.blocks[idx] = (g(m.weight), g(m.bias))
+                self.blocks[idx] = (g(m.weight), g(m.bias), m.num_groups)
         cin = mods[holder.plan[0][1]].weight.shape[1]
         self.in_affine = None
         if not holder.centered:  # ddpm.py:163-168: h = 2x - 1 for data in [0, 1]
@@ -109,7 +138,11 @@ class UNetEngine:
         key = float(label)
         if key in self._label_cache:
             return self._label_cache[key]
-        temb = timestep_embedding(key, self.h.nf).to(self.dev)
+        if self.fourier:  # layerspp.py:39-41, same float32 torch expression as the reference
+            xp = torch.tensor([key], dtype=torch.float32)[:, None] * self.fourier_w[None, :] * 2 * math.pi
+            temb = torch.cat([torch.sin(xp), torch.cos(xp)], dim=-1).to(self.dev)
+        else:
+            temb = timestep_embedding(key, self.h.nf).to(self.dev)
         temb = U.dense(temb, *self.temb_w[0], act_in=0)
         temb = U.dense(temb, *self.temb_w[1], act_in=2)
         out = {}
@@ -126,36 +159,60 @@ class UNetEngine:
 
     # ---- blocks --------------------------------------------------------------------------------
     def _res(self, blk: _Res, bias0, x0, x1=None):
-        mr = U.gn_stats(x0, x1, self.GROUPS, self.EPS)
-        a = U.prep(x0, x1, mean_rstd=mr, groups=self.GROUPS, gamma=blk.gn0[0], beta=blk.gn0[1], act=1)
+        mr = U.gn_stats(x0, x1, blk.groups0, self.EPS)
+        if blk.up or blk.down:
+            # layerspp.py:244-257: FIR resampling of BOTH act(GN(x)) and x before the convolutions
+            assert x1 is None
+            _, hf = U.prep(x0, mean_rstd=mr, groups=blk.groups0, gamma=blk.gn0[0], beta=blk.gn0[1], act=1,
+                           want_operand=False, want_f32=True)
+            if blk.up:
+                hf, xr = U.upfirdn2d_nhwc(hf, blk.fir, 2, 1, 2, 1), U.upfirdn2d_nhwc(x0, blk.fir, 2, 1, 2, 1)
+            else:
+                hf, xr = U.upfirdn2d_nhwc(hf, blk.fir, 1, 2, 1, 1), U.upfirdn2d_nhwc(x0, blk.fir, 1, 2, 1, 1)
+            a = U.prep(hf)
+            x0 = xr
+        else:
+            a = U.prep(x0, x1, mean_rstd=mr, groups=blk.groups0, gamma=blk.gn0[0], beta=blk.gn0[1], act=1)
         h = U.conv(a, blk.conv0, bias=bias0)
-        mr = U.gn_stats(h, None, self.GROUPS, self.EPS)
-        a = U.prep(h, mean_rstd=mr, groups=self.GROUPS, gamma=blk.gn1[0], beta=blk.gn1[1], act=1)
+        mr = U.gn_stats(h, None, blk.groups1, self.EPS)
+        a = U.prep(h, mean_rstd=mr, groups=blk.groups1, gamma=blk.gn1[0], beta=blk.gn1[1], act=1)
         if blk.short is not None:
             xs = U.conv(U.prep(x0, x1), blk.short)
+        elif x1 is not None:
+            raise _lib.IdbError("res-block with a concatenated input needs a shortcut projection")
         else:
             xs = x0
-        return U.conv(a, blk.conv1, residual=xs)
+        return U.conv(a, blk.conv1, residual=xs, out_scale=blk.out_scale)
 
     def _attn(self, blk: _Attn, x):
-        mr = U.gn_stats(x, None, self.GROUPS, self.EPS)
-        a = U.prep(x, mean_rstd=mr, groups=self.GROUPS, gamma=blk.gn[0], beta=blk.gn[1])
+        mr = U.gn_stats(x, None, blk.groups, self.EPS)
+        a = U.prep(x, mean_rstd=mr, groups=blk.groups, gamma=blk.gn[0], beta=blk.gn[1])
         qkv = U.conv(a, blk.qkv)
         c = blk.c
         o = U.attention(qkv, 1, c, 0, c, 2 * c, c, float(int(c) ** (-0.5)))
-        return U.conv(U.prep(o), blk.proj, residual=x)
+        return U.conv(U.prep(o), blk.proj, residual=x, out_scale=blk.out_scale)
 
     def forward(self, x_nchw: torch.Tensor, label: float, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """x [B, C, H, W] fp32 (device) -> raw network output [B, H, W, Cout] fp32 NHWC (ddpm.py:149-213)."""
         if not (x_nchw.is_cuda and x_nchw.dtype == torch.float32 and x_nchw.is_contiguous() and x_nchw.dim() == 4):
             raise _lib.IdbError("UNetEngine.forward: contiguous float32 CUDA [B, C, H, W] required")
         biases = self._biases_for(label)
-        h, hs = None, []
+        h, hs, pyramid = None, [], None
         for kind, idx, extra in self.h.plan:
             blk = self.blocks.get(idx)
             if kind == "conv_in":
                 ga, be = self.in_affine if self.in_affine else (None, None)
-                h = U.conv(U.prep(x_nchw, nchw=True, gamma=ga, beta=be), blk)
+                if extra.get("pyramid"):  # ncsnpp.py:268-271: the (rescaled) input also feeds the input pyramid
+                    a, pyramid = U.prep(x_nchw, nchw=True, gamma=ga, beta=be, want_f32=True)
+                else:
+                    a = U.prep(x_nchw, nchw=True, gamma=ga, beta=be)
+                h = U.conv(a, blk)
+            elif kind == "pyr_down":
+                # conv_downsample_2d (up_or_down_sampling.py:144-178) then (pyramid + h) / sqrt(2) (ncsnpp.py:300-304)
+                f = U.upfirdn2d_nhwc(pyramid, blk.fir, 1, 1, 2, 2)
+                h = U.conv(U.prep(f, mode=U.PREP_STRIDE2), blk.conv, residual=h, out_scale=self.rescale,
+                           out_hw=(h.shape[1], h.shape[2]))
+                pyramid = h
             elif kind == "push":
                 hs.append(h)
             elif kind == "res":
@@ -173,8 +230,8 @@ class UNetEngine:
                 else:
                     h = U.prep(h, mode=U.PREP_UP2, want_operand=False, want_f32=True)[1]
             elif kind == "gn_out":
-                mr = U.gn_stats(h, None, self.GROUPS, self.EPS)
-                h = U.prep(h, mean_rstd=mr, groups=self.GROUPS, gamma=blk[0], beta=blk[1], act=1)
+                mr = U.gn_stats(h, None, blk[2], self.EPS)
+                h = U.prep(h, mean_rstd=mr, groups=blk[2], gamma=blk[0], beta=blk[1], act=1)
             elif kind == "conv_out":
                 h = U.conv(h, blk, out=out)
         assert not hs

@@ -15,7 +15,7 @@ import math
 import torch
 import torch.nn as nn
 
-from .models import register_model
+from .models import get_model, register_model  # noqa: F401
 
 
 def fan_avg_uniform_(t: torch.Tensor, scale: float = 1.0, in_axis: int = 1, out_axis: int = 0) -> torch.Tensor:
@@ -164,5 +164,145 @@ class DDPM(_Holder):
         assert not hs_c
         add("gn_out", _gn(in_ch))
         add("conv_out", _conv3x3(in_ch, m.output_channels, init_scale=0.0))
+        self.all_modules = nn.ModuleList(mods)
+        self.plan = plan
+
+
+# ------------------------------------------------------------------------------------------------
+# NCSN++ (models/ncsnpp.py:40-236) in the configuration BASELINE config 4 names: style_gan_base.py:106-129 with
+# model.name='ncsnpp' -- Fourier embedding, BigGAN res-blocks with FIR up/down-sampling, skip rescale,
+# progressive_input='residual' (input pyramid), progressive='none'.
+# Blocks: layerspp.py GaussianFourierProjection :32-41, AttnBlockpp :62-91, Downsample (FIR conv) :129-163,
+# ResnetBlockBigGANpp :212-274; up_or_down_sampling.py Conv2d :23-57.
+# ------------------------------------------------------------------------------------------------
+def _gnpp(ch):
+    return nn.GroupNorm(num_groups=min(ch // 4, 32), num_channels=ch, eps=1e-6)
+
+
+class GaussianFourierProjection(_Holder):
+    def __init__(self, embedding_size=256, scale=1.0):
+        super().__init__()
+        self.W = nn.Parameter(torch.randn(embedding_size) * scale, requires_grad=False)
+
+
+class ResnetBlockBigGANpp(_Holder):
+    def __init__(self, in_ch, out_ch=None, temb_dim=None, up=False, down=False, dropout=0.1, fir=False,
+                 fir_kernel=(1, 3, 3, 1), skip_rescale=True, init_scale=0.0):
+        super().__init__()
+        out_ch = out_ch or in_ch
+        self.in_ch, self.out_ch, self.up, self.down = in_ch, out_ch, up, down
+        self.fir, self.fir_kernel, self.skip_rescale = fir, tuple(fir_kernel), skip_rescale
+        self.GroupNorm_0 = _gnpp(in_ch)
+        self.Conv_0 = _conv3x3(in_ch, out_ch)
+        if temb_dim is not None:
+            self.Dense_0 = _dense(temb_dim, out_ch)
+        self.GroupNorm_1 = _gnpp(out_ch)
+        self.Dropout_0 = nn.Dropout(dropout)
+        self.Conv_1 = _conv3x3(out_ch, out_ch, init_scale=init_scale)
+        if in_ch != out_ch or up or down:
+            self.Conv_2 = nn.Conv2d(in_ch, out_ch, 1)
+            fan_avg_uniform_(self.Conv_2.weight)
+            nn.init.zeros_(self.Conv_2.bias)
+
+
+class AttnBlockpp(_Holder):
+    def __init__(self, channels, skip_rescale=False, init_scale=0.0):
+        super().__init__()
+        self.channels, self.skip_rescale = channels, skip_rescale
+        self.GroupNorm_0 = _gnpp(channels)
+        self.NIN_0, self.NIN_1, self.NIN_2 = NIN(channels, channels), NIN(channels, channels), NIN(channels, channels)
+        self.NIN_3 = NIN(channels, channels, init_scale=init_scale)
+
+
+class _FirConv2d(_Holder):
+    """up_or_down_sampling.Conv2d parameters (weight [out, in, k, k], bias)."""
+
+    def __init__(self, in_ch, out_ch, kernel=3):
+        super().__init__()
+        self.weight = nn.Parameter(fan_avg_uniform_(torch.empty(out_ch, in_ch, kernel, kernel)))
+        self.bias = nn.Parameter(torch.zeros(out_ch))
+
+
+class DownsampleFirConv(_Holder):
+    """layerspp.Downsample(fir=True, with_conv=True): FIR pre-filter + stride-2 3x3 conv (conv_downsample_2d)."""
+
+    def __init__(self, in_ch, out_ch, fir_kernel=(1, 3, 3, 1)):
+        super().__init__()
+        self.fir_kernel = tuple(fir_kernel)
+        self.Conv2d_0 = _FirConv2d(in_ch, out_ch)
+
+
+@register_model("ncsnpp")
+class NCSNpp(_Holder):
+    def __init__(self, config):
+        super().__init__()
+        m = config.model
+        want = dict(nonlinearity="swish", embedding_type="fourier", resblock_type="biggan", progressive="none",
+                    progressive_input="residual")
+        for k, v in want.items():
+            if str(getattr(m, k)).lower() != v:
+                raise NotImplementedError(f"iddiff_b200 NCSN++ engine is built for model.{k}={v!r} (style_gan_base.py), "
+                                          f"got {getattr(m, k)!r}")
+        if not (m.fir and m.conditional and config.training.continuous):
+            raise NotImplementedError("NCSN++ engine: fir=True, conditional=True, continuous training only")
+        self.nf = nf = m.nf
+        ch_mult = tuple(m.ch_mult)
+        nrb = m.num_res_blocks
+        self.attn_resolutions = tuple(m.attn_resolutions)
+        nres = len(ch_mult)
+        res_all = [config.data.effective_image_size // (2 ** i) for i in range(nres)]
+        self.centered = config.data.centered
+        self.skip_rescale = m.skip_rescale
+        self.embedding_type = "fourier"
+        channels = config.data.num_channels
+        temb_dim = 4 * nf
+        mods, plan = [], []
+
+        def add(kind, mod, **extra):
+            plan.append((kind, len(mods), extra))
+            mods.append(mod)
+
+        def res(i, o=None, **kw):
+            return ResnetBlockBigGANpp(i, o, temb_dim, dropout=m.dropout, fir=m.fir, fir_kernel=m.fir_kernel,
+                                       skip_rescale=m.skip_rescale, init_scale=m.init_scale, **kw)
+
+        attn = lambda c: AttnBlockpp(c, skip_rescale=m.skip_rescale, init_scale=m.init_scale)
+        mods.append(GaussianFourierProjection(embedding_size=nf, scale=m.fourier_scale))
+        mods.append(_dense(2 * nf, temb_dim))
+        mods.append(_dense(temb_dim, temb_dim))
+        add("conv_in", _conv3x3(channels, nf), pyramid=True)
+        plan.append(("push", -1, {}))
+        hs_c, in_ch, pyr_ch = [nf], nf, channels
+        for lvl in range(nres):
+            for _ in range(nrb):
+                out_ch = nf * ch_mult[lvl]
+                add("res", res(in_ch, out_ch))
+                in_ch = out_ch
+                if res_all[lvl] in self.attn_resolutions:
+                    add("attn", attn(in_ch))
+                plan.append(("push", -1, {}))
+                hs_c.append(in_ch)
+            if lvl != nres - 1:
+                add("res", res(in_ch, down=True))
+                add("pyr_down", DownsampleFirConv(pyr_ch, in_ch, m.fir_kernel))
+                pyr_ch = in_ch
+                plan.append(("push", -1, {}))
+                hs_c.append(in_ch)
+        in_ch = hs_c[-1]
+        add("res", res(in_ch))
+        add("attn", attn(in_ch))
+        add("res", res(in_ch))
+        for lvl in reversed(range(nres)):
+            for _ in range(nrb + 1):
+                out_ch = nf * ch_mult[lvl]
+                add("res", res(in_ch + hs_c.pop(), out_ch), skip=True)
+                in_ch = out_ch
+            if res_all[lvl] in self.attn_resolutions:
+                add("attn", attn(in_ch))
+            if lvl != 0:
+                add("res", res(in_ch, up=True))
+        assert not hs_c
+        add("gn_out", _gnpp(in_ch))
+        add("conv_out", _conv3x3(in_ch, channels, init_scale=m.init_scale))
         self.all_modules = nn.ModuleList(mods)
         self.plan = plan

@@ -128,16 +128,17 @@ def prep(x0: torch.Tensor, x1: Optional[torch.Tensor] = None, *, mode: int = PRE
 
 
 def conv(a: Operand, pc: PackedConv, *, bias: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None,
-         out_scale: float = 1.0, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+         out_scale: float = 1.0, out: Optional[torch.Tensor] = None, out_hw=None) -> torch.Tensor:
     """out [N,H,W,Cout] fp32 = out_scale * (conv(a, W) + bias + residual).  `bias` overrides pc.bias (the host folds
     the time-embedding projection into it)."""
     if a.cp != pc.cp or a.planes != pc.planes:
         raise _lib.IdbError(f"conv: operand (Cp={a.cp}, planes={a.planes}) does not match weights (Cp={pc.cp}, planes={pc.planes})")
+    oh, ow = out_hw if out_hw is not None else (a.h, a.w)
     if out is None:
-        out = torch.empty(a.n, a.h, a.w, pc.cout, dtype=torch.float32, device=a.hi.device)
+        out = torch.empty(a.n, oh, ow, pc.cout, dtype=torch.float32, device=a.hi.device)
     b = bias if bias is not None else pc.bias
     ld_res = residual.shape[-1] if residual is not None else 0
-    _lib.call("idb_conv2d", _lib.ptr(a.hi), _lib.ptr(a.lo), a.planes, a.n, a.h, a.w, a.cp, _lib.ptr(pc.w_hi),
+    _lib.call("idb_conv2d", _lib.ptr(a.hi), _lib.ptr(a.lo), a.planes, a.n, a.h, a.w, oh, ow, a.cp, _lib.ptr(pc.w_hi),
               _lib.ptr(pc.w_lo), len(pc.taps), pc.taps_c, pc.np_, pc.cout, 1.0 / (ACT_SCALE * pc.w_scale), float(out_scale),
               _lib.ptr(b), _lib.ptr(residual), ld_res, _lib.ptr(out), out.shape[-1], _lib.stream_ptr())
     return out
@@ -160,4 +161,27 @@ def dense(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], a
     out = torch.empty(a, n, dtype=torch.float32, device=x.device)
     _lib.call("idb_anchor_linear", _lib.ptr(x), k, act_in, 1.0, _lib.ptr(weight), weight.stride(0), _lib.ptr(bias), None,
               0, 0.0, _lib.ptr(out), n, a, n, k, _lib.stream_ptr())
+    return out
+
+
+def fir_kernel(taps, gain: float, device) -> torch.Tensor:
+    """up_or_down_sampling._setup_kernel (:165-172) * gain, in numpy float32 like the reference."""
+    import numpy as np
+    k = np.asarray(taps, dtype=np.float32)
+    if k.ndim == 1:
+        k = np.outer(k, k)
+    k /= np.sum(k)
+    return torch.from_numpy(np.ascontiguousarray(k * gain)).to(device)
+
+
+def upfirdn2d_nhwc(x: torch.Tensor, k: torch.Tensor, up: int, down: int, pad0: int, pad1: int) -> torch.Tensor:
+    """The reference op on an NHWC activation: [major = N, H, W, minor = C] is exactly its native layout
+    (op/upfirdn2d.cpp:12-22), so no NCHW reshape is needed."""
+    n, h, w, c = x.shape
+    kh, kw = k.shape
+    oh = (h * up + pad0 + pad1 - kh) // down + 1
+    ow = (w * up + pad0 + pad1 - kw) // down + 1
+    out = torch.empty(n, oh, ow, c, dtype=torch.float32, device=x.device)
+    _lib.call("idb_upfirdn2d", _lib.ptr(x), _lib.ptr(k), n, h, w, c, kh, kw, up, up, down, down, pad0, pad1, pad0, pad1,
+              _lib.ptr(out), _lib.stream_ptr())
     return out

@@ -169,14 +169,15 @@ int idb_conv_prep(const float* src0, int C0, const float* src1, int C1, int N, i
 /* nn.Conv2d / NIN as an implicit GEMM on tcgen05 (3 MMAs per product on fp16 hi/lo pairs, fp32 accumulate in TMEM):
  *   out[n,h,w,co] = out_scale * (acc_scale * sum_{t,ci} A[plane_t][n, h+dy_t, w+dx_t, ci] * Wt[co][t][ci]
  *                                + bias[co] + residual[n,h,w,co])
- * A = idb_conv_prep output [planes][N][H][W][Cp]; reads outside the image are zero (TMA out-of-bounds fill = the
+ * A = idb_conv_prep output [planes][N][Ha][Wa][Cp] (Ha >= H, Wa >= W: the planes of a stride-2 read of an odd-sized
+ * tensor are one row/column larger than the output); reads outside the planes are zero (TMA out-of-bounds fill = the
  * convolution's zero padding).  Wt = idb_pack_weight of the matrix [Cout][n_taps*Cp] (tap-major, channel-minor).
  * taps_host: HOST array [n_taps][3] = (plane, dy, dx).  3x3 pad 1: plane 0, dy,dx in {-1,0,1};  3x3 stride 2 after
  * pad (0,1,0,1): tap (ky,kx) -> plane 2(ky&1)+(kx&1), dy = ky>>1, dx = kx>>1;  1x1 / NIN: one tap (0,0,0).
  * bias [Cout] / residual [N][H][W][ld_res] may be NULL.  H, W powers of two (<= 128) so that 128-pixel tiles are boxes.
  * Replaces cuDNN conv + bias add + temb add (layers.py:662-664; t is constant on this path so Dense_0(act(temb)) is
  * folded into `bias` by the host) + residual add (:675) + skip rescale (layerspp.py:271-274). */
-int idb_conv2d(const void* a_hi, const void* a_lo, int planes, int N, int H, int W, int Cp, const void* w_hi,
+int idb_conv2d(const void* a_hi, const void* a_lo, int planes, int N, int Ha, int Wa, int H, int W, int Cp, const void* w_hi,
                const void* w_lo, int n_taps, const int* taps_host, int Np, int Cout, float acc_scale, float out_scale,
                const float* bias, const float* residual, int ld_res, float* out, int ldo, void* stream);
 

@@ -121,6 +121,11 @@ DDPM_SMALL = dict(nf=32, ch_mult=(1, 2), num_res_blocks=1, attn_resolutions=(8,)
                   nonlinearity="swish")
 
 
+NCSNPP_SMALL = dict(DDPM_SMALL, nf=16, fir=True, fir_kernel=[1, 3, 3, 1], skip_rescale=True, resblock_type="biggan",
+                    progressive="none", progressive_input="residual", progressive_combine="sum",
+                    embedding_type="fourier", init_scale=0.0, fourier_scale=16)
+
+
 def unet_config(spec: dict, name: str = "ddpm"):
     """A config carrying the keys models/ddpm.py:84-109 reads, for the reference and for iddiff_b200 alike."""
     from iddiff_b200.config import ConfigDict

@@ -16,6 +16,11 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 sys.path.insert(0, ROOT)
 
+from unittest import mock  # noqa: E402
+import torch.utils.cpp_extension as _cpp  # noqa: E402
+
+_cpp.load = lambda *a, **k: mock.MagicMock()  # the reference's `op` package: no nvcc JIT, its CPU branches run
+
 from oracle import gen_golden as GG  # noqa: E402  (installs the shims, imports the reference's dim_reduction)
 from oracle import fixtures as FX  # noqa: E402
 from oracle import img_oracle as IO  # noqa: E402
@@ -23,15 +28,17 @@ from oracle import img_oracle as IO  # noqa: E402
 GOLD = GG.GOLD
 
 
-def gen_ddpm(name="unet_ddpm_small", spec=FX.DDPM_SMALL, seed=7, B=64, svd_points=3):
+def gen_unet(name="unet_ddpm_small", spec=FX.DDPM_SMALL, seed=7, B=64, svd_points=3, model="ddpm"):
     import models.ddpm  # noqa: F401  (reference; registers 'ddpm')
+    import models.ncsnpp  # noqa: F401  (reference; registers 'ncsnpp')
     from models import utils as mutils
     from iddiff_b200 import unet_models
-    holder = unet_models.DDPM(FX.unet_config(spec))
+    holder = unet_models.get_model(model)(FX.unet_config(spec, model))
+    oracle_forward = {"ddpm": IO.ddpm_forward, "ncsnpp": IO.ncsnpp_forward}[model]
     state = FX.make_unet_state(holder, seed)
     size, cin = spec["image_size"], spec["input_channels"]
     model_kw = {k: v for k, v in spec.items() if k not in ("image_size", "centered")}
-    cfg = GG.base_config("vesde", [cin, size, size], B, "ddpm", "base", svd_points, **model_kw)
+    cfg = GG.base_config("vesde", [cin, size, size], B, model, "base", svd_points, **model_kw)
     cfg.data.update(dict(centered=spec["centered"], effective_image_size=size, image_size=size, num_channels=cin))
     ref = mutils.create_model(cfg)
     ref.load_state_dict(state, strict=True)
@@ -42,7 +49,7 @@ def gen_ddpm(name="unet_ddpm_small", spec=FX.DDPM_SMALL, seed=7, B=64, svd_point
     label = float((torch.ones(1) * 1e-5 * 999)[0])
     with torch.no_grad():
         y = ref(x, torch.full((5,), label))
-        y_oracle = IO.ddpm_forward(state, spec, x, torch.full((5,), label))
+        y_oracle = oracle_forward(state, spec, x, torch.full((5,), label))
     print("oracle vs reference forward: max abs diff", float((y - y_oracle).abs().max()), "scale", float(y.abs().max()))
     # path-level golden: anchors = smooth synthetic images, one loader batch of exactly B rows
     imgs = FX.smooth_images(svd_points, cin, size, seed + 2)
@@ -65,7 +72,9 @@ def gen_ddpm(name="unet_ddpm_small", spec=FX.DDPM_SMALL, seed=7, B=64, svd_point
 
 def main(what):
     if "ddpm" in what:
-        gen_ddpm()
+        gen_unet()
+    if "ncsnpp" in what:
+        gen_unet("unet_ncsnpp_small", FX.NCSNPP_SMALL, seed=11, model="ncsnpp")
 
 
 if __name__ == "__main__":

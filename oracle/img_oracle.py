@@ -167,3 +167,126 @@ def unet_score_matrix(forward, state, cfg, x0, z, mean_coeff, std, label, batch=
             rows.append(-forward(state, cfg, x, lab) / std)
     S = torch.cat(rows).flatten(1)
     return S - S.mean(0, keepdim=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# NCSN++ (models/ncsnpp.py:238-388) for the style_gan_base configuration with model.name='ncsnpp':
+# Fourier embedding, BigGAN++ res-blocks with FIR resampling, skip rescale, input pyramid ('residual'), progressive='none'.
+# ------------------------------------------------------------------------------------------------
+def upfirdn2d_torch(x, k, up=1, down=1, pad=(0, 0)):
+    """op/upfirdn2d.py:145-200 on NCHW tensors (same pads on both axes), any float dtype."""
+    import torch
+    import torch.nn.functional as F
+    n, c, h, w = x.shape
+    k = torch.as_tensor(k, dtype=x.dtype)
+    st = x.new_zeros(n, c, h * up, w * up)
+    st[:, :, ::up, ::up] = x
+    p0, p1 = pad
+    st = F.pad(st, [max(p0, 0), max(p1, 0), max(p0, 0), max(p1, 0)])
+    st = st[:, :, max(-p0, 0):st.shape[2] - max(-p1, 0), max(-p0, 0):st.shape[3] - max(-p1, 0)]
+    wt = torch.flip(k, [0, 1])[None, None].repeat(c, 1, 1, 1)
+    out = F.conv2d(st, wt, groups=c)
+    return out[:, :, ::down, ::down]
+
+
+def _fir(taps, gain, dtype):
+    import torch
+    k = np.asarray(taps, dtype=np.float32)
+    k = np.outer(k, k)
+    k /= np.sum(k)
+    return torch.from_numpy(k * np.float32(gain)).to(dtype)
+
+
+def ncsnpp_forward(state, cfg, x, labels):
+    """cfg: DDPM keys + fir_kernel, fourier_scale (unused here: W is in the state), skip_rescale=True."""
+    import math
+    import torch
+    import torch.nn.functional as F
+    dt = x.dtype
+    P = lambda i, name: state[f"all_modules.{i}.{name}"].to(dt)
+    has = lambda i, name: f"all_modules.{i}.{name}" in state
+    nf, ch_mult, nrb = cfg["nf"], cfg["ch_mult"], cfg["num_res_blocks"]
+    nres = len(ch_mult)
+    taps = cfg["fir_kernel"]
+    rs = math.sqrt(2.0)
+    idx = [0]
+
+    def nxt():
+        idx[0] += 1
+        return idx[0] - 1
+
+    def gn(i, name, h):
+        c = h.shape[1]
+        return F.group_norm(h, min(c // 4, 32), P(i, name + ".weight"), P(i, name + ".bias"), eps=1e-6)
+
+    def nin(i, name, h):
+        return torch.einsum("bchw,co->bohw", h, P(i, name + ".W")) + P(i, name + ".b")[None, :, None, None]
+
+    def res(h, temb, up=False, down=False):  # layerspp.py:241-274
+        i = nxt()
+        x_ = h
+        a = _silu(gn(i, "GroupNorm_0", h))
+        if up:  # upsample_2d: gain factor^2, pad (2, 1)
+            k = _fir(taps, 4.0, dt)
+            a, x_ = upfirdn2d_torch(a, k, up=2, pad=(2, 1)), upfirdn2d_torch(x_, k, up=2, pad=(2, 1))
+        elif down:  # downsample_2d: pad (1, 1)
+            k = _fir(taps, 1.0, dt)
+            a, x_ = upfirdn2d_torch(a, k, down=2, pad=(1, 1)), upfirdn2d_torch(x_, k, down=2, pad=(1, 1))
+        out = F.conv2d(a, P(i, "Conv_0.weight"), P(i, "Conv_0.bias"), padding=1)
+        out = out + F.linear(_silu(temb), P(i, "Dense_0.weight"), P(i, "Dense_0.bias"))[:, :, None, None]
+        out = F.conv2d(_silu(gn(i, "GroupNorm_1", out)), P(i, "Conv_1.weight"), P(i, "Conv_1.bias"), padding=1)
+        if has(i, "Conv_2.weight"):
+            x_ = F.conv2d(x_, P(i, "Conv_2.weight"), P(i, "Conv_2.bias"))
+        return (x_ + out) / rs
+
+    def attn(h):  # layerspp.py:75-91
+        i = nxt()
+        B, C, H, W = h.shape
+        g = gn(i, "GroupNorm_0", h)
+        q, k, v = nin(i, "NIN_0", g), nin(i, "NIN_1", g), nin(i, "NIN_2", g)
+        w = torch.einsum("bchw,bcij->bhwij", q, k) * (int(C) ** (-0.5))
+        w = F.softmax(w.reshape(B, H, W, H * W), dim=-1).reshape(B, H, W, H, W)
+        o = nin(i, "NIN_3", torch.einsum("bhwij,bcij->bchw", w, v))
+        return (h + o) / rs
+
+    i = nxt()
+    proj = labels.to(dt)[:, None] * P(i, "W")[None, :] * 2 * math.pi   # layerspp.py:39-41
+    temb = torch.cat([torch.sin(proj), torch.cos(proj)], dim=-1)
+    i = nxt()
+    temb = F.linear(temb, P(i, "weight"), P(i, "bias"))
+    i = nxt()
+    temb = F.linear(_silu(temb), P(i, "weight"), P(i, "bias"))
+
+    h = x if cfg["centered"] else 2 * x - 1.0
+    pyramid = h
+    i = nxt()
+    hs = [F.conv2d(h, P(i, "weight"), P(i, "bias"), padding=1)]
+    for lvl in range(nres):
+        for _ in range(nrb):
+            h = res(hs[-1], temb)
+            if h.shape[-1] in cfg["attn_resolutions"]:
+                h = attn(h)
+            hs.append(h)
+        if lvl != nres - 1:
+            h = res(hs[-1], temb, down=True)
+            i = nxt()  # conv_downsample_2d: FIR pad (2, 2), then 3x3 stride 2 (up_or_down_sampling.py:144-178)
+            f = upfirdn2d_torch(pyramid, _fir(taps, 1.0, dt), pad=(2, 2))
+            pyramid = F.conv2d(f, P(i, "Conv2d_0.weight"), stride=2) + P(i, "Conv2d_0.bias")[None, :, None, None]
+            pyramid = (pyramid + h) / rs
+            h = pyramid
+            hs.append(h)
+    h = hs[-1]
+    h = res(h, temb)
+    h = attn(h)
+    h = res(h, temb)
+    for lvl in reversed(range(nres)):
+        for _ in range(nrb + 1):
+            h = res(torch.cat([h, hs.pop()], dim=1), temb)
+        if h.shape[-1] in cfg["attn_resolutions"]:
+            h = attn(h)
+        if lvl != 0:
+            h = res(h, temb, up=True)
+    i = nxt()
+    h = _silu(F.group_norm(h, min(h.shape[1] // 4, 32), P(i, "weight"), P(i, "bias"), eps=1e-6))
+    i = nxt()
+    return F.conv2d(h, P(i, "weight"), P(i, "bias"), padding=1)

@@ -8,10 +8,17 @@ from oracle import img_oracle as IO
 from oracle import id_oracle as O
 
 
-def _setup():
+import pytest
+
+MODELS = {"ddpm": ("unet_ddpm_small", FX.DDPM_SMALL, IO.ddpm_forward),
+          "ncsnpp": ("unet_ncsnpp_small", FX.NCSNPP_SMALL, IO.ncsnpp_forward)}
+
+
+def _setup(model="ddpm"):
     from iddiff_b200 import unet_models
-    g = FX.golden("unet_ddpm_small")
-    holder = unet_models.DDPM(FX.unet_config(FX.DDPM_SMALL))
+    gold, spec, _ = MODELS[model]
+    g = FX.golden(gold)
+    holder = unet_models.get_model(model)(FX.unet_config(spec, model))
     state = FX.make_unet_state(holder, int(g["seed"]))
     wsum = sum(v.double().abs().sum().item() for v in state.values())
     assert abs(wsum - float(g["w_checksum"])) < 1e-6 * wsum, "fixture weights drifted from the ones the reference ran"
@@ -31,18 +38,29 @@ def test_holder_state_dict_layout_and_plan():
         raise AssertionError("the holder must not have a PyTorch forward path")
 
 
-def test_ddpm_forward_oracle_matches_reference():
-    g, _, state = _setup()
+def test_ncsnpp_holder_state_dict_layout():
+    g, holder, state = _setup("ncsnpp")
+    holder.load_state_dict(state, strict=True)   # the REAL reference loaded the same dict strict=True (gen_golden_unet)
+    kinds = [k for k, _, _ in holder.plan]
+    assert kinds.count("pyr_down") == 1 and kinds.count("res") == 10 and "all_modules.0.W" in state
+
+
+@pytest.mark.parametrize("model", ["ddpm", "ncsnpp"])
+def test_unet_forward_oracle_matches_reference(model):
+    g, _, state = _setup(model)
+    _, spec, fwd = MODELS[model]
     x = torch.from_numpy(g["x"])
     lab = torch.full((x.shape[0],), float(g["label"]))
     with torch.no_grad():
-        y = IO.ddpm_forward(state, FX.DDPM_SMALL, x, lab)
+        y = fwd(state, spec, x, lab)
     scale = np.abs(g["y"]).max()
     assert np.abs(y.numpy() - g["y"]).max() < 1e-5 * scale
 
 
-def test_ddpm_path_oracle_matches_reference_spectrum():
-    g, _, state = _setup()
+@pytest.mark.parametrize("model", ["ddpm", "ncsnpp"])
+def test_unet_path_oracle_matches_reference_spectrum(model):
+    g, _, state = _setup(model)
+    _, spec, fwd = MODELS[model]
     B, K, nb = int(g["B"]), int(g["K"]), int(g["nb"])
     x0 = torch.from_numpy(g["x0"])
     z = FX.seeded_noise(int(g["seed"]) + 3, x0.shape[0], nb, B, x0.shape[1:])
@@ -51,7 +69,7 @@ def test_ddpm_path_oracle_matches_reference_spectrum():
     std = float(O.ve_marginal(torch.zeros(1, 1), t, 1e-2, 4.0)[1][0])
     a = 0
     za = z[a].reshape(nb * B, *x0.shape[1:])[:K]
-    S = IO.unet_score_matrix(IO.ddpm_forward, state, FX.DDPM_SMALL, x0[a], za, 1.0, std, float(g["label"]))
+    S = IO.unet_score_matrix(fwd, state, spec, x0[a], za, 1.0, std, float(g["label"]))
     s = torch.linalg.svdvals(S).double().numpy()
     np.testing.assert_allclose(s, g["singular_values"][a], rtol=1e-3)
     assert O.id_from_spectrum(s.tolist()) == int(g["dims"][a])

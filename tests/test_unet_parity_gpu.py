@@ -15,11 +15,17 @@ from oracle import id_oracle as O  # noqa: E402
 from oracle import img_oracle as IO  # noqa: E402
 
 
-def _engine():
+MODELS = {"ddpm": ("unet_ddpm_small", FX.DDPM_SMALL, IO.ddpm_forward),
+          "ncsnpp": ("unet_ncsnpp_small", FX.NCSNPP_SMALL, IO.ncsnpp_forward)}
+BOTH = pytest.mark.parametrize("model", ["ddpm", "ncsnpp"])
+
+
+def _engine(model="ddpm"):
     from iddiff_b200 import unet_models
     from iddiff_b200.unet_engine import UNetEngine
-    g = FX.golden("unet_ddpm_small")
-    holder = unet_models.DDPM(FX.unet_config(FX.DDPM_SMALL))
+    gold, spec, _ = MODELS[model]
+    g = FX.golden(gold)
+    holder = unet_models.get_model(model)(FX.unet_config(spec, model))
     state = FX.make_unet_state(holder, int(g["seed"]))
     holder.load_state_dict(state, strict=True)
     eng = UNetEngine.from_module(holder, "cuda:0")
@@ -27,8 +33,10 @@ def _engine():
     return g, state, eng
 
 
-def test_ddpm_forward_vs_reference_golden():
-    g, state, eng = _engine()
+@BOTH
+def test_unet_forward_vs_reference_golden(model):
+    g, state, eng = _engine(model)
+    _, spec, fwd = MODELS[model]
     x = torch.from_numpy(g["x"]).cuda()
     y = eng.forward(x, float(g["label"]))           # NHWC
     got = y.permute(0, 3, 1, 2).cpu().numpy()
@@ -37,16 +45,17 @@ def test_ddpm_forward_vs_reference_golden():
     # and against the fp64 evaluation of the oracle: the engine must be at least as close to the truth as 5x the
     # fp32 reference is
     with torch.no_grad():
-        y64 = IO.ddpm_forward(state, FX.DDPM_SMALL, torch.from_numpy(g["x"]).double(),
+        y64 = fwd(state, spec, torch.from_numpy(g["x"]).double(),
                               torch.full((x.shape[0],), float(g["label"]), dtype=torch.float64)).numpy()
     ref_err = np.abs(g["y"] - y64).max()
     eng_err = np.abs(got - y64).max()
     assert eng_err < max(5 * ref_err, 2e-6 * scale), (eng_err, ref_err)
 
 
-def test_ddpm_forward_batch_sizes_and_chunking():
+@BOTH
+def test_unet_forward_batch_sizes_and_chunking(model):
     """Ragged image counts (1, 7, 130: partial 128-pixel tiles at the 8x8 level pack 2 images per tile)."""
-    g, state, eng = _engine()
+    g, state, eng = _engine(model)
     gen = torch.Generator().manual_seed(3)
     x = torch.rand(130, 3, 16, 16, generator=gen)
     full = eng.forward(x.cuda(), float(g["label"])).cpu()
@@ -55,8 +64,10 @@ def test_ddpm_forward_batch_sizes_and_chunking():
         assert torch.equal(part, full[:n])
 
 
-def test_ddpm_manifold_dimension_vs_reference_golden():
-    g, state, eng = _engine()
+@BOTH
+def test_unet_manifold_dimension_vs_reference_golden(model):
+    g, state, eng = _engine(model)
+    _, spec, fwd = MODELS[model]
     from iddiff_b200 import sde_lib
     B, K, nb = int(g["B"]), int(g["K"]), int(g["nb"])
     x0 = torch.from_numpy(g["x0"])
@@ -70,7 +81,7 @@ def test_ddpm_manifold_dimension_vs_reference_golden():
     want = g["singular_values"]
     # the reference's own rounding floor from the fp64 oracle on anchor 0
     za = z[0].reshape(K, *x0.shape[1:]).double()
-    S64 = IO.unet_score_matrix(IO.ddpm_forward, state, FX.DDPM_SMALL, x0[0].double(), za, mc, std, float(g["label"]))
+    S64 = IO.unet_score_matrix(fwd, state, spec, x0[0].double(), za, mc, std, float(g["label"]))
     s64 = torch.linalg.svdvals(S64).numpy()
     floor = np.abs(want[0] - s64).max()
     assert np.all(np.abs(sv[0] - s64) <= 1e-3 * s64 + floor), np.abs(sv[0] / s64 - 1).max()
@@ -83,13 +94,15 @@ def test_ddpm_manifold_dimension_vs_reference_golden():
         assert np.abs(head[a] - g["scores_head"][a]).max() < 2e-4 * scale
 
 
-def test_ddpm_drop_in_get_manifold_dimension(tmp_path):
+@BOTH
+def test_unet_drop_in_get_manifold_dimension(tmp_path, model):
     """The reference entry point end to end for an image model: config (model.name='ddpm') -> Lightning-style
     checkpoint -> image anchors from a loader batch -> {'singular_values': ...}, against the REAL reference's output."""
     from iddiff_b200 import dim_reduction as DR, plot_utils
     from iddiff_b200 import unet_models
-    g = FX.golden("unet_ddpm_small")
-    holder = unet_models.DDPM(FX.unet_config(FX.DDPM_SMALL))
+    gold, spec, _ = MODELS[model]
+    g = FX.golden(gold)
+    holder = unet_models.get_model(model)(FX.unet_config(spec, model))
     state = FX.make_unet_state(holder, int(g["seed"]))
     ckpt = tmp_path / "last.ckpt"
     torch.save({"state_dict": {"score_model." + k: v for k, v in state.items()}}, ckpt)
@@ -98,7 +111,7 @@ def test_ddpm_drop_in_get_manifold_dimension(tmp_path):
     n_used, svd_points = x0.shape[0], int(g["svd_points"])
     imgs = FX.smooth_images(svd_points, 3, 16, int(g["seed"]) + 2)
     assert torch.equal(imgs[:n_used], x0)
-    cfg = FX.unet_config(FX.DDPM_SMALL)
+    cfg = FX.unet_config(spec, model)
     cfg.logging = dict(log_path=str(tmp_path), log_name="run", svd_points=svd_points)
     cfg.dim_estimation = {}
     cfg.device = "cuda:0"
