@@ -60,7 +60,7 @@ def build_engine(config, score_model: Optional[torch.nn.Module] = None, device="
             if path:
                 models.load_checkpoint_into(score_model, path)
         return FcnEngine.from_module(score_model, device=device)
-    if name in ("ddpm", "ncsnpp"):
+    if name in ("ddpm", "ncsnpp", "BeatGANsUNetModel"):
         from . import models, unet_models  # noqa: F401  (registers 'ddpm')
         from .unet_engine import UNetEngine
         if score_model is None:

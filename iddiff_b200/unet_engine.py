@@ -87,25 +87,62 @@ class _PyrDown:
         self.fir = U.fir_kernel(m.fir_kernel, 1.0, dev)
 
 
-class UNetEngine:
-    """DDPM U-Net (models/ddpm.py) on the sm_100a kernels.  Build with `UNetEngine.from_module(holder, device)`."""
+class _BRes:
+    """BeatGANs ResBlock (BeatGANsblocks.py:83-255): GN32-SiLU-[avg-pool | nearest up]-conv, scale-shift conditioning
+    (apply_conditions :258-332), GN32-SiLU-conv, 1x1 skip when the channel count changes."""
 
-    EPS = 1e-6
+    def __init__(self, m, dev):
+        g = lambda t: _f32(t, dev)
+        self.in_ch, self.out_ch, self.up, self.down = m.in_ch, m.out_ch, m.up, m.down
+        self.groups0, self.groups1 = m.in_layers[0].num_groups, m.out_layers[0].num_groups
+        self.gn0 = (g(m.in_layers[0].weight), g(m.in_layers[0].bias))
+        self.gn1 = (g(m.out_layers[0].weight), g(m.out_layers[0].bias))
+        self.conv0 = U.pack_conv(g(m.in_layers[2].weight), g(m.in_layers[2].bias))
+        self.conv1 = U.pack_conv(g(m.out_layers[3].weight), g(m.out_layers[3].bias))
+        self.emb = (g(m.emb_layers[1].weight), g(m.emb_layers[1].bias))
+        sc = m.skip_connection
+        self.short = U.pack_conv(g(sc.weight), g(sc.bias)) if isinstance(sc, torch.nn.Conv2d) else None
+
+
+class _BAttn:
+    """BeatGANs AttentionBlock + QKVAttentionLegacy (BeatGANsblocks.py:399-491)."""
+
+    def __init__(self, m, dev):
+        g = lambda t: _f32(t, dev)
+        self.c, self.heads = m.channels, m.num_heads
+        self.groups = m.norm.num_groups
+        self.gn = (g(m.norm.weight), g(m.norm.bias))
+        self.qkv = U.pack_conv(g(m.qkv.weight)[:, :, 0].contiguous(), g(m.qkv.bias))
+        self.proj = U.pack_conv(g(m.proj_out.weight)[:, :, 0].contiguous(), g(m.proj_out.bias))
+
+
+class UNetEngine:
+    """The U-Net score networks (models/ddpm.py, models/ncsnpp.py, models/BeatGANsUNET.py) on the sm_100a kernels.
+    Build with `UNetEngine.from_module(holder, device)`."""
 
     def __init__(self, holder, device):
         self.dev = torch.device(device)
         self.h = holder
         g = lambda t: t.detach().to(self.dev, torch.float32).contiguous()
-        mods = holder.all_modules
-        self.fourier = getattr(holder, "embedding_type", "positional") == "fourier"
-        t0 = 1 if self.fourier else 0
-        self.fourier_w = mods[0].W.detach().float().cpu() if self.fourier else None
-        self.temb_w = [(g(mods[t0].weight), g(mods[t0].bias)), (g(mods[t0 + 1].weight), g(mods[t0 + 1].bias))]
+        self.EPS = float(holder.gn_eps)
+        self.embedding = getattr(holder, "embedding_type", "positional")
+        self.fourier = self.embedding == "fourier"
+        if self.embedding == "beatgans":
+            lin = [holder.time_embed[0], holder.time_embed[2]]
+        else:
+            t0 = 1 if self.fourier else 0
+            lin = [holder.all_modules[t0], holder.all_modules[t0 + 1]]
+        self.fourier_w = holder.all_modules[0].W.detach().float().cpu() if self.fourier else None
+        self.temb_w = [(g(l.weight), g(l.bias)) for l in lin]
         self.rescale = float(1.0 / math.sqrt(2.0)) if getattr(holder, "skip_rescale", False) else 1.0
         self.blocks: Dict[int, object] = {}
         for kind, idx, _ in holder.plan:
-            m = mods[idx] if idx >= 0 else None
-            if kind == "res":
+            m = holder.plan_module(idx) if idx >= 0 else None
+            if kind == "bres":
+                self.blocks[idx] = _BRes(m, self.dev)
+            elif kind == "battn":
+                self.blocks[idx] = _BAttn(m, self.dev)
+            elif kind == "res":
                 self.blocks[idx] = _Res(m, self.dev)
             elif kind == "attn":
                 self.blocks[idx] = _Attn(m, self.dev)
@@ -120,12 +157,12 @@ class UNetEngine:
                 self.blocks[idx] = _PyrDown(m, self.dev)
             elif kind == "gn_out":
                 self.blocks[idx] = (g(m.weight), g(m.bias), m.num_groups)
-        cin = mods[holder.plan[0][1]].weight.shape[1]
+        cin = holder.plan_module(holder.plan[0][1]).weight.shape[1]
         self.in_affine = None
         if not holder.centered:  # ddpm.py:163-168: h = 2x - 1 for data in [0, 1]
             self.in_affine = (torch.full((cin,), 2.0, device=self.dev), torch.full((cin,), -1.0, device=self.dev))
         self.cin = cin
-        self.cout = mods[holder.plan[-1][1]].weight.shape[0]
+        self.cout = holder.plan_module(holder.plan[-1][1]).weight.shape[0]
         self._label_cache: Dict[float, Dict[int, torch.Tensor]] = {}
 
     @classmethod
@@ -141,13 +178,28 @@ class UNetEngine:
         if self.fourier:  # layerspp.py:39-41, same float32 torch expression as the reference
             xp = torch.tensor([key], dtype=torch.float32)[:, None] * self.fourier_w[None, :] * 2 * math.pi
             temb = torch.cat([torch.sin(xp), torch.cos(xp)], dim=-1).to(self.dev)
+        elif self.embedding == "beatgans":  # BeatGANs_nn.py:107-125: cos first, frequencies exp(-ln(1e4) i / half)
+            half = self.h.nf // 2
+            freqs = torch.exp(-math.log(10000) * torch.arange(start=0, end=half, dtype=torch.float32) / half)
+            args = torch.tensor([key], dtype=torch.float32)[:, None] * freqs[None]
+            temb = torch.cat([torch.cos(args), torch.sin(args)], dim=-1)
+            if self.h.nf % 2:
+                temb = torch.cat([temb, torch.zeros_like(temb[:, :1])], dim=-1)
+            temb = temb.to(self.dev)
         else:
             temb = timestep_embedding(key, self.h.nf).to(self.dev)
         temb = U.dense(temb, *self.temb_w[0], act_in=0)
         temb = U.dense(temb, *self.temb_w[1], act_in=2)
         out = {}
         for idx, blk in self.blocks.items():
-            if isinstance(blk, _Res) and blk.dense is not None:
+            if isinstance(blk, _BRes):
+                # apply_conditions (BeatGANsblocks.py:258-332): GN(h) * (1 + scale) + shift with (scale, shift) =
+                # chunk(Linear(SiLU(emb))) -- constants of the label, folded into the GroupNorm affine (parameter
+                # preparation on [C]-sized vectors, done once per label like weight packing).
+                ss = U.dense(temb, *blk.emb, act_in=2).reshape(-1)
+                scale1 = 1.0 + ss[:blk.out_ch]
+                out[idx] = ((blk.gn1[0] * scale1).contiguous(), (blk.gn1[1] * scale1 + ss[blk.out_ch:]).contiguous())
+            elif isinstance(blk, _Res) and blk.dense is not None:
                 proj = U.dense(temb, *blk.dense, act_in=2)            # [1, out_ch]
                 eff = torch.empty_like(proj)
                 # idb_fused_bias_act as a plain "add the per-channel vector" (act 1 = linear, scale 1)
@@ -192,6 +244,33 @@ class UNetEngine:
         o = U.attention(qkv, 1, c, 0, c, 2 * c, c, float(int(c) ** (-0.5)))
         return U.conv(U.prep(o), blk.proj, residual=x, out_scale=blk.out_scale)
 
+    def _bres(self, blk: _BRes, affine1, x0, x1=None):
+        mode = U.PREP_UP2 if blk.up else (U.PREP_AVGPOOL2 if blk.down else U.PREP_SAME)
+        mr = U.gn_stats(x0, x1, blk.groups0, self.EPS)
+        a = U.prep(x0, x1, mode=mode, mean_rstd=mr, groups=blk.groups0, gamma=blk.gn0[0], beta=blk.gn0[1], act=1)
+        h = U.conv(a, blk.conv0)
+        mr = U.gn_stats(h, None, blk.groups1, self.EPS)
+        a = U.prep(h, mean_rstd=mr, groups=blk.groups1, gamma=affine1[0], beta=affine1[1], act=1)
+        if blk.up or blk.down:   # x_upd on the skip branch (BeatGANsblocks.py:199-204); channel count unchanged
+            assert x1 is None and blk.short is None
+            xs = U.prep(x0, mode=mode, want_operand=False, want_f32=True)[1]
+        elif blk.short is not None:
+            xs = U.conv(U.prep(x0, x1), blk.short)
+        elif x1 is not None:
+            raise _lib.IdbError("res-block with a lateral input needs a skip projection")
+        else:
+            xs = x0
+        return U.conv(a, blk.conv1, residual=xs)
+
+    def _battn(self, blk: _BAttn, x):
+        mr = U.gn_stats(x, None, blk.groups, self.EPS)
+        a = U.prep(x, mean_rstd=mr, groups=blk.groups, gamma=blk.gn[0], beta=blk.gn[1])
+        qkv = U.conv(a, blk.qkv)
+        dh = blk.c // blk.heads
+        # legacy head layout: qkv.reshape(bs * heads, 3 * ch, T) -> head h owns channels [3 ch h, 3 ch (h + 1)) = q | k | v
+        o = U.attention(qkv, blk.heads, dh, 0, dh, 2 * dh, 3 * dh, 1.0 / math.sqrt(dh))
+        return U.conv(U.prep(o), blk.proj, residual=x)
+
     def forward(self, x_nchw: torch.Tensor, label: float, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """x [B, C, H, W] fp32 (device) -> raw network output [B, H, W, Cout] fp32 NHWC (ddpm.py:149-213)."""
         if not (x_nchw.is_cuda and x_nchw.dtype == torch.float32 and x_nchw.is_contiguous() and x_nchw.dim() == 4):
@@ -217,6 +296,10 @@ class UNetEngine:
                 hs.append(h)
             elif kind == "res":
                 h = self._res(blk, biases.get(idx), h, hs.pop() if extra.get("skip") else None)
+            elif kind == "bres":
+                h = self._bres(blk, biases[idx], h, hs.pop() if extra.get("skip") else None)
+            elif kind == "battn":
+                h = self._battn(blk, h)
             elif kind == "attn":
                 h = self._attn(blk, h)
             elif kind == "down":

@@ -48,6 +48,11 @@ def _gn(ch):
 
 
 class _Holder(nn.Module):
+    gn_eps = 1e-6
+
+    def plan_module(self, idx):
+        return self.all_modules[idx]
+
     def forward(self, *a, **k):
         raise RuntimeError(f"{type(self).__name__} holds weights only; the forward pass runs in unet_engine.UNetEngine "
                            "(no PyTorch/CPU path for this network here)")
@@ -306,3 +311,134 @@ class NCSNpp(_Holder):
         add("conv_out", _conv3x3(in_ch, channels, init_scale=m.init_scale))
         self.all_modules = nn.ModuleList(mods)
         self.plan = plan
+
+
+# ------------------------------------------------------------------------------------------------
+# BeatGANs U-Net (models/BeatGANsUNET.py:18-284; blocks models/BeatGANsblocks.py: ResBlock :83-255,
+# apply_conditions :258-332, Upsample/Downsample :335-396, AttentionBlock :399-451, QKVAttentionLegacy :468-491;
+# models/BeatGANs_nn.py: GroupNorm32 :23-25, normalization :98-104, timestep_embedding :107-125, zero_module).
+# Parameter names follow the reference's nn.Sequential / ModuleList nesting (input_blocks.<k>.<j>.in_layers.0.weight ...).
+# ------------------------------------------------------------------------------------------------
+def _gn32(ch):
+    return nn.GroupNorm(min(32, ch), ch)  # GroupNorm32: default eps 1e-5
+
+
+class BeatResBlock(_Holder):
+    def __init__(self, channels, emb_channels, dropout, out_channels=None, up=False, down=False, has_lateral=False,
+                 use_zero_module=True):
+        super().__init__()
+        out_channels = out_channels or channels
+        self.in_ch, self.out_ch, self.up, self.down, self.has_lateral = channels, out_channels, up, down, has_lateral
+        self.in_layers = nn.Sequential(_gn32(channels), nn.SiLU(), nn.Conv2d(channels, out_channels, 3, padding=1))
+        self.emb_layers = nn.Sequential(nn.SiLU(), nn.Linear(emb_channels, 2 * out_channels))
+        conv = nn.Conv2d(out_channels, out_channels, 3, padding=1)
+        if use_zero_module:
+            for p in conv.parameters():
+                p.detach().zero_()
+        self.out_layers = nn.Sequential(_gn32(out_channels), nn.SiLU(), nn.Dropout(p=dropout), conv)
+        self.skip_connection = nn.Identity() if out_channels == channels else nn.Conv2d(channels, out_channels, 1)
+
+
+class BeatAttentionBlock(_Holder):
+    def __init__(self, channels, num_heads=1, num_head_channels=-1):
+        super().__init__()
+        self.channels = channels
+        self.num_heads = num_heads if num_head_channels == -1 else channels // num_head_channels
+        self.norm = _gn32(channels)
+        self.qkv = nn.Conv1d(channels, channels * 3, 1)
+        self.proj_out = nn.Conv1d(channels, channels, 1)
+        for p in self.proj_out.parameters():
+            p.detach().zero_()
+
+
+class _Seq(nn.Sequential):
+    def forward(self, *a, **k):
+        raise RuntimeError("weight holder only; the forward pass runs in unet_engine.UNetEngine")
+
+
+@register_model("BeatGANsUNetModel")
+class BeatGANsUNetModel(_Holder):
+    gn_eps = 1e-5
+
+    def __init__(self, config):
+        super().__init__()
+        c = config.model
+        if not c.resblock_updown or c.num_classes is not None or c.resnet_two_cond or c.use_new_attention_order:
+            raise NotImplementedError("BeatGANs engine: resblock_updown=True, no classes, one condition, legacy attention "
+                                      "order (style_gan_BeatGAN.py) only")
+        if c.dims != 2 or c.input_channel_mult or c.num_input_res_blocks:
+            raise NotImplementedError("BeatGANs engine: dims=2, symmetric channel_mult / num_res_blocks only")
+        self.nf = self.time_emb_channels = c.time_embed_channels or c.model_channels
+        E = c.embed_channels
+        self.centered = True          # no 2x - 1 in BeatGANsUNET.py:257
+        self.embedding_type = "beatgans"
+        self.time_embed = _Seq(nn.Linear(self.time_emb_channels, E), nn.SiLU(), nn.Linear(E, E))
+        mult = tuple(c.channel_mult)
+        heads_up = c.num_heads if c.num_heads_upsample == -1 else c.num_heads_upsample
+        mods, plan = [], []
+
+        def add(kind, mod, **extra):
+            plan.append((kind, len(mods), extra))
+            mods.append(mod)
+
+        def res(ch, out=None, **kw):
+            return BeatResBlock(ch, E, c.dropout, out_channels=out, use_zero_module=c.resnet_use_zero_module, **kw)
+
+        ch = input_ch = int(mult[0] * c.model_channels)
+        conv_in = nn.Conv2d(c.in_channels, ch, 3, padding=1)
+        self.input_blocks = nn.ModuleList([_Seq(conv_in)])
+        add("conv_in", conv_in)
+        plan.append(("push", -1, {}))
+        chans = [ch]
+        resolution = c.image_size
+        for level, m_ in enumerate(mult):
+            for _ in range(c.num_res_blocks):
+                layers = [res(ch, int(m_ * c.model_channels))]
+                add("bres", layers[0])
+                ch = int(m_ * c.model_channels)
+                if resolution in c.attention_resolutions:
+                    layers.append(BeatAttentionBlock(ch, c.num_heads, c.num_head_channels))
+                    add("battn", layers[-1])
+                self.input_blocks.append(_Seq(*layers))
+                plan.append(("push", -1, {}))
+                chans.append(ch)
+            if level != len(mult) - 1:
+                resolution //= 2
+                blk = res(ch, ch, down=True)
+                self.input_blocks.append(_Seq(blk))
+                add("bres", blk)
+                plan.append(("push", -1, {}))
+                chans.append(ch)
+        mid = [res(ch), BeatAttentionBlock(ch, c.num_heads, c.num_head_channels), res(ch)]
+        self.middle_block = _Seq(*mid)
+        add("bres", mid[0])
+        add("battn", mid[1])
+        add("bres", mid[2])
+        self.output_blocks = nn.ModuleList([])
+        for level, m_ in list(enumerate(mult))[::-1]:
+            for i in range(c.num_res_blocks + 1):
+                ich = chans.pop()
+                layers = [res(ch + ich, int(c.model_channels * m_), has_lateral=True)]
+                add("bres", layers[0], skip=True)
+                ch = int(c.model_channels * m_)
+                if resolution in c.attention_resolutions:
+                    layers.append(BeatAttentionBlock(ch, heads_up, c.num_head_channels))
+                    add("battn", layers[-1])
+                if level and i == c.num_res_blocks:
+                    resolution *= 2
+                    layers.append(res(ch, ch, up=True))
+                    add("bres", layers[-1])
+                self.output_blocks.append(_Seq(*layers))
+        assert not chans
+        conv_out = nn.Conv2d(input_ch, c.out_channels, 3, padding=1)
+        if c.resnet_use_zero_module:
+            for p in conv_out.parameters():
+                p.detach().zero_()
+        self.out = _Seq(_gn32(ch), nn.SiLU(), conv_out)
+        add("gn_out", self.out[0])
+        add("conv_out", conv_out)
+        self._plan_modules = mods   # plain list: the modules are registered under the reference's names above
+        self.plan = plan
+
+    def plan_module(self, idx):
+        return self._plan_modules[idx]

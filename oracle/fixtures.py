@@ -126,10 +126,21 @@ NCSNPP_SMALL = dict(DDPM_SMALL, nf=16, fir=True, fir_kernel=[1, 3, 3, 1], skip_r
                     embedding_type="fourier", init_scale=0.0, fourier_scale=16)
 
 
+BEATGANS_SMALL = dict(image_size=16, centered=True, input_channels=3, in_channels=3, model_channels=32, out_channels=3,
+                      num_res_blocks=1, num_input_res_blocks=None, embed_channels=8, attention_resolutions=(8,),
+                      time_embed_channels=None, dropout=0.1, channel_mult=(1, 2), input_channel_mult=None,
+                      conv_resample=True, dims=2, num_classes=None, use_checkpoint=False, num_heads=2,
+                      num_head_channels=-1, num_heads_upsample=-1, resblock_updown=True, use_new_attention_order=False,
+                      resnet_two_cond=False, resnet_cond_channels=None, resnet_use_zero_module=True,
+                      attn_checkpoint=False)
+
+
 def unet_config(spec: dict, name: str = "ddpm"):
     """A config carrying the keys models/ddpm.py:84-109 reads, for the reference and for iddiff_b200 alike."""
     from iddiff_b200.config import ConfigDict
     model = {k: v for k, v in spec.items() if k not in ("image_size", "centered")}
+    if name.startswith("BeatGANs"):
+        model["image_size"] = spec["image_size"]
     return ConfigDict(model=dict(name=name, sigma_min=1e-2, sigma_max=4.0, beta_min=0.1, beta_max=20.0,
                                  num_scales=1000, checkpoint_path=None, **model),
                       data=dict(effective_image_size=spec["image_size"], image_size=spec["image_size"],
@@ -150,8 +161,10 @@ def make_unet_state(holder, seed: int) -> Dict[str, torch.Tensor]:
         u = torch.rand(v.shape, generator=g, dtype=torch.float64) * 2 - 1
         if v.dim() >= 2:
             fan_in = v.shape[0] if k.endswith(".W") else v[0].numel()
+            if k.endswith("emb_layers.1.weight"):
+                fan_in *= 16   # BeatGANs scale-shift projection: keep (1 + scale) well away from 0
             t = u * math.sqrt(3.0 / fan_in)
-        elif "GroupNorm" in k and k.endswith("weight") or (v.dim() == 1 and _is_norm_weight(holder, k)):
+        elif v.dim() == 1 and _is_norm_weight(holder, k):
             t = 1.0 + 0.2 * u
         else:
             t = 0.1 * u

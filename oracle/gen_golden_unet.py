@@ -31,13 +31,17 @@ GOLD = GG.GOLD
 def gen_unet(name="unet_ddpm_small", spec=FX.DDPM_SMALL, seed=7, B=64, svd_points=3, model="ddpm"):
     import models.ddpm  # noqa: F401  (reference; registers 'ddpm')
     import models.ncsnpp  # noqa: F401  (reference; registers 'ncsnpp')
+    import models.BeatGANsUNET  # noqa: F401  (reference; registers 'BeatGANsUNetModel')
     from models import utils as mutils
     from iddiff_b200 import unet_models
     holder = unet_models.get_model(model)(FX.unet_config(spec, model))
-    oracle_forward = {"ddpm": IO.ddpm_forward, "ncsnpp": IO.ncsnpp_forward}[model]
+    oracle_forward = {"ddpm": IO.ddpm_forward, "ncsnpp": IO.ncsnpp_forward,
+                      "BeatGANsUNetModel": IO.beatgans_forward}[model]
     state = FX.make_unet_state(holder, seed)
     size, cin = spec["image_size"], spec["input_channels"]
     model_kw = {k: v for k, v in spec.items() if k not in ("image_size", "centered")}
+    if model.startswith("BeatGANs"):
+        model_kw["image_size"] = size
     cfg = GG.base_config("vesde", [cin, size, size], B, model, "base", svd_points, **model_kw)
     cfg.data.update(dict(centered=spec["centered"], effective_image_size=size, image_size=size, num_channels=cin))
     ref = mutils.create_model(cfg)
@@ -73,6 +77,8 @@ def gen_unet(name="unet_ddpm_small", spec=FX.DDPM_SMALL, seed=7, B=64, svd_point
 def main(what):
     if "ddpm" in what:
         gen_unet()
+    if "beatgans" in what:
+        gen_unet("unet_beatgans_small", FX.BEATGANS_SMALL, seed=13, model="BeatGANsUNetModel")
     if "ncsnpp" in what:
         gen_unet("unet_ncsnpp_small", FX.NCSNPP_SMALL, seed=11, model="ncsnpp")
 

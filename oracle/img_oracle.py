@@ -290,3 +290,88 @@ def ncsnpp_forward(state, cfg, x, labels):
     h = _silu(F.group_norm(h, min(h.shape[1] // 4, 32), P(i, "weight"), P(i, "bias"), eps=1e-6))
     i = nxt()
     return F.conv2d(h, P(i, "weight"), P(i, "bias"), padding=1)
+
+
+# ------------------------------------------------------------------------------------------------
+# BeatGANs U-Net (models/BeatGANsUNET.py:235-284), state_dict keys as in the reference module tree.
+# ------------------------------------------------------------------------------------------------
+def beatgans_forward(state, cfg, x, t):
+    import math
+    import torch
+    import torch.nn.functional as F
+    dt = x.dtype
+    P = lambda name: state[name].to(dt)
+    mult, nrb, mc = cfg["channel_mult"], cfg["num_res_blocks"], cfg["model_channels"]
+    heads = cfg["num_heads"]
+
+    def gn(prefix, h):  # GroupNorm32(min(32, C), C), eps 1e-5 (BeatGANs_nn.py:23-25, 98-104)
+        return F.group_norm(h, min(32, h.shape[1]), P(prefix + ".weight"), P(prefix + ".bias"), eps=1e-5)
+
+    def res(prefix, h, emb, lateral=None, up=False, down=False):  # BeatGANsblocks.py:185-255
+        if lateral is not None:
+            h = torch.cat([h, lateral], dim=1)
+        x_ = h
+        a = _silu(gn(prefix + ".in_layers.0", h))
+        if up:
+            a, x_ = F.interpolate(a, scale_factor=2, mode="nearest"), F.interpolate(x_, scale_factor=2, mode="nearest")
+        elif down:
+            a, x_ = F.avg_pool2d(a, 2), F.avg_pool2d(x_, 2)
+        a = F.conv2d(a, P(prefix + ".in_layers.2.weight"), P(prefix + ".in_layers.2.bias"), padding=1)
+        e = F.linear(_silu(emb), P(prefix + ".emb_layers.1.weight"), P(prefix + ".emb_layers.1.bias"))
+        scale, shift = torch.chunk(e[:, :, None, None], 2, dim=1)
+        a = gn(prefix + ".out_layers.0", a) * (1 + scale) + shift          # apply_conditions :318-323
+        a = F.conv2d(_silu(a), P(prefix + ".out_layers.3.weight"), P(prefix + ".out_layers.3.bias"), padding=1)
+        if prefix + ".skip_connection.weight" in state:
+            x_ = F.conv2d(x_, P(prefix + ".skip_connection.weight"), P(prefix + ".skip_connection.bias"))
+        return x_ + a
+
+    def attn(prefix, h):  # BeatGANsblocks.py:437-443, 475-491
+        b, c, hh, ww = h.shape
+        xf = h.reshape(b, c, -1)
+        qkv = F.conv1d(gn(prefix + ".norm", xf), P(prefix + ".qkv.weight"), P(prefix + ".qkv.bias"))
+        ch = c // heads
+        q, k, v = qkv.reshape(b * heads, ch * 3, -1).split(ch, dim=1)
+        s = 1 / math.sqrt(math.sqrt(ch))
+        w = torch.softmax(torch.einsum("bct,bcs->bts", q * s, k * s), dim=-1)
+        a = torch.einsum("bts,bcs->bct", w, v).reshape(b, -1, xf.shape[-1])
+        a = F.conv1d(a, P(prefix + ".proj_out.weight"), P(prefix + ".proj_out.bias"))
+        return (xf + a).reshape(b, c, hh, ww)
+
+    half = mc // 2   # BeatGANs_nn.py:107-125
+    freqs = torch.exp(-math.log(10000) * torch.arange(start=0, end=half, dtype=torch.float32) / half).to(dt)
+    args = t.to(dt)[:, None] * freqs[None]
+    emb = torch.cat([torch.cos(args), torch.sin(args)], dim=-1)
+    emb = F.linear(emb, P("time_embed.0.weight"), P("time_embed.0.bias"))
+    emb = F.linear(_silu(emb), P("time_embed.2.weight"), P("time_embed.2.bias"))
+
+    h = F.conv2d(x, P("input_blocks.0.0.weight"), P("input_blocks.0.0.bias"), padding=1)
+    hs, k, resolution = [h], 1, cfg["image_size"]
+    for level in range(len(mult)):
+        for _ in range(nrb):
+            h = res(f"input_blocks.{k}.0", h, emb)
+            if resolution in cfg["attention_resolutions"]:
+                h = attn(f"input_blocks.{k}.1", h)
+            hs.append(h)
+            k += 1
+        if level != len(mult) - 1:
+            resolution //= 2
+            h = res(f"input_blocks.{k}.0", h, emb, down=True)
+            hs.append(h)
+            k += 1
+    h = res("middle_block.0", h, emb)
+    h = attn("middle_block.1", h)
+    h = res("middle_block.2", h, emb)
+    k = 0
+    for level in reversed(range(len(mult))):
+        for i in range(nrb + 1):
+            h = res(f"output_blocks.{k}.0", h, emb, lateral=hs.pop())
+            j = 1
+            if resolution in cfg["attention_resolutions"]:
+                h = attn(f"output_blocks.{k}.{j}", h)
+                j += 1
+            if level and i == nrb:
+                resolution *= 2
+                h = res(f"output_blocks.{k}.{j}", h, emb, up=True)
+            k += 1
+    h = _silu(gn("out.0", h))
+    return F.conv2d(h, P("out.2.weight"), P("out.2.bias"), padding=1)

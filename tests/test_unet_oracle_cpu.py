@@ -11,7 +11,8 @@ from oracle import id_oracle as O
 import pytest
 
 MODELS = {"ddpm": ("unet_ddpm_small", FX.DDPM_SMALL, IO.ddpm_forward),
-          "ncsnpp": ("unet_ncsnpp_small", FX.NCSNPP_SMALL, IO.ncsnpp_forward)}
+          "ncsnpp": ("unet_ncsnpp_small", FX.NCSNPP_SMALL, IO.ncsnpp_forward),
+          "BeatGANsUNetModel": ("unet_beatgans_small", FX.BEATGANS_SMALL, IO.beatgans_forward)}
 
 
 def _setup(model="ddpm"):
@@ -45,7 +46,7 @@ def test_ncsnpp_holder_state_dict_layout():
     assert kinds.count("pyr_down") == 1 and kinds.count("res") == 10 and "all_modules.0.W" in state
 
 
-@pytest.mark.parametrize("model", ["ddpm", "ncsnpp"])
+@pytest.mark.parametrize("model", ["ddpm", "ncsnpp", "BeatGANsUNetModel"])
 def test_unet_forward_oracle_matches_reference(model):
     g, _, state = _setup(model)
     _, spec, fwd = MODELS[model]
@@ -57,7 +58,7 @@ def test_unet_forward_oracle_matches_reference(model):
     assert np.abs(y.numpy() - g["y"]).max() < 1e-5 * scale
 
 
-@pytest.mark.parametrize("model", ["ddpm", "ncsnpp"])
+@pytest.mark.parametrize("model", ["ddpm", "ncsnpp", "BeatGANsUNetModel"])
 def test_unet_path_oracle_matches_reference_spectrum(model):
     g, _, state = _setup(model)
     _, spec, fwd = MODELS[model]

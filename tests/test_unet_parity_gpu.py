@@ -16,8 +16,9 @@ from oracle import img_oracle as IO  # noqa: E402
 
 
 MODELS = {"ddpm": ("unet_ddpm_small", FX.DDPM_SMALL, IO.ddpm_forward),
-          "ncsnpp": ("unet_ncsnpp_small", FX.NCSNPP_SMALL, IO.ncsnpp_forward)}
-BOTH = pytest.mark.parametrize("model", ["ddpm", "ncsnpp"])
+          "ncsnpp": ("unet_ncsnpp_small", FX.NCSNPP_SMALL, IO.ncsnpp_forward),
+          "BeatGANsUNetModel": ("unet_beatgans_small", FX.BEATGANS_SMALL, IO.beatgans_forward)}
+BOTH = pytest.mark.parametrize("model", ["ddpm", "ncsnpp", "BeatGANsUNetModel"])
 
 
 def _engine(model="ddpm"):
