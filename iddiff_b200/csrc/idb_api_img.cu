@@ -143,4 +143,20 @@ int idb_attention(const float* qkv, int N, int T, int ld, int heads, int dh, int
     return api_check(idb::launch_attention(p, static_cast<cudaStream_t>(stream)), "idb_attention");
 }
 
+int idb_row_gram(const float* X, int ld, int K, int D, double scale, double* colmean, double* G, void* stream) {
+    if (!X || !colmean || !G || K <= 0 || D <= 0 || ld < D) return api_fail("idb_row_gram: bad argument");
+    return api_check(idb::launch_row_gram(X, ld, K, D, scale, colmean, G, static_cast<cudaStream_t>(stream)),
+                     "idb_row_gram");
+}
+
+size_t idb_spectrum_large_workspace_bytes(int n) { return idb::spectrum_large_workspace_bytes(n > 0 ? n : 1); }
+
+int idb_spectrum_large(double* G, int n, int n_out, float* sv, void* workspace, void* stream) {
+    if (!G || !sv || !workspace || n <= 0 || n_out <= 0 || n_out > n) return api_fail("idb_spectrum_large: bad argument");
+    if (n > 14000) return api_fail("idb_spectrum_large: n <= 14000 (two n-vectors per CTA in shared memory)");
+    return api_check(idb::launch_spectrum_large(G, n, n_out, sv, workspace, idb::api_num_sms(),
+                                                static_cast<cudaStream_t>(stream)),
+                     "idb_spectrum_large");
+}
+
 }  // extern "C"

@@ -1,0 +1,284 @@
+// Spectrum stage for IMAGE-sized score matrices (BASELINE configs 4-5: K = 4096 ... 16768 rows, D = 12288 columns,
+// so n = min(K, D) is 4096 ... 12288 and the Gram matrix no longer fits one SM):
+//
+//   row_gram_kernel        G = (s (X - mean))(s (X - mean))^T, K x K, fp64 -- the row side, used when K < D
+//                          (north_star: "S.S^T or S^T.S, whichever side is smaller")
+//   tridiag_coop_kernel    Householder tridiagonalisation of ONE n x n fp64 matrix by the whole GPU: a cooperative
+//                          (grid-synchronised) kernel, trailing block streamed from L2/HBM by every SM
+//   bisect_large_kernel    Sturm bisection, 256 eigenvalues per CTA, d / e^2 in shared memory
+//
+// Replaces torch.linalg.svd at dim_reduction.py:197-198 (LAPACK gesdd of the K x D matrix on the host: 16 s at
+// 4096 x 12288).  Roofline: memory-bound -- per eliminated column the trailing m x m block is read once
+// for the symmetric matrix-vector product and read + written once for the rank-2 update: 24 m^2 bytes, 8 n^3 in total.
+#include "idb_common.cuh"
+#include "idb_kernels.h"
+#include <cooperative_groups.h>
+#include <math.h>
+
+namespace cg = cooperative_groups;
+
+namespace idb {
+
+// ---------------------------------- row-side centred Gram -----------------------------------
+// One CTA = one 64 x 64 tile (ti <= tj) of G; contraction over the D columns in 16-wide slabs through shared memory.
+__global__ void __launch_bounds__(256) row_gram_kernel(const float* __restrict__ X, int ld, int K, int D, double scale,
+                                                       const double* __restrict__ colmean, double* __restrict__ G) {
+    __shared__ double sA[16][64 + 1];
+    __shared__ double sB[16][64 + 1];
+    const int T = (K + 63) >> 6;
+    int ti = 0, rem = blockIdx.x;
+    while (rem >= T - ti) { rem -= T - ti; ++ti; }
+    const int tj = ti + rem;
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    double acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.0;
+    for (int d0 = 0; d0 < D; d0 += 16) {
+        for (int i = threadIdx.x; i < 16 * 64; i += 256) {
+            const int r = i >> 4, dd = i & 15;  // 16 consecutive columns of one row: 64 contiguous bytes
+            const int d = d0 + dd;
+            const int ra = ti * 64 + r, rb = tj * 64 + r;
+            double va = 0.0, vb = 0.0;
+            if (d < D) {
+                const double mu = colmean[d];
+                if (ra < K) va = ((double)__ldg(X + (size_t)ra * ld + d) - mu) * scale;
+                if (rb < K) vb = ((double)__ldg(X + (size_t)rb * ld + d) - mu) * scale;
+            }
+            sA[dd][r] = va;
+            sB[dd][r] = vb;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < 16; ++kk) {
+            double av[4], bv[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) av[i] = sA[kk][ty * 4 + i];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) bv[j] = sB[kk][tx * 4 + j];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fma(av[i], bv[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int r = ti * 64 + ty * 4 + i;
+        if (r >= K) continue;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int c = tj * 64 + tx * 4 + j;
+            if (c >= K) continue;
+            G[(size_t)r * K + c] = acc[i][j];
+            if (ti != tj) G[(size_t)c * K + r] = acc[i][j];
+        }
+    }
+}
+
+// column means of X[K][D] (fp64), one thread per column, rows strided over blockIdx.y slices with atomics
+__global__ void __launch_bounds__(256) colsum_kernel(const float* __restrict__ X, int ld, int K, int D, int rows_per,
+                                                     double* __restrict__ colsum) {
+    const int c = blockIdx.x * 256 + threadIdx.x;
+    if (c >= D) return;
+    const int k0 = blockIdx.y * rows_per, k1 = min(K, k0 + rows_per);
+    double a = 0.0;
+    for (int k = k0; k < k1; ++k) a += (double)__ldg(X + (size_t)k * ld + c);
+    atomicAdd(colsum + c, a);
+}
+__global__ void scale_vec_kernel(double* v, int n, double s) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) v[i] *= s;
+}
+
+cudaError_t launch_row_gram(const float* X, int ld, int K, int D, double scale, double* colmean, double* G,
+                            cudaStream_t stream) {
+    if (K <= 0 || D <= 0) return cudaSuccess;
+    cudaError_t e = cudaMemsetAsync(colmean, 0, (size_t)D * sizeof(double), stream);
+    if (e != cudaSuccess) return e;
+    const int slices = K >= 2048 ? 16 : 1;
+    const int rows_per = (K + slices - 1) / slices;
+    colsum_kernel<<<dim3((D + 255) / 256, slices), 256, 0, stream>>>(X, ld, K, D, rows_per, colmean);
+    scale_vec_kernel<<<(D + 255) / 256, 256, 0, stream>>>(colmean, D, 1.0 / (double)K);
+    const int T = (K + 63) / 64;
+    row_gram_kernel<<<T * (T + 1) / 2, 256, 0, stream>>>(X, ld, K, D, scale, colmean, G);
+    return cudaGetLastError();
+}
+
+// ---------------------------------- cooperative tridiagonalisation --------------------------
+constexpr int TC_THREADS = 512;
+constexpr int TC_WARPS = TC_THREADS / 32;
+
+__device__ __forceinline__ double tc_warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double tc_block_sum(double v, double* red) {
+    v = tc_warp_sum(v);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    double t = 0.0;
+#pragma unroll
+    for (int w = 0; w < TC_WARPS; ++w) t += red[w];
+    return t;
+}
+
+// A: full symmetric n x n, row-major, overwritten.  d[n], e[n] out (e[n-1] = 0).  p: n doubles of scratch.
+// LAPACK dsytd2 / dlarfg arithmetic: H = I - tau v v^T, p = tau A v, w = p - (tau/2)(p.v) v, A <- A - v w^T - w v^T.
+__global__ void __launch_bounds__(TC_THREADS, 1) tridiag_coop_kernel(double* __restrict__ A, int n,
+                                                                     double* __restrict__ d, double* __restrict__ e,
+                                                                     double* __restrict__ p) {
+    cg::grid_group grid = cg::this_grid();
+    extern __shared__ __align__(16) double tc_smem[];
+    double* v = tc_smem;        // [n] Householder vector, indexed by absolute row (valid for rows > k)
+    double* w = tc_smem + n;    // [n]
+    __shared__ double red[TC_WARPS];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int gw = blockIdx.x * TC_WARPS + warp, n_gw = gridDim.x * TC_WARPS;
+
+    for (int k = 0; k + 2 < n; ++k) {
+        // (a) every CTA builds the reflector of column k from row k (symmetric copy, contiguous)
+        const double* rowk = A + (size_t)k * n;
+        double ss = 0.0;
+        for (int j = k + 2 + tid; j < n; j += TC_THREADS) {
+            const double x = rowk[j];
+            v[j] = x;
+            ss = fma(x, x, ss);
+        }
+        ss = tc_block_sum(ss, red);           // ||x[1:]||^2
+        const double alpha = rowk[k + 1];
+        double tau = 0.0, beta = alpha;
+        if (ss > 0.0) {
+            const double nrm = sqrt(fma(alpha, alpha, ss));
+            beta = alpha >= 0.0 ? -nrm : nrm;
+            tau = (beta - alpha) / beta;
+            const double inv = 1.0 / (alpha - beta);
+            for (int j = k + 2 + tid; j < n; j += TC_THREADS) v[j] *= inv;
+        }
+        if (tid == 0) v[k + 1] = 1.0;
+        if (blockIdx.x == 0 && tid == 0) {
+            d[k] = rowk[k];
+            e[k] = beta;
+        }
+        __syncthreads();
+        if (tau != 0.0) {   // uniform over the grid (same data, same arithmetic)
+            // (b) p = tau * A[k+1:, k+1:] v : one warp per row, rows dealt cyclically over the grid's warps
+            for (int i = k + 1 + gw; i < n; i += n_gw) {
+                const double* row = A + (size_t)i * n;
+                double s = 0.0;
+                for (int j = k + 1 + lane; j < n; j += 32) s = fma(row[j], v[j], s);
+                s = tc_warp_sum(s);
+                if (lane == 0) p[i] = tau * s;
+            }
+            grid.sync();
+            // (c) w = p - (tau/2)(p.v) v  (redundantly per CTA), then the rank-2 update of the CTA's rows
+            double pv = 0.0;
+            for (int j = k + 1 + tid; j < n; j += TC_THREADS) {
+                const double pj = p[j];
+                w[j] = pj;
+                pv = fma(pj, v[j], pv);
+            }
+            pv = tc_block_sum(pv, red);
+            const double kk = -0.5 * tau * pv;
+            for (int j = k + 1 + tid; j < n; j += TC_THREADS) w[j] = fma(kk, v[j], w[j]);
+            __syncthreads();
+            for (int i = k + 1 + gw; i < n; i += n_gw) {
+                double* row = A + (size_t)i * n;
+                const double vi = v[i], wi = w[i];
+                for (int j = k + 1 + lane; j < n; j += 32) row[j] = row[j] - vi * w[j] - wi * v[j];
+            }
+            grid.sync();
+        }
+    }
+    if (blockIdx.x == 0 && tid == 0) {
+        if (n >= 2) {
+            d[n - 2] = A[(size_t)(n - 2) * n + (n - 2)];
+            e[n - 2] = A[(size_t)(n - 1) * n + (n - 2)];
+        }
+        d[n - 1] = A[(size_t)(n - 1) * n + (n - 1)];
+        e[n - 1] = 0.0;
+    }
+}
+
+// ---------------------------------- bisection over many CTAs --------------------------------
+__global__ void __launch_bounds__(256) bisect_large_kernel(const double* __restrict__ dg, const double* __restrict__ eg,
+                                                           int n, int n_out, float* __restrict__ sv) {
+    extern __shared__ __align__(16) double bl_smem[];
+    double* d = bl_smem;
+    double* e2 = bl_smem + n;
+    __shared__ double s_lo[8], s_hi[8], s_em[8];
+    double lo = 1e300, hi = -1e300, em = 0.0;
+    for (int i = threadIdx.x; i < n; i += 256) {
+        const double di = dg[i], ei = eg[i];
+        d[i] = di;
+        e2[i] = ei * ei;
+        const double el = i > 0 ? fabs(eg[i - 1]) : 0.0, er = i + 1 < n ? fabs(ei) : 0.0;
+        lo = fmin(lo, di - el - er);
+        hi = fmax(hi, di + el + er);
+        em = fmax(em, ei * ei);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        lo = fmin(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+        hi = fmax(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+        em = fmax(em, __shfl_xor_sync(0xffffffffu, em, o));
+    }
+    if ((threadIdx.x & 31) == 0) { s_lo[threadIdx.x >> 5] = lo; s_hi[threadIdx.x >> 5] = hi; s_em[threadIdx.x >> 5] = em; }
+    __syncthreads();
+    for (int q = 0; q < 8; ++q) { lo = fmin(lo, s_lo[q]); hi = fmax(hi, s_hi[q]); em = fmax(em, s_em[q]); }
+    const double span = fmax(fabs(lo), fabs(hi));
+    lo = lo - 1e-14 * span - 1e-300;
+    hi = hi + 1e-14 * span + 1e-300;
+    const double pivmin = 2.2250738585072014e-308 * fmax(1.0, em);
+    const int k = blockIdx.x * 256 + threadIdx.x;   // k-th smallest eigenvalue
+    if (k >= n || n - 1 - k >= n_out) return;
+    const double atol = 1e-17 * fmax(fabs(lo), fabs(hi));
+    for (int it = 0; it < 200; ++it) {
+        const double mid = 0.5 * (lo + hi);
+        if (hi - lo <= fmax(atol, 4.4e-16 * fmax(fabs(lo), fabs(hi))) || mid <= lo || mid >= hi) break;
+        double q = d[0] - mid;
+        int cnt = q < 0.0;
+        for (int i = 1; i < n; ++i) {
+            if (fabs(q) < pivmin) q = -pivmin;
+            q = d[i] - mid - e2[i - 1] / q;
+            cnt += q < 0.0;
+        }
+        if (cnt > k) hi = mid; else lo = mid;
+    }
+    sv[n - 1 - k] = (float)sqrt(fmax(0.5 * (lo + hi), 0.0));
+}
+
+size_t spectrum_large_workspace_bytes(int n) { return (size_t)3 * n * sizeof(double) + 256; }
+
+cudaError_t launch_spectrum_large(double* G, int n, int n_out, float* sv, void* workspace, int num_sms,
+                                  cudaStream_t stream) {
+    if (n <= 0) return cudaSuccess;
+    double* d = reinterpret_cast<double*>(workspace);
+    double* e = d + n;
+    double* p = e + n;
+    const size_t smem = (size_t)2 * n * sizeof(double);
+    if (smem > 220 * 1024) return cudaErrorInvalidValue;
+    cudaError_t err = cudaFuncSetAttribute(tridiag_coop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (err != cudaSuccess) return err;
+    int per_sm = 0;
+    err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tridiag_coop_kernel, TC_THREADS, smem);
+    if (err != cudaSuccess) return err;
+    if (per_sm < 1) return cudaErrorInvalidValue;
+    int grid = num_sms;   // one CTA per SM
+    const int max_useful = (n + TC_WARPS - 1) / TC_WARPS;
+    if (grid > max_useful) grid = max_useful;
+    void* args[] = {&G, &n, &d, &e, &p};
+    err = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(tridiag_coop_kernel), dim3(grid), dim3(TC_THREADS), args,
+                                      smem, stream);
+    if (err != cudaSuccess) return err;
+    err = cudaFuncSetAttribute(bisect_large_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (err != cudaSuccess) return err;
+    bisect_large_kernel<<<(n + 255) / 256, 256, smem, stream>>>(d, e, n, n_out, sv);
+    return cudaGetLastError();
+}
+
+}  // namespace idb

@@ -135,6 +135,12 @@ struct AttnParams {
 };
 cudaError_t launch_attention(const AttnParams& p, cudaStream_t stream);
 
+cudaError_t launch_row_gram(const float* X, int ld, int K, int D, double scale, double* colmean, double* G,
+                            cudaStream_t stream);
+size_t spectrum_large_workspace_bytes(int n);
+cudaError_t launch_spectrum_large(double* G, int n, int n_out, float* sv, void* workspace, int num_sms,
+                                  cudaStream_t stream);
+
 // helpers of the C-ABI translation units (thread-local error string lives in idb_api.cu)
 int api_fail(const char* what);
 int api_check(cudaError_t e, const char* where);

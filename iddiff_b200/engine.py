@@ -59,6 +59,7 @@ class SpectrumResult:
     scores: Optional[torch.Tensor] = None  # [A, K, D] fp32 raw scores when requested
 
 
+LARGE_N = 1024  # above this, one Gram matrix is solved by the whole GPU (idb_spectrum_large)
 SPECTRUM_METHOD = _lib.SPECTRUM_TRIDIAG  # default solver; _lib.SPECTRUM_JACOBI selects the one-sided Jacobi
 
 
@@ -70,22 +71,37 @@ def spectrum_from_rows(X: torch.Tensor, K: int, D: int, scale: float, rows_per_a
     A, R, ld = X.shape
     if rows_per_anchor is not None and rows_per_anchor != R:
         raise _lib.IdbError("rows_per_anchor mismatch")
-    if K < D:
-        raise NotImplementedError("K < D (row-side Gram) is not built yet; see DESIGN.md scope")
     dev = X.device
-    colmean = torch.empty(A, D, dtype=torch.float64, device=dev)
-    G = torch.empty(A, D, D, dtype=torch.float64, device=dev)
     st = stream_ptr()
-    with _stage("center_gram", A * (K * D * 4.0 + D * D * 8.0)):
-        call("idb_center_gram", ptr(X), R * ld, ld, A, K, D, float(scale), ptr(colmean), ptr(G), st)
-    n = D
-    n_out = min(K, D)
-    ws_bytes = _lib.load().idb_spectrum_workspace_bytes(A, n)
-    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+    n = min(K, D)          # the smaller side of the centred score matrix carries all its singular values
+    n_out = n
     sv = torch.empty(A, n_out, dtype=torch.float32, device=dev)
-    sweeps = torch.empty(A, dtype=torch.int32, device=dev)
-    with _stage("spectrum", A * (n * n * 8.0 + n_out * 4.0)):
-        call("idb_spectrum", ptr(G), A, n, n_out, SPECTRUM_METHOD if method is None else method, ptr(sv),
+    sweeps = torch.zeros(A, dtype=torch.int32, device=dev)
+    colmean = torch.empty(A, D, dtype=torch.float64, device=dev)
+    large = n > LARGE_N
+    G = torch.empty(1 if large else A, n, n, dtype=torch.float64, device=dev)
+    if large:
+        # image-sized matrices: one anchor at a time, the whole GPU on each (cooperative tridiagonalisation)
+        ws = torch.empty(_lib.load().idb_spectrum_large_workspace_bytes(n), dtype=torch.uint8, device=dev)
+        for a in range(A):
+            with _stage("center_gram", K * D * 4.0 + n * n * 8.0):
+                if K < D:
+                    call("idb_row_gram", ptr(X[a]), ld, K, D, float(scale), ptr(colmean[a]), ptr(G), st)
+                else:
+                    call("idb_center_gram", ptr(X[a]), R * ld, ld, 1, K, D, float(scale), ptr(colmean[a]), ptr(G), st)
+            with _stage("spectrum", n * n * 8.0 + n_out * 4.0):
+                call("idb_spectrum_large", ptr(G), n, n_out, ptr(sv[a]), ptr(ws), st)
+    else:
+        with _stage("center_gram", A * (K * D * 4.0 + n * n * 8.0)):
+            if K < D:
+                for a in range(A):
+                    call("idb_row_gram", ptr(X[a]), ld, K, D, float(scale), ptr(colmean[a]), ptr(G[a]), st)
+            else:
+                call("idb_center_gram", ptr(X), R * ld, ld, A, K, D, float(scale), ptr(colmean), ptr(G), st)
+        ws_bytes = _lib.load().idb_spectrum_workspace_bytes(A, n)
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        with _stage("spectrum", A * (n * n * 8.0 + n_out * 4.0)):
+            call("idb_spectrum", ptr(G), A, n, n_out, SPECTRUM_METHOD if method is None else method, ptr(sv),
                  ptr(sweeps), ptr(ws), st)
     dims = torch.empty(A, dtype=torch.int32, device=dev)
     if n_out >= 3:

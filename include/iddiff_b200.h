@@ -188,6 +188,19 @@ int idb_conv2d(const void* a_hi, const void* a_lo, int planes, int N, int Ha, in
 int idb_attention(const float* qkv, int N, int T, int ld, int heads, int dh, int q0, int k0, int v0, int head_stride,
                   float scale, float* out, int ld_out, void* stream);
 
+/* Row-side centred Gram for one anchor when K < D (image shapes: K = 4096 perturbations, D = 12288 pixels):
+ * colmean[D] (fp64) and G[K][K] = (scale (X - mean)) (scale (X - mean))^T in fp64; its eigenvalues are the squared
+ * singular values of the centred K x D score matrix, the same ones the D-side Gram of idb_center_gram has
+ * (dim_reduction.py:190-199).  X [K][ld] fp32. */
+int idb_row_gram(const float* X, int ld, int K, int D, double scale, double* colmean, double* G, void* stream);
+
+/* Singular values from ONE large Gram matrix (n up to 14000) by the whole GPU: cooperative Householder
+ * tridiagonalisation (fp64, G is overwritten) + Sturm bisection.  sv [n_out] fp32 descending.
+ * workspace: idb_spectrum_large_workspace_bytes(n).  Replaces torch.linalg.svd at dim_reduction.py:197-198 for
+ * image-sized score matrices. */
+size_t idb_spectrum_large_workspace_bytes(int n);
+int idb_spectrum_large(double* G, int n, int n_out, float* sv, void* workspace, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

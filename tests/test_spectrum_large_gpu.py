@@ -1,0 +1,60 @@
+"""GPU: the image-sized spectrum stage -- row-side Gram (K < D) and the cooperative whole-GPU eigensolver (n > 1024) --
+against torch.linalg.svdvals in fp64 of the same centred matrix (the reference's dim_reduction.py:190-199 in exact
+arithmetic).  Tolerance 1e-3 relative per value as in BASELINE.json; measured errors are ~1e-6.  When K <= D the
+centred matrix has rank K-1: its last singular value is structurally zero (the reference returns rounding noise
+there), so it is compared absolutely."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _matrix(K, D, rank, seed, decay=1e-3):
+    g = torch.Generator().manual_seed(seed)
+    r = min(rank, K, D)
+    U = torch.randn(K, r, generator=g, dtype=torch.float64)
+    V = torch.randn(r, D, generator=g, dtype=torch.float64)
+    s = torch.logspace(0, np.log10(decay), r, dtype=torch.float64)
+    X = (U * s) @ V / np.sqrt(K) + 3.0 + 1e-4 * torch.randn(K, D, generator=g, dtype=torch.float64)
+    return X.float()
+
+
+@pytest.mark.parametrize("K,D,rank", [(96, 300, 40), (257, 640, 300), (700, 701, 50),      # row side, one-CTA solver
+                                      (2000, 1500, 200), (1300, 3000, 2000), (1100, 1100, 64)])  # whole-GPU solver
+def test_spectrum_from_rows_all_shapes(K, D, rank):
+    from iddiff_b200 import engine as E
+    from oracle import id_oracle as O
+    A = 2
+    X = torch.stack([_matrix(K, D, rank, 10 + a) for a in range(A)])
+    res = E.spectrum_from_rows(X.cuda(), K, D, -1.0 / 0.01)
+    torch.cuda.synchronize()
+    n = min(K, D)
+    assert tuple(res.singular_values.shape) == (A, n)
+    for a in range(A):
+        Xc = X[a].double()
+        Xc = (Xc - Xc.mean(0, keepdim=True)) * (-1.0 / 0.01)
+        want = torch.linalg.svdvals(Xc).numpy()
+        got = res.singular_values[a].cpu().numpy().astype(np.float64)
+        m = n - 1 if K <= D else n
+        # Gram-side floor: eigenvalues of G carry eps64 * s_max^2, i.e. sqrt(eps64) * s_max ~ 1e-8 s_max on a singular value
+        np.testing.assert_allclose(got[:m], want[:m], rtol=1e-3, atol=1e-7 * want[0])
+        if m < n:
+            assert abs(got[-1]) < 1e-4 * want[0]
+        assert np.all(np.diff(got) <= 0)
+        if K > D:
+            assert int(res.dims[a]) == O.id_from_spectrum(got.tolist())
+
+
+def test_spectrum_large_matches_small_solver_on_same_gram():
+    """n = 900 through both solvers (the one-CTA kernel and the cooperative one) -- same Gram matrix, same spectrum."""
+    from iddiff_b200 import engine as E
+    X = _matrix(1200, 900, 300, 3)[None].cuda()
+    small = E.spectrum_from_rows(X, 1200, 900, 1.0).singular_values.cpu().numpy()
+    old = E.LARGE_N
+    try:
+        E.LARGE_N = 256
+        large = E.spectrum_from_rows(X, 1200, 900, 1.0).singular_values.cpu().numpy()
+    finally:
+        E.LARGE_N = old
+    np.testing.assert_allclose(large, small, rtol=2e-5, atol=1e-6 * small[0, 0])
