@@ -84,10 +84,61 @@ __global__ void __launch_bounds__(UF_TX* UF_TY) upfirdn2d_kernel(const UpFirDnPa
     }
 }
 
+// Channel-minor fast path (minor % 4 == 0, the NHWC activations of the U-Net engine): one thread = one output pixel x
+// 4 channels; taps are gathered straight from global memory as float4 (neighbouring outputs share them through L1/L2),
+// consecutive threads walk the channel axis so every load and store is a coalesced 16-byte access.  Same (ky, kx)
+// ascending fp32 accumulation order as the tiled kernel above.
+__global__ void __launch_bounds__(256) upfirdn2d_nhwc_kernel(const UpFirDnParams p) {
+    __shared__ float s_k[1024];
+    for (int i = threadIdx.x; i < p.kh * p.kw; i += 256) {
+        const int ky = i / p.kw, kx = i % p.kw;
+        s_k[i] = p.kernel[(p.kh - 1 - ky) * p.kw + (p.kw - 1 - kx)];
+    }
+    __syncthreads();
+    const unsigned c4n = (unsigned)p.minor >> 2;
+    const unsigned total = (unsigned)p.major * p.out_h * p.out_w * c4n;
+    for (unsigned i = blockIdx.x * 256u + threadIdx.x; i < total; i += gridDim.x * 256u) {
+        const unsigned c4 = i % c4n;
+        unsigned r = i / c4n;
+        const int ox = (int)(r % (unsigned)p.out_w); r /= (unsigned)p.out_w;
+        const int oy = (int)(r % (unsigned)p.out_h);
+        const unsigned m = r / (unsigned)p.out_h;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int ky = 0; ky < p.kh; ++ky) {
+            const int sy = oy * p.down_y + ky - p.pad_y0;
+            if (sy < 0 || sy % p.up_y) continue;
+            const int iy = sy / p.up_y;
+            if (iy >= p.in_h) continue;
+            for (int kx = 0; kx < p.kw; ++kx) {
+                const int sx = ox * p.down_x + kx - p.pad_x0;
+                if (sx < 0 || sx % p.up_x) continue;
+                const int ix = sx / p.up_x;
+                if (ix >= p.in_w) continue;
+                const float4 v = __ldg(reinterpret_cast<const float4*>(
+                    p.in + (((size_t)m * p.in_h + iy) * p.in_w + ix) * p.minor) + c4);
+                const float k = s_k[ky * p.kw + kx];
+                acc.x = fmaf(v.x, k, acc.x); acc.y = fmaf(v.y, k, acc.y);
+                acc.z = fmaf(v.z, k, acc.z); acc.w = fmaf(v.w, k, acc.w);
+            }
+        }
+        reinterpret_cast<float4*>(p.out + (((size_t)m * p.out_h + oy) * p.out_w + ox) * p.minor)[c4] = acc;
+    }
+}
+
 cudaError_t launch_upfirdn2d(UpFirDnParams p, int num_sms, cudaStream_t stream) {
     p.out_h = (p.in_h * p.up_y + p.pad_y0 + p.pad_y1 - p.kh) / p.down_y + 1;
     p.out_w = (p.in_w * p.up_x + p.pad_x0 + p.pad_x1 - p.kw) / p.down_x + 1;
     if (p.out_h <= 0 || p.out_w <= 0 || p.major <= 0) return cudaSuccess;
+    {
+        const long long total4 = (long long)p.major * p.out_h * p.out_w * (p.minor >> 2);
+        const bool al = ((reinterpret_cast<uintptr_t>(p.in) | reinterpret_cast<uintptr_t>(p.out)) & 15) == 0;
+        if (p.minor % 4 == 0 && al && total4 < (1ll << 32)) {
+            long long grid = (total4 + 255) / 256;
+            if (grid > (long long)num_sms * 32) grid = (long long)num_sms * 32;
+            upfirdn2d_nhwc_kernel<<<(unsigned)grid, 256, 0, stream>>>(p);
+            return cudaGetLastError();
+        }
+    }
     const int patch_h = ((UF_TY - 1) * p.down_y + p.kh - 1) / p.up_y + 2;
     const int patch_w = ((UF_TX - 1) * p.down_x + p.kw - 1) / p.up_x + 2;
     const size_t budget = 96 * 1024;

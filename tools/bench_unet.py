@@ -1,56 +1,106 @@
 #!/usr/bin/env python
-"""Score-evals/s of the full-size DDPM U-Net (style_gan_base.py: nf=128, ch_mult (1,2,2,3,3), 4 res-blocks, attention at
-16x16, 64x64x3, 116 M parameters, 79.7 GFLOP/image by SURVEY 8a a10) on one B200, with a per-stage breakdown.
-Development tool (the headline bench is bench.py); prints one JSON line."""
+"""Score-evals/s and ID-estimates/s of the full-size image score networks on one B200 (BASELINE configs 4-5):
+  ddpm     style_gan_base.py (model.name='ddpm'): nf=128, ch_mult (1,2,2,3,3), 4 res-blocks, attn@16, 116.1 M params, 79.7 GFLOP/img
+  ncsnpp   same with model.name='ncsnpp' (BASELINE config 4): 126.3 M params, 88.6 GFLOP/img
+  beatgans style_gan_64d_BeatGAN.py (BASELINE config 5): 87.5 M params, 37.4 GFLOP/img
+(FLOPs per image: SURVEY 8a, FlopCounterMode of the reference.)  Random-init weights with the zero-initialised
+convolutions re-randomised (appendix A.11); synthetic 64x64x3 images.  Development / profiling tool -- the headline
+bench is bench.py.  Prints one JSON line.
+
+  python tools/bench_unet.py --model ncsnpp --batch 128               # forward only
+  python tools/bench_unet.py --model ncsnpp --anchors 1 --K 4096      # whole path: perturb -> net -> Gram -> spectrum -> ID
+"""
 import argparse
 import json
 import os
 import sys
-import time
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import torch  # noqa: E402
 
-FULL = dict(nf=128, ch_mult=(1, 2, 2, 3, 3), num_res_blocks=4, attn_resolutions=(16,), image_size=64,
+DDPM = dict(nf=128, ch_mult=(1, 2, 2, 3, 3), num_res_blocks=4, attn_resolutions=(16,), image_size=64,
             resamp_with_conv=True, centered=False, input_channels=3, output_channels=3, dropout=0.0, conditional=True,
             nonlinearity="swish")
-GFLOP_PER_IMAGE = 79.7
+NCSNPP = dict(DDPM, fir=True, fir_kernel=[1, 3, 3, 1], skip_rescale=True, resblock_type="biggan", progressive="none",
+              progressive_input="residual", progressive_combine="sum", embedding_type="fourier", init_scale=0.0,
+              fourier_scale=16)
+BEAT = dict(image_size=64, centered=True, input_channels=3, in_channels=3, model_channels=128, out_channels=3,
+            num_res_blocks=2, num_input_res_blocks=None, embed_channels=64, attention_resolutions=(16,),
+            time_embed_channels=None, dropout=0.3, channel_mult=(1, 1, 2, 3, 4), input_channel_mult=None,
+            conv_resample=True, dims=2, num_classes=None, use_checkpoint=False, num_heads=1, num_head_channels=-1,
+            num_heads_upsample=-1, resblock_updown=True, use_new_attention_order=False, resnet_two_cond=False,
+            resnet_cond_channels=None, resnet_use_zero_module=True, attn_checkpoint=False)
+MODELS = {"ddpm": ("ddpm", DDPM, 79.7), "ncsnpp": ("ncsnpp", NCSNPP, 88.6), "beatgans": ("BeatGANsUNetModel", BEAT, 37.4)}
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--batch", type=int, default=128)
-    ap.add_argument("--steps", type=int, default=3)
-    ap.add_argument("--warmup", type=int, default=2)
-    args = ap.parse_args()
+def build(model):
     from oracle import fixtures as FX
-    from iddiff_b200 import unet_models, _lib
+    from iddiff_b200 import unet_models
     from iddiff_b200.unet_engine import UNetEngine
-    holder = unet_models.DDPM(FX.unet_config(FULL))
+    name, spec, gflop = MODELS[model]
+    torch.manual_seed(0)
+    holder = unet_models.get_model(name)(FX.unet_config(spec, name))
     with torch.no_grad():  # re-randomise the zero-initialised convolutions (appendix A.11)
         for k, p in holder.named_parameters():
             if p.dim() >= 2 and float(p.abs().max()) < 1e-3:
                 unet_models.fan_avg_uniform_(p, 1.0)
-    n_params = sum(p.numel() for p in holder.parameters())
     eng = UNetEngine.from_module(holder, "cuda:0")
-    x = torch.rand(args.batch, 3, 64, 64, device="cuda")
-    for _ in range(args.warmup):
-        eng.forward(x, 0.00999)
-    torch.cuda.synchronize()
-    l0 = _lib.launch_count
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record()
-    for _ in range(args.steps):
-        y = eng.forward(x, 0.00999)
-    ev1.record()
-    torch.cuda.synchronize()
-    ms = ev0.elapsed_time(ev1) / args.steps
-    print(json.dumps({"model": "ddpm full (style_gan_base)", "params_M": n_params / 1e6, "batch": args.batch,
-                      "ms_per_forward": ms, "images_per_s": args.batch / ms * 1e3,
-                      "tflops_algorithmic": args.batch * GFLOP_PER_IMAGE / ms, "launches_per_forward":
-                      (_lib.launch_count - l0) / args.steps, "finite": bool(torch.isfinite(y).all()),
-                      "out_absmax": float(y.abs().max())}))
+    eng.image_shape = (3, 64, 64)
+    return eng, sum(p.numel() for p in holder.parameters()), gflop
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--model", default="ddpm", choices=list(MODELS))
+    ap.add_argument("--batch", type=int, default=128)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=2)
+    ap.add_argument("--anchors", type=int, default=0, help="> 0: time the whole manifold_dimension path")
+    ap.add_argument("--K", type=int, default=4096)
+    args = ap.parse_args()
+    from iddiff_b200 import _lib, engine as E
+    eng, n_params, gflop = build(args.model)
+    out = {"model": args.model, "params_M": n_params / 1e6, "gflop_per_image": gflop}
+    if args.anchors == 0:
+        x = torch.rand(args.batch, 3, 64, 64, device="cuda")
+        for _ in range(args.warmup):
+            eng.forward(x, 0.00999)
+        torch.cuda.synchronize()
+        l0 = _lib.launch_count
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        for _ in range(args.steps):
+            y = eng.forward(x, 0.00999)
+        ev1.record()
+        torch.cuda.synchronize()
+        ms = ev0.elapsed_time(ev1) / args.steps
+        out.update({"batch": args.batch, "ms_per_forward": ms, "score_evals_per_s": args.batch / ms * 1e3,
+                    "tflops_algorithmic": args.batch * gflop / ms, "launches_per_forward":
+                    (_lib.launch_count - l0) / args.steps, "finite": bool(torch.isfinite(y).all())})
+    else:
+        from oracle import fixtures as FX
+        from iddiff_b200 import sde_lib
+        sde = sde_lib.VESDE(sigma_min=0.009, sigma_max=50.0, N=1000)   # style_gan_base.py:100-101
+        mc, std = sde.coefficients(1e-5)
+        x0 = FX.smooth_images(args.anchors, 3, 64, 5).reshape(args.anchors, -1).cuda()
+        eng.estimate(x0[:1], min(args.K, 256), mc, std, 0.00999, seed=0, image_chunk=args.batch)   # warm-up
+        torch.cuda.synchronize()
+        E.EVENT_LOG = {}
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        r = eng.estimate(x0, args.K, mc, std, 0.00999, seed=1, image_chunk=args.batch)
+        ev1.record()
+        torch.cuda.synchronize()
+        ms = ev0.elapsed_time(ev1)
+        stages = {k: sum(a.elapsed_time(b) for a, b, _ in v) for k, v in E.EVENT_LOG.items()}
+        E.EVENT_LOG = None
+        out.update({"anchors": args.anchors, "K": args.K, "D": 12288, "n": min(args.K, 12288), "ms_total": ms,
+                    "id_estimates_per_s": args.anchors / ms * 1e3, "score_evals_per_s": args.anchors * args.K / ms * 1e3,
+                    "score_net_tflops_algorithmic": args.anchors * args.K * gflop / stages["score_net"],
+                    "stages_ms": stages, "dims": r.dims.cpu().tolist(),
+                    "sv_head": r.singular_values[0, :3].cpu().tolist(), "sv_tail": r.singular_values[0, -3:].cpu().tolist()})
+    print(json.dumps(out))
 
 
 if __name__ == "__main__":
