@@ -95,3 +95,12 @@ class TensorDataModule:
     def train_dataloader(self):
         B = self.config.training.batch_size
         return [self.data[i:i + B] for i in range(0, len(self.data), B)]
+
+    def val_dataloader(self):
+        """(batch, labels) pairs when config.data.return_labels is set (dim_reduction.py:19-22 of the reference reads
+        the VALIDATION loader with labels for the conditional variant); labels come from config.data.labels."""
+        B = getattr(getattr(self.config, "validation", None), "batch_size", None) or self.config.training.batch_size
+        if not getattr(self.config.data, "return_labels", False):
+            return [self.data[i:i + B] for i in range(0, len(self.data), B)]
+        labels = torch.as_tensor(self.config.data.labels)
+        return [(self.data[i:i + B], labels[i:i + B]) for i in range(0, len(self.data), B)]

@@ -68,6 +68,11 @@ def build_engine(config, score_model: Optional[torch.nn.Module] = None, device="
             path = lookup(config, "model.checkpoint_path")
             if path:
                 models.load_checkpoint_into(score_model, path)
+        elif not hasattr(score_model, "plan"):
+            # a live reference module (training callback, callbacks.py:403-432): same state_dict layout -> our holder
+            holder = models.create_model(config)
+            holder.load_state_dict(score_model.state_dict(), strict=True)
+            score_model = holder
         eng = UNetEngine.from_module(score_model, device=device)
         eng.image_shape = tuple(config.data.shape)
         return eng
@@ -192,3 +197,71 @@ def get_manifold_dimension(config, name=None, return_svd=False, *, score_model=N
         return info
     with open(os.path.join(save_path, f"{name}.pkl"), "wb") as f:
         pickle.dump(info, f)
+
+
+def get_conditional_manifold_dimension(config, name=None, *, score_model=None, loader=None, seed=None, label=1,
+                                       times=None):
+    """Drop-in for the reference's `get_conditional_manifold_dimension(config, name=None)` (dim_reduction.py:12-114):
+    the same spectra for 12 diffusion times `linspace(sampling_eps, 0.3, 12)`, only anchors whose label equals 1
+    (`:57-58`), from the VALIDATION loader with labels (`:19-22`), N-1 anchors (`:53-54,60-61`), one directory per
+    time `svd/%.3f/` holding images.pkl, labels_svd.pkl, labels.pkl (`:101-114`).  All 12 time slices of an anchor
+    group reuse one engine; per slice the whole group is one device batch."""
+    import numpy as np
+    log_path, log_name = config.logging.log_path, config.logging.log_name
+    Path(os.path.join(log_path, log_name, "svd")).mkdir(parents=True, exist_ok=True)
+    config.data.return_labels = True
+    if loader is None:
+        from .data import create_lightning_datamodule
+        dm = create_lightning_datamodule(config)
+        dm.setup()
+        loader = dm.val_dataloader()
+    loader = list(loader)
+    sde, sampling_eps = sde_lib.configure_sde(config)
+    device = torch.device(lookup(config, "device", "cuda"))
+    if device.type != "cuda":
+        raise _lib.IdbError("iddiff_b200 runs on CUDA devices only; the CPU path is the reference itself")
+    engine = build_engine(config, score_model, device)
+    num_datapoints = lookup(config, "dim_estimation.num_datapoints", 26)
+    if times is None:
+        times = torch.linspace(sampling_eps, 0.3, 12)
+
+    # the anchors every time slice visits (the reference re-walks the loader per slice; the selection is the same)
+    picked, idx = [], 0
+    for orig_batch, orig_labels in loader:
+        batchsize = orig_batch.size(0)
+        if idx + 1 >= num_datapoints:
+            break
+        for x, y in zip(orig_batch, orig_labels):
+            if y.item() != label:
+                continue
+            if idx + 1 >= num_datapoints:
+                break
+            picked.append((x, batchsize, y.item()))
+            idx += 1
+    out = {}
+    for t_slice in times:
+        t = float(t_slice)
+        t_save_path = os.path.join(log_path, log_name, "svd", "%.3f" % t)
+        Path(t_save_path).mkdir(parents=True, exist_ok=True)
+        singular_values = [None] * len(picked)
+        groups: Dict[int, List[int]] = {}
+        for i, (_, B, _) in enumerate(picked):
+            groups.setdefault(B, []).append(i)
+        for B, idxs in groups.items():
+            x = torch.stack([picked[i][0] for i in idxs]).float()
+            _, _, K = k_schedule(picked[idxs[0]][0].shape, B)
+            res = estimate_anchors(engine, x.flatten(1), K, sde, t, seed=0 if seed is None else seed,
+                                   anchor_id0=idxs[0])
+            sv = res["singular_values"].double().tolist()
+            for j, i in enumerate(idxs):
+                singular_values[i] = sv[j]
+        imgs = [p[0].permute(1, 2, 0) if p[0].dim() == 3 else p[0] for p in picked]
+        imgs = torch.stack(imgs).numpy() if imgs else np.zeros((0,))
+        with open(os.path.join(t_save_path, "images.pkl"), "wb") as f:
+            pickle.dump({"images": imgs}, f)
+        with open(os.path.join(t_save_path, "labels_svd.pkl"), "wb") as f:
+            pickle.dump({"singular_values": singular_values}, f)
+        with open(os.path.join(t_save_path, "labels.pkl"), "wb") as f:
+            pickle.dump({"labels": [p[2] for p in picked]}, f)
+        out["%.3f" % t] = singular_values
+    get_conditional_manifold_dimension.last = out

@@ -1,5 +1,5 @@
 """CLI with the reference's flags for this path (main.py:17-26,32-43,70-71):
-    python -m iddiff_b200.main --config <file.py|file.pkl> --mode manifold_dimension [--checkpoint_path P] [--log_path L]
+    python -m iddiff_b200.main --config <file.py|file.pkl> --mode manifold_dimension|conditional_manifold_dimension [--checkpoint_path P] [--log_path L]
 """
 import argparse
 import importlib.util
@@ -22,7 +22,7 @@ def read_config(path):
 def main(argv=None):
     ap = argparse.ArgumentParser()
     ap.add_argument("--config", required=True)
-    ap.add_argument("--mode", required=True, choices=["manifold_dimension"])
+    ap.add_argument("--mode", required=True, choices=["manifold_dimension", "conditional_manifold_dimension"])
     ap.add_argument("--checkpoint_path", default=None)
     ap.add_argument("--log_path", default=None)
     a = ap.parse_args(argv)
@@ -31,7 +31,10 @@ def main(argv=None):
         config.model.checkpoint_path = a.checkpoint_path
     if a.log_path is not None:
         config.logging.log_path = a.log_path
-    run_lib.get_manifold_dimension(config)
+    if a.mode == "conditional_manifold_dimension":   # main.py:72-73
+        run_lib.get_conditional_manifold_dimension(config)
+    else:
+        run_lib.get_manifold_dimension(config)
 
 
 if __name__ == "__main__":

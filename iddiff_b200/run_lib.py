@@ -4,3 +4,8 @@ from . import dim_reduction
 
 def get_manifold_dimension(config, name=None):
     dim_reduction.get_manifold_dimension(config, name)
+
+
+def get_conditional_manifold_dimension(config, name=None):
+    """run_lib.py:327-328 in the reference."""
+    dim_reduction.get_conditional_manifold_dimension(config, name)

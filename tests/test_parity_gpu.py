@@ -218,3 +218,40 @@ def test_ksphere_drop_in_runs_from_config(tmp_path):
     sv = np.asarray(info["singular_values"])
     assert sv.shape == (3, 100) and np.all(np.diff(sv, axis=1) <= 0) and np.isfinite(sv).all()
     assert sv[:, 0].min() > 20 * sv[:, 1].max()          # radial-only field: one dominant direction (appendix A.10)
+
+
+def test_score_spectrum_callback_uses_live_weights(tmp_path):
+    """the training callback (callbacks.py:403-432) on LIVE module weights -- no checkpoint on disk."""
+    import pickle
+    from iddiff_b200 import callbacks, models
+    from iddiff_b200.config import ConfigDict
+    g = FX.golden("fcn_small_ve")
+    D, H, L, B = int(g["D"]), int(g["H"]), int(g["L"]), int(g["B"])
+    x0 = torch.from_numpy(g["x0"])
+    cfg = ConfigDict(logging=dict(log_path=str(tmp_path), log_name="cb", svd_points=int(g["svd_points"]), svd_frequency=2,
+                                  save_svd=True),
+                     dim_estimation={}, device="cuda:0", training=dict(sde="vesde", batch_size=B, lightning_module="base"),
+                     data=dict(datamodule="Tensor", anchors=x0[torch.arange(B) % x0.shape[0]], shape=[D],
+                               use_data_mean=False),
+                     model=dict(name="fcn", checkpoint_path="/nonexistent/last.ckpt", state_size=D, hidden_layers=L,
+                                hidden_nodes=H, dropout=0.0, sigma_min=1e-2, sigma_max=4.0, beta_min=0.1, beta_max=20.0,
+                                num_scales=1000))
+    live = models.create_model(cfg)
+    live.load_state_dict(FX.golden_fcn_state(g))
+
+    class PL:
+        config, score_model, current_epoch, logged = cfg, live, 1, {}
+
+        def log(self, k, v, **kw):
+            self.logged[k] = v
+
+    pl = PL()
+    cb = callbacks.get_callback_by_name("ScoreSpectrumVisualization")()
+    cb.on_validation_epoch_end(None, pl)
+    assert cb.last_dims == g["dims"].tolist()          # same integer IDs the reference computed for these weights
+    assert abs(pl.logged["dim"] - float(np.mean(g["dims"]))) < 1e-9
+    with open(tmp_path / "cb" / "svd" / "svd_1.pkl", "rb") as f:
+        assert len(pickle.load(f)["singular_values"]) == x0.shape[0]
+    pl.current_epoch, pl.logged = 2, {}
+    cb.on_validation_epoch_end(None, pl)               # (2 + 1) % 2 != 0 -> skipped
+    assert pl.logged == {}
