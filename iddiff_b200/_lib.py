@@ -31,6 +31,7 @@ SIGNATURES = {
     "idb_abi_version": (_i, []),
     "idb_last_error": (C.c_char_p, []),
     "idb_perturb": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _f, _f, _u64, _u64, _vp, _i, _f, _vp, _vp, _vp]),
+    "idb_perturb_rows": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _f, _f, _u64, _u64, C.c_uint32, _vp, _i, _f, _vp, _vp, _vp]),
     "idb_pack_weight": (_i, [_vp, _i, _i, _i, _i, _i, _i, _f, _vp, _vp, _vp]),
     "idb_anchor_linear": (_i, [_vp, _i, _i, _f, _vp, _i, _vp, _vp, _i, _f, _vp, _i, _i, _i, _i, _vp]),
     "idb_fcn_hidden_layer": (_i, [_vp, _vp, _vp, _vp, _i, _f, _f, _i, _i, _i, _vp, _i, _vp, _vp, _vp]),
@@ -78,7 +79,7 @@ def load():
 
 
 # CUDA kernels each entry point enqueues (for bench.py's `gpu_launches` claim)
-KERNELS_PER_CALL = {"idb_perturb": 1, "idb_pack_weight": 1, "idb_anchor_linear": 1, "idb_fcn_hidden_layer": 1,
+KERNELS_PER_CALL = {"idb_perturb": 1, "idb_perturb_rows": 1, "idb_pack_weight": 1, "idb_anchor_linear": 1, "idb_fcn_hidden_layer": 1,
                     "idb_fcn_output_layer": 1, "idb_fcn_anchor_layer": 1, "idb_fcn_scores": 1, "idb_ksphere_gt_score": 1, "idb_center_gram": 2,
                     "idb_spectrum": 2, "idb_id_from_spectrum": 1, "idb_upfirdn2d": 1, "idb_fused_bias_act": 1,
                     "idb_groupnorm_stats": 2, "idb_conv_prep": 1, "idb_conv2d": 1, "idb_attention": 1,

@@ -34,9 +34,20 @@ extern "C" {
 int idb_abi_version(void) { return 1; }
 const char* idb_last_error(void) { return g_err; }
 
+int idb_perturb_rows(const float* x0, const float* z, int n_anchors, int K, int D, int Kp, int Dp, float mean_coeff,
+                     float std, uint64_t seed, uint64_t anchor_id0, uint32_t row0, float* x_out, int fmt, float d_scale,
+                     void* d_hi, void* d_lo, void* stream);
+
 int idb_perturb(const float* x0, const float* z, int n_anchors, int K, int D, int Kp, int Dp, float mean_coeff,
                 float std, uint64_t seed, uint64_t anchor_id0, float* x_out, int fmt, float d_scale, void* d_hi,
                 void* d_lo, void* stream) {
+    return idb_perturb_rows(x0, z, n_anchors, K, D, Kp, Dp, mean_coeff, std, seed, anchor_id0, 0u, x_out, fmt, d_scale,
+                            d_hi, d_lo, stream);
+}
+
+int idb_perturb_rows(const float* x0, const float* z, int n_anchors, int K, int D, int Kp, int Dp, float mean_coeff,
+                     float std, uint64_t seed, uint64_t anchor_id0, uint32_t row0, float* x_out, int fmt, float d_scale,
+                     void* d_hi, void* d_lo, void* stream) {
     if (!x0 || n_anchors < 0 || K <= 0 || D <= 0) return fail("idb_perturb: bad shape");
     if (d_hi && fmt != IDB_FMT_BF16 && fmt != IDB_FMT_FP16) return fail("idb_perturb: unknown fmt");
     if (d_hi && !(d_scale > 0.f)) return fail("idb_perturb: d_scale must be positive");
@@ -48,7 +59,7 @@ int idb_perturb(const float* x0, const float* z, int n_anchors, int K, int D, in
     p.x0 = x0; p.z = z; p.n_anchors = n_anchors; p.K = K; p.D = D;
     p.Kp = d_hi ? Kp : K;
     p.Dp = d_hi ? Dp : ((D + 7) & ~7);
-    p.mean_coeff = mean_coeff; p.std = std; p.seed = seed; p.anchor_id0 = anchor_id0;
+    p.mean_coeff = mean_coeff; p.std = std; p.seed = seed; p.anchor_id0 = anchor_id0; p.row0 = row0;
     p.fmt = fmt; p.d_scale = d_scale;
     p.x_out = x_out; p.d_hi = static_cast<uint8_t*>(d_hi); p.d_lo = static_cast<uint8_t*>(d_lo);
     return check(idb::launch_perturb(p, static_cast<cudaStream_t>(stream)), "idb_perturb");

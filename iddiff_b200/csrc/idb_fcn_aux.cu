@@ -56,7 +56,7 @@ __global__ void __launch_bounds__(256) perturb_kernel(const PerturbParams p) {
                 const uint2 key = make_uint2((uint32_t)p.seed, (uint32_t)(p.seed >> 32));
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
-                    const uint4 r = philox4x32_10(make_uint4((uint32_t)(ch * 2 + h), (uint32_t)k, (uint32_t)aid,
+                    const uint4 r = philox4x32_10(make_uint4((uint32_t)(ch * 2 + h), (uint32_t)k + p.row0, (uint32_t)aid,
                                                              (uint32_t)(aid >> 32)), key);
                     box_muller(r.x, r.y, zz[4 * h + 0], zz[4 * h + 1]);
                     box_muller(r.z, r.w, zz[4 * h + 2], zz[4 * h + 3]);

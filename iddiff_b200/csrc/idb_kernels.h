@@ -38,6 +38,7 @@ struct PerturbParams {
     float mean_coeff, std;
     uint64_t seed;
     uint64_t anchor_id0;  // global id of anchor 0 of this call (Philox stream key)
+    uint32_t row0;        // global index of perturbation row 0 of this call (K sharded over ranks)
     int fmt;          // operand format of d_hi/d_lo (0 = bf16 pair, 1 = fp16 pair)
     float d_scale;    // deviations are multiplied by this (power of two) before the split
     float* x_out;     // optional fp32 [n_anchors][K][D] (perturbed points, reference arithmetic)

@@ -113,6 +113,21 @@ def all_gather_spectra(sv: torch.Tensor, dims: torch.Tensor, n_total: int, group
     return out_sv[:n_total], out_dims[:n_total]
 
 
+def all_gather_rows(S_loc: torch.Tensor, K: int, group=None) -> torch.Tensor:
+    """K-sharding of ONE huge anchor (SURVEY 8e second row): every rank holds the score rows [lo, hi) =
+    shard_range(K, rank, world) of S [A, K, D]; one all-gather (NCCL over NVLink on GPUs, gloo in the CPU tests) gives
+    every rank the full [A, K, D] matrix in global row order.  Shards are padded to the common size for the collective."""
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    A, k_loc, D = S_loc.shape
+    per = (K + world - 1) // world
+    if k_loc < per:
+        S_loc = torch.cat([S_loc, S_loc.new_zeros(A, per - k_loc, D)], dim=1)
+    buf = S_loc.new_empty(world * A, per, D)   # concatenation along dim 0 (the form both NCCL and gloo accept)
+    dist.all_gather_into_tensor(buf, S_loc.contiguous(), group=group)
+    return buf.view(world, A, per, D).permute(1, 0, 2, 3).reshape(A, world * per, D)[:, :K].contiguous()
+
+
 def estimate_anchors(engine, anchors: torch.Tensor, K: int, sde, t: float, *, seed: int = 0,
                      z: Optional[torch.Tensor] = None, chunk: Optional[int] = None, anchor_id0: int = 0,
                      mem_budget_bytes: int = 24 << 30) -> Dict[str, torch.Tensor]:

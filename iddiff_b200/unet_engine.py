@@ -324,6 +324,38 @@ class UNetEngine:
     def bytes_per_anchor(self, K: int, D: int) -> int:
         return K * D * 4 * 2 + D * D * 8
 
+    def score_rows(self, x0: torch.Tensor, k_rows: int, row0: int, mean_coeff: float, std: float, label: float, *,
+                   seed: int = 0, anchor_id0: int = 0, image_shape=None, image_chunk: int = 128) -> torch.Tensor:
+        """Raw network outputs for perturbation rows [row0, row0 + k_rows) of every anchor -> [A, k_rows, H*W*C]
+        (Philox noise keyed by the GLOBAL row, so the rows do not depend on how K is sharded over ranks)."""
+        A, D = x0.shape
+        c, hh, ww = image_shape if image_shape is not None else self.image_shape
+        x = torch.empty(A, k_rows, D, dtype=torch.float32, device=self.dev)
+        with _stage("perturb", A * k_rows * D * 4.0):
+            _lib.call("idb_perturb_rows", _lib.ptr(x0), None, A, k_rows, D, 0, 0, float(mean_coeff), float(std), seed,
+                      anchor_id0, row0, _lib.ptr(x), 0, 1.0, None, None, _lib.stream_ptr())
+        S = torch.empty(A, k_rows, hh * ww * self.cout, dtype=torch.float32, device=self.dev)
+        xi, So = x.view(A * k_rows, c, hh, ww), S.view(A * k_rows, hh, ww, self.cout)
+        with _stage("score_net", 0.0):
+            for s in range(0, A * k_rows, image_chunk):
+                e = min(A * k_rows, s + image_chunk)
+                self.forward(xi[s:e], label, out=So[s:e])
+        return S
+
+    def estimate_row_sharded(self, x0: torch.Tensor, K: int, mean_coeff: float, std: float, label: float, *,
+                             seed: int = 0, anchor_id0: int = 0, group=None, image_chunk: int = 128) -> SpectrumResult:
+        """One (or a few) huge anchors over all ranks of the process group: rank r evaluates the score network on its
+        K / world rows, ONE all-gather assembles S on every rank, the spectrum stage runs replicated."""
+        import torch.distributed as dist
+        from .dim_reduction import all_gather_rows, shard_range
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        lo, hi = shard_range(K, rank, world)
+        S_loc = self.score_rows(x0, hi - lo, lo, mean_coeff, std, label, seed=seed, anchor_id0=anchor_id0,
+                                image_chunk=image_chunk)
+        with _stage("all_gather_rows", 0.0):
+            S = all_gather_rows(S_loc, K, group)
+        return spectrum_from_rows(S, K, S.shape[2], -1.0 / std)
+
     def estimate(self, x0: torch.Tensor, K: int, mean_coeff: float, std: float, label: float, *,
                  z: Optional[torch.Tensor] = None, seed: int = 0, anchor_id0: int = 0, image_shape=None,
                  image_chunk: int = 128, want_scores: bool = False) -> SpectrumResult:

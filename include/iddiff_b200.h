@@ -41,6 +41,13 @@ int idb_perturb(const float* x0, const float* z, int n_anchors, int K, int D, in
                 float std, uint64_t seed, uint64_t anchor_id0, float* x_out, int fmt, float d_scale, void* d_hi,
                 void* d_lo, void* stream);
 
+/* Same, for a SLICE of the K perturbation rows of each anchor: the K rows computed by this call are rows
+ * [row0, row0 + K) of the anchor's global perturbation set (Philox counter = global row), so one huge anchor can be
+ * sharded by rows over the GPUs of a box ("one huge anchor") with results independent of the world size. */
+int idb_perturb_rows(const float* x0, const float* z, int n_anchors, int K, int D, int Kp, int Dp, float mean_coeff,
+                     float std, uint64_t seed, uint64_t anchor_id0, uint32_t row0, float* x_out, int fmt, float d_scale,
+                     void* d_hi, void* d_lo, void* stream);
+
 /* Operand formats of the tensor-core chain.  Every operand is a hi/lo PAIR of 16-bit numbers (v ~= hi + lo) so
  * that three tcgen05.mma (hi.hi + lo.hi + hi.lo) reproduce an fp32-accurate product:
  *   IDB_FMT_BF16  bf16 pairs, 16 significand bits, fp32 exponent range, no scaling needed (scales must be 1);

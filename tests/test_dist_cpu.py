@@ -53,3 +53,37 @@ def test_shard_range_edges():
     assert [shard_range(4096, r, 8) for r in (0, 7)] == [(0, 512), (3584, 4096)]
     assert [shard_range(3, r, 4) for r in range(4)] == [(0, 1), (1, 2), (2, 3), (3, 3)]
     assert shard_range(0, 0, 2) == (0, 0)
+
+
+def _rows_worker(rank, world, port, K, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from iddiff_b200.dim_reduction import all_gather_rows, shard_range
+    lo, hi = shard_range(K, rank, world)
+    A, D = 2, 3
+    # S[a, k, d] = 1000 a + 10 k + d for the rows this rank owns
+    k = torch.arange(lo, hi, dtype=torch.float32)
+    S_loc = (1000 * torch.arange(A, dtype=torch.float32)[:, None, None] + 10 * k[None, :, None]
+             + torch.arange(D, dtype=torch.float32)[None, None, :])
+    S = all_gather_rows(S_loc, K)
+    q.put((rank, S.tolist()))
+    dist.destroy_process_group()
+
+
+def test_row_sharding_of_one_anchor_world2():
+    """SURVEY 8e second row: K perturbation rows of one anchor sharded over ranks, one all-gather, global row order."""
+    for K in (7, 8):
+        ctx = mp.get_context("spawn")
+        q = ctx.Queue()
+        port = _free_port()
+        procs = [ctx.Process(target=_rows_worker, args=(r, 2, port, K, q)) for r in range(2)]
+        for p in procs:
+            p.start()
+        res = sorted(q.get(timeout=120) for _ in procs)
+        for p in procs:
+            p.join(timeout=60)
+            assert p.exitcode == 0
+        want = (1000 * torch.arange(2.)[:, None, None] + 10 * torch.arange(float(K))[None, :, None]
+                + torch.arange(3.)[None, None, :]).tolist()
+        for _, S in res:
+            assert S == want

@@ -1,0 +1,72 @@
+#!/usr/bin/env python
+"""Multi-GPU check + timing of the K-sharded path (one huge anchor over N GPUs):
+    python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 tools/check_kshard.py [--model beatgans] [--K 4096]
+Rank 0 prints one JSON line: time of the sharded run, of the single-GPU run, and their maximum spectrum difference
+(Philox noise is keyed by the global row, so the two must agree to rounding)."""
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tools"))
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--model", default="beatgans")
+    ap.add_argument("--K", type=int, default=4096)
+    args = ap.parse_args()
+    os.environ.setdefault("NCCL_DEBUG", "WARN")
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    world, rank = dist.get_world_size(), dist.get_rank()
+    import bench_unet
+    from oracle import fixtures as FX
+    from iddiff_b200 import sde_lib, unet_models
+    from iddiff_b200.unet_engine import UNetEngine
+    name, spec, gflop = bench_unet.MODELS[args.model]
+    torch.manual_seed(0)
+    holder = unet_models.get_model(name)(FX.unet_config(spec, name))
+    with torch.no_grad():
+        for k, p in holder.named_parameters():
+            if p.dim() >= 2 and float(p.abs().max()) < 1e-3:
+                unet_models.fan_avg_uniform_(p, 1.0)
+    eng = UNetEngine.from_module(holder, dev)
+    eng.image_shape = (3, 64, 64)
+    sde = sde_lib.VESDE(sigma_min=0.009, sigma_max=50.0, N=1000)
+    mc, std = sde.coefficients(1e-5)
+    x0 = FX.smooth_images(1, 3, 64, 5).reshape(1, -1).to(dev)
+
+    def timed(fn):
+        dist.barrier(); torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); r = fn(); e1.record()
+        dist.barrier(); torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return r, float(t[0])
+
+    eng.estimate_row_sharded(x0, 256, mc, std, 0.00999, seed=0)                      # warm-up
+    r_sh, ms_sh = timed(lambda: eng.estimate_row_sharded(x0, args.K, mc, std, 0.00999, seed=1))
+    out = {"model": args.model, "K": args.K, "n_gpus": world, "ms_sharded": ms_sh,
+           "score_evals_per_s": args.K / ms_sh * 1e3}
+    if rank == 0:
+        S = eng.score_rows(x0, args.K, 0, mc, std, 0.00999, seed=1)
+        from iddiff_b200.engine import spectrum_from_rows
+        r_1 = spectrum_from_rows(S, args.K, S.shape[2], -1.0 / std)
+        a, b = r_sh.singular_values[0, :-1].double(), r_1.singular_values[0, :-1].double()
+        out["max_rel_diff_vs_single_gpu"] = float(((a - b).abs() / b).max())
+        out["dims_equal"] = r_sh.dims.cpu().tolist() == r_1.dims.cpu().tolist()
+        print(json.dumps(out), flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
