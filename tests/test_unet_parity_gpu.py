@@ -178,3 +178,32 @@ def test_conditional_manifold_dimension_t_sweep(tmp_path):
     S = IO.unet_score_matrix(fwd, state, spec, imgs[2], z, mc, std, label)
     want = torch.linalg.svdvals(S).numpy()
     np.testing.assert_allclose(by_t[t][1, :8], want[:8], rtol=0.1)
+
+
+def test_full_size_beatgans_properties():
+    """BASELINE config 5 at its full network size (87.5 M parameters, 64x64x3, D = 12288), K = 256 rows, through
+    size-independent properties: chunking invariance (bit-identical), finite sorted spectrum with K-1 non-trivial values,
+    K-sharding invariance of the Philox rows (rows [128, 256) computed alone equal rows 128.. of the full run), and
+    linearity of the read-out in 1/std."""
+    import sys, os
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    import bench_unet
+    from iddiff_b200 import sde_lib
+    from iddiff_b200.engine import spectrum_from_rows
+    eng, n_params, _ = bench_unet.build("beatgans")
+    assert abs(n_params - 87.48e6) < 0.02e6          # SURVEY 8a a14: 87.5 M (64d)
+    sde = sde_lib.VESDE(sigma_min=0.01, sigma_max=50.0, N=1000)
+    mc, std = sde.coefficients(1e-5)
+    x0 = FX.smooth_images(1, 3, 64, 5).reshape(1, -1).cuda()
+    K = 256
+    S = eng.score_rows(x0, K, 0, mc, std, 0.00999, seed=4, image_chunk=128)
+    S64 = eng.score_rows(x0, K, 0, mc, std, 0.00999, seed=4, image_chunk=64)
+    assert torch.equal(S, S64)
+    tail = eng.score_rows(x0, 128, 128, mc, std, 0.00999, seed=4)
+    assert torch.equal(tail, S[:, 128:])
+    r = spectrum_from_rows(S, K, 12288, -1.0 / std)
+    sv = r.singular_values[0].cpu().numpy()
+    assert sv.shape == (K,) and np.isfinite(sv).all() and np.all(np.diff(sv) <= 0)
+    assert sv[-2] > 1e-3 * sv[0] and sv[-1] < 1e-4 * sv[0]     # centred K x D matrix with K < D has rank K - 1
+    r2 = spectrum_from_rows(S, K, 12288, -2.0 / std)
+    np.testing.assert_allclose(r2.singular_values[0, :-1].cpu().numpy(), 2 * sv[:-1], rtol=1e-5)

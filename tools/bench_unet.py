@@ -58,6 +58,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=2)
     ap.add_argument("--anchors", type=int, default=0, help="> 0: time the whole manifold_dimension path")
     ap.add_argument("--K", type=int, default=4096)
+    ap.add_argument("--cpu-baseline", type=int, default=0, help="time the oracle's CPU forward (reference arithmetic, "
+                    "torch CPU fp32, all host cores) on this many images and report score-evals/s")
     args = ap.parse_args()
     from iddiff_b200 import _lib, engine as E
     eng, n_params, gflop = build(args.model)
@@ -100,6 +102,26 @@ def main():
                     "score_net_tflops_algorithmic": args.anchors * args.K * gflop / stages["score_net"],
                     "stages_ms": stages, "dims": r.dims.cpu().tolist(),
                     "sv_head": r.singular_values[0, :3].cpu().tolist(), "sv_tail": r.singular_values[0, -3:].cpu().tolist()})
+    if args.cpu_baseline:
+        import time
+        from oracle import fixtures as FX
+        from oracle import img_oracle as IO
+        name, spec, _ = MODELS[args.model]
+        fwd = {"ddpm": IO.ddpm_forward, "ncsnpp": IO.ncsnpp_forward, "beatgans": IO.beatgans_forward}[args.model]
+        state = {k: v.detach().cpu() for k, v in eng.h.state_dict().items()}
+        torch.set_num_threads(os.cpu_count() or 1)
+        xb = torch.rand(args.cpu_baseline, 3, 64, 64)
+        lab = torch.full((args.cpu_baseline,), 0.00999)
+        with torch.no_grad():
+            fwd(state, spec, xb[:1], lab[:1])
+            t0 = time.perf_counter()
+            yc = fwd(state, spec, xb, lab)
+            dt = time.perf_counter() - t0
+        yg = eng.forward(xb.cuda(), 0.00999).permute(0, 3, 1, 2).cpu()
+        out["cpu_baseline"] = {"value": args.cpu_baseline / dt, "unit": "score-evals/s", "cores": torch.get_num_threads(),
+                               "kind": "port", "sample": f"{args.cpu_baseline} images, one forward of the oracle restatement "
+                               f"of the reference network (torch CPU fp32) in {dt:.1f} s",
+                               "gpu_vs_cpu_max_abs_diff": float((yg - yc).abs().max()), "out_absmax": float(yc.abs().max())}
     print(json.dumps(out))
 
 
