@@ -153,16 +153,29 @@ __device__ __forceinline__ void prep_load8(const PrepParams& p, int n, int y, in
     }
 }
 
-// ((x - mean) * rstd) * gamma + beta, then SiLU: the reference's order of operations (F.group_norm, then act)
+// ((x - mean) * rstd) * gamma + beta, then SiLU: the reference's order of operations (F.group_norm, then act).
+// The pass is issue-bound (ncu: 0.71 warp instructions per scheduler-cycle at 3.6 TB/s), so SiLU uses the 2-instruction
+// ex2.approx exponential and the approximate divide: |error| <= ~3e-7 relative, below the fp32 accumulation error of
+// the convolution that consumes the operand.
+template <bool VEC>
 __device__ __forceinline__ void prep_transform8(const PrepParams& p, const PrepChunk& k, int c0, int C, float (&v)[8]) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         float o = v[j];
         if (p.mean_rstd) o = (o - k.m[j]) * k.r[j];
         if (p.gamma) o = fmaf(o, k.g[j], k.b[j]);
-        if (p.act == 1) o = __fdividef(o, 1.f + expf(-o));
-        v[j] = (c0 + j < C) ? o : 0.f;
+        if (p.act == 1) o = __fdividef(o, 1.f + __expf(-o));
+        v[j] = (VEC || c0 + j < C) ? o : 0.f;
     }
+}
+
+// two values -> packed fp16 (hi, hi) and (lo, lo) words with the paired conversion instructions
+__device__ __forceinline__ void split2_fp16(float a, float b, uint32_t& hi, uint32_t& lo) {
+    const __half2 h = __floats2half2_rn(a, b);
+    const float2 back = __half22float2(h);
+    const __half2 l = __floats2half2_rn(a - back.x, b - back.y);
+    hi = *reinterpret_cast<const uint32_t*>(&h);
+    lo = *reinterpret_cast<const uint32_t*>(&l);
 }
 
 template <bool VEC, bool POOL>
@@ -226,7 +239,7 @@ __global__ void __launch_bounds__(256, POOL ? 2 : 4) conv_prep_kernel(const Prep
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     prep_load8<VEC>(p, n, 2 * yo + (q >> 1), 2 * xo + (q & 1), c0, C, a);
-                    prep_transform8(p, k, c0, C, a);
+                    prep_transform8<VEC>(p, k, c0, C, a);
 #pragma unroll
                     for (int j = 0; j < 8; ++j) v[j] += a[j];
                 }
@@ -234,15 +247,15 @@ __global__ void __launch_bounds__(256, POOL ? 2 : 4) conv_prep_kernel(const Prep
                 for (int j = 0; j < 8; ++j) v[j] *= 0.25f;
             } else if (p.mode == 0) {
                 prep_load8<VEC>(p, n, yo, xo, c0, C, v);
-                prep_transform8(p, k, c0, C, v);
+                prep_transform8<VEC>(p, k, c0, C, v);
             } else if (p.mode == 1) {  // nearest-neighbour x2 (F.interpolate 'nearest', layers.py:600)
                 prep_load8<VEC>(p, n, yo >> 1, xo >> 1, c0, C, v);
-                prep_transform8(p, k, c0, C, v);
+                prep_transform8<VEC>(p, k, c0, C, v);
             } else if (p.mode == 2) {  // parity plane (py, px) of a stride-2 read: src[2*yo + py][2*xo + px]
                 const int y = 2 * yo + (plane >> 1), x = 2 * xo + (plane & 1);
                 if (y < p.Hs && x < p.Ws) {
                     prep_load8<VEC>(p, n, y, x, c0, C, v);
-                    prep_transform8(p, k, c0, C, v);
+                    prep_transform8<VEC>(p, k, c0, C, v);
                 } else {
 #pragma unroll
                     for (int j = 0; j < 8; ++j) v[j] = 0.f;
@@ -252,7 +265,7 @@ __global__ void __launch_bounds__(256, POOL ? 2 : 4) conv_prep_kernel(const Prep
         if (p.out_hi) {
             uint32_t h[4], l[4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) split_pair16(v[2 * j] * p.scale, v[2 * j + 1] * p.scale, 1, h[j], l[j]);
+            for (int j = 0; j < 4; ++j) split2_fp16(v[2 * j] * p.scale, v[2 * j + 1] * p.scale, h[j], l[j]);
             *reinterpret_cast<uint4*>(p.out_hi + ((size_t)pix * p.Cp + c0) * 2) = make_uint4(h[0], h[1], h[2], h[3]);
             *reinterpret_cast<uint4*>(p.out_lo + ((size_t)pix * p.Cp + c0) * 2) = make_uint4(l[0], l[1], l[2], l[3]);
         }

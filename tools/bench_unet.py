@@ -86,12 +86,12 @@ def main():
         sde = sde_lib.VESDE(sigma_min=0.009, sigma_max=50.0, N=1000)   # style_gan_base.py:100-101
         mc, std = sde.coefficients(1e-5)
         x0 = FX.smooth_images(args.anchors, 3, 64, 5).reshape(args.anchors, -1).cuda()
-        eng.estimate(x0[:1], min(args.K, 256), mc, std, 0.00999, seed=0, image_chunk=args.batch)   # warm-up
+        eng.estimate(x0[:1], min(args.K, 1024), mc, std, 0.00999, seed=0)   # warm-up (captures the forward graph)
         torch.cuda.synchronize()
         E.EVENT_LOG = {}
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ev0.record()
-        r = eng.estimate(x0, args.K, mc, std, 0.00999, seed=1, image_chunk=args.batch)
+        r = eng.estimate(x0, args.K, mc, std, 0.00999, seed=1)
         ev1.record()
         torch.cuda.synchronize()
         ms = ev0.elapsed_time(ev1)
