@@ -204,6 +204,130 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tridiag_coop_kernel(double* __r
     }
 }
 
+// Fused variant (n <= TCF_MAX_N, three n-vectors in shared memory): the rank-2 update of step k-1 and the symmetric
+// matrix-vector product of step k are ONE pass over the trailing block -- every row is owned by a fixed warp
+// (row i -> warp i mod #warps), which reads it, applies the pending pair (v, w) of the previous step, writes it back and
+// dots it with the new reflector u in the same sweep.  16 m^2 bytes and one grid synchronisation per column instead of
+// 24 m^2 and two.  Row k itself gets the pending pair applied on the fly when its reflector is formed.
+constexpr int TCF_MAX_N = 9000;
+
+__global__ void __launch_bounds__(TC_THREADS, 1) tridiag_fused_kernel(double* __restrict__ A, int n,
+                                                                      double* __restrict__ d, double* __restrict__ e,
+                                                                      double* __restrict__ pbuf) {
+    cg::grid_group grid = cg::this_grid();
+    extern __shared__ __align__(16) double tc_smem[];
+    double* v = tc_smem;            // pending pair of step k-1 (valid for rows >= k)
+    double* w = tc_smem + n;
+    double* u = tc_smem + 2 * n;    // reflector of step k (valid for rows >= k+1)
+    __shared__ double red[TC_WARPS];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int gw = blockIdx.x * TC_WARPS + warp, n_gw = gridDim.x * TC_WARPS;
+    bool pend = false;
+
+    for (int k = 0; k + 2 < n; ++k) {
+        double* p = pbuf + (size_t)(k & 1) * n;
+        // (1) row k with the pending pair applied -> d[k], reflector u of column k
+        const double* rowk = A + (size_t)k * n;
+        const double vk = pend ? v[k] : 0.0, wk = pend ? w[k] : 0.0;
+        double ss = 0.0;
+        for (int j = k + 2 + tid; j < n; j += TC_THREADS) {
+            double x = rowk[j];
+            if (pend) x = x - vk * w[j] - wk * v[j];
+            u[j] = x;
+            ss = fma(x, x, ss);
+        }
+        ss = tc_block_sum(ss, red);
+        double alpha = rowk[k + 1], dk = rowk[k];
+        if (pend) {
+            alpha = alpha - vk * w[k + 1] - wk * v[k + 1];
+            dk = dk - 2.0 * vk * wk;
+        }
+        double tau = 0.0, beta = alpha;
+        if (ss > 0.0) {
+            const double nrm = sqrt(fma(alpha, alpha, ss));
+            beta = alpha >= 0.0 ? -nrm : nrm;
+            tau = (beta - alpha) / beta;
+            const double inv = 1.0 / (alpha - beta);
+            for (int j = k + 2 + tid; j < n; j += TC_THREADS) u[j] *= inv;
+        }
+        if (tid == 0) u[k + 1] = 1.0;
+        if (blockIdx.x == 0 && tid == 0) {
+            d[k] = dk;
+            e[k] = beta;
+        }
+        __syncthreads();
+        // (2) one pass over the rows this warp owns: apply (v, w), write back, p[i] = tau * <row_i, u>
+        if (pend || tau != 0.0) {
+            int i = gw + ((k + 1 - gw + n_gw - 1) / n_gw) * n_gw;   // first owned row >= k+1 (gw may exceed k+1)
+            if (gw >= k + 1) i = gw;
+            for (; i < n; i += n_gw) {
+                double* row = A + (size_t)i * n;
+                const double vi = pend ? v[i] : 0.0, wi = pend ? w[i] : 0.0;
+                double s = 0.0;
+                if ((n & 1) == 0) {   // 16-byte accesses: pairs (j, j+1), j even
+                    for (int j = ((k + 1) & ~1) + 2 * lane; j < n; j += 64) {
+                        double2 a = *reinterpret_cast<const double2*>(row + j);
+                        if (pend) {
+                            const double2 wj = *reinterpret_cast<const double2*>(w + j);
+                            const double2 vj = *reinterpret_cast<const double2*>(v + j);
+                            a.x = a.x - vi * wj.x - wi * vj.x;
+                            a.y = a.y - vi * wj.y - wi * vj.y;
+                            *reinterpret_cast<double2*>(row + j) = a;   // column k (if j == k) is dead data
+                        }
+                        const double2 uj = *reinterpret_cast<const double2*>(u + j);
+                        if (j >= k + 1) s = fma(a.x, uj.x, s);
+                        s = fma(a.y, uj.y, s);
+                    }
+                } else {
+                    for (int j = k + 1 + lane; j < n; j += 32) {
+                        double a = row[j];
+                        if (pend) {
+                            a = a - vi * w[j] - wi * v[j];
+                            row[j] = a;
+                        }
+                        s = fma(a, u[j], s);
+                    }
+                }
+                s = tc_warp_sum(s);
+                if (lane == 0) p[i] = tau * s;
+            }
+        }
+        grid.sync();
+        // (3) w_new = p - (tau/2)(p.u) u ;  (v, w) <- (u, w_new)
+        if (tau != 0.0) {
+            double pv = 0.0;
+            for (int j = k + 1 + tid; j < n; j += TC_THREADS) pv = fma(p[j], u[j], pv);
+            pv = tc_block_sum(pv, red);
+            const double kk = -0.5 * tau * pv;
+            for (int j = k + 1 + tid; j < n; j += TC_THREADS) {
+                const double uj = u[j];
+                w[j] = fma(kk, uj, p[j]);
+                v[j] = uj;
+            }
+            pend = true;
+        } else {
+            pend = false;
+        }
+        __syncthreads();
+    }
+    if (blockIdx.x == 0 && tid == 0) {
+        const int a = n - 2, b = n - 1;
+        if (n >= 2) {
+            double daa = A[(size_t)a * n + a], eab = A[(size_t)a * n + b];
+            if (pend) {
+                daa -= 2.0 * v[a] * w[a];
+                eab -= v[a] * w[b] + w[a] * v[b];
+            }
+            d[a] = daa;
+            e[a] = eab;
+        }
+        double dbb = A[(size_t)b * n + b];
+        if (pend && n >= 2) dbb -= 2.0 * v[b] * w[b];
+        d[b] = dbb;
+        e[b] = 0.0;
+    }
+}
+
 // ---------------------------------- bisection over many CTAs --------------------------------
 __global__ void __launch_bounds__(256) bisect_large_kernel(const double* __restrict__ dg, const double* __restrict__ eg,
                                                            int n, int n_out, float* __restrict__ sv) {
@@ -252,7 +376,7 @@ __global__ void __launch_bounds__(256) bisect_large_kernel(const double* __restr
     sv[n - 1 - k] = (float)sqrt(fmax(0.5 * (lo + hi), 0.0));
 }
 
-size_t spectrum_large_workspace_bytes(int n) { return (size_t)3 * n * sizeof(double) + 256; }
+size_t spectrum_large_workspace_bytes(int n) { return (size_t)4 * n * sizeof(double) + 256; }
 
 cudaError_t launch_spectrum_large(double* G, int n, int n_out, float* sv, void* workspace, int num_sms,
                                   cudaStream_t stream) {
@@ -260,20 +384,23 @@ cudaError_t launch_spectrum_large(double* G, int n, int n_out, float* sv, void* 
     double* d = reinterpret_cast<double*>(workspace);
     double* e = d + n;
     double* p = e + n;
+    const bool fused = n <= TCF_MAX_N;
+    void* kernel = fused ? reinterpret_cast<void*>(tridiag_fused_kernel) : reinterpret_cast<void*>(tridiag_coop_kernel);
+    const size_t tsmem = (size_t)(fused ? 3 : 2) * n * sizeof(double);
     const size_t smem = (size_t)2 * n * sizeof(double);
-    if (smem > 220 * 1024) return cudaErrorInvalidValue;
-    cudaError_t err = cudaFuncSetAttribute(tridiag_coop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (tsmem > 220 * 1024) return cudaErrorInvalidValue;
+    cudaError_t err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem);
     if (err != cudaSuccess) return err;
     int per_sm = 0;
-    err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tridiag_coop_kernel, TC_THREADS, smem);
+    err = fused ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tridiag_fused_kernel, TC_THREADS, tsmem)
+                : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tridiag_coop_kernel, TC_THREADS, tsmem);
     if (err != cudaSuccess) return err;
     if (per_sm < 1) return cudaErrorInvalidValue;
     int grid = num_sms;   // one CTA per SM
     const int max_useful = (n + TC_WARPS - 1) / TC_WARPS;
     if (grid > max_useful) grid = max_useful;
     void* args[] = {&G, &n, &d, &e, &p};
-    err = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(tridiag_coop_kernel), dim3(grid), dim3(TC_THREADS), args,
-                                      smem, stream);
+    err = cudaLaunchCooperativeKernel(kernel, dim3(grid), dim3(TC_THREADS), args, tsmem, stream);
     if (err != cudaSuccess) return err;
     err = cudaFuncSetAttribute(bisect_large_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;

@@ -21,7 +21,7 @@ def _matrix(K, D, rank, seed, decay=1e-3):
 
 
 @pytest.mark.parametrize("K,D,rank", [(96, 300, 40), (257, 640, 300), (700, 701, 50),      # row side, one-CTA solver
-                                      (2000, 1500, 200), (1300, 3000, 2000), (1100, 1100, 64)])  # whole-GPU solver
+                                      (2000, 1500, 200), (1300, 3000, 2000), (1100, 1100, 64), (1400, 1201, 90)])  # whole-GPU solver
 def test_spectrum_from_rows_all_shapes(K, D, rank):
     from iddiff_b200 import engine as E
     from oracle import id_oracle as O
