@@ -20,61 +20,92 @@ namespace cg = cooperative_groups;
 namespace idb {
 
 // ---------------------------------- row-side centred Gram -----------------------------------
-// One CTA = one 64 x 64 tile (ti <= tj) of G; contraction over the D columns in 16-wide slabs through shared memory.
+// One CTA = one 64 x 64 tile (ti <= tj) of G; contraction over the D columns in 16-wide slabs through shared memory on
+// the fp64 tensor-core path (mma.sync m8n8k4 f64, SASS DMMA): 8 warps x (2 x 4) MMA tiles.  Rows are staged row-major
+// ([64][20] doubles: float4 global loads along the contiguous column axis, conflict-free fragment reads).
+__device__ __forceinline__ void rg_dmma884(double& c0, double& c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
+                 : "+d"(c0), "+d"(c1)
+                 : "d"(a), "d"(b));
+}
+constexpr int RG_LD = 20;
+
 __global__ void __launch_bounds__(256) row_gram_kernel(const float* __restrict__ X, int ld, int K, int D, double scale,
                                                        const double* __restrict__ colmean, double* __restrict__ G) {
-    __shared__ double sA[16][64 + 1];
-    __shared__ double sB[16][64 + 1];
+    __shared__ __align__(16) double sA[64][RG_LD];
+    __shared__ __align__(16) double sB[64][RG_LD];
     const int T = (K + 63) >> 6;
     int ti = 0, rem = blockIdx.x;
     while (rem >= T - ti) { rem -= T - ti; ++ti; }
     const int tj = ti + rem;
-    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
-    double acc[4][4];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int i0 = (warp >> 1) * 16, j0 = (warp & 1) * 32;
+    const int fr = lane >> 2, fk = lane & 3;
+    double acc[2][4][2];
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
+    for (int m = 0; m < 2; ++m)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = 0.0;
+        for (int n = 0; n < 4; ++n) acc[m][n][0] = acc[m][n][1] = 0.0;
+    const int sr = threadIdx.x >> 2, sq = (threadIdx.x & 3) << 2;   // staging: row sr, columns sq .. sq+3 of the slab
+    const int ra = ti * 64 + sr, rb = tj * 64 + sr;
+    const bool vec = (ld & 3) == 0 && (D & 3) == 0 && ((reinterpret_cast<uintptr_t>(X) & 15) == 0);
     for (int d0 = 0; d0 < D; d0 += 16) {
-        for (int i = threadIdx.x; i < 16 * 64; i += 256) {
-            const int r = i >> 4, dd = i & 15;  // 16 consecutive columns of one row: 64 contiguous bytes
-            const int d = d0 + dd;
-            const int ra = ti * 64 + r, rb = tj * 64 + r;
-            double va = 0.0, vb = 0.0;
-            if (d < D) {
-                const double mu = colmean[d];
-                if (ra < K) va = ((double)__ldg(X + (size_t)ra * ld + d) - mu) * scale;
-                if (rb < K) vb = ((double)__ldg(X + (size_t)rb * ld + d) - mu) * scale;
+        const int d = d0 + sq;
+        double va[4] = {0.0, 0.0, 0.0, 0.0}, vb[4] = {0.0, 0.0, 0.0, 0.0};
+        if (vec && d < D) {
+            const double m0 = colmean[d], m1 = colmean[d + 1], m2 = colmean[d + 2], m3 = colmean[d + 3];
+            if (ra < K) {
+                const float4 f = __ldg(reinterpret_cast<const float4*>(X + (size_t)ra * ld + d));
+                va[0] = ((double)f.x - m0) * scale; va[1] = ((double)f.y - m1) * scale;
+                va[2] = ((double)f.z - m2) * scale; va[3] = ((double)f.w - m3) * scale;
             }
-            sA[dd][r] = va;
-            sB[dd][r] = vb;
+            if (rb < K) {
+                const float4 f = __ldg(reinterpret_cast<const float4*>(X + (size_t)rb * ld + d));
+                vb[0] = ((double)f.x - m0) * scale; vb[1] = ((double)f.y - m1) * scale;
+                vb[2] = ((double)f.z - m2) * scale; vb[3] = ((double)f.w - m3) * scale;
+            }
+        } else if (!vec) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                if (d + q < D) {
+                    const double mu = colmean[d + q];
+                    if (ra < K) va[q] = ((double)__ldg(X + (size_t)ra * ld + d + q) - mu) * scale;
+                    if (rb < K) vb[q] = ((double)__ldg(X + (size_t)rb * ld + d + q) - mu) * scale;
+                }
+            }
         }
+        *reinterpret_cast<double2*>(&sA[sr][sq]) = make_double2(va[0], va[1]);
+        *reinterpret_cast<double2*>(&sA[sr][sq + 2]) = make_double2(va[2], va[3]);
+        *reinterpret_cast<double2*>(&sB[sr][sq]) = make_double2(vb[0], vb[1]);
+        *reinterpret_cast<double2*>(&sB[sr][sq + 2]) = make_double2(vb[2], vb[3]);
         __syncthreads();
 #pragma unroll
-        for (int kk = 0; kk < 16; ++kk) {
-            double av[4], bv[4];
+        for (int k4 = 0; k4 < 16; k4 += 4) {
+            double af[2], bf[4];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) av[i] = sA[kk][ty * 4 + i];
+            for (int m = 0; m < 2; ++m) af[m] = sA[i0 + m * 8 + fr][k4 + fk];   // A[i][k] = row i, column k
 #pragma unroll
-            for (int j = 0; j < 4; ++j) bv[j] = sB[kk][tx * 4 + j];
+            for (int n = 0; n < 4; ++n) bf[n] = sB[j0 + n * 8 + fr][k4 + fk];   // B[k][j] = row j, column k
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
+            for (int m = 0; m < 2; ++m)
 #pragma unroll
-                for (int j = 0; j < 4; ++j) acc[i][j] = fma(av[i], bv[j], acc[i][j]);
+                for (int n = 0; n < 4; ++n) rg_dmma884(acc[m][n][0], acc[m][n][1], af[m], bf[n]);
         }
         __syncthreads();
     }
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int r = ti * 64 + ty * 4 + i;
+    for (int m = 0; m < 2; ++m) {
+        const int r = ti * 64 + i0 + m * 8 + fr;
         if (r >= K) continue;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int c = tj * 64 + tx * 4 + j;
-            if (c >= K) continue;
-            G[(size_t)r * K + c] = acc[i][j];
-            if (ti != tj) G[(size_t)c * K + r] = acc[i][j];
-        }
+        for (int n = 0; n < 4; ++n)
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                const int c = tj * 64 + j0 + n * 8 + 2 * fk + q;
+                if (c >= K) continue;
+                G[(size_t)r * K + c] = acc[m][n][q];
+                if (ti != tj) G[(size_t)c * K + r] = acc[m][n][q];
+            }
     }
 }
 

@@ -36,11 +36,21 @@ __global__ void __launch_bounds__(256) colmean_kernel(const float* __restrict__ 
 
 // ---------------------------------- centred Gram (fp64) -------------------------------------
 // One CTA = one 64 x 64 tile of G for one anchor (upper-triangular tile pairs only; mirrored on store).
+// The contraction runs on the fp64 tensor-core path (mma.sync m8n8k4 f64, SASS DMMA): 8 warps, each a 16 x 32 block of the
+// tile = 2 x 4 MMA tiles, operands converted fp32 -> centred fp64 while they are staged in shared memory.
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
+                 : "+d"(c0), "+d"(c1)
+                 : "d"(a), "d"(b));
+}
+
+constexpr int CG_LD = 72;  // padded row (doubles): the 4 k-rows of a fragment load fall into disjoint bank halves
+
 __global__ void __launch_bounds__(256) center_gram_kernel(const float* __restrict__ X, long long anchor_stride, int ld,
                                                           int K, int D, double scale,
                                                           const double* __restrict__ colmean, double* __restrict__ G) {
-    __shared__ double sA[16][64];
-    __shared__ double sB[16][64];
+    __shared__ double sA[16][CG_LD];
+    __shared__ double sB[16][CG_LD];
     // decode (ti <= tj) from the linear pair index
     const int T = (D + 63) >> 6;
     int ti = 0, rem = blockIdx.x;
@@ -49,53 +59,66 @@ __global__ void __launch_bounds__(256) center_gram_kernel(const float* __restric
     const int a = blockIdx.y;
     const float* Xa = X + (size_t)a * anchor_stride;
     const double* mu = colmean + (size_t)a * D;
-    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
-    double acc[4][4];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int i0 = (warp >> 1) * 16, j0 = (warp & 1) * 32;
+    const int fr = lane >> 2, fk = lane & 3;   // fragment row / k index of this lane
+    double acc[2][4][2];
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
+    for (int m = 0; m < 2; ++m)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = 0.0;
+        for (int n = 0; n < 4; ++n) acc[m][n][0] = acc[m][n][1] = 0.0;
 
+    // staging: thread -> (k row kk = t / 16, 4 consecutive columns c4 = (t % 16) * 4) of both operand tiles
+    const int skk = threadIdx.x >> 4, sc = (threadIdx.x & 15) << 2;
+    double mua[4], mub[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const int ca = ti * 64 + sc + q, cb = tj * 64 + sc + q;
+        mua[q] = ca < D ? mu[ca] : 0.0;
+        mub[q] = cb < D ? mu[cb] : 0.0;
+    }
     for (int k0 = 0; k0 < K; k0 += 16) {
-        for (int i = threadIdx.x; i < 16 * 64; i += 256) {
-            const int kk = i >> 6, c = i & 63;
-            const int k = k0 + kk;
-            const int ca = ti * 64 + c, cb = tj * 64 + c;
+        const int k = k0 + skk;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int ca = ti * 64 + sc + q, cb = tj * 64 + sc + q;
             double va = 0.0, vb = 0.0;
             if (k < K) {
-                if (ca < D) va = ((double)Xa[(size_t)k * ld + ca] - mu[ca]) * scale;
-                if (cb < D) vb = ((double)Xa[(size_t)k * ld + cb] - mu[cb]) * scale;
+                if (ca < D) va = ((double)__ldg(Xa + (size_t)k * ld + ca) - mua[q]) * scale;
+                if (cb < D) vb = ((double)__ldg(Xa + (size_t)k * ld + cb) - mub[q]) * scale;
             }
-            sA[kk][c] = va;
-            sB[kk][c] = vb;
+            sA[skk][sc + q] = va;
+            sB[skk][sc + q] = vb;
         }
         __syncthreads();
 #pragma unroll
-        for (int kk = 0; kk < 16; ++kk) {
-            double av[4], bv[4];
+        for (int k4 = 0; k4 < 16; k4 += 4) {
+            double af[2], bf[4];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) av[i] = sA[kk][ty * 4 + i];
+            for (int m = 0; m < 2; ++m) af[m] = sA[k4 + fk][i0 + m * 8 + fr];   // A[i][k] = X[k][i]
 #pragma unroll
-            for (int j = 0; j < 4; ++j) bv[j] = sB[kk][tx * 4 + j];
+            for (int n = 0; n < 4; ++n) bf[n] = sB[k4 + fk][j0 + n * 8 + fr];   // B[k][j] = X[k][j]
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
+            for (int m = 0; m < 2; ++m)
 #pragma unroll
-                for (int j = 0; j < 4; ++j) acc[i][j] = fma(av[i], bv[j], acc[i][j]);
+                for (int n = 0; n < 4; ++n) dmma884(acc[m][n][0], acc[m][n][1], af[m], bf[n]);
         }
         __syncthreads();
     }
     double* Ga = G + (size_t)a * D * D;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int r = ti * 64 + ty * 4 + i;
+    for (int m = 0; m < 2; ++m) {
+        const int r = ti * 64 + i0 + m * 8 + fr;
         if (r >= D) continue;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int c = tj * 64 + tx * 4 + j;
-            if (c >= D) continue;
-            Ga[(size_t)r * D + c] = acc[i][j];
-            if (ti != tj) Ga[(size_t)c * D + r] = acc[i][j];
-        }
+        for (int n = 0; n < 4; ++n)
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                const int c = tj * 64 + j0 + n * 8 + 2 * fk + q;
+                if (c >= D) continue;
+                Ga[(size_t)r * D + c] = acc[m][n][q];
+                if (ti != tj) Ga[(size_t)c * D + r] = acc[m][n][q];
+            }
     }
 }
 
