@@ -204,9 +204,11 @@ def run_ours(args):
         """Inputs resident in HBM; spectra and IDs stay on the device (all-gathered when world > 1)."""
         svs, dims = [], []
         for s in range(0, A, chunk):
-            r = eng.estimate(dev_shard[s:s + chunk], K, mc, std, label, seed=step_idx, anchor_id0=rank * A + s)
+            r = eng.estimate(dev_shard[s:s + chunk], K, mc, std, label, seed=step_idx, anchor_id0=rank * A + s,
+                             defer=args.overlap)
             svs.append(r.singular_values)
             dims.append(r.dims)
+        eng.join()
         step_device.sweeps = r.sweeps
         sv, dm = torch.cat(svs), torch.cat(dims)
         if world > 1:
@@ -320,6 +322,8 @@ def main():
     ap.add_argument("--chunk", type=int, default=128, help="anchors per device batch")
     ap.add_argument("--cpu-budget-s", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--overlap", type=int, default=0, help="1: spectrum stage of chunk i on a second stream, overlapping "
+                    "the GEMM chain of chunk i+1 (measured: no gain -- the persistent GEMM CTAs own every SM's shared memory)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)

@@ -394,7 +394,8 @@ __global__ void __launch_bounds__(256) bisect_large_kernel(const double* __restr
     const double atol = 1e-17 * fmax(fabs(lo), fabs(hi));
     for (int it = 0; it < 200; ++it) {
         const double mid = 0.5 * (lo + hi);
-        if (hi - lo <= fmax(atol, 4.4e-16 * fmax(fabs(lo), fabs(hi))) || mid <= lo || mid >= hi) break;
+        // the result is rounded to fp32 after a square root: 4e-10 relative on lambda is 3e-3 ulp of sqrt(lambda)
+            if (hi - lo <= fmax(atol, 4e-10 * fmax(fabs(lo), fabs(hi))) || mid <= lo || mid >= hi) break;
         double q = d[0] - mid;
         int cnt = q < 0.0;
         for (int i = 1; i < n; ++i) {

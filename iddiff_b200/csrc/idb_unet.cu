@@ -283,6 +283,79 @@ __global__ void __launch_bounds__(256, POOL ? 2 : 4) conv_prep_kernel(const Prep
     }
 }
 
+// Same-size fast path (mode 0, NHWC sources, 8-channel aligned, one plane) -- 70 % of the prep traffic of a U-Net.
+// The source pixel IS the output pixel, so the hot loop has no spatial index arithmetic at all: n = pix >> log2(HW)
+// (or one division) selects the GroupNorm statistics, every per-channel quantity sits in registers.
+template <bool HW_POW2>
+__global__ void __launch_bounds__(256, 4) conv_prep_same_kernel(const PrepParams p, int hw_shift, unsigned hw) {
+    const unsigned chunks = (unsigned)(p.Cp >> 3);
+    const int C = p.C0 + p.C1;
+    const unsigned n_pix = (unsigned)p.N * hw;
+    const unsigned gtid = blockIdx.x * 256u + threadIdx.x;
+    const unsigned ch = gtid % chunks;
+    const unsigned pix_stride = (gridDim.x * 256u) / chunks;
+    const int c0 = (int)ch * 8;
+    const bool live = c0 < C;
+    PrepChunk k;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int c = live ? c0 + j : 0;
+        k.g[j] = (live && p.gamma) ? __ldg(p.gamma + c) : 1.f;
+        k.b[j] = (live && p.gamma && p.beta) ? __ldg(p.beta + c) : 0.f;
+        k.m[j] = 0.f; k.r[j] = 1.f;
+    }
+    const float* src = p.src0;
+    unsigned ldc = 0;
+    if (live) {
+        if (c0 < p.C0) { src = p.src0 + c0; ldc = (unsigned)p.C0; } else { src = p.src1 + (c0 - p.C0); ldc = (unsigned)p.C1; }
+    }
+    const int ga = live ? c0 / p.cg : 0, gb = live ? (c0 + 4) / p.cg : 0;
+    const bool two = (p.cg & 3) == 0;     // at most two groups per chunk; otherwise per-channel lookups
+    int gj[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) gj[j] = live ? (c0 + j) / p.cg : 0;
+    const float2* mr_base = reinterpret_cast<const float2*>(p.mean_rstd);
+    for (unsigned pix = gtid / chunks; pix < n_pix; pix += pix_stride) {
+        float v[8];
+        if (live) {
+            const float4* q = reinterpret_cast<const float4*>(src + (size_t)pix * ldc);
+            const float4 a0 = __ldg(q), a1 = __ldg(q + 1);
+            v[0] = a0.x; v[1] = a0.y; v[2] = a0.z; v[3] = a0.w; v[4] = a1.x; v[5] = a1.y; v[6] = a1.z; v[7] = a1.w;
+            if (mr_base) {
+                const unsigned n = HW_POW2 ? pix >> hw_shift : pix / hw;
+                const float2* mrp = mr_base + (size_t)n * p.groups;
+                if (two) {
+                    const float2 x = __ldg(mrp + ga), y = __ldg(mrp + gb);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) { k.m[j] = x.x; k.r[j] = x.y; k.m[j + 4] = y.x; k.r[j + 4] = y.y; }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const float2 mr = __ldg(mrp + gj[j]);
+                        k.m[j] = mr.x; k.r[j] = mr.y;
+                    }
+                }
+            }
+            prep_transform8<true>(p, k, c0, C, v);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = 0.f;
+        }
+        if (p.out_hi) {
+            uint32_t h[4], l[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) split2_fp16(v[2 * j] * p.scale, v[2 * j + 1] * p.scale, h[j], l[j]);
+            *reinterpret_cast<uint4*>(p.out_hi + ((size_t)pix * p.Cp + c0) * 2) = make_uint4(h[0], h[1], h[2], h[3]);
+            *reinterpret_cast<uint4*>(p.out_lo + ((size_t)pix * p.Cp + c0) * 2) = make_uint4(l[0], l[1], l[2], l[3]);
+        }
+        if (p.out_f32 && live) {
+            float4* dst = reinterpret_cast<float4*>(p.out_f32 + (size_t)pix * C + c0);
+            dst[0] = make_float4(v[0], v[1], v[2], v[3]);
+            dst[1] = make_float4(v[4], v[5], v[6], v[7]);
+        }
+    }
+}
+
 static int ilog2_exact(int v) {
     if (v <= 0 || (v & (v - 1))) return -1;
     int s = 0;
@@ -310,6 +383,12 @@ cudaError_t launch_conv_prep(const PrepParams& p_in, int num_sms, cudaStream_t s
     auto al32 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
     const bool vec = !p.src_nchw && p.C0 % 8 == 0 && p.C1 % 8 == 0 && al32(p.src0) && (!p.src1 || al32(p.src1)) &&
                      (!p.out_f32 || al32(p.out_f32));
+    if (vec && p.mode == 0 && p.planes == 1) {
+        const int hw_shift = ilog2_exact(p.Ho * p.Wo);
+        if (hw_shift >= 0) conv_prep_same_kernel<true><<<(unsigned)grid, 256, 0, stream>>>(p, hw_shift, (unsigned)(p.Ho * p.Wo));
+        else conv_prep_same_kernel<false><<<(unsigned)grid, 256, 0, stream>>>(p, 0, (unsigned)(p.Ho * p.Wo));
+        return cudaGetLastError();
+    }
     if (p.mode == 3) {
         if (vec) conv_prep_kernel<true, true><<<(unsigned)grid, 256, 0, stream>>>(p);
         else conv_prep_kernel<false, true><<<(unsigned)grid, 256, 0, stream>>>(p);

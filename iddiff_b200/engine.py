@@ -128,6 +128,7 @@ class FcnEngine:
         for t in self.w + self.b:
             _require_cuda(t, "FCN parameter")
         self.dev = self.w[0].device
+        self._side = None
         self.D = self.w[-1].shape[0]
         if self.w[0].shape[1] != self.D + 1:
             raise _lib.IdbError("first layer must take state_size + 1 inputs (time column, models/fcn.py:35-38)")
@@ -259,11 +260,30 @@ class FcnEngine:
                  self.w_inv_scale[l] / self.a_scale, M, self.Np[l], self.Kc[l], ptr(d_out), st)
         return d_out, P[-1]
 
+    def join(self):
+        """Makes the current stream wait for every spectrum stage deferred with estimate(..., defer=True)."""
+        if self._side is not None:
+            torch.cuda.current_stream(self.dev).wait_stream(self._side)
+
     def estimate(self, x0: torch.Tensor, K: int, mean_coeff: float, std: float, label: float,
                  z: Optional[torch.Tensor] = None, seed: int = 0, anchor_id0: int = 0,
-                 want_scores: bool = False) -> SpectrumResult:
+                 want_scores: bool = False, defer: bool = False) -> SpectrumResult:
+        """defer=True: the spectrum stage (fp64 Gram, eigen-solver, read-out: small latency-bound kernels) is enqueued
+        on a second CUDA stream so that it overlaps the tensor-core chain of the NEXT chunk; the caller must call
+        join() before reading the results on its own stream."""
         d_out, a_out = self.deviations(x0, K, mean_coeff, std, label, z, seed, anchor_id0)
         # centring removes the anchor part exactly: spectrum of (-(a + d)/std - mean) = spectrum of (d - mean(d))/std
+        if defer and not want_scores:
+            main = torch.cuda.current_stream(self.dev)
+            if self._side is None:
+                self._side = torch.cuda.Stream(device=self.dev)
+            self._side.wait_stream(main)
+            with torch.cuda.stream(self._side):
+                res = spectrum_from_rows(d_out, K, self.D, 1.0 / std)
+            d_out.record_stream(self._side)
+            for t in (res.singular_values, res.dims, res.sweeps):
+                t.record_stream(main)
+            return res
         res = spectrum_from_rows(d_out, K, self.D, 1.0 / std)
         if want_scores:
             A, Kp, ld = d_out.shape
