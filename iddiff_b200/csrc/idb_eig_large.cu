@@ -359,6 +359,33 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tridiag_fused_kernel(double* __
     }
 }
 
+// #eigenvalues of the symmetric tridiagonal (d, e) below x, from the sign changes of the leading principal minors
+//   p_0 = 1, p_1 = d_0 - x, p_i = (d_{i-1} - x) p_{i-1} - e_{i-2}^2 p_{i-2}      (Sturm sequence, product form).
+// The quotient form q_i = p_i / p_{i-1} used by LAPACK's dlaebz costs an fp64 division (~10 fp64 instructions) per
+// step and fp64 vector issue is the scarce resource here (measured: the quotient form ran at the fp64 issue limit);
+// this form is 3 fp64 instructions per step, signs and magnitudes are examined on the integer pipe, and the pair is
+// rescaled by an exact power of two whenever it leaves [2^-400, 2^400].
+__device__ __forceinline__ int sturm_count_l(const double* __restrict__ d, const double* __restrict__ e2, int n, double x) {
+    double p0 = 1.0, p1 = d[0] - x;
+    if (p1 == 0.0) p1 = -1e-300;
+    int cnt = __double2hiint(p1) < 0;
+    for (int i = 1; i < n; ++i) {
+        double p2 = fma(d[i] - x, p1, -(e2[i - 1] * p0));
+        int hi = __double2hiint(p2);
+        if (((hi & 0x7ff00000) == 0) && p2 == 0.0) {       // exact zero: takes the sign opposite to p1 (a sign change)
+            p2 = -p1 * 0x1p-60;
+            hi = __double2hiint(p2);
+        }
+        cnt += (hi ^ __double2hiint(p1)) < 0;
+        const int ex = (hi >> 20) & 0x7ff;                   // biased exponent
+        if (ex > 1023 + 400) { p2 *= 0x1p-400; p1 *= 0x1p-400; }
+        else if (ex < 1023 - 400) { p2 *= 0x1p400; p1 *= 0x1p400; }
+        p0 = p1;
+        p1 = p2;
+    }
+    return cnt;
+}
+
 // ---------------------------------- bisection over many CTAs --------------------------------
 __global__ void __launch_bounds__(256) bisect_large_kernel(const double* __restrict__ dg, const double* __restrict__ eg,
                                                            int n, int n_out, float* __restrict__ sv) {
@@ -388,21 +415,14 @@ __global__ void __launch_bounds__(256) bisect_large_kernel(const double* __restr
     const double span = fmax(fabs(lo), fabs(hi));
     lo = lo - 1e-14 * span - 1e-300;
     hi = hi + 1e-14 * span + 1e-300;
-    const double pivmin = 2.2250738585072014e-308 * fmax(1.0, em);
     const int k = blockIdx.x * 256 + threadIdx.x;   // k-th smallest eigenvalue
     if (k >= n || n - 1 - k >= n_out) return;
     const double atol = 1e-17 * fmax(fabs(lo), fabs(hi));
     for (int it = 0; it < 200; ++it) {
         const double mid = 0.5 * (lo + hi);
         // the result is rounded to fp32 after a square root: 4e-10 relative on lambda is 3e-3 ulp of sqrt(lambda)
-            if (hi - lo <= fmax(atol, 4e-10 * fmax(fabs(lo), fabs(hi))) || mid <= lo || mid >= hi) break;
-        double q = d[0] - mid;
-        int cnt = q < 0.0;
-        for (int i = 1; i < n; ++i) {
-            if (fabs(q) < pivmin) q = -pivmin;
-            q = d[i] - mid - e2[i - 1] / q;
-            cnt += q < 0.0;
-        }
+        if (hi - lo <= fmax(atol, 4e-10 * fmax(fabs(lo), fabs(hi))) || mid <= lo || mid >= hi) break;
+        const int cnt = sturm_count_l(d, e2, n, mid);
         if (cnt > k) hi = mid; else lo = mid;
     }
     sv[n - 1 - k] = (float)sqrt(fmax(0.5 * (lo + hi), 0.0));
