@@ -151,12 +151,17 @@ int idb_row_gram(const float* X, int ld, int K, int D, double scale, double* col
 
 size_t idb_spectrum_large_workspace_bytes(int n) { return idb::spectrum_large_workspace_bytes(n > 0 ? n : 1); }
 
-int idb_spectrum_large(double* G, int n, int n_out, float* sv, void* workspace, void* stream) {
+int idb_spectrum_large_variant(double* G, int n, int n_out, float* sv, void* workspace, int variant, void* stream) {
     if (!G || !sv || !workspace || n <= 0 || n_out <= 0 || n_out > n) return api_fail("idb_spectrum_large: bad argument");
-    if (n > 14000) return api_fail("idb_spectrum_large: n <= 14000 (two n-vectors per CTA in shared memory)");
+    if (n > 14000) return api_fail("idb_spectrum_large: n <= 14000 (d and e^2 of the bisection in shared memory)");
+    if (variant < -1 || variant > 2) return api_fail("idb_spectrum_large_variant: variant in {-1, 0, 1, 2}");
     return api_check(idb::launch_spectrum_large(G, n, n_out, sv, workspace, idb::api_num_sms(),
-                                                static_cast<cudaStream_t>(stream)),
+                                                static_cast<cudaStream_t>(stream), variant),
                      "idb_spectrum_large");
+}
+
+int idb_spectrum_large(double* G, int n, int n_out, float* sv, void* workspace, void* stream) {
+    return idb_spectrum_large_variant(G, n, n_out, sv, workspace, 0, stream);
 }
 
 }  // extern "C"

@@ -235,42 +235,71 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tridiag_coop_kernel(double* __r
     }
 }
 
-// Fused variant (n <= TCF_MAX_N, three n-vectors in shared memory): the rank-2 update of step k-1 and the symmetric
-// matrix-vector product of step k are ONE pass over the trailing block -- every row is owned by a fixed warp
-// (row i -> warp i mod #warps), which reads it, applies the pending pair (v, w) of the previous step, writes it back and
-// dots it with the new reflector u in the same sweep.  16 m^2 bytes and one grid synchronisation per column instead of
-// 24 m^2 and two.  Row k itself gets the pending pair applied on the fly when its reflector is formed.
+// Fused variant: the rank-2 update of step k-1 and the symmetric matrix-vector product of step k are ONE pass over the
+// trailing block -- every row is owned by a fixed warp (row i -> warp i mod #warps), which reads it, applies the
+// pending pair (v, w) of the previous step, writes it back and dots it with the new reflector u in the same sweep.
+// 16 m^2 bytes and one grid synchronisation per column instead of 24 m^2 and two.  Row k itself gets the pending pair
+// applied on the fly when its reflector is formed.  (v, w, u) must sit in shared memory for the sweep: three
+// n-vectors fit one SM up to n = TCF_MAX_N; above that
 constexpr int TCF_MAX_N = 9000;
+// the 64-wide column chunks of the trailing block are dealt round-robin over C classes of CTAs, a CTA of class c keeps
+// only ITS chunks of (v, w, u) in shared memory (3 n / C doubles) and produces the partial products p_c[i]; the full
+// reflector of every step lives in a double-buffered global copy (ubuf, written by CTA 0, L2-resident) and w is
+// re-derived where a row index needs it: w[i] = kk u[i] + sum_c p_c[i].  Same 16 m^2 bytes and one grid
+// synchronisation per column as the C = 1 kernel; n = 12288 (K = 16768 rows of a 64x64x3 image) runs with C = 2.
+constexpr int TCF_UNROLL = 8;
 
-__global__ void __launch_bounds__(TC_THREADS, 1) tridiag_fused_kernel(double* __restrict__ A, int n,
-                                                                      double* __restrict__ d, double* __restrict__ e,
-                                                                      double* __restrict__ pbuf) {
+template <int C>
+__global__ void __launch_bounds__(TC_THREADS, 1) tridiag_fused_cls_kernel(double* __restrict__ A, int n,
+                                                                          double* __restrict__ d, double* __restrict__ e,
+                                                                          double* __restrict__ pbuf,
+                                                                          double* __restrict__ ubuf) {
     cg::grid_group grid = cg::this_grid();
     extern __shared__ __align__(16) double tc_smem[];
-    double* v = tc_smem;            // pending pair of step k-1 (valid for rows >= k)
-    double* w = tc_smem + n;
-    double* u = tc_smem + 2 * n;    // reflector of step k (valid for rows >= k+1)
+    const int Ls = ((((n + 63) >> 6) + C - 1) / C) << 6;
+    double* v = tc_smem;
+    double* w = tc_smem + Ls;
+    double* u = tc_smem + 2 * Ls;
     __shared__ double red[TC_WARPS];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int gw = blockIdx.x * TC_WARPS + warp, n_gw = gridDim.x * TC_WARPS;
+    const int cls = blockIdx.x % C, rg = blockIdx.x / C, n_rg = gridDim.x / C;
+    const int gw = rg * TC_WARPS + warp, n_gw = n_rg * TC_WARPS;
+    const bool lead = blockIdx.x == 0;
+    for (int j = tid; j < 3 * Ls; j += TC_THREADS) tc_smem[j] = 0.0;
+    __syncthreads();
     bool pend = false;
+    double kk_prev = 0.0;
+    auto own = [&](int j) { return ((j >> 6) % C) == cls; };
+    auto loc = [&](int j) { return (((j >> 6) / C) << 6) | (j & 63); };
+    auto psum = [&](const double* p, int j) {
+        double t = p[j];
+#pragma unroll
+        for (int c = 1; c < C; ++c) t += p[(size_t)c * n + j];
+        return t;
+    };
 
     for (int k = 0; k + 2 < n; ++k) {
-        double* p = pbuf + (size_t)(k & 1) * n;
+        const double* pp = pbuf + (size_t)((k + 1) & 1) * C * n;   // partial products of step k-1
+        double* pc = pbuf + (size_t)(k & 1) * C * n;               // ... of this step
+        const double* up = ubuf + (size_t)((k + 1) & 1) * n;       // reflector of step k-1 (= pending v)
+        double* uc = ubuf + (size_t)(k & 1) * n;                   // reflector of this step
+        auto wprev = [&](int j) { return fma(kk_prev, up[j], psum(pp, j)); };
         // (1) row k with the pending pair applied -> d[k], reflector u of column k
         const double* rowk = A + (size_t)k * n;
-        const double vk = pend ? v[k] : 0.0, wk = pend ? w[k] : 0.0;
+        double vk = 0.0, wk = 0.0;
+        if (pend) { vk = up[k]; wk = wprev(k); }
         double ss = 0.0;
         for (int j = k + 2 + tid; j < n; j += TC_THREADS) {
             double x = rowk[j];
-            if (pend) x = x - vk * w[j] - wk * v[j];
-            u[j] = x;
+            if (pend) x = x - vk * wprev(j) - wk * up[j];
+            if (own(j)) u[loc(j)] = x;
+            if (lead) uc[j] = x;
             ss = fma(x, x, ss);
         }
         ss = tc_block_sum(ss, red);
         double alpha = rowk[k + 1], dk = rowk[k];
         if (pend) {
-            alpha = alpha - vk * w[k + 1] - wk * v[k + 1];
+            alpha = alpha - vk * wprev(k + 1) - wk * up[k + 1];
             dk = dk - 2.0 * vk * wk;
         }
         double tau = 0.0, beta = alpha;
@@ -279,82 +308,115 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tridiag_fused_kernel(double* __
             beta = alpha >= 0.0 ? -nrm : nrm;
             tau = (beta - alpha) / beta;
             const double inv = 1.0 / (alpha - beta);
-            for (int j = k + 2 + tid; j < n; j += TC_THREADS) u[j] *= inv;
+            for (int j = k + 2 + tid; j < n; j += TC_THREADS) {
+                if (own(j)) u[loc(j)] *= inv;
+                if (lead) uc[j] *= inv;
+            }
         }
-        if (tid == 0) u[k + 1] = 1.0;
-        if (blockIdx.x == 0 && tid == 0) {
-            d[k] = dk;
-            e[k] = beta;
+        if (tid == 0) {
+            if (own(k + 1)) u[loc(k + 1)] = 1.0;
+            if (lead) {
+                uc[k + 1] = 1.0;
+                d[k] = dk;
+                e[k] = beta;
+            }
         }
         __syncthreads();
-        // (2) one pass over the rows this warp owns: apply (v, w), write back, p[i] = tau * <row_i, u>
+        // (2) one pass over this warp's rows, this CTA's column chunks
         if (pend || tau != 0.0) {
-            int i = gw + ((k + 1 - gw + n_gw - 1) / n_gw) * n_gw;   // first owned row >= k+1 (gw may exceed k+1)
+            int i = gw + ((k + 1 - gw + n_gw - 1) / n_gw) * n_gw;
             if (gw >= k + 1) i = gw;
+            const int q0 = (k + 1) >> 6;
+            const int qs = q0 + ((cls - q0 % C) + C) % C;   // first chunk of this class holding a column >= k+1
             for (; i < n; i += n_gw) {
                 double* row = A + (size_t)i * n;
-                const double vi = pend ? v[i] : 0.0, wi = pend ? w[i] : 0.0;
+                double vi = 0.0, wi = 0.0;
+                if (pend) { vi = up[i]; wi = wprev(i); }
                 double s = 0.0;
-                if ((n & 1) == 0) {   // 16-byte accesses: pairs (j, j+1), j even
-                    for (int j = ((k + 1) & ~1) + 2 * lane; j < n; j += 64) {
-                        double2 a = *reinterpret_cast<const double2*>(row + j);
-                        if (pend) {
-                            const double2 wj = *reinterpret_cast<const double2*>(w + j);
-                            const double2 vj = *reinterpret_cast<const double2*>(v + j);
-                            a.x = a.x - vi * wj.x - wi * vj.x;
-                            a.y = a.y - vi * wj.y - wi * vj.y;
-                            *reinterpret_cast<double2*>(row + j) = a;   // column k (if j == k) is dead data
+                if ((n & 1) == 0) {
+                    // TCF_UNROLL independent 16-byte loads per lane in flight before the first dependent store
+                    for (int q = qs; (q << 6) < n; q += TCF_UNROLL * C) {
+                        double2 a[TCF_UNROLL];
+#pragma unroll
+                        for (int t = 0; t < TCF_UNROLL; ++t) {
+                            const int j = ((q + t * C) << 6) + 2 * lane;
+                            if (j < n) a[t] = *reinterpret_cast<const double2*>(row + j);
                         }
-                        const double2 uj = *reinterpret_cast<const double2*>(u + j);
-                        if (j >= k + 1) s = fma(a.x, uj.x, s);
-                        s = fma(a.y, uj.y, s);
+#pragma unroll
+                        for (int t = 0; t < TCF_UNROLL; ++t) {
+                            const int qq = q + t * C;
+                            const int j = (qq << 6) + 2 * lane;
+                            if (j >= n) break;
+                            const int lj = ((qq / C) << 6) + 2 * lane;
+                            if (pend) {
+                                const double2 wj = *reinterpret_cast<const double2*>(w + lj);
+                                const double2 vj = *reinterpret_cast<const double2*>(v + lj);
+                                a[t].x = a[t].x - vi * wj.x - wi * vj.x;
+                                a[t].y = a[t].y - vi * wj.y - wi * vj.y;
+                                *reinterpret_cast<double2*>(row + j) = a[t];   // columns <= k are dead data
+                            }
+                            const double2 uj = *reinterpret_cast<const double2*>(u + lj);
+                            if (j >= k + 1) s = fma(a[t].x, uj.x, s);
+                            if (j + 1 >= k + 1) s = fma(a[t].y, uj.y, s);
+                        }
                     }
                 } else {
-                    for (int j = k + 1 + lane; j < n; j += 32) {
-                        double a = row[j];
-                        if (pend) {
-                            a = a - vi * w[j] - wi * v[j];
-                            row[j] = a;
+                    for (int q = qs; (q << 6) < n; q += C) {
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) {
+                            const int j = (q << 6) + lane + 32 * h;
+                            if (j >= n || j < k + 1) continue;
+                            const int lj = ((q / C) << 6) + lane + 32 * h;
+                            double a = row[j];
+                            if (pend) {
+                                a = a - vi * w[lj] - wi * v[lj];
+                                row[j] = a;
+                            }
+                            s = fma(a, u[lj], s);
                         }
-                        s = fma(a, u[j], s);
                     }
                 }
                 s = tc_warp_sum(s);
-                if (lane == 0) p[i] = tau * s;
+                if (lane == 0) pc[(size_t)cls * n + i] = tau * s;
             }
         }
         grid.sync();
-        // (3) w_new = p - (tau/2)(p.u) u ;  (v, w) <- (u, w_new)
+        // (3) w_new = p - (tau/2)(p.u) u ;  (v, w) <- (u, w_new) for this CTA's chunks
         if (tau != 0.0) {
             double pv = 0.0;
-            for (int j = k + 1 + tid; j < n; j += TC_THREADS) pv = fma(p[j], u[j], pv);
+            for (int j = k + 1 + tid; j < n; j += TC_THREADS) pv = fma(psum(pc, j), uc[j], pv);
             pv = tc_block_sum(pv, red);
             const double kk = -0.5 * tau * pv;
             for (int j = k + 1 + tid; j < n; j += TC_THREADS) {
-                const double uj = u[j];
-                w[j] = fma(kk, uj, p[j]);
-                v[j] = uj;
+                if (!own(j)) continue;
+                const int lj = loc(j);
+                const double uj = u[lj];
+                w[lj] = fma(kk, uj, psum(pc, j));
+                v[lj] = uj;
             }
+            kk_prev = kk;
             pend = true;
         } else {
             pend = false;
         }
         __syncthreads();
     }
-    if (blockIdx.x == 0 && tid == 0) {
+    if (lead && tid == 0) {
         const int a = n - 2, b = n - 1;
-        if (n >= 2) {
-            double daa = A[(size_t)a * n + a], eab = A[(size_t)a * n + b];
-            if (pend) {
-                daa -= 2.0 * v[a] * w[a];
-                eab -= v[a] * w[b] + w[a] * v[b];
-            }
-            d[a] = daa;
-            e[a] = eab;
+        const int kl = n - 3;   // last eliminated column (only meaningful when pend)
+        const double* pp = pbuf + (size_t)(kl & 1) * C * n;
+        const double* up = ubuf + (size_t)(kl & 1) * n;
+        double va = 0.0, vb = 0.0, wa = 0.0, wb = 0.0;
+        if (pend) {
+            va = up[a]; vb = up[b];
+            wa = fma(kk_prev, va, psum(pp, a));
+            wb = fma(kk_prev, vb, psum(pp, b));
         }
-        double dbb = A[(size_t)b * n + b];
-        if (pend && n >= 2) dbb -= 2.0 * v[b] * w[b];
-        d[b] = dbb;
+        if (n >= 2) {
+            d[a] = A[(size_t)a * n + a] - 2.0 * va * wa;
+            e[a] = A[(size_t)a * n + b] - (va * wb + wa * vb);
+        }
+        d[b] = A[(size_t)b * n + b] - 2.0 * vb * wb;
         e[b] = 0.0;
     }
 }
@@ -428,32 +490,67 @@ __global__ void __launch_bounds__(256) bisect_large_kernel(const double* __restr
     sv[n - 1 - k] = (float)sqrt(fmax(0.5 * (lo + hi), 0.0));
 }
 
-size_t spectrum_large_workspace_bytes(int n) { return (size_t)4 * n * sizeof(double) + 256; }
+// d[n], e[n], partial products [2][classes <= 2][n], reflectors [2][n]
+size_t spectrum_large_workspace_bytes(int n) { return (size_t)8 * n * sizeof(double) + 256; }
 
+template <int C>
+static cudaError_t launch_tridiag_cls(double* G, int n, double* d, double* e, double* p, double* u, int num_sms,
+                                      cudaStream_t stream) {
+    const int Ls = ((((n + 63) >> 6) + C - 1) / C) << 6;
+    const size_t tsmem = (size_t)3 * Ls * sizeof(double);
+    if (tsmem > 220 * 1024) return cudaErrorInvalidValue;
+    cudaError_t err = cudaFuncSetAttribute(tridiag_fused_cls_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)tsmem);
+    if (err != cudaSuccess) return err;
+    int per_sm = 0;
+    err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tridiag_fused_cls_kernel<C>, TC_THREADS, tsmem);
+    if (err != cudaSuccess) return err;
+    if (per_sm < 1) return cudaErrorInvalidValue;
+    int grid = num_sms;
+    const int max_useful = C * ((n + TC_WARPS - 1) / TC_WARPS);
+    if (grid > max_useful) grid = max_useful;
+    grid = (grid / C) * C;
+    if (grid < C) return cudaErrorInvalidValue;
+    void* args[] = {&G, &n, &d, &e, &p, &u};
+    return cudaLaunchCooperativeKernel(reinterpret_cast<void*>(tridiag_fused_cls_kernel<C>), dim3(grid),
+                                       dim3(TC_THREADS), args, tsmem, stream);
+}
+
+// classes: 0 = choose (1 up to TCF_MAX_N, 2 above), 1 = one-class fused kernel, 2 = two column classes,
+// -1 = the unfused two-pass kernel (kept as the cross-check of the fused ones)
 cudaError_t launch_spectrum_large(double* G, int n, int n_out, float* sv, void* workspace, int num_sms,
-                                  cudaStream_t stream) {
+                                  cudaStream_t stream, int classes) {
     if (n <= 0) return cudaSuccess;
     double* d = reinterpret_cast<double*>(workspace);
     double* e = d + n;
     double* p = e + n;
-    const bool fused = n <= TCF_MAX_N;
-    void* kernel = fused ? reinterpret_cast<void*>(tridiag_fused_kernel) : reinterpret_cast<void*>(tridiag_coop_kernel);
-    const size_t tsmem = (size_t)(fused ? 3 : 2) * n * sizeof(double);
+    double* u = p + (size_t)4 * n;
+    if (classes == 0) classes = n <= TCF_MAX_N ? 1 : 2;
+    cudaError_t err;
+    if (classes == 2) {
+        err = launch_tridiag_cls<2>(G, n, d, e, p, u, num_sms, stream);
+        if (err != cudaSuccess) return err;
+    } else if (classes == 1) {
+        err = launch_tridiag_cls<1>(G, n, d, e, p, u, num_sms, stream);
+        if (err != cudaSuccess) return err;
+    } else {
+        void* kernel = reinterpret_cast<void*>(tridiag_coop_kernel);
+        const size_t tsmem = (size_t)2 * n * sizeof(double);
+        if (tsmem > 220 * 1024) return cudaErrorInvalidValue;
+        err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem);
+        if (err != cudaSuccess) return err;
+        int per_sm = 0;
+        err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tridiag_coop_kernel, TC_THREADS, tsmem);
+        if (err != cudaSuccess) return err;
+        if (per_sm < 1) return cudaErrorInvalidValue;
+        int grid = num_sms;   // one CTA per SM
+        const int max_useful = (n + TC_WARPS - 1) / TC_WARPS;
+        if (grid > max_useful) grid = max_useful;
+        void* args[] = {&G, &n, &d, &e, &p};
+        err = cudaLaunchCooperativeKernel(kernel, dim3(grid), dim3(TC_THREADS), args, tsmem, stream);
+        if (err != cudaSuccess) return err;
+    }
     const size_t smem = (size_t)2 * n * sizeof(double);
-    if (tsmem > 220 * 1024) return cudaErrorInvalidValue;
-    cudaError_t err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem);
-    if (err != cudaSuccess) return err;
-    int per_sm = 0;
-    err = fused ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tridiag_fused_kernel, TC_THREADS, tsmem)
-                : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tridiag_coop_kernel, TC_THREADS, tsmem);
-    if (err != cudaSuccess) return err;
-    if (per_sm < 1) return cudaErrorInvalidValue;
-    int grid = num_sms;   // one CTA per SM
-    const int max_useful = (n + TC_WARPS - 1) / TC_WARPS;
-    if (grid > max_useful) grid = max_useful;
-    void* args[] = {&G, &n, &d, &e, &p};
-    err = cudaLaunchCooperativeKernel(kernel, dim3(grid), dim3(TC_THREADS), args, tsmem, stream);
-    if (err != cudaSuccess) return err;
     err = cudaFuncSetAttribute(bisect_large_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
     bisect_large_kernel<<<(n + 255) / 256, 256, smem, stream>>>(d, e, n, n_out, sv);

@@ -140,7 +140,7 @@ cudaError_t launch_row_gram(const float* X, int ld, int K, int D, double scale, 
                             cudaStream_t stream);
 size_t spectrum_large_workspace_bytes(int n);
 cudaError_t launch_spectrum_large(double* G, int n, int n_out, float* sv, void* workspace, int num_sms,
-                                  cudaStream_t stream);
+                                  cudaStream_t stream, int classes = 0);
 
 // helpers of the C-ABI translation units (thread-local error string lives in idb_api.cu)
 int api_fail(const char* what);

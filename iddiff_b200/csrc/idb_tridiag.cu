@@ -185,7 +185,7 @@ __global__ void __launch_bounds__(256) bisect_kernel(const uint8_t* __restrict__
     extern __shared__ __align__(16) uint8_t bis_smem[];
     double* d = reinterpret_cast<double*>(bis_smem);
     double* e2 = d + n;
-    __shared__ double s_lo, s_hi, s_pivmin;
+    __shared__ double s_lo, s_hi;
     const int a = blockIdx.x;
     const size_t per_anchor = tri_packed_bytes(n) + 2 * (size_t)n * sizeof(double);
     const double* dg = reinterpret_cast<const double*>(workspace + (size_t)a * per_anchor + tri_packed_bytes(n));
@@ -207,7 +207,6 @@ __global__ void __launch_bounds__(256) bisect_kernel(const uint8_t* __restrict__
         const double span = fmax(fabs(lo), fabs(hi));
         s_lo = lo - 1e-14 * span - 1e-300;
         s_hi = hi + 1e-14 * span + 1e-300;
-        s_pivmin = 2.2250738585072014e-308 * fmax(1.0, emax);
     }
     __syncthreads();
     int it = 0;

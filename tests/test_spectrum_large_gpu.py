@@ -58,3 +58,27 @@ def test_spectrum_large_matches_small_solver_on_same_gram():
     finally:
         E.LARGE_N = old
     np.testing.assert_allclose(large, small, rtol=2e-5, atol=1e-6 * small[0, 0])
+
+
+@pytest.mark.parametrize("n", [1201, 1536, 2050])
+def test_tridiagonalisation_variants_agree(n):
+    """The three whole-GPU tridiagonalisation kernels (unfused two-pass, fused, fused with two column classes -- the one
+    n = 12288 runs) on the same fp64 Gram matrix, through the C-ABI, against fp64 eigvalsh of that matrix."""
+    from iddiff_b200 import _lib
+    g = torch.Generator().manual_seed(n)
+    B = torch.randn(n, n + 40, generator=g, dtype=torch.float64) * torch.logspace(0, -3, n, dtype=torch.float64)[:, None]
+    G = (B @ B.T).cuda()
+    want = torch.linalg.eigvalsh(G.cpu()).clamp_min(0).sqrt().flip(0).numpy()
+    lib = _lib.load()
+    ws = torch.empty(lib.idb_spectrum_large_workspace_bytes(n), dtype=torch.uint8, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    out = {}
+    for variant in (-1, 1, 2):
+        A = G.clone()
+        sv = torch.empty(n, dtype=torch.float32, device="cuda")
+        _lib.call("idb_spectrum_large_variant", A.data_ptr(), n, n, sv.data_ptr(), ws.data_ptr(), variant, st)
+        torch.cuda.synchronize()
+        out[variant] = sv.cpu().numpy().astype(np.float64)
+        np.testing.assert_allclose(out[variant], want, rtol=1e-5, atol=1e-7 * want[0])
+    np.testing.assert_allclose(out[2], out[1], rtol=1e-6, atol=1e-8 * want[0])
+    np.testing.assert_allclose(out[-1], out[1], rtol=1e-6, atol=1e-8 * want[0])
