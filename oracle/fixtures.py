@@ -121,6 +121,12 @@ DDPM_SMALL = dict(nf=32, ch_mult=(1, 2), num_res_blocks=1, attn_resolutions=(8,)
                   nonlinearity="swish")
 
 
+# the paper's image configs (squares / gaussian_blobs / MNIST: one channel, 32x32, ch_mult (1,2,2,2), attention at 16;
+# configs/dimension_estimation/paper/image_data/squares/10.py:101-135) at a reduced width
+DDPM_GRAY_SMALL = dict(DDPM_SMALL, nf=32, ch_mult=(1, 2, 2, 2), num_res_blocks=2, attn_resolutions=(16,), image_size=32,
+                       input_channels=1, output_channels=1)
+
+
 NCSNPP_SMALL = dict(DDPM_SMALL, nf=16, fir=True, fir_kernel=[1, 3, 3, 1], skip_rescale=True, resblock_type="biggan",
                     progressive="none", progressive_input="residual", progressive_combine="sum",
                     embedding_type="fourier", init_scale=0.0, fourier_scale=16)

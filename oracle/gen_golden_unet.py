@@ -77,6 +77,8 @@ def gen_unet(name="unet_ddpm_small", spec=FX.DDPM_SMALL, seed=7, B=64, svd_point
 def main(what):
     if "ddpm" in what:
         gen_unet()
+    if "gray" in what:
+        gen_unet("unet_ddpm_gray_small", FX.DDPM_GRAY_SMALL, seed=17, B=64, model="ddpm")
     if "beatgans" in what:
         gen_unet("unet_beatgans_small", FX.BEATGANS_SMALL, seed=13, model="BeatGANsUNetModel")
     if "ncsnpp" in what:

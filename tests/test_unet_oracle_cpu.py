@@ -11,15 +11,24 @@ from oracle import id_oracle as O
 import pytest
 
 MODELS = {"ddpm": ("unet_ddpm_small", FX.DDPM_SMALL, IO.ddpm_forward),
+          "ddpm_gray": ("unet_ddpm_gray_small", FX.DDPM_GRAY_SMALL, IO.ddpm_forward),   # the paper's 1x32x32 configs
           "ncsnpp": ("unet_ncsnpp_small", FX.NCSNPP_SMALL, IO.ncsnpp_forward),
           "BeatGANsUNetModel": ("unet_beatgans_small", FX.BEATGANS_SMALL, IO.beatgans_forward)}
+
+
+def _name(model):
+    return "ddpm" if model == "ddpm_gray" else model
+
+
+def _shape(spec):
+    return (spec["input_channels"], spec["image_size"], spec["image_size"])
 
 
 def _setup(model="ddpm"):
     from iddiff_b200 import unet_models
     gold, spec, _ = MODELS[model]
     g = FX.golden(gold)
-    holder = unet_models.get_model(model)(FX.unet_config(spec, model))
+    holder = unet_models.get_model(_name(model))(FX.unet_config(spec, _name(model)))
     state = FX.make_unet_state(holder, int(g["seed"]))
     wsum = sum(v.double().abs().sum().item() for v in state.values())
     assert abs(wsum - float(g["w_checksum"])) < 1e-6 * wsum, "fixture weights drifted from the ones the reference ran"
@@ -46,7 +55,7 @@ def test_ncsnpp_holder_state_dict_layout():
     assert kinds.count("pyr_down") == 1 and kinds.count("res") == 10 and "all_modules.0.W" in state
 
 
-@pytest.mark.parametrize("model", ["ddpm", "ncsnpp", "BeatGANsUNetModel"])
+@pytest.mark.parametrize("model", ["ddpm", "ddpm_gray", "ncsnpp", "BeatGANsUNetModel"])
 def test_unet_forward_oracle_matches_reference(model):
     g, _, state = _setup(model)
     _, spec, fwd = MODELS[model]
@@ -58,7 +67,7 @@ def test_unet_forward_oracle_matches_reference(model):
     assert np.abs(y.numpy() - g["y"]).max() < 1e-5 * scale
 
 
-@pytest.mark.parametrize("model", ["ddpm", "ncsnpp", "BeatGANsUNetModel"])
+@pytest.mark.parametrize("model", ["ddpm", "ddpm_gray", "ncsnpp", "BeatGANsUNetModel"])
 def test_unet_path_oracle_matches_reference_spectrum(model):
     g, _, state = _setup(model)
     _, spec, fwd = MODELS[model]
