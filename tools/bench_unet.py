@@ -31,7 +31,10 @@ BEAT = dict(image_size=64, centered=True, input_channels=3, in_channels=3, model
             conv_resample=True, dims=2, num_classes=None, use_checkpoint=False, num_heads=1, num_head_channels=-1,
             num_heads_upsample=-1, resblock_updown=True, use_new_attention_order=False, resnet_two_cond=False,
             resnet_cond_channels=None, resnet_use_zero_module=True, attn_checkpoint=False)
-MODELS = {"ddpm": ("ddpm", DDPM, 79.7), "ncsnpp": ("ncsnpp", NCSNPP, 88.6), "beatgans": ("BeatGANsUNetModel", BEAT, 37.4)}
+# the paper's synthetic-image configs (squares / gaussian_blobs: 1x32x32, configs/.../squares/10.py:101-135); its
+# FLOPs per image are counted here from the convolution / dense / attention shapes of the plan (2 * MAC)
+SQUARES = dict(DDPM, ch_mult=(1, 2, 2, 2), image_size=32, input_channels=1, output_channels=1)
+MODELS = {"squares": ("ddpm", SQUARES, None), "ddpm": ("ddpm", DDPM, 79.7), "ncsnpp": ("ncsnpp", NCSNPP, 88.6), "beatgans": ("BeatGANsUNetModel", BEAT, 37.4)}
 
 
 def build(model):
@@ -46,7 +49,7 @@ def build(model):
             if p.dim() >= 2 and float(p.abs().max()) < 1e-3:
                 unet_models.fan_avg_uniform_(p, 1.0)
     eng = UNetEngine.from_module(holder, "cuda:0")
-    eng.image_shape = (3, 64, 64)
+    eng.image_shape = (spec["input_channels"], spec["image_size"], spec["image_size"])
     return eng, sum(p.numel() for p in holder.parameters()), gflop
 
 
@@ -64,8 +67,17 @@ def main():
     from iddiff_b200 import _lib, engine as E
     eng, n_params, gflop = build(args.model)
     out = {"model": args.model, "params_M": n_params / 1e6, "gflop_per_image": gflop}
+    C, S, _ = eng.image_shape
+    D = C * S * S
+    if gflop is None:   # measured from the oracle's forward with torch's FLOP counter (same arithmetic as the reference)
+        from torch.utils.flop_counter import FlopCounterMode
+        from oracle import img_oracle as IO
+        state = {k: v.detach().cpu() for k, v in eng.h.state_dict().items()}
+        with FlopCounterMode(display=False) as fc, torch.no_grad():
+            IO.ddpm_forward(state, MODELS[args.model][1], torch.rand(1, C, S, S), torch.full((1,), 0.00999))
+        gflop = out["gflop_per_image"] = fc.get_total_flops() / 1e9
     if args.anchors == 0:
-        x = torch.rand(args.batch, 3, 64, 64, device="cuda")
+        x = torch.rand(args.batch, C, S, S, device="cuda")
         for _ in range(args.warmup):
             eng.forward(x, 0.00999)
         torch.cuda.synchronize()
@@ -85,7 +97,7 @@ def main():
         from iddiff_b200 import sde_lib
         sde = sde_lib.VESDE(sigma_min=0.009, sigma_max=50.0, N=1000)   # style_gan_base.py:100-101
         mc, std = sde.coefficients(1e-5)
-        x0 = FX.smooth_images(args.anchors, 3, 64, 5).reshape(args.anchors, -1).cuda()
+        x0 = FX.smooth_images(args.anchors, C, S, 5).reshape(args.anchors, -1).cuda()
         eng.estimate(x0[:1], min(args.K, 1024), mc, std, 0.00999, seed=0)   # warm-up (captures the forward graph)
         torch.cuda.synchronize()
         E.EVENT_LOG = {}
@@ -97,7 +109,7 @@ def main():
         ms = ev0.elapsed_time(ev1)
         stages = {k: sum(a.elapsed_time(b) for a, b, _ in v) for k, v in E.EVENT_LOG.items()}
         E.EVENT_LOG = None
-        out.update({"anchors": args.anchors, "K": args.K, "D": 12288, "n": min(args.K, 12288), "ms_total": ms,
+        out.update({"anchors": args.anchors, "K": args.K, "D": D, "n": min(args.K, D), "ms_total": ms,
                     "id_estimates_per_s": args.anchors / ms * 1e3, "score_evals_per_s": args.anchors * args.K / ms * 1e3,
                     "score_net_tflops_algorithmic": args.anchors * args.K * gflop / stages["score_net"],
                     "stages_ms": stages, "dims": r.dims.cpu().tolist(),
@@ -107,10 +119,10 @@ def main():
         from oracle import fixtures as FX
         from oracle import img_oracle as IO
         name, spec, _ = MODELS[args.model]
-        fwd = {"ddpm": IO.ddpm_forward, "ncsnpp": IO.ncsnpp_forward, "beatgans": IO.beatgans_forward}[args.model]
+        fwd = {"squares": IO.ddpm_forward, "ddpm": IO.ddpm_forward, "ncsnpp": IO.ncsnpp_forward, "beatgans": IO.beatgans_forward}[args.model]
         state = {k: v.detach().cpu() for k, v in eng.h.state_dict().items()}
         torch.set_num_threads(os.cpu_count() or 1)
-        xb = torch.rand(args.cpu_baseline, 3, 64, 64)
+        xb = torch.rand(args.cpu_baseline, C, S, S)
         lab = torch.full((args.cpu_baseline,), 0.00999)
         with torch.no_grad():
             fwd(state, spec, xb[:1], lab[:1])
