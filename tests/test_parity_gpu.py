@@ -255,3 +255,47 @@ def test_score_spectrum_callback_uses_live_weights(tmp_path):
     pl.current_epoch, pl.logged = 2, {}
     cb.on_validation_epoch_end(None, pl)               # (2 + 1) % 2 != 0 -> skipped
     assert pl.logged == {}
+
+
+def test_short_trained_fcn_recovers_the_sphere_and_matches_the_oracle():
+    """SURVEY 8d C2 'short-trained variant': 5000 denoising-score-matching steps (tools/train_fcn.py -- the reference's
+    objective, losses.py:164-188, optimiser loop in torch) on the 50-sphere in R^200, then the path on the trained
+    weights.  The spectrum has the paper's shape (149 normal directions, a gap, 51 small values) so the estimate is
+    meaningful -- and it must equal the oracle's on the same weights, anchors and noise: spectra rtol 1e-3 (plus the
+    reference arithmetic's own fp32 floor, from the fp64 evaluation), integer ID exact = 51."""
+    import os, sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    import train_fcn
+    from iddiff_b200 import data, models
+    from iddiff_b200.config import ConfigDict
+    D, H, L, K, p = 200, 2048, 5, 1501, 50
+    dev = torch.device("cuda:0")
+    torch.manual_seed(0)
+    cfg = ConfigDict(model=dict(name="fcn", state_size=D, hidden_layers=L, hidden_nodes=H, dropout=0.0),
+                     training=dict(sde="vesde", batch_size=500), data=dict(use_data_mean=False))
+    holder = models.create_model(cfg).to(dev)
+    pts = data.ksphere_points(50004, 1, D, p, 0.0, "random_isometry").float()
+    train_fcn.short_train(holder, pts[:50000].to(dev), 5000)
+    x0 = pts[50000:].contiguous()
+    n = x0.shape[0]
+    sde, t = _sde("vesde")
+    mc, std, label = _coeffs(sde, t)
+    z = torch.randn(n, K, D, generator=torch.Generator().manual_seed(5))
+    eng = FcnEngine.from_module(holder, device=dev)
+    res = eng.estimate(x0.to(dev), K, mc, std, label, z=z.to(dev))
+    torch.cuda.synchronize()
+    sv = res.singular_values.cpu().numpy().astype(np.float64)
+    ws, bs = FX.fcn_state_to_lists({k: v.detach().cpu() for k, v in holder.state_dict().items()}, L)
+    params = dict(sigma_min=1e-2, sigma_max=4.0)
+    score_fn = O.make_score_fn("fcn", "vesde", params, fcn_params=(ws, bs))
+    s64 = O.fcn_centred_spectrum_fp64(ws, bs, x0, z, "vesde", params)
+    for a in range(n):
+        vec_t = torch.ones(K) * 1e-5
+        mean, sd = O.marginal("vesde", x0[a].repeat(K, 1), vec_t, **params)
+        with torch.no_grad():
+            want = np.asarray(O.centred_spectrum(score_fn(mean + sd[:, None] * z[a], vec_t)))
+        floor = np.abs(want - s64[a]).max()
+        assert np.all(np.abs(sv[a] - want) <= SV_RTOL * want + floor), np.abs(sv[a] / want - 1).max()
+        assert O.id_from_spectrum(want.tolist()) == p + 1
+        assert sv[a, D - p - 2] > 4 * sv[a, D - p - 1]        # the gap after the 149 normal directions
+    assert res.dims.cpu().tolist() == [p + 1] * n
