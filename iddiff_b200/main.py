@@ -3,9 +3,31 @@
 """
 import argparse
 import importlib.util
+import os
 import pickle
+import sys
+import types
 
 from . import run_lib
+from .config import ConfigDict
+
+
+def _ensure_ml_collections():
+    """The reference's config files start with `import ml_collections` (e.g. configs/dimension_estimation/paper/
+    euclidean_data/ksphere/50dim.py:1,8).  Where the package is not installed, a module of that name exposing this
+    package's ConfigDict stand-in lets those files load unmodified."""
+    try:
+        import ml_collections  # noqa: F401
+        return
+    except ImportError:
+        pass
+    mod = types.ModuleType("ml_collections")
+    mod.ConfigDict = ConfigDict
+    sub = types.ModuleType("ml_collections.config_dict")
+    sub.ConfigDict = ConfigDict
+    mod.config_dict = sub
+    sys.modules["ml_collections"] = mod
+    sys.modules["ml_collections.config_dict"] = sub
 
 
 def read_config(path):
@@ -13,10 +35,29 @@ def read_config(path):
     if path.endswith(".pkl"):
         with open(path, "rb") as f:
             return pickle.load(f)
-    spec = importlib.util.spec_from_file_location("idb_user_config", path)
-    mod = importlib.util.module_from_spec(spec)
-    spec.loader.exec_module(mod)
-    return mod.get_config()
+    _ensure_ml_collections()
+    # configs that build on others import them as `configs.<...>` (style_gan_2d.py:7): make the tree that holds the
+    # file's top-level `configs` package importable while the file is executed
+    root, added = os.path.dirname(os.path.abspath(path)), None
+    while root != os.path.dirname(root):
+        if os.path.basename(root) == "configs":
+            added = os.path.dirname(root)
+            break
+        root = os.path.dirname(root)
+    cached = {k: sys.modules.pop(k) for k in list(sys.modules) if k == "configs" or k.startswith("configs.")}
+    if added is not None:
+        sys.path.insert(0, added)
+    try:
+        spec = importlib.util.spec_from_file_location("idb_user_config", path)
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        return mod.get_config()
+    finally:
+        if added is not None and added in sys.path:
+            sys.path.remove(added)
+        for k in [k for k in sys.modules if k == "configs" or k.startswith("configs.")]:
+            del sys.modules[k]
+        sys.modules.update(cached)
 
 
 def main(argv=None):

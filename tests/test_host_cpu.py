@@ -120,3 +120,56 @@ def test_drop_in_rejects_cpu_device_and_missing_num_datapoints():
         with pytest.raises(IdbError, match="CUDA devices only"):
             DR.get_manifold_dimension(cfg, return_svd=True)
         assert os.path.isdir(os.path.join(td, "x", "svd"))        # the reference creates the directory first
+
+
+def test_read_config_loads_reference_style_config_files(tmp_path):
+    """main.py:32-34 / configs/utils.py:6-10: a config FILE written the reference's way (`import ml_collections`,
+    a `get_config()` building nested ConfigDicts, a base config imported as `configs.<...>`) loads unmodified, with or
+    without ml_collections installed; a pickled config loads too."""
+    import pickle
+    from iddiff_b200 import main as M, config as C
+    pkg = tmp_path / "repo" / "configs" / "sub"
+    pkg.mkdir(parents=True)
+    (tmp_path / "repo" / "configs" / "__init__.py").write_text("")
+    (pkg / "__init__.py").write_text("")
+    (pkg / "base.py").write_text(
+        "import ml_collections\n"
+        "def get_config():\n"
+        "  config = ml_collections.ConfigDict()\n"
+        "  config.logging = logging = ml_collections.ConfigDict()\n"
+        "  logging.svd_points = 5\n"
+        "  config.model = model = ml_collections.ConfigDict()\n"
+        "  model.name = 'fcn'\n"
+        "  model.sigma_min = 0.01\n"
+        "  config.dim_estimation = ml_collections.ConfigDict()\n"
+        "  return config\n")
+    (pkg / "derived.py").write_text(
+        "import ml_collections\n"
+        "from configs.sub.base import get_config as get_base_config\n"
+        "def get_config():\n"
+        "  config = get_base_config()\n"
+        "  config.model.sigma_max = 4\n"
+        "  config.data = data = ml_collections.ConfigDict()\n"
+        "  data.shape = [200]\n"
+        "  return config\n")
+    cfg = M.read_config(str(pkg / "derived.py"))
+    assert cfg.model.name == "fcn" and cfg.model.sigma_max == 4 and cfg.data.shape == [200]
+    assert C.lookup(cfg, "logging.svd_points") == 5 and C.lookup(cfg, "dim_estimation.num_datapoints") is None
+    with open(tmp_path / "c.pkl", "wb") as f:
+        pickle.dump(C.ConfigDict(model=dict(name="ddpm")), f)
+    assert M.read_config(str(tmp_path / "c.pkl")).model.name == "ddpm"
+
+
+def test_read_config_loads_the_reference_tree_when_present():
+    """In the build container the reference checkout exists: its own dimension-estimation config files load."""
+    import os
+    import pytest
+    from iddiff_b200 import main as M, dim_reduction as DR
+    root = "/root/reference/configs/dimension_estimation/paper"
+    if not os.path.isdir(root):
+        pytest.skip("reference checkout not on this machine")
+    cfg = M.read_config(os.path.join(root, "euclidean_data/ksphere/50dim.py"))
+    assert cfg.model.name == "fcn" and cfg.training.sde == "vesde" and cfg.logging.svd_points > 0
+    img = M.read_config(os.path.join(root, "image_data/squares/10.py"))
+    assert img.model.name == "ddpm" and list(img.data.shape) == [1, 32, 32]
+    assert DR.k_schedule(img.data.shape, img.training.batch_size)[2] == 4480   # SURVEY appendix A.2

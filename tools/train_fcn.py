@@ -59,7 +59,8 @@ def short_train(holder, train_points, steps, *, batch=500, lr=2e-4, warmup=500, 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--D", type=int, default=200)
-    ap.add_argument("--manifold-dim", type=int, default=50)
+    ap.add_argument("--manifold-dim", default="50", help="k, or k1,k2,... for a union of spheres (BASELINE config 3)")
+    ap.add_argument("--angle-std", type=float, default=-1, help="> 0: non-uniform density on the sphere (KSphereDataset.py:92-94)")
     ap.add_argument("--hidden", type=int, default=2048)
     ap.add_argument("--layers", type=int, default=5)
     ap.add_argument("--steps", type=int, default=20000)
@@ -86,24 +87,30 @@ def main():
                                 checkpoint_path=None),
                      training=dict(sde="vesde", batch_size=args.batch), data=dict(use_data_mean=False))
     holder = models.create_model(cfg).to(dev)           # owns the weights in the reference's state_dict layout
-    pts = data.ksphere_points(args.train_points + args.eval_anchors, 1, args.D, args.manifold_dim, 0.0,
-                              "random_isometry").float()
-    train, anchors = pts[:args.train_points].to(dev), pts[args.train_points:].contiguous()
+    mdims = [int(v) for v in str(args.manifold_dim).split(",")]
+    S = len(mdims)
+    per_train, per_eval = args.train_points // S, args.eval_anchors // S
+    pts = data.ksphere_points(per_train + per_eval, S, args.D, mdims if S > 1 else mdims[0], 0.0, "random_isometry",
+                              angle_std=args.angle_std).float().reshape(S, per_train + per_eval, args.D)
+    train = pts[:, :per_train].reshape(-1, args.D).to(dev)
+    anchors = pts[:, per_train:].reshape(-1, args.D).contiguous()      # component-major
     sde = sde_lib.VESDE(sigma_min=args.sigma_min, sigma_max=args.sigma_max, N=1000)
     eps_t = 1e-5
 
     def evaluate(step, loss, t_train):
         eng = E.FcnEngine.from_module(holder, device=dev)
         r = estimate_anchors(eng, anchors, args.K, sde, eps_t, seed=step)
-        dims = r["dims"].tolist()
         sv = r["singular_values"]
-        print(json.dumps({"step": step, "loss": loss, "train_s": t_train, "true_manifold_dim": args.manifold_dim,
-                          "dims_median": sorted(dims)[len(dims) // 2], "dims_min": min(dims), "dims_max": max(dims),
-                          "dims_head": dims[:8],
-                          "sv_anchor0": {"0": float(sv[0, 0]), str(args.D - args.manifold_dim - 2): float(sv[0, args.D - args.manifold_dim - 2]),
-                                         str(args.D - args.manifold_dim - 1): float(sv[0, args.D - args.manifold_dim - 1]),
-                                         str(args.D - args.manifold_dim): float(sv[0, args.D - args.manifold_dim]),
-                                         "last": float(sv[0, -1])}}), flush=True)
+        comps = []
+        for c, k in enumerate(mdims):
+            dims = r["dims"][c * per_eval:(c + 1) * per_eval].tolist()
+            a = c * per_eval
+            comps.append({"true_manifold_dim": k, "dims_median": sorted(dims)[len(dims) // 2], "dims_min": min(dims),
+                          "dims_max": max(dims), "dims_head": dims[:8],
+                          "sv_first_anchor": {"0": float(sv[a, 0]), str(args.D - k - 2): float(sv[a, args.D - k - 2]),
+                                              str(args.D - k - 1): float(sv[a, args.D - k - 1]),
+                                              str(args.D - k): float(sv[a, args.D - k]), "last": float(sv[a, -1])}})
+        print(json.dumps({"step": step, "loss": loss, "train_s": t_train, "D": args.D, "components": comps}), flush=True)
 
     evaluate(0, None, 0.0)
     t0 = time.perf_counter()
@@ -118,7 +125,7 @@ def main():
     if args.out:
         os.makedirs(os.path.dirname(os.path.abspath(args.out)), exist_ok=True)
         torch.save({"state_dict": {"score_model." + k: v.detach().cpu() for k, v in holder.state_dict().items()},
-                    "config": {"D": args.D, "manifold_dim": args.manifold_dim, "steps": args.steps, "lr": args.lr,
+                    "config": {"D": args.D, "manifold_dim": mdims, "angle_std": args.angle_std, "steps": args.steps, "lr": args.lr,
                                "batch": args.batch, "seed": args.seed}}, args.out)
 
 
