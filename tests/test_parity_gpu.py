@@ -299,3 +299,97 @@ def test_short_trained_fcn_recovers_the_sphere_and_matches_the_oracle():
         assert O.id_from_spectrum(want.tolist()) == p + 1
         assert sv[a, D - p - 2] > 4 * sv[a, D - p - 1]        # the gap after the 149 normal directions
     assert res.dims.cpu().tolist() == [p + 1] * n
+
+
+def test_cli_manifold_dimension_from_a_reference_style_config_file(tmp_path):
+    """main.py:17-26,70-71: `--config file.py --mode manifold_dimension --checkpoint_path P --log_path L` with a config
+    file written like configs/dimension_estimation/paper/euclidean_data/ksphere/50dim.py (imports ml_collections,
+    KSphere data module, FCN) -> `<log_path>/<log_name>/svd/None.pkl` holding svd_points-1 spectra."""
+    import pickle
+    from iddiff_b200 import main as M, models
+    from iddiff_b200.config import ConfigDict
+    D, H, L = 64, 256, 2
+    cfg_py = tmp_path / "sphere.py"
+    cfg_py.write_text(
+        "import ml_collections\n"
+        "def get_config():\n"
+        "  config = ml_collections.ConfigDict()\n"
+        "  config.device = 'cuda:0'\n"
+        "  config.logging = logging = ml_collections.ConfigDict()\n"
+        "  logging.log_path = '/nonexistent'\n"
+        "  logging.log_name = 'cli'\n"
+        "  logging.svd_points = 5\n"
+        "  config.training = training = ml_collections.ConfigDict()\n"
+        "  training.lightning_module = 'base'\n"
+        "  training.batch_size = 100\n"
+        "  training.workers = 0\n"
+        "  training.sde = 'vesde'\n"
+        "  config.data = data = ml_collections.ConfigDict()\n"
+        "  data.datamodule = 'KSphere'\n"
+        "  data.data_samples = 400\n"
+        "  data.n_spheres = 1\n"
+        f"  data.ambient_dim = {D}\n"
+        "  data.manifold_dim = 7\n"
+        "  data.noise_std = 0.0\n"
+        "  data.embedding_type = 'random_isometry'\n"
+        "  data.split = [0.8, 0.1, 0.1]\n"
+        "  data.use_data_mean = False\n"
+        f"  data.shape = [{D}]\n"
+        "  config.model = model = ml_collections.ConfigDict()\n"
+        "  model.checkpoint_path = None\n"
+        "  model.name = 'fcn'\n"
+        f"  model.state_size = {D}\n"
+        f"  model.hidden_layers = {L}\n"
+        f"  model.hidden_nodes = {H}\n"
+        "  model.dropout = 0.0\n"
+        "  model.sigma_min = 1e-2\n"
+        "  model.sigma_max = 4\n"
+        "  model.num_scales = 1000\n"
+        "  config.dim_estimation = ml_collections.ConfigDict()\n"
+        "  return config\n")
+    torch.manual_seed(3)
+    holder = models.create_model(ConfigDict(model=dict(name="fcn", state_size=D, hidden_layers=L, hidden_nodes=H,
+                                                       dropout=0.0)))
+    ckpt = tmp_path / "last.ckpt"
+    torch.save({"state_dict": {"score_model." + k: v for k, v in holder.state_dict().items()}}, ckpt)
+    M.main(["--config", str(cfg_py), "--mode", "manifold_dimension", "--checkpoint_path", str(ckpt),
+            "--log_path", str(tmp_path)])
+    with open(tmp_path / "cli" / "svd" / "None.pkl", "rb") as f:
+        info = pickle.load(f)
+    sv = np.asarray(info["singular_values"])
+    assert sv.shape == (4, D) and np.isfinite(sv).all() and np.all(np.diff(sv, axis=1) <= 0) and sv[:, 0].min() > 0
+
+
+def test_c3_shape_union_of_spheres_against_the_oracle():
+    """BASELINE config 3 at its full shape (R^500, FCN H=2048 L=5, K=1501): anchors from the union of a 10- and a
+    30-sphere (KSphereDataset list form, :27-30), a network with a decisive gap (fixtures.make_gap_fcn_state), engine
+    against the oracle's fp32 reference arithmetic and its fp64 evaluation on the same noise -- spectra rtol 1e-3
+    (+ the reference's own rounding floor), integer ID exact."""
+    from iddiff_b200 import data
+    D, H, L, K, rank = 500, 2048, 5, 1501, 31
+    state = FX.make_gap_fcn_state(D, H, L, seed=77, gap_rank=rank)
+    ws, bs = FX.fcn_state_to_lists(state, L)
+    dev = torch.device("cuda:0")
+    torch.manual_seed(4)
+    pts = data.ksphere_points(2, 2, D, [10, 30], 0.0, "random_isometry").float()     # 2 anchors per component
+    n = pts.shape[0]
+    sde, t = _sde("vesde")
+    mc, std, label = _coeffs(sde, t)
+    z = torch.randn(n, K, D, generator=torch.Generator().manual_seed(6))
+    eng = FcnEngine([w.to(dev) for w in ws], [b.to(dev) for b in bs])
+    res = eng.estimate(pts.to(dev), K, mc, std, label, z=z.to(dev))
+    torch.cuda.synchronize()
+    sv = res.singular_values.cpu().numpy().astype(np.float64)
+    assert sv.shape == (n, D)
+    s64 = O.fcn_centred_spectrum_fp64(ws, bs, pts, z, "vesde", SDE_PARAMS)
+    score_fn = O.make_score_fn("fcn", "vesde", SDE_PARAMS, fcn_params=(ws, bs))
+    for a in range(n):
+        vec_t = torch.ones(K) * 1e-5
+        mean, sd = O.marginal("vesde", pts[a].repeat(K, 1), vec_t, **SDE_PARAMS)
+        with torch.no_grad():
+            want = np.asarray(O.centred_spectrum(score_fn(mean + sd[:, None] * z[a], vec_t)))
+        floor = np.abs(want - s64[a]).max()
+        assert np.all(np.abs(sv[a] - want) <= SV_RTOL * want + floor), np.abs(sv[a] / want - 1).max()
+        assert np.all(np.abs(sv[a] - s64[a]) <= SV_RTOL * s64[a] + floor)
+        assert O.id_from_spectrum(want.tolist()) == rank
+    assert res.dims.cpu().tolist() == [rank] * n
