@@ -149,6 +149,219 @@ __global__ void __launch_bounds__(TRI_THREADS, 1) tridiag_kernel(const double* _
     }
 }
 
+// Fused variant (default): the rank-2 update of step k-1 and the symmetric matrix-vector product of step k in ONE pass
+// over the packed trailing block.  A warp owns rows i = r0 + warp, r0 + warp + #warps, ... and walks each along its
+// contiguous columns (conflict-free); an element A[i][j] is read once, gets the pending pair (v, w) applied, is
+// written back, and feeds BOTH halves of the symmetric product: the row sum p_i (a warp reduction) and the column sum
+// p_j, which a lane accumulates in registers for its own columns j = r0 + lane + 32 t over all rows of the warp.  The
+// per-warp column sums meet in shared memory.  2 accesses of the matrix per eliminated column instead of 4, and 5
+// block-wide synchronisations instead of 10 -- the stage is latency-bound (one anchor per SM), so that is its time.
+constexpr int TF_THREADS = 512;
+constexpr int TF_WARPS = TF_THREADS / 32;
+constexpr int TF_RB = 4;
+
+__host__ __device__ inline size_t tf_vec_bytes(int n) { return (size_t)(4 + TF_WARPS) * ((n + 1) & ~1) * sizeof(double); }
+
+__device__ __forceinline__ double tf_block_sum(double v, double* red) {
+    v = warp_sum(v);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    double t = 0.0;
+#pragma unroll
+    for (int w = 0; w < TF_WARPS; ++w) t += red[w];
+    return t;
+}
+
+template <int T, bool CACHE, bool SMEM_A>
+__global__ void __launch_bounds__(TF_THREADS, 1) tridiag_fused_small_kernel(const double* __restrict__ G, int n,
+                                                                            uint8_t* __restrict__ workspace) {
+    extern __shared__ __align__(16) uint8_t tri_smem[];
+    __shared__ double red[TF_WARPS];
+    const int a = blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const size_t per_anchor = tri_packed_bytes(n) + 2 * (size_t)n * sizeof(double);
+    uint8_t* ws = workspace + (size_t)a * per_anchor;
+    const int nv = (n + 1) & ~1;
+    double* vec = reinterpret_cast<double*>(tri_smem);
+    double* v = vec;                 // pending pair of the previous step (rows >= k)
+    double* w = vec + nv;
+    double* u = vec + 2 * nv;        // reflector of this step (rows >= k+1)
+    double* rowp = vec + 3 * nv;     // row half of A u, then p
+    double* cpart = vec + 4 * nv;    // [TF_WARPS][nv] column half of A u, per warp
+    double* A;   // compile-time address space: shared-memory loads/stores with 32-bit addressing when it fits
+    if (SMEM_A) A = vec + (4 + TF_WARPS) * nv;
+    else A = reinterpret_cast<double*>(ws);
+    double* d_out = reinterpret_cast<double*>(ws + tri_packed_bytes(n));
+    double* e_out = d_out + n;
+    const double* Ga = G + (size_t)a * n * n;
+
+    for (int idx = tid; idx < n * n; idx += TF_THREADS) {
+        const int i = idx / n, j = idx - i * n;
+        if (j <= i) A[(size_t)i * (i + 1) / 2 + j] = Ga[idx];
+    }
+    __syncthreads();
+
+    bool pend = false;
+    for (int k = 0; k + 2 < n; ++k) {
+        const int r0 = k + 1;
+        // (1) column k of the trailing rows with the pending pair applied -> d[k], reflector u (LAPACK dlarfg)
+        const double vk = pend ? v[k] : 0.0, wk = pend ? w[k] : 0.0;
+        double part = 0.0;
+        for (int r = r0 + 1 + tid; r < n; r += TF_THREADS) {
+            double x = A[r * (r + 1) / 2 + k];
+            if (pend) x = x - v[r] * wk - w[r] * vk;
+            u[r] = x;
+            part = fma(x, x, part);
+        }
+        const double xnorm2 = tf_block_sum(part, red);
+        double alpha = A[(size_t)r0 * (r0 + 1) / 2 + k], dk = A[(size_t)k * (k + 1) / 2 + k];
+        if (pend) {
+            alpha = alpha - v[r0] * wk - w[r0] * vk;
+            dk = dk - 2.0 * vk * wk;
+        }
+        double tau = 0.0, beta = alpha;
+        if (xnorm2 > 0.0) {
+            beta = -copysign(sqrt(alpha * alpha + xnorm2), alpha);
+            tau = (beta - alpha) / beta;
+            const double inv = 1.0 / (alpha - beta);
+            for (int r = r0 + 1 + tid; r < n; r += TF_THREADS) u[r] *= inv;   // same thread wrote u[r]
+        }
+        if (tid == 0) {
+            u[r0] = 1.0;
+            d_out[k] = dk;
+            e_out[k] = beta;
+        }
+        __syncthreads();
+        // (2) one pass over the trailing block
+        if (pend || tau != 0.0) {
+            double cacc[T], uj[CACHE ? T : 1], wj[CACHE ? T : 1], vj[CACHE ? T : 1];
+#pragma unroll
+            for (int t = 0; t < T; ++t) {
+                cacc[t] = 0.0;
+                if (CACHE) {
+                    const int j = r0 + lane + 32 * t;
+                    const bool in = j < n;
+                    uj[t] = in ? u[j] : 0.0;
+                    wj[t] = in && pend ? w[j] : 0.0;
+                    vj[t] = in && pend ? v[j] : 0.0;
+                }
+            }
+            // TF_RB rows of this warp in flight together: independent dependency chains and interleaved reductions
+            for (int ib = r0 + warp; ib < n; ib += TF_WARPS * TF_RB) {
+                double* Ai[TF_RB];
+                double vi[TF_RB], wi[TF_RB], ui[TF_RB], sr[TF_RB];
+                int ir[TF_RB];
+#pragma unroll
+                for (int b = 0; b < TF_RB; ++b) {
+                    const int i = ib + b * TF_WARPS;
+                    const bool on = i < n;
+                    ir[b] = on ? i : -1;                       // -1: no column satisfies j <= i
+                    const int ic = on ? i : r0;
+                    Ai[b] = A + (size_t)ic * (ic + 1) / 2;
+                    vi[b] = on && pend ? v[ic] : 0.0;
+                    wi[b] = on && pend ? w[ic] : 0.0;
+                    ui[b] = on ? u[ic] : 0.0;
+                    sr[b] = 0.0;
+                }
+                const int imax = min(ib + (TF_RB - 1) * TF_WARPS, n - 1);
+#pragma unroll
+                for (int t = 0; t < T; ++t) {
+                    if (r0 + 32 * t > imax) break;             // warp-uniform: no row of this batch reaches these columns
+                    const int j = r0 + lane + 32 * t;
+                    const double ujt = CACHE ? uj[t] : (j < n ? u[j] : 0.0);
+                    const double wjt = CACHE ? wj[t] : (pend && j < n ? w[j] : 0.0);
+                    const double vjt = CACHE ? vj[t] : (pend && j < n ? v[j] : 0.0);
+                    // branch-free: every load is issued up front from a safe address, masked lanes contribute zeros
+                    double x[TF_RB];
+#pragma unroll
+                    for (int b = 0; b < TF_RB; ++b) x[b] = Ai[b][j <= ir[b] ? j : r0];
+#pragma unroll
+                    for (int b = 0; b < TF_RB; ++b) {
+                        const bool in = j <= ir[b];
+                        const double xn = x[b] - vi[b] * wjt - wi[b] * vjt;      // vi = wi = 0 unless pending
+                        if (in && pend) Ai[b][j] = xn;
+                        sr[b] = fma(xn, in ? ujt : 0.0, sr[b]);
+                        cacc[t] = fma(xn, j < ir[b] ? ui[b] : 0.0, cacc[t]);
+                    }
+                }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+                    for (int b = 0; b < TF_RB; ++b) sr[b] += __shfl_xor_sync(0xffffffffu, sr[b], o);
+                if (lane == 0)
+#pragma unroll
+                    for (int b = 0; b < TF_RB; ++b)
+                        if (ir[b] >= 0) rowp[ir[b]] = sr[b];
+            }
+#pragma unroll
+            for (int t = 0; t < T; ++t) {
+                const int j = r0 + lane + 32 * t;
+                if (j < n) cpart[warp * nv + j] = cacc[t];
+            }
+        }
+        __syncthreads();
+        // (3) p = tau A u,  w_new = p - (tau/2)(p.u) u,  (v, w) <- (u, w_new)
+        if (tau != 0.0) {
+            double pv = 0.0;
+            for (int r = r0 + tid; r < n; r += TF_THREADS) {
+                double sr = rowp[r];
+#pragma unroll
+                for (int q = 0; q < TF_WARPS; ++q) sr += cpart[q * nv + r];
+                sr *= tau;
+                rowp[r] = sr;
+                pv = fma(sr, u[r], pv);
+            }
+            pv = tf_block_sum(pv, red);
+            const double kk = -0.5 * tau * pv;
+            for (int r = r0 + tid; r < n; r += TF_THREADS) w[r] = fma(kk, u[r], rowp[r]);   // same thread wrote rowp[r]
+            double* tmp = v;
+            v = u;
+            u = tmp;
+            pend = true;
+        } else {
+            pend = false;
+        }
+        __syncthreads();
+    }
+    if (tid == 0) {
+        const int ia = n - 2, ib = n - 1;
+        double va = 0.0, vb = 0.0, wa = 0.0, wb = 0.0;
+        if (pend) {
+            vb = v[ib]; wb = w[ib];
+            if (n >= 2) { va = v[ia]; wa = w[ia]; }
+        }
+        if (n >= 2) {
+            d_out[ia] = A[(size_t)ia * (ia + 1) / 2 + ia] - 2.0 * va * wa;
+            e_out[ia] = A[(size_t)ib * (ib + 1) / 2 + ia] - (vb * wa + wb * va);
+        }
+        d_out[ib] = A[(size_t)ib * (ib + 1) / 2 + ib] - 2.0 * vb * wb;
+        e_out[ib] = 0.0;
+    }
+}
+
+template <int T, bool CACHE>
+static cudaError_t launch_tridiag_fused_small(const double* G, int n_anchors, int n, void* workspace, cudaStream_t stream) {
+    const size_t need = tf_vec_bytes(n) + tri_packed_bytes(n);
+    const bool a_in_smem = need <= TRI_SMEM_MAX;
+    const size_t smem = a_in_smem ? need : tf_vec_bytes(n);
+    if (smem > TRI_SMEM_MAX) return cudaErrorInvalidValue;
+    uint8_t* ws = reinterpret_cast<uint8_t*>(workspace);
+    cudaError_t e;
+    if (a_in_smem) {
+        e = cudaFuncSetAttribute(tridiag_fused_small_kernel<T, CACHE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)smem);
+        if (e != cudaSuccess) return e;
+        tridiag_fused_small_kernel<T, CACHE, true><<<n_anchors, TF_THREADS, smem, stream>>>(G, n, ws);
+    } else {
+        e = cudaFuncSetAttribute(tridiag_fused_small_kernel<T, CACHE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)smem);
+        if (e != cudaSuccess) return e;
+        tridiag_fused_small_kernel<T, CACHE, false><<<n_anchors, TF_THREADS, smem, stream>>>(G, n, ws);
+    }
+    return cudaGetLastError();
+}
+
 // #eigenvalues of the symmetric tridiagonal (d, e) below x, from the sign changes of the leading principal minors
 //   p_0 = 1, p_1 = d_0 - x, p_i = (d_{i-1} - x) p_{i-1} - e_{i-2}^2 p_{i-2}      (Sturm sequence, product form).
 // The quotient form q_i = p_i / p_{i-1} used by LAPACK's dlaebz costs an fp64 division (~10 fp64 instructions) per
@@ -230,15 +443,22 @@ __global__ void __launch_bounds__(256) bisect_kernel(const uint8_t* __restrict__
 cudaError_t launch_spectrum_tridiag(const double* G, int n_anchors, int n, int n_out, float* sv, int* iters,
                                     void* workspace, cudaStream_t stream) {
     if (n_anchors <= 0 || n <= 0) return cudaSuccess;
-    const size_t need = tri_vec_bytes(n) + tri_packed_bytes(n);
-    const int a_in_smem = need <= TRI_SMEM_MAX;
-    const size_t smem = a_in_smem ? need : tri_vec_bytes(n);
-    if (smem > TRI_SMEM_MAX) return cudaErrorInvalidValue;
-    cudaError_t e = cudaFuncSetAttribute(tridiag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    tridiag_kernel<<<n_anchors, TRI_THREADS, smem, stream>>>(G, n, reinterpret_cast<uint8_t*>(workspace), a_in_smem);
-    e = cudaGetLastError();
-    if (e != cudaSuccess) return e;
+    cudaError_t e;
+    if (n <= 225) {   // fused one-pass kernel (7 column slots per lane); measured slower than the four-pass kernel once
+                      // the packed matrix no longer fits shared memory (n = 500: 23 vs 21 ms, n = 1024: 174 vs 129 ms)
+        e = launch_tridiag_fused_small<7, true>(G, n_anchors, n, workspace, stream);
+        if (e != cudaSuccess) return e;
+    } else {
+        const size_t need = tri_vec_bytes(n) + tri_packed_bytes(n);
+        const int a_in_smem = need <= TRI_SMEM_MAX;
+        const size_t smem = a_in_smem ? need : tri_vec_bytes(n);
+        if (smem > TRI_SMEM_MAX) return cudaErrorInvalidValue;
+        e = cudaFuncSetAttribute(tridiag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        tridiag_kernel<<<n_anchors, TRI_THREADS, smem, stream>>>(G, n, reinterpret_cast<uint8_t*>(workspace), a_in_smem);
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
     const size_t bsmem = 2 * (size_t)n * sizeof(double);
     if (bsmem > 48 * 1024) {
         e = cudaFuncSetAttribute(bisect_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bsmem);
