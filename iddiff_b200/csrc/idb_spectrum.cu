@@ -328,49 +328,61 @@ cudaError_t launch_spectrum(const double* G, int n_anchors, int n, int n_out, fl
 // plot_utils.py:224-229 in the reference's own arithmetic: Python floats (fp64) on the fp32 singular
 // values widened by s.tolist(); softmax as in plot_utils.py:211-214 (x - max, exp, / sum), first-occurrence
 // argmax with NumPy's NaN rule (the first NaN wins).  dims = -1 flags the reference's ZeroDivisionError.
+// One warp per anchor (lanes stride over the gaps; the three passes -- max, sum, first-occurrence argmax -- are warp
+// reductions).
 __global__ void __launch_bounds__(128) id_readout_kernel(const float* __restrict__ sv, int A, int n, int ld,
                                                          int* __restrict__ dims) {
-    const int a = blockIdx.x * blockDim.x + threadIdx.x;
+    const int a = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
     if (a >= A) return;
     const float* s = sv + (size_t)a * ld;
     const double nf = (double)s[1] - (double)s[2];
     if (nf == 0.0) {
-        dims[a] = -1;
+        if (lane == 0) dims[a] = -1;
         return;
     }
-    const int m = n - 2;  // len(diff)
-    double mx = ((double)s[1] - (double)s[2]) / nf;
-    bool has_nan = mx != mx;
-    for (int i = 2; i < n - 1 && !has_nan; ++i) {
-        const double d = ((double)s[i] - (double)s[i + 1]) / nf;
+    const int m = n - 2;  // len(diff); diff[q] = (s[q+1] - s[q+2]) / nf, q = 0 .. m-1
+    const unsigned full = 0xffffffffu;
+    double mx = -INFINITY;
+    bool has_nan = false;
+    for (int q = lane; q < m; q += 32) {
+        const double d = ((double)s[q + 1] - (double)s[q + 2]) / nf;
         if (d != d) has_nan = true;
         else if (d > mx) mx = d;
     }
-    if (has_nan) {
+    if (__any_sync(full, has_nan)) {
         // np.max propagates NaN -> every soft entry is NaN -> argmax = 0
-        dims[a] = m;
+        if (lane == 0) dims[a] = m;
         return;
     }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(full, mx, o));
     double sum = 0.0;
-    for (int i = 1; i < n - 1; ++i) sum += exp(((double)s[i] - (double)s[i + 1]) / nf - mx);
-    int best = 0;
+    for (int q = lane; q < m; q += 32) sum += exp(((double)s[q + 1] - (double)s[q + 2]) / nf - mx);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(full, sum, o);
+    int best = 0x7fffffff, first_nan = 0x7fffffff;
     double bv = -1.0;
-    bool nan_found = false;
-    for (int i = 1; i < n - 1; ++i) {
-        const double v = exp(((double)s[i] - (double)s[i + 1]) / nf - mx) / sum;
-        if (v != v) {
-            if (!nan_found) { best = i - 1; nan_found = true; }
-        } else if (!nan_found && v > bv) {
-            bv = v;
-            best = i - 1;
-        }
+    for (int q = lane; q < m; q += 32) {
+        const double v = exp(((double)s[q + 1] - (double)s[q + 2]) / nf - mx) / sum;
+        if (v != v) first_nan = min(first_nan, q);
+        else if (v > bv) { bv = v; best = q; }       // strict: the lane keeps its first occurrence
     }
-    dims[a] = m - best;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const double ov = __shfl_xor_sync(full, bv, o);
+        const int ob = __shfl_xor_sync(full, best, o);
+        const int on = __shfl_xor_sync(full, first_nan, o);
+        if (ov > bv || (ov == bv && ob < best)) { bv = ov; best = ob; }
+        first_nan = min(first_nan, on);
+    }
+    if (best == 0x7fffffff) best = 0;
+    if (lane == 0) dims[a] = m - (first_nan != 0x7fffffff ? first_nan : best);
 }
 
 cudaError_t launch_id_readout(const float* sv, int n_anchors, int n, int ld, int* dims, cudaStream_t stream) {
     if (n_anchors <= 0) return cudaSuccess;
-    id_readout_kernel<<<(n_anchors + 127) / 128, 128, 0, stream>>>(sv, n_anchors, n, ld, dims);
+    id_readout_kernel<<<(n_anchors + 3) / 4, 128, 0, stream>>>(sv, n_anchors, n, ld, dims);
     return cudaGetLastError();
 }
 
