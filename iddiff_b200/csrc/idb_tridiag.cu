@@ -278,11 +278,14 @@ __global__ void __launch_bounds__(TF_THREADS, 1) tridiag_fused_small_kernel(cons
                     for (int b = 0; b < TF_RB; ++b) x[b] = Ai[b][j <= ir[b] ? j : r0];
 #pragma unroll
                     for (int b = 0; b < TF_RB; ++b) {
-                        const bool in = j <= ir[b];
-                        const double xn = x[b] - vi[b] * wjt - wi[b] * vjt;      // vi = wi = 0 unless pending
-                        if (in && pend) Ai[b][j] = xn;
-                        sr[b] = fma(xn, in ? ujt : 0.0, sr[b]);
-                        cacc[t] = fma(xn, j < ir[b] ? ui[b] : 0.0, cacc[t]);
+                        // warp-uniform skip: fp64 issue is the scarce resource here, a fully masked row costs nothing
+                        if (r0 + 32 * t <= ir[b]) {
+                            const bool in = j <= ir[b];
+                            const double xn = x[b] - vi[b] * wjt - wi[b] * vjt;      // vi = wi = 0 unless pending
+                            if (in && pend) Ai[b][j] = xn;
+                            sr[b] = fma(xn, in ? ujt : 0.0, sr[b]);
+                            cacc[t] = fma(xn, j < ir[b] ? ui[b] : 0.0, cacc[t]);
+                        }
                     }
                 }
 #pragma unroll
