@@ -104,3 +104,88 @@ class TensorDataModule:
             return [self.data[i:i + B] for i in range(0, len(self.data), B)]
         labels = torch.as_tensor(self.config.data.labels)
         return [(self.data[i:i + B], labels[i:i + B]) for i in range(0, len(self.data), B)]
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# The paper's synthetic image manifolds (configs/dimension_estimation/paper/image_data/{squares,gaussian_blobs}):
+# `data.datamodule = 'Synthetic'`, `data.dataset_type = 'FixedSquaresManifold' | 'FixedGaussiansManifold'`
+# (lightning_data_modules/SyntheticDataset.py:81-183,388-431).  Both are driven by Python's `random` seeded with
+# config.seed; the draws below happen in the reference's order (geometry first, then per image one draw per shape), so
+# the same seed gives the same images.  Generation is vectorised over the images instead of the reference's per-pixel
+# Python loops; accumulation stays in fp32 in the shapes' order, which is what the element-wise `+=` there does.
+def fixed_squares_images(seed, num_samples, num_squares, square_range, img_size):
+    """FixedSquaresManifold: `num_squares` squares at fixed places, each image paints every square with its own uniform
+    intensity (overlaps add) -> [num_samples, 1, S, S] fp32; the manifold dimension is num_squares."""
+    import random
+    random.seed(seed)
+    info = []
+    for _ in range(num_squares):
+        side = random.choice(square_range)
+        start, finish = (side + 1) // 2, img_size - (side + 1) // 2
+        x = random.choice(np.arange(start, finish))
+        y = random.choice(np.arange(start, finish))
+        info.append((int(x), int(y), int(side)))
+    c = torch.tensor([[random.random() for _ in range(num_squares)] for _ in range(num_samples)], dtype=torch.float64)
+    c = c.to(torch.float32)                     # `img[...] += c` rounds the Python float to the image's fp32
+    img = torch.zeros(num_samples, img_size, img_size)
+    for i, (x, y, side) in enumerate(info):
+        x0, y0 = x - ((side + 1) // 2 - 1), y - ((side + 1) // 2 - 1)
+        img[:, x0:x0 + side, y0:y0 + side] += c[:, i, None, None]
+    return img.unsqueeze(1)
+
+
+def fixed_gaussians_images(seed, num_samples, num_gaussians, std_range, img_size):
+    """FixedGaussiansManifold: `num_gaussians` bumps at fixed centres (sampled without replacement), each image draws
+    every bump's width uniformly from std_range; the sum is rescaled to [0, 1] per image."""
+    import random
+    random.seed(seed)
+    pairs = [[i, j] for i in range(img_size) for j in range(img_size)]
+    centers = random.sample(pairs, k=num_gaussians)
+    xx, yy = torch.meshgrid((torch.arange(img_size), torch.arange(img_size)), indexing="ij")
+    data = []
+    for _ in range(num_samples):
+        img = torch.zeros(img_size, img_size)
+        for cx, cy in centers:
+            std = random.uniform(std_range[0], std_range[1])
+            c = 1 / (np.sqrt(2 * np.pi) * std)
+            d = -1 / (2 * std ** 2)
+            arg = d * ((xx - cx) ** 2 + (yy - cy) ** 2)                  # int64 * Python float -> fp32 tensor
+            bump = torch.from_numpy(np.exp(arg.numpy()))                 # NumPy's fp32 exp, as np.exp(tensor) there
+            bump *= c
+            img += bump
+        lo, hi = torch.min(img), torch.max(img)
+        img -= lo
+        img /= hi - lo
+        data.append(img.to(torch.float32).unsqueeze(0))
+    return torch.stack(data)
+
+
+@register_lightning_datamodule("Synthetic")
+class SyntheticDataModule:
+    def __init__(self, config):
+        self.config = config
+
+    def setup(self, stage=None):
+        d = self.config.data
+        kind = d.dataset_type
+        seed = self.config.seed
+        if kind == "FixedSquaresManifold":
+            self.data = fixed_squares_images(seed, d.data_samples, d.num_squares, list(d.square_range), d.image_size)
+        elif kind == "FixedGaussiansManifold":
+            self.data = fixed_gaussians_images(seed, d.data_samples, d.num_gaussians, list(d.std_range), d.image_size)
+        else:
+            raise NotImplementedError(f"Synthetic dataset_type {kind!r}: the dimension-estimation configs use "
+                                      "FixedSquaresManifold and FixedGaussiansManifold")
+        n = len(self.data)
+        split = list(d.split)
+        lens = [int(split[0] * n), int(split[1] * n), int(split[2] * n)]
+        self.train_data, self.valid_data, self.test_data = random_split(self.data, lens)
+
+    def train_dataloader(self):
+        t = self.config.training
+        return DataLoader(self.train_data, batch_size=t.batch_size, num_workers=getattr(t, "workers", 0), shuffle=True)
+
+    def val_dataloader(self):
+        v = getattr(self.config, "validation", None)
+        B = getattr(v, "batch_size", None) or self.config.training.batch_size
+        return DataLoader(self.valid_data, batch_size=B, num_workers=getattr(v, "workers", 0) or 0, shuffle=False)

@@ -89,8 +89,8 @@ def configure_sde(config):
     if name == "subvpsde":
         return subVPSDE(beta_min=m.beta_min, beta_max=m.beta_max, N=m.num_scales), 1e-3
     if name == "vesde":
-        if getattr(config.data, "use_data_mean", False):
-            raise NotImplementedError("data.use_data_mean needs a dataset statistics file; not on this path offline")
+        # data.use_data_mean (BaseSdeGenerativeModel.py:36-41) loads a dataset mean that only shifts prior_sampling
+        # (sde_lib.py:368-371); marginal_prob -- all this path uses -- does not read it, so the flag changes nothing here
         return VESDE(sigma_min=m.sigma_min, sigma_max=m.sigma_max, N=m.num_scales), 1e-5
     if name == "snrsde":
         return SNRSDE(N=m.num_scales), 1e-3

@@ -173,3 +173,29 @@ def test_read_config_loads_the_reference_tree_when_present():
     img = M.read_config(os.path.join(root, "image_data/squares/10.py"))
     assert img.model.name == "ddpm" and list(img.data.shape) == [1, 32, 32]
     assert DR.k_schedule(img.data.shape, img.training.batch_size)[2] == 4480
+
+
+def test_synthetic_image_manifolds_match_the_reference_generators():
+    """'Synthetic' data module (the paper's squares / gaussian_blobs configs): the vectorised generators reproduce the
+    images the REAL reference's FixedSquaresManifold / FixedGaussiansManifold built from the same seed
+    (tests/golden/synthetic_images.npz via oracle/gen_golden_data.py) bit for bit, and the module serves batches of
+    the config's shape."""
+    import numpy as np
+    import torch
+    from iddiff_b200 import data
+    from iddiff_b200.config import ConfigDict
+    from oracle import fixtures as FX
+    g = FX.golden("synthetic_images")
+    for seed in (42, 7):
+        sq = data.fixed_squares_images(seed, 24, 10, [3, 5], 32)
+        assert sq.dtype == torch.float32 and np.array_equal(sq.numpy(), g[f"squares_{seed}"])
+        ga = data.fixed_gaussians_images(seed, 24, 10, [1, 5], 32)
+        assert ga.dtype == torch.float32 and np.array_equal(ga.numpy(), g[f"gaussians_{seed}"])
+    cfg = ConfigDict(seed=42, training=dict(batch_size=8, workers=0),
+                     data=dict(datamodule="Synthetic", dataset_type="FixedSquaresManifold", data_samples=40,
+                               split=[0.8, 0.1, 0.1], image_size=32, num_squares=10, square_range=[3, 5],
+                               return_labels=False, shape=[1, 32, 32]))
+    dm = data.create_lightning_datamodule(cfg)
+    dm.setup()
+    batch = next(iter(dm.train_dataloader()))
+    assert tuple(batch.shape) == (8, 1, 32, 32) and len(dm.train_data) == 32 and len(dm.valid_data) == 4

@@ -217,3 +217,33 @@ def test_full_size_beatgans_properties():
     assert sv[-2] > 1e-3 * sv[0] and sv[-1] < 1e-4 * sv[0]     # centred K x D matrix with K < D has rank K - 1
     r2 = spectrum_from_rows(S, K, 12288, -2.0 / std)
     np.testing.assert_allclose(r2.singular_values[0, :-1].cpu().numpy(), 2 * sv[:-1], rtol=1e-5)
+
+
+def test_drop_in_runs_the_papers_squares_config_shape_from_the_synthetic_datamodule(tmp_path):
+    """configs/dimension_estimation/paper/image_data/squares/10.py end to end at a reduced width: data module
+    'Synthetic' / FixedSquaresManifold (anchors from its shuffled train loader, as dim_reduction.py:150-163 takes
+    them), model.name='ddpm' on 1x32x32, checkpoint, pickle out."""
+    import pickle
+    from iddiff_b200 import dim_reduction as DR, unet_models
+    spec = FX.DDPM_GRAY_SMALL
+    holder = unet_models.get_model("ddpm")(FX.unet_config(spec, "ddpm"))
+    state = FX.make_unet_state(holder, 23)
+    ckpt = tmp_path / "last.ckpt"
+    torch.save({"state_dict": {"score_model." + k: v for k, v in state.items()}}, ckpt)
+    cfg = FX.unet_config(spec, "ddpm")
+    cfg.seed = 42
+    cfg.logging = dict(log_path=str(tmp_path), log_name="squares", svd_points=3)
+    cfg.dim_estimation = {}
+    cfg.device = "cuda:0"
+    cfg.training.batch_size = 16
+    cfg.training.workers = 0
+    cfg.training.lightning_module = "base"
+    cfg.data.update(dict(datamodule="Synthetic", dataset_type="FixedSquaresManifold", data_samples=64,
+                         split=[0.75, 0.125, 0.125], image_size=32, num_squares=10, square_range=[3, 5],
+                         return_labels=False, shape=[1, 32, 32], use_data_mean=False))
+    cfg.model.checkpoint_path = str(ckpt)
+    torch.manual_seed(0)
+    assert DR.get_manifold_dimension(cfg, name="squares") is None
+    with open(tmp_path / "squares" / "svd" / "squares.pkl", "rb") as f:
+        sv = np.asarray(pickle.load(f)["singular_values"])
+    assert sv.shape == (2, 1024) and np.isfinite(sv).all() and np.all(np.diff(sv, axis=1) <= 0) and sv[:, 0].min() > 0
