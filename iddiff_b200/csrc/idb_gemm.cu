@@ -32,11 +32,33 @@ constexpr int GEMM_THREADS = 64 + EPI_THREADS;
 constexpr size_t GEMM_SMEM = 1024 /*align slack*/ + (size_t)STAGES * STAGE_BYTES + 2 * 2 * BN * sizeof(float) + 256;
 
 
+// 32-byte store of two 16-byte halves (first -> lower address); dst 32-byte aligned
+__device__ __forceinline__ void st_global_256(void* dst, const uint32_t* first, const uint32_t* second) {
+    asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst), "r"(first[0]), "r"(first[1]),
+                 "r"(first[2]), "r"(first[3]), "r"(second[0]), "r"(second[1]), "r"(second[2]), "r"(second[3])
+                 : "memory");
+}
+
+// expm1 for the deviation argument: |d| is small on this path (perturbations of size sigma around the anchor), so the
+// common case is a degree-6 Taylor polynomial in Horner form (|d| < 1/16: truncation d^6/5040 < 1.2e-11 relative, below
+// half an fp32 ulp) -- 6 FMAs instead of expm1f's ~25 instructions in the epilogue that bounds the first layer.
+__device__ __forceinline__ float expm1_small(float d) {
+    if (fabsf(d) < 0.0625f) {
+        float q = fmaf(d, 1.f / 720.f, 1.f / 120.f);
+        q = fmaf(d, q, 1.f / 24.f);
+        q = fmaf(d, q, 1.f / 6.f);
+        q = fmaf(d, q, 0.5f);
+        q = fmaf(d, q, 1.f);
+        return d * q;
+    }
+    return expm1f(d);
+}
+
 // ELU(a + d) - ELU(a) without cancellation; em1 = expm1(a) (only read when a <= 0).
 __device__ __forceinline__ float elu_deviation(float a, float em1, float d) {
     const float s = a + d;
     if (a > 0.f) return s > 0.f ? d : expm1f(s) - a;
-    return s > 0.f ? s - em1 : (em1 + 1.f) * expm1f(d);
+    return s > 0.f ? s - em1 : (em1 + 1.f) * expm1_small(d);
 }
 
 template <int kMode>
@@ -184,12 +206,15 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_bf16x3_kernel(const Gemm
                     uint8_t* row_hi = p.out_hi + ((n >> 6) * (size_t)p.M + m) * 128;
                     uint8_t* row_lo = p.out_lo + ((n >> 6) * (size_t)p.M + m) * 128;
                     const int chunk0 = (int)((n & 63) >> 3);
+                    // Two adjacent 16-byte chunks of the swizzled 128-byte row differ only in bit 0 of the chunk index, so a
+                    // pair is one aligned 32-byte sector: one 256-bit store per pair (halves swapped on odd rows) writes
+                    // whole sectors instead of two half-filled ones.
 #pragma unroll
-                    for (int ch = 0; ch < 4; ++ch) {
-                        uint32_t h[4], l[4];
+                    for (int pp = 0; pp < 2; ++pp) {
+                        uint32_t h[8], l[8];
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            const int c = ch * 8 + j * 2;
+                        for (int j = 0; j < 8; ++j) {
+                            const int c = pp * 16 + j * 2;
                             float e0, e1;
                             if (kMode == 0) {
                                 e0 = elu_deviation(sa[c], se[c], __uint_as_float(v[c]));
@@ -201,9 +226,11 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_bf16x3_kernel(const Gemm
                             }
                             split_pair16(e0 * p.out_scale, e1 * p.out_scale, p.fmt, h[j], l[j]);
                         }
-                        const int sw = ((chunk0 + ch) ^ (int)(m & 7)) << 4;
-                        *reinterpret_cast<uint4*>(row_hi + sw) = make_uint4(h[0], h[1], h[2], h[3]);
-                        *reinterpret_cast<uint4*>(row_lo + sw) = make_uint4(l[0], l[1], l[2], l[3]);
+                        const int c0 = (chunk0 + 2 * pp) ^ (int)(m & 7);       // swizzled position of the pair's first chunk
+                        const int off = (c0 & ~1) << 4;
+                        const bool swap = c0 & 1;
+                        st_global_256(row_hi + off, swap ? h + 4 : h, swap ? h : h + 4);
+                        st_global_256(row_lo + off, swap ? l + 4 : l, swap ? l : l + 4);
                     }
                 }
             }
