@@ -47,6 +47,17 @@ __device__ __forceinline__ void tma_tensor5d_g2s(void* smem_dst, const CUtensorM
 }
 }  // namespace
 
+__device__ __forceinline__ void st_global_256f(float* dst, const float (&o)[8]) {
+    asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst), "f"(o[0]), "f"(o[1]), "f"(o[2]),
+                 "f"(o[3]), "f"(o[4]), "f"(o[5]), "f"(o[6]), "f"(o[7])
+                 : "memory");
+}
+__device__ __forceinline__ void ld_global_nc_256(const float* src, float (&q)[8]) {
+    asm volatile("ld.global.nc.v8.f32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=f"(q[0]), "=f"(q[1]), "=f"(q[2]), "=f"(q[3]), "=f"(q[4]), "=f"(q[5]), "=f"(q[6]), "=f"(q[7])
+                 : "l"(src));
+}
+
 template <int BN>
 __global__ void __launch_bounds__(C_THREADS, 1) conv_fp16x3_kernel(const __grid_constant__ ConvParams p) {
     using Cfg = ConvCfg<BN>;
@@ -148,6 +159,7 @@ __global__ void __launch_bounds__(C_THREADS, 1) conv_fp16x3_kernel(const __grid_
         const int quarter = warp & 3;
         const int cgroup = (warp - 2) >> 2;
         const int r = quarter * 32 + lane;  // row of the tile = TMEM lane = output pixel
+        const bool ptrs32 = ((reinterpret_cast<uintptr_t>(p.out) | reinterpret_cast<uintptr_t>(p.residual)) & 31) == 0;
         int it = 0;
         for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
             const int as = it & 1;
@@ -172,7 +184,26 @@ __global__ void __launch_bounds__(C_THREADS, 1) conv_fp16x3_kernel(const __grid_
                 if (!row_ok) continue;
                 float* dst = p.out + pix * p.ldo + c0;
                 const float* res = p.residual ? p.residual + pix * p.ld_res + c0 : nullptr;
-                if (c0 + 32 <= p.Cout && (p.ldo & 3) == 0 && (!res || (p.ld_res & 3) == 0)) {
+                if (c0 + 32 <= p.Cout && (p.ldo & 7) == 0 && (!res || (p.ld_res & 7) == 0) && ptrs32) {
+                    // a thread owns 128 contiguous bytes of its pixel: 256-bit accesses move whole 32-byte sectors
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        float o[8], q[8];
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) {
+                            const float b = p.bias ? __ldg(p.bias + c0 + 8 * j + e) : 0.f;
+                            o[e] = __uint_as_float(v[8 * j + e]) * p.acc_scale + b;
+                        }
+                        if (res) {
+                            ld_global_nc_256(res + 8 * j, q);
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) o[e] += q[e];
+                        }
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) o[e] *= p.out_scale;
+                        st_global_256f(dst + 8 * j, o);
+                    }
+                } else if (c0 + 32 <= p.Cout && (p.ldo & 3) == 0 && (!res || (p.ld_res & 3) == 0)) {
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {
                         float4 o;
