@@ -122,15 +122,94 @@ __global__ void __launch_bounds__(256) center_gram_kernel(const float* __restric
     }
 }
 
+// 40-wide tiles (5 warps, each one 8-row strip of 5 MMA tiles) for column counts that pad badly to 64: D = 200 is
+// exactly 5 x 40, so the upper triangle costs 15 x 40^2 = 24 000 outputs instead of 10 x 64^2 = 40 960 -- the stage is
+// bound by the fp64 tensor pipe, so that ratio is its time.
+constexpr int CG40 = 40;
+constexpr int CG40_LD = 52;   // row stride = 4 (mod 16) doubles: the 4 k-rows of a half-warp's fragment load hit disjoint banks
+
+__global__ void __launch_bounds__(160) center_gram40_kernel(const float* __restrict__ X, long long anchor_stride, int ld,
+                                                            int K, int D, double scale,
+                                                            const double* __restrict__ colmean, double* __restrict__ G) {
+    __shared__ double sA[16][CG40_LD];
+    __shared__ double sB[16][CG40_LD];
+    const int T = (D + CG40 - 1) / CG40;
+    int ti = 0, rem = blockIdx.x;
+    while (rem >= T - ti) { rem -= T - ti; ++ti; }
+    const int tj = ti + rem;
+    const int a = blockIdx.y;
+    const float* Xa = X + (size_t)a * anchor_stride;
+    const double* mu = colmean + (size_t)a * D;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int i0 = warp * 8;
+    const int fr = lane >> 2, fk = lane & 3;
+    double acc[5][2];
+#pragma unroll
+    for (int n = 0; n < 5; ++n) acc[n][0] = acc[n][1] = 0.0;
+    const int skk = threadIdx.x / 10, sc = (threadIdx.x % 10) << 2;   // 16 k-rows x 10 groups of 4 columns
+    double mua[4], mub[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const int ca = ti * CG40 + sc + q, cb = tj * CG40 + sc + q;
+        mua[q] = ca < D ? mu[ca] : 0.0;
+        mub[q] = cb < D ? mu[cb] : 0.0;
+    }
+    for (int k0 = 0; k0 < K; k0 += 16) {
+        const int k = k0 + skk;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int ca = ti * CG40 + sc + q, cb = tj * CG40 + sc + q;
+            double va = 0.0, vb = 0.0;
+            if (k < K) {
+                if (ca < D) va = ((double)__ldg(Xa + (size_t)k * ld + ca) - mua[q]) * scale;
+                if (cb < D) vb = ((double)__ldg(Xa + (size_t)k * ld + cb) - mub[q]) * scale;
+            }
+            sA[skk][sc + q] = va;
+            sB[skk][sc + q] = vb;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k4 = 0; k4 < 16; k4 += 4) {
+            const double af = sA[k4 + fk][i0 + fr];
+            double bf[5];
+#pragma unroll
+            for (int n = 0; n < 5; ++n) bf[n] = sB[k4 + fk][n * 8 + fr];
+#pragma unroll
+            for (int n = 0; n < 5; ++n) dmma884(acc[n][0], acc[n][1], af, bf[n]);
+        }
+        __syncthreads();
+    }
+    double* Ga = G + (size_t)a * D * D;
+    const int r = ti * CG40 + i0 + fr;
+    if (r >= D) return;
+#pragma unroll
+    for (int n = 0; n < 5; ++n)
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            const int c = tj * CG40 + n * 8 + 2 * fk + q;
+            if (c >= D) continue;
+            Ga[(size_t)r * D + c] = acc[n][q];
+            if (ti != tj) Ga[(size_t)c * D + r] = acc[n][q];
+        }
+}
+
 cudaError_t launch_center_gram(const float* X, long long anchor_stride, int ld, int n_anchors, int K, int D,
                                double scale, double* colmean, double* G, cudaStream_t stream) {
     if (n_anchors <= 0 || D <= 0) return cudaSuccess;
     colmean_kernel<<<dim3((D + 31) / 32, n_anchors), 256, 0, stream>>>(X, anchor_stride, ld, K, D, colmean);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    const int T = (D + 63) / 64;
-    center_gram_kernel<<<dim3(T * (T + 1) / 2, n_anchors), 256, 0, stream>>>(X, anchor_stride, ld, K, D, scale,
-                                                                             colmean, G);
+    const int T = (D + 63) / 64, T40 = (D + CG40 - 1) / CG40;
+    const long long cost64 = (long long)T * (T + 1) / 2 * 64 * 64, cost40 = (long long)T40 * (T40 + 1) / 2 * CG40 * CG40;
+    // padded outputs computed; the narrow tiles have a worse shared-load : MMA ratio (6 : 5 against 6 : 8), so they only pay
+    // where they save >= 40 % of the outputs (measured: D = 200 0.82 -> 0.71 ms per 128 anchors, D = 100 0.31 -> 0.33)
+    if (cost40 * 100 < cost64 * 60) {
+        center_gram40_kernel<<<dim3(T40 * (T40 + 1) / 2, n_anchors), 160, 0, stream>>>(X, anchor_stride, ld, K, D, scale,
+                                                                                      colmean, G);
+    } else {
+        center_gram_kernel<<<dim3(T * (T + 1) / 2, n_anchors), 256, 0, stream>>>(X, anchor_stride, ld, K, D, scale,
+                                                                                 colmean, G);
+    }
     return cudaGetLastError();
 }
 
