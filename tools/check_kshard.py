@@ -20,7 +20,6 @@ def main():
     ap.add_argument("--model", default="beatgans")
     ap.add_argument("--K", type=int, default=4096)
     args = ap.parse_args()
-    os.environ.setdefault("NCCL_DEBUG", "WARN")
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
