@@ -107,25 +107,45 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
-def cpu_reference_run(model, anchors, budget_s, max_anchors):
-    """The reference's algorithm for this path on the host cores (oracle port: same ATen/MKL/LAPACK back-ends the
-    reference's CPU path uses, dim_reduction.py:150-206).  Runs anchors one by one until `budget_s` is spent.
-    The ONLY place bench.py touches oracle/: as the timed CPU baseline, never on the product path."""
-    from oracle import id_oracle as O
+def cpu_reference_run(model, anchors, budget_s, max_anchors, per_call=4):
+    """The reference's CPU implementation of this path on the host cores.  kind "reference": the UNMODIFIED
+    dim_reduction.get_manifold_dimension (imported from /root/reference here, from the git-ignored copy oracle/_ref on
+    the GPU box -- oracle/build_ref.sh) with an injected loader, `per_call` anchors per call; kind "port": the oracle
+    restatement (same ATen/MKL/LAPACK back-ends), only when no copy of the reference is present.  Runs until
+    `budget_s` is spent.  The ONLY place bench.py touches oracle/: as the timed CPU baseline, never on the product path."""
     torch.set_num_threads(os.cpu_count() or 1)
-    lin = [m for m in model.mlp if isinstance(m, torch.nn.Linear)]
-    ws, bs = [m.weight.detach() for m in lin], [m.bias.detach() for m in lin]
-    params = dict(sigma_min=SIGMA_MIN, sigma_max=SIGMA_MAX)
-    score_fn = O.make_score_fn("fcn", "vesde", params, N=N_SCALES, fcn_params=(ws, bs))
-    torch.manual_seed(1234)
+    from oracle import ref_runner as RR
     done, t0 = 0, time.perf_counter()
-    with torch.no_grad():
-        while done < max_anchors and (done < 2 or time.perf_counter() - t0 < budget_s):
-            batch = anchors[done:done + 1].repeat(B_LOADER, 1)  # one loader batch whose first row is the anchor
-            O.manifold_dimension([batch], 2, score_fn, "vesde", params)
-            done += 1
+    if RR.available():
+        ref = RR.FcnReference({k: v.detach().cpu() for k, v in model.state_dict().items()}, D, H, L, B_LOADER,
+                              SIGMA_MIN, SIGMA_MAX)
+        t0 = time.perf_counter()
+        while done < max_anchors and (done == 0 or time.perf_counter() - t0 < budget_s):
+            n = min(per_call, max_anchors - done)
+            ref.run(anchors[done:done + n])
+            done += n
+        kind = "reference"
+    else:
+        from oracle import id_oracle as O
+        lin = [m for m in model.mlp if isinstance(m, torch.nn.Linear)]
+        ws, bs = [m.weight.detach() for m in lin], [m.bias.detach() for m in lin]
+        params = dict(sigma_min=SIGMA_MIN, sigma_max=SIGMA_MAX)
+        score_fn = O.make_score_fn("fcn", "vesde", params, N=N_SCALES, fcn_params=(ws, bs))
+        torch.manual_seed(1234)
+        with torch.no_grad():
+            while done < max_anchors and (done < 2 or time.perf_counter() - t0 < budget_s):
+                batch = anchors[done:done + 1].repeat(B_LOADER, 1)  # one loader batch whose first row is the anchor
+                O.manifold_dimension([batch], 2, score_fn, "vesde", params)
+                done += 1
+        kind = "port"
     dt = time.perf_counter() - t0
-    return done / dt, done, dt, torch.get_num_threads()
+    return done / dt, done, dt, torch.get_num_threads(), kind
+
+
+CPU_KIND_TEXT = {"reference": "the UNMODIFIED reference dim_reduction.get_manifold_dimension (dim_reduction.py:116-211; "
+                              "module build + checkpoint load + autograd graphs + full LAPACK SVD included) on torch CPU",
+                 "port": "oracle port of dim_reduction.py:150-206 on torch CPU (ATen/MKL + LAPACK gesdd); no copy of "
+                         "the reference present (oracle/_ref missing)"}
 
 
 def run_reference_arm(args):
@@ -141,9 +161,9 @@ def run_reference_arm(args):
         off += per_step
     t0 = time.perf_counter()
     n = 0
-    cores = 1
+    cores, kind = 1, "port"
     for _ in range(args.steps):
-        _, done, _, cores = cpu_reference_run(model, anchors[off:off + per_step], 1e9, per_step)
+        _, done, _, cores, kind = cpu_reference_run(model, anchors[off:off + per_step], 1e9, per_step)
         off += per_step
         n += done
     dt = time.perf_counter() - t0
@@ -153,9 +173,8 @@ def run_reference_arm(args):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": workload_config(args, per_step),
             "score_evals_per_s": v * K,
-            "cpu_baseline": {"value": v, "unit": "anchors/s", "cores": cores, "kind": "port",
-                             "sample": f"{per_step} anchors per step x {args.steps} steps, K={K}, oracle port of "
-                                       "dim_reduction.py:150-206 on torch CPU (ATen/MKL + LAPACK gesdd)"},
+            "cpu_baseline": {"value": v, "unit": "anchors/s", "cores": cores, "kind": kind,
+                             "sample": f"{per_step} anchors per step x {args.steps} steps, K={K}, " + CPU_KIND_TEXT[kind]},
             "e2e": {"value": v, "unit": "anchors/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -165,7 +184,7 @@ def workload_config(args, anchors_per_rank):
     return {"workload": "BASELINE configs[1]: 50-sphere in R^200, FCN score net (H=2048, L=5, random-init seed 0), "
                         f"VESDE sigma_min=0.01 t=1e-5, K={K} perturbations per anchor",
             "anchors_per_gpu_per_step": anchors_per_rank, "K": K, "D": D, "H": H, "L": L,
-            "parallelism": f"anchors sharded over {args.gpus} GPU(s), one all-gather of spectra per step",
+            "parallelism": f"anchors sharded over {args.gpus} GPU(s), ONE all-gather per step (spectra + bit-cast IDs packed [A, n+1]), on a side stream",
             "l2": "inputs_exceed_l2 (activations of one chunk are GBs; 126 MB L2)"}
 
 
@@ -202,32 +221,52 @@ def run_ours(args):
     sde = sde_lib.VESDE(sigma_min=SIGMA_MIN, sigma_max=SIGMA_MAX, N=N_SCALES)
     mc, std = sde.coefficients(T_EPS)
     label = float((torch.ones(1) * T_EPS * (sde.N - 1))[0])
-    anchors_all = make_anchors(A * world)                   # same on every rank (seeded); rank takes its shard
-    host_shard = anchors_all[rank * A:(rank + 1) * A].contiguous().pin_memory()
-    dev_shard = host_shard.to(dev)
     n_sv = min(K, D)
-    gathered_sv = torch.empty(world * A, n_sv, device=dev) if world > 1 else None
-    gathered_dims = torch.empty(world * A, dtype=torch.int32, device=dev) if world > 1 else None
+    comm = torch.cuda.Stream(device=dev) if world > 1 else None
 
-    def step_device(step_idx):
-        """Inputs resident in HBM; spectra and IDs stay on the device (all-gathered when world > 1)."""
-        svs, dims = [], []
-        for s in range(0, A, chunk):
-            r = eng.estimate(dev_shard[s:s + chunk], K, mc, std, label, seed=step_idx, anchor_id0=rank * A + s,
-                             defer=args.overlap)
-            svs.append(r.singular_values)
-            dims.append(r.dims)
-        eng.join()
-        step_device.sweeps = r.sweeps
-        sv, dm = torch.cat(svs), torch.cat(dims)
-        if world > 1:
-            dist.all_gather_into_tensor(gathered_sv, sv)
-            dist.all_gather_into_tensor(gathered_dims, dm)
-        return sv, dm
+    class Shard:
+        """This rank's anchors + the pre-allocated result buffers of one workload size (a anchors per GPU).  Results of a
+        step are PACKED as [a, n_sv + 1] fp32 -- the spectra and, bit-cast in the last column, the int32 IDs -- so the
+        path's one collective is ONE all-gather; it runs on a side stream and overlaps the next step (two buffers)."""
 
-    def step_e2e(step_idx):
-        """Public API with HOST buffers: pinned anchors in, spectra + IDs back on the host."""
-        return estimate_anchors(eng, host_shard, K, sde, T_EPS, seed=step_idx, chunk=chunk, anchor_id0=rank * A)
+        def __init__(self, a):
+            self.a = a
+            anchors_all = make_anchors(a * world)               # same on every rank (seeded); rank takes its shard
+            self.anchors_all = anchors_all
+            self.host = anchors_all[rank * a:(rank + 1) * a].contiguous().pin_memory()
+            self.dev = self.host.to(dev)
+            self.packed = [torch.empty(a, n_sv + 1, device=dev) for _ in range(2)]
+            self.gathered = [torch.empty(world * a, n_sv + 1, device=dev) for _ in range(2)] if world > 1 else None
+            self.done = [None, None]
+
+        def step(self, step_idx):
+            """Inputs resident in HBM; spectra and IDs stay on the device (all-gathered when world > 1)."""
+            b = step_idx & 1
+            if self.done[b] is not None:
+                torch.cuda.current_stream().wait_event(self.done[b])   # the gather that last read this buffer
+            out = self.packed[b]
+            ck = min(chunk, self.a)
+            for s in range(0, self.a, ck):
+                r = eng.estimate(self.dev[s:s + ck], K, mc, std, label, seed=step_idx, anchor_id0=rank * self.a + s,
+                                 defer=args.overlap)
+                if args.overlap:
+                    eng.join()
+                out[s:s + ck, :n_sv].copy_(r.singular_values)
+                out[s:s + ck, n_sv].copy_(r.dims.view(torch.float32))
+            self.sweeps = r.sweeps
+            if world > 1:
+                ready = torch.cuda.Event()
+                ready.record()
+                comm.wait_event(ready)
+                with torch.cuda.stream(comm):
+                    dist.all_gather_into_tensor(self.gathered[b], out)
+                    self.done[b] = torch.cuda.Event()
+                    self.done[b].record()
+            return out
+
+        def finish(self):
+            if world > 1:
+                torch.cuda.current_stream().wait_stream(comm)
 
     def barrier():
         if world > 1:
@@ -241,9 +280,21 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t[0])
 
+    def timed_steps(shard, n_steps, first_idx):
+        barrier()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        for i in range(n_steps):
+            out = shard.step(first_idx + i)
+        shard.finish()
+        ev1.record()
+        barrier()
+        return out, max_over_ranks(ev0.elapsed_time(ev1))
+
+    main_shard = Shard(A)
     for i in range(args.warmup):
-        step_device(i)
-    barrier()
+        main_shard.step(i)
+    main_shard.finish()
 
     # ---- timed region: EXACTLY `steps` device-resident steps, CUDA events on the launching stream
     sampler = ClockSampler(local)
@@ -251,39 +302,73 @@ def run_ours(args):
         sampler.start()
     E.EVENT_LOG = {}
     launches0 = _lib.launch_count
-    barrier()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record()
-    for i in range(args.steps):
-        sv, dm = step_device(args.warmup + i)
-    ev1.record()
-    barrier()
-    ms_total = max_over_ranks(ev0.elapsed_time(ev1))
+    out, ms_total = timed_steps(main_shard, args.steps, args.warmup)
     launches = _lib.launch_count - launches0
     clocks = sampler.stop() if rank == 0 else None
     log, E.EVENT_LOG = E.EVENT_LOG, None
+    sv, dm = out[:, :n_sv], out[:, n_sv].contiguous().view(torch.int32)
     stages = {}
     for name, evs in log.items():
         ms = [a.elapsed_time(b) for a, b, _ in evs]
         stages[name] = {"launches": len(ms), "ms_total": sum(ms), "ms_avg": sum(ms) / len(ms),
                         "work_per_launch": evs[0][2]}
 
-    # ---- e2e: same steps through the public API with host buffers (copies inside the timed region)
+    # ---- e2e: same steps through the public API with host buffers (copies AND the all-gather inside the timed region)
+    grp = dist.group.WORLD if world > 1 else None
+
+    def step_e2e(step_idx):
+        return estimate_anchors(eng, main_shard.host, K, sde, T_EPS, seed=step_idx, chunk=chunk, anchor_id0=rank * A,
+                                gather_group=grp, n_total=A * world)
+
     step_e2e(0)
     barrier()
     t0 = time.perf_counter()
     for i in range(args.steps):
-        out = step_e2e(args.warmup + i)
+        res = step_e2e(args.warmup + i)
     barrier()
     e2e_s = max_over_ranks(time.perf_counter() - t0)
-    h2d = host_shard.numel() * 4
-    d2h = sum(v.numel() * v.element_size() for v in out.values())
+    h2d = main_shard.host.numel() * 4
+    d2h = sum(v.numel() * v.element_size() for v in res.values())
+
+    # ---- strong scaling: a FIXED 4096 anchors split over the ranks (N = 1: one GPU takes them all)
+    strong = None
+    if args.strong_anchors > 0 and args.strong_anchors % world == 0:
+        sh = Shard(args.strong_anchors // world)
+        sh.step(0)
+        sh.finish()
+        _, ms_strong = timed_steps(sh, 2, 1)
+        strong = {"anchors_total": args.strong_anchors, "anchors_per_gpu": args.strong_anchors // world,
+                  "ms_per_step": ms_strong / 2, "value": args.strong_anchors * 2 / (ms_strong / 1e3), "unit": "anchors/s",
+                  "scaling": "strong"}
+        del sh
+
+    peaks, peak_src = measured_peaks()
+    extra = {}
+    main_sweeps = main_shard.sweeps.cpu()
+    anchors_cpu = main_shard.anchors_all
+    sv, dm = sv.clone(), dm.clone()
+    if args.extra:
+        del main_shard, out
+        torch.cuda.empty_cache()
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import extra_workloads as XW
+        try:
+            if world == 1:
+                extra["C1_ksphere"] = XW.ksphere_c1(dev)
+                extra["C4_ncsnpp"] = XW.image_config("ncsnpp", dev, peaks, K=4096)
+                extra["C5_beatgans"] = XW.image_config("beatgans", dev, peaks, K=4096)
+            else:   # config 5 across GPUs: ONE anchor, its K rows sharded over the ranks (partial Grams + all-reduce)
+                extra["C5_beatgans_k_sharded"] = XW.image_config("beatgans", dev, peaks, K=4096, cpu_images=0,
+                                                                 group=dist.group.WORLD)
+                extra["C5_beatgans_k_sharded_K16768"] = XW.image_config("beatgans", dev, peaks, K=16768, cpu_images=0,
+                                                                        group=dist.group.WORLD)
+        except Exception as exc:   # the headline line must still be printed
+            extra["error"] = f"{type(exc).__name__}: {exc}"
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
-    peaks, peak_src = measured_peaks()
     total_anchors = A * world * args.steps
     value = total_anchors / (ms_total / 1e3)
     hid = stages["hidden"]
@@ -305,16 +390,16 @@ def run_ours(args):
                                    else ""), "config": workload_config(args, A),
             "score_evals_per_s": value * K, "score_net_tflops_algorithmic": value * K * FLOPS_PER_EVAL / 1e12,
             "sanity": {"dims_head": dm[:8].cpu().tolist(), "sv0": float(sv[0, 0]), "sv_last": float(sv[0, -1]),
-                       "jacobi_sweeps_max": int(step_device.sweeps.max())},
+                       "jacobi_sweeps_max": int(main_sweeps.max())},
             "stages_ms_per_step": {k: v["ms_total"] / args.steps for k, v in stages.items()},
             "roofline": roofline, "clocks": clocks, "gpu_launches": launches,
             "e2e": {"value": total_anchors / e2e_s, "unit": "anchors/s", "h2d_bytes_per_step": h2d,
-                    "d2h_bytes_per_step": d2h}}
+                    "d2h_bytes_per_step": d2h},
+            "strong_scaling": strong, "extra_workloads": extra}
     if world == 1 and not args.no_cpu_baseline:
-        v, done, dt, cores = cpu_reference_run(model, anchors_all, args.cpu_budget_s, 64)
-        line["cpu_baseline"] = {"value": v, "unit": "anchors/s", "cores": cores, "kind": "port",
-                                "sample": f"{done} anchors of the same workload (K={K}) in {dt:.1f} s, oracle port of "
-                                          "dim_reduction.py:150-206 on torch CPU"}
+        v, done, dt, cores, kind = cpu_reference_run(model, anchors_cpu, args.cpu_budget_s, 64)
+        line["cpu_baseline"] = {"value": v, "unit": "anchors/s", "cores": cores, "kind": kind,
+                                "sample": f"{done} anchors of the same workload (K={K}) in {dt:.1f} s, " + CPU_KIND_TEXT[kind]}
     else:
         line["cpu_baseline"] = None
     print(json.dumps(line), flush=True)
@@ -335,6 +420,8 @@ def main():
     ap.add_argument("--short-train", type=int, default=0, help="untimed set-up: this many denoising-score-matching steps "
                     "(tools/train_fcn.py, rank 0, broadcast) before the bench, so that the reported dims are the "
                     "sphere's (51) instead of a random network's; same arithmetic per step either way")
+    ap.add_argument("--extra", type=int, default=1, help="0: skip the extra_workloads (C1 / C4 / C5, K-sharded at N > 1)")
+    ap.add_argument("--strong-anchors", type=int, default=4096, help="fixed anchor count of the strong-scaling leg (0: skip)")
     ap.add_argument("--overlap", type=int, default=0, help="1: spectrum stage of chunk i on a second stream, overlapping "
                     "the GEMM chain of chunk i+1 (measured: no gain -- the persistent GEMM CTAs own every SM's shared memory)")
     args = ap.parse_args()

@@ -164,6 +164,22 @@ int idb_center_gram(const float* X, long long anchor_stride, int ld, int n_ancho
                  "idb_center_gram");
 }
 
+int idb_column_sums(const float* X, long long anchor_stride, int ld, int n_anchors, int K, int D, double* colsum,
+                    void* stream) {
+    if (!X || !colsum || n_anchors < 0 || K <= 0 || D <= 0 || ld < D) return fail("idb_column_sums: bad argument");
+    return check(idb::launch_column_sums(X, anchor_stride, ld, n_anchors, K, D, 1.0, colsum,
+                                         static_cast<cudaStream_t>(stream)),
+                 "idb_column_sums");
+}
+
+int idb_gram_about(const float* X, long long anchor_stride, int ld, int n_anchors, int K, int D, double scale,
+                   const double* center, double* G, void* stream) {
+    if (!X || !center || !G || n_anchors < 0 || K <= 0 || D <= 0 || ld < D) return fail("idb_gram_about: bad argument");
+    return check(idb::launch_gram_about(X, anchor_stride, ld, n_anchors, K, D, scale, center, G,
+                                        static_cast<cudaStream_t>(stream)),
+                 "idb_gram_about");
+}
+
 size_t idb_spectrum_workspace_bytes(int n_anchors, int n) {
     if (n_anchors <= 0 || n <= 0) return 256;
     const size_t a = idb::spectrum_workspace_bytes(n_anchors, n), b = idb::tridiag_workspace_bytes(n_anchors, n);

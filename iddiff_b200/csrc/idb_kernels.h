@@ -60,6 +60,10 @@ cudaError_t launch_ksphere_score(const float* x, const float* sigma_or_null, flo
                                  int manifold_dim, float* out, cudaStream_t stream);
 
 // column means (fp64) and centred Gram G = (scale (X - mean))^T (scale (X - mean)) in fp64
+cudaError_t launch_column_sums(const float* X, long long anchor_stride, int ld, int n_anchors, int K, int D,
+                               double divisor, double* out, cudaStream_t stream);
+cudaError_t launch_gram_about(const float* X, long long anchor_stride, int ld, int n_anchors, int K, int D,
+                              double scale, const double* colmean, double* G, cudaStream_t stream);
 cudaError_t launch_center_gram(const float* X, long long anchor_stride, int ld, int n_anchors, int K, int D,
                                double scale, double* colmean, double* G, cudaStream_t stream);
 

@@ -16,7 +16,7 @@ namespace idb {
 
 // ---------------------------------- column means --------------------------------------------
 __global__ void __launch_bounds__(256) colmean_kernel(const float* __restrict__ X, long long anchor_stride, int ld,
-                                                      int K, int D, double* __restrict__ colmean) {
+                                                      int K, int D, double divisor, double* __restrict__ colmean) {
     __shared__ double s_part[8][33];
     const int c = blockIdx.x * 32 + (threadIdx.x & 31);
     const int rg = threadIdx.x >> 5;
@@ -30,7 +30,7 @@ __global__ void __launch_bounds__(256) colmean_kernel(const float* __restrict__ 
         double t = 0.0;
 #pragma unroll
         for (int i = 0; i < 8; ++i) t += s_part[i][threadIdx.x];
-        colmean[(size_t)blockIdx.y * D + c] = t / (double)K;
+        colmean[(size_t)blockIdx.y * D + c] = t / divisor;
     }
 }
 
@@ -193,12 +193,24 @@ __global__ void __launch_bounds__(160) center_gram40_kernel(const float* __restr
         }
 }
 
+cudaError_t launch_column_sums(const float* X, long long anchor_stride, int ld, int n_anchors, int K, int D,
+                               double divisor, double* out, cudaStream_t stream) {
+    if (n_anchors <= 0 || D <= 0) return cudaSuccess;
+    colmean_kernel<<<dim3((D + 31) / 32, n_anchors), 256, 0, stream>>>(X, anchor_stride, ld, K, D, divisor, out);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_center_gram(const float* X, long long anchor_stride, int ld, int n_anchors, int K, int D,
                                double scale, double* colmean, double* G, cudaStream_t stream) {
-    if (n_anchors <= 0 || D <= 0) return cudaSuccess;
-    colmean_kernel<<<dim3((D + 31) / 32, n_anchors), 256, 0, stream>>>(X, anchor_stride, ld, K, D, colmean);
-    cudaError_t e = cudaGetLastError();
+    cudaError_t e = launch_column_sums(X, anchor_stride, ld, n_anchors, K, D, (double)K, colmean, stream);
     if (e != cudaSuccess) return e;
+    return launch_gram_about(X, anchor_stride, ld, n_anchors, K, D, scale, colmean, G, stream);
+}
+
+// Gram of the rows about a GIVEN centre vector (the K-sharded mode passes the all-reduced global column mean)
+cudaError_t launch_gram_about(const float* X, long long anchor_stride, int ld, int n_anchors, int K, int D,
+                              double scale, const double* colmean, double* G, cudaStream_t stream) {
+    if (n_anchors <= 0 || D <= 0) return cudaSuccess;
     const int T = (D + 63) / 64, T40 = (D + CG40 - 1) / CG40;
     const long long cost64 = (long long)T * (T + 1) / 2 * 64 * 64, cost40 = (long long)T40 * (T40 + 1) / 2 * CG40 * CG40;
     // padded outputs computed; the narrow tiles have a worse shared-load : MMA ratio (6 : 5 against 6 : 8), so they only pay

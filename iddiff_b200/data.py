@@ -81,6 +81,17 @@ class KSphereDataModule:
         return DataLoader(self.train_data, batch_size=t.batch_size, num_workers=getattr(t, "workers", 0),
                           shuffle=True)
 
+    def _eval_loader(self, data, section, shuffle):
+        v = getattr(self.config, section, None)
+        B = getattr(v, "batch_size", None) or self.config.training.batch_size
+        return DataLoader(data, batch_size=B, num_workers=getattr(v, "workers", 0) or 0, shuffle=shuffle)
+
+    def val_dataloader(self):   # KSphereDataset.py:131-132 (shuffle=True there too)
+        return self._eval_loader(self.valid_data, "validation", True)
+
+    def test_dataloader(self):  # KSphereDataset.py:134-135
+        return self._eval_loader(self.test_data, "eval", False)
+
 
 @register_lightning_datamodule("Tensor")
 class TensorDataModule:

@@ -47,6 +47,18 @@ def gather_anchors(loader, num_datapoints: int):
     return out
 
 
+def batch_size_runs(sizes: Sequence[int]):
+    """Maximal runs of CONSECUTIVE anchors that share a loader batch size (hence K): [(B, [i, i+1, ...])].  One
+    device batch per run keeps the Philox key of every anchor equal to its global index, whatever the grouping."""
+    runs: List = []
+    for i, B in enumerate(sizes):
+        if runs and runs[-1][0] == B:
+            runs[-1][1].append(i)
+        else:
+            runs.append((B, [i]))
+    return runs
+
+
 def build_engine(config, score_model: Optional[torch.nn.Module] = None, device="cuda"):
     """Recognises the model class by config.model.name and ingests its weights into a device engine."""
     name = config.model.name
@@ -96,21 +108,33 @@ def shard_range(n_anchors: int, rank: int, world: int):
     return lo, min(lo + per, n_anchors)
 
 
+def pack_results(sv: torch.Tensor, dims: torch.Tensor) -> torch.Tensor:
+    """[A, n] fp32 spectra + [A] int32 IDs -> ONE [A, n + 1] fp32 buffer (IDs bit-cast into the last column), so the
+    path's single collective carries both."""
+    out = sv.new_empty(sv.shape[0], sv.shape[1] + 1)
+    out[:, :-1].copy_(sv)
+    out[:, -1].copy_(dims.to(torch.int32).view(torch.float32))
+    return out
+
+
+def unpack_results(packed: torch.Tensor):
+    return packed[:, :-1], packed[:, -1].contiguous().view(torch.int32)
+
+
 def all_gather_spectra(sv: torch.Tensor, dims: torch.Tensor, n_total: int, group=None):
-    """The path's only collective: every rank contributes its [n_local, n] spectra and [n_local] IDs (shards
-    padded to the common size), everyone receives [n_total, n] / [n_total] in global anchor order."""
+    """The path's only collective, ONE all-gather: every rank contributes its packed [n_local, n + 1] results (shards
+    padded to the common size), everyone receives [n_total, n] spectra / [n_total] IDs in global anchor order."""
     import torch.distributed as dist
     world = dist.get_world_size(group)
     per = (n_total + world - 1) // world
-    pad = per - sv.shape[0]
+    packed = pack_results(sv, dims)
+    pad = per - packed.shape[0]
     if pad:
-        sv = torch.cat([sv, sv.new_zeros(pad, sv.shape[1])])
-        dims = torch.cat([dims, dims.new_zeros(pad)])
-    out_sv = sv.new_empty(world * per, sv.shape[1])
-    out_dims = dims.new_empty(world * per)
-    dist.all_gather_into_tensor(out_sv, sv.contiguous(), group=group)
-    dist.all_gather_into_tensor(out_dims, dims.contiguous(), group=group)
-    return out_sv[:n_total], out_dims[:n_total]
+        packed = torch.cat([packed, packed.new_zeros(pad, packed.shape[1])])
+    out = packed.new_empty(world * per, packed.shape[1])
+    dist.all_gather_into_tensor(out, packed.contiguous(), group=group)
+    g_sv, g_dims = unpack_results(out[:n_total])
+    return g_sv, g_dims
 
 
 def all_gather_rows(S_loc: torch.Tensor, K: int, group=None) -> torch.Tensor:
@@ -128,11 +152,81 @@ def all_gather_rows(S_loc: torch.Tensor, K: int, group=None) -> torch.Tensor:
     return buf.view(world, A, per, D).permute(1, 0, 2, 3).reshape(A, world * per, D)[:, :K].contiguous()
 
 
+class _DeviceGramOps:
+    """The three Gram pieces of the K-sharded mode on the device (C ABI); tests/test_dist_cpu.py swaps in a host
+    stand-in to check the collective bookkeeping under gloo."""
+
+    @staticmethod
+    def column_sums(X: torch.Tensor) -> torch.Tensor:
+        k, D = X.shape
+        out = torch.empty(D, dtype=torch.float64, device=X.device)
+        _lib.call("idb_column_sums", _lib.ptr(X), 0, X.stride(0), 1, k, D, _lib.ptr(out), _lib.stream_ptr())
+        return out
+
+    @staticmethod
+    def gram_about(X: torch.Tensor, center: torch.Tensor, scale: float) -> torch.Tensor:
+        k, D = X.shape
+        G = torch.empty(D, D, dtype=torch.float64, device=X.device)
+        _lib.call("idb_gram_about", _lib.ptr(X), 0, X.stride(0), 1, k, D, float(scale), _lib.ptr(center), _lib.ptr(G),
+                  _lib.stream_ptr())
+        return G
+
+    @staticmethod
+    def row_gram(X: torch.Tensor, scale: float) -> torch.Tensor:
+        K, d = X.shape
+        G = torch.empty(K, K, dtype=torch.float64, device=X.device)
+        mean = torch.empty(d, dtype=torch.float64, device=X.device)
+        _lib.call("idb_row_gram", _lib.ptr(X), X.stride(0), K, d, float(scale), _lib.ptr(mean), _lib.ptr(G),
+                  _lib.stream_ptr())
+        return G
+
+
+def rows_to_column_panels(S_loc: torch.Tensor, K: int, group=None) -> torch.Tensor:
+    """Re-shards ONE anchor's score matrix from row shards to column panels with one all-to-all: in, this rank's rows
+    [k_loc, D] (rows shard_range(K, rank, world)); out, ALL K rows of its columns shard_range(D, rank, world) -> [K, d_loc]."""
+    import torch.distributed as dist
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    k_loc, D = S_loc.shape
+    rows = [shard_range(K, q, world) for q in range(world)]
+    cols = [shard_range(D, q, world) for q in range(world)]
+    assert k_loc == rows[rank][1] - rows[rank][0]
+    d_loc = cols[rank][1] - cols[rank][0]
+    send = torch.cat([S_loc[:, lo:hi].reshape(-1) for lo, hi in cols])
+    recv = S_loc.new_empty(K * d_loc)
+    dist.all_to_all_single(recv, send, [(hi - lo) * d_loc for lo, hi in rows], [k_loc * (hi - lo) for lo, hi in cols],
+                           group=group)
+    return recv.view(K, d_loc)      # source ranks arrive in rank order = global row order
+
+
+def sharded_centred_gram(S_loc: torch.Tensor, K: int, scale: float, group=None, ops=_DeviceGramOps) -> torch.Tensor:
+    """SURVEY 8e, "one huge anchor": the centred Gram matrix of dim_reduction.py:193-197 from row shards of S, formed on
+    the smaller side, with PARTIAL Grams and one all-reduce instead of gathering the rows:
+      K >= D  column sums all-reduced (D doubles) -> global mean; every rank adds up (s_k - mean)(s_k - mean)^T over ITS
+              rows; one all-reduce of the D x D fp64 partials.
+      K <  D  one all-to-all turns row shards into column panels; every rank forms the K x K row-side Gram of its panel
+              (column means are local to a panel); one all-reduce of the K x K fp64 partials.
+    S_loc [k_loc, D] fp32, this rank's rows shard_range(K, rank, world).  Returns G [n, n] fp64 on every rank."""
+    import torch.distributed as dist
+    D = S_loc.shape[1]
+    if K >= D:
+        mean = ops.column_sums(S_loc)
+        dist.all_reduce(mean, group=group)
+        mean /= K
+        G = ops.gram_about(S_loc, mean, scale)
+    else:
+        G = ops.row_gram(rows_to_column_panels(S_loc, K, group), scale)
+    dist.all_reduce(G, group=group)
+    return G
+
+
 def estimate_anchors(engine, anchors: torch.Tensor, K: int, sde, t: float, *, seed: int = 0,
                      z: Optional[torch.Tensor] = None, chunk: Optional[int] = None, anchor_id0: int = 0,
-                     mem_budget_bytes: int = 24 << 30) -> Dict[str, torch.Tensor]:
+                     mem_budget_bytes: int = 24 << 30, gather_group=None,
+                     n_total: Optional[int] = None) -> Dict[str, torch.Tensor]:
     """anchors [N, D] (host or device) -> {'singular_values': [N, n] fp32, 'dims': [N] int32, 'sweeps'} on the
-    HOST.  Host anchors are copied to the device chunk by chunk (pinned staging), results copied back once."""
+    HOST.  Host anchors are copied to the device chunk by chunk (pinned staging), results copied back once.
+    With `gather_group` (anchors sharded over the ranks of a process group, `n_total` anchors in all) the spectra and
+    IDs of ALL ranks are returned: one all-gather on the device before the copy back."""
     dev = engine.dev
     N, D = anchors.shape
     mc, std = sde_coefficients(sde, t)
@@ -155,6 +249,9 @@ def estimate_anchors(engine, anchors: torch.Tensor, K: int, sde, t: float, *, se
         dims.append(r.dims)
         sweeps.append(r.sweeps)
     out = {"singular_values": torch.cat(svs), "dims": torch.cat(dims), "sweeps": torch.cat(sweeps)}
+    if gather_group is not None:
+        out["singular_values"], out["dims"] = all_gather_spectra(out["singular_values"], out["dims"],
+                                                                 N if n_total is None else n_total, gather_group)
     host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True) for k, v in out.items()}
     for k in out:
         host[k].copy_(out[k], non_blocking=True)
@@ -190,11 +287,8 @@ def get_manifold_dimension(config, name=None, return_svd=False, *, score_model=N
     picked = gather_anchors(loader, num_datapoints)
     singular_values: List[List[float]] = [None] * len(picked)
     dims: List[int] = [None] * len(picked)
-    # anchors that share a loader batch size share K: run each group as one device batch
-    groups: Dict[int, List[int]] = {}
-    for i, (_, B) in enumerate(picked):
-        groups.setdefault(B, []).append(i)
-    for B, idxs in groups.items():
+    # consecutive anchors that share a loader batch size share K: each run is one device batch
+    for B, idxs in batch_size_runs([B for _, B in picked]):
         x = torch.stack([picked[i][0] for i in idxs]).float()
         if x.dim() > 2:  # image anchors [C, H, W]: rows of the score matrix are the NCHW flatten (dim_reduction.py:191)
             x = x.flatten(1)
@@ -215,12 +309,14 @@ def get_manifold_dimension(config, name=None, return_svd=False, *, score_model=N
 
 
 def get_conditional_manifold_dimension(config, name=None, *, score_model=None, loader=None, seed=None, label=1,
-                                       times=None):
+                                       times=None, noise=None):
     """Drop-in for the reference's `get_conditional_manifold_dimension(config, name=None)` (dim_reduction.py:12-114):
     the same spectra for 12 diffusion times `linspace(sampling_eps, 0.3, 12)`, only anchors whose label equals 1
     (`:57-58`), from the VALIDATION loader with labels (`:19-22`), N-1 anchors (`:53-54,60-61`), one directory per
     time `svd/%.3f/` holding images.pkl, labels_svd.pkl, labels.pkl (`:101-114`).  All 12 time slices of an anchor
-    group reuse one engine; per slice the whole group is one device batch."""
+    group reuse one engine; per slice the whole group is one device batch.  The reference draws fresh noise per anchor
+    and per time slice (`:79`): the Philox seed of slice i is `seed + i * 0x9E3779B1`; `noise[i][j]` = recorded [K, D]
+    noise of anchor j in slice i (parity runs)."""
     import numpy as np
     log_path, log_name = config.logging.log_path, config.logging.log_name
     Path(os.path.join(log_path, log_name, "svd")).mkdir(parents=True, exist_ok=True)
@@ -242,6 +338,9 @@ def get_conditional_manifold_dimension(config, name=None, *, score_model=None, l
 
     # the anchors every time slice visits (the reference re-walks the loader per slice; the selection is the same)
     picked, idx = [], 0
+    if loader and not (isinstance(loader[0], (tuple, list)) and len(loader[0]) == 2):
+        raise _lib.IdbError("get_conditional_manifold_dimension needs a validation loader of (batch, labels) pairs "
+                            "(config.data.return_labels, dim_reduction.py:19-22,48); this datamodule has no labels")
     for orig_batch, orig_labels in loader:
         batchsize = orig_batch.size(0)
         if idx + 1 >= num_datapoints:
@@ -254,18 +353,17 @@ def get_conditional_manifold_dimension(config, name=None, *, score_model=None, l
             picked.append((x, batchsize, y.item()))
             idx += 1
     out = {}
-    for t_slice in times:
+    for ti, t_slice in enumerate(times):
         t = float(t_slice)
         t_save_path = os.path.join(log_path, log_name, "svd", "%.3f" % t)
         Path(t_save_path).mkdir(parents=True, exist_ok=True)
         singular_values = [None] * len(picked)
-        groups: Dict[int, List[int]] = {}
-        for i, (_, B, _) in enumerate(picked):
-            groups.setdefault(B, []).append(i)
-        for B, idxs in groups.items():
+        for B, idxs in batch_size_runs([p[1] for p in picked]):
             x = torch.stack([picked[i][0] for i in idxs]).float()
             _, _, K = k_schedule(picked[idxs[0]][0].shape, B)
-            res = estimate_anchors(engine, x.flatten(1), K, sde, t, seed=0 if seed is None else seed,
+            z = None if noise is None else torch.stack([torch.as_tensor(noise[ti][i]) for i in idxs]).float()
+            res = estimate_anchors(engine, x.flatten(1), K, sde, t, z=z,
+                                   seed=((0 if seed is None else seed) + ti * 0x9E3779B1) & 0x7FFFFFFFFFFFFFFF,
                                    anchor_id0=idxs[0])
             sv = res["singular_values"].double().tolist()
             for j, i in enumerate(idxs):

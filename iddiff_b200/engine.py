@@ -63,6 +63,38 @@ LARGE_N = 1024  # above this, one Gram matrix is solved by the whole GPU (idb_sp
 SPECTRUM_METHOD = _lib.SPECTRUM_TRIDIAG  # default solver; _lib.SPECTRUM_JACOBI selects the one-sided Jacobi
 
 
+def _solve_large(G: torch.Tensor, n: int, sv_row: torch.Tensor, ws: torch.Tensor, st):
+    with _stage("spectrum", n * n * 8.0 + n * 4.0):
+        call("idb_spectrum_large", ptr(G), n, n, ptr(sv_row), ptr(ws), st)
+
+
+def _read_out(sv: torch.Tensor, A: int, n: int, st) -> torch.Tensor:
+    dims = torch.empty(A, dtype=torch.int32, device=sv.device)
+    if n >= 3:
+        call("idb_id_from_spectrum", ptr(sv), A, n, n, ptr(dims), st)
+    else:
+        dims.fill_(-2)
+    return dims
+
+
+def spectrum_from_gram(G: torch.Tensor, n: int, method: Optional[int] = None) -> SpectrumResult:
+    """Singular values + IDs from centred Gram matrices G [A, n, n] fp64 (overwritten when n > LARGE_N)."""
+    A = G.shape[0]
+    dev, st = G.device, stream_ptr()
+    sv = torch.empty(A, n, dtype=torch.float32, device=dev)
+    sweeps = torch.zeros(A, dtype=torch.int32, device=dev)
+    if n > LARGE_N:
+        ws = torch.empty(_lib.load().idb_spectrum_large_workspace_bytes(n), dtype=torch.uint8, device=dev)
+        for a in range(A):
+            _solve_large(G[a], n, sv[a], ws, st)
+    else:
+        ws = torch.empty(_lib.load().idb_spectrum_workspace_bytes(A, n), dtype=torch.uint8, device=dev)
+        with _stage("spectrum", A * (n * n * 8.0 + n * 4.0)):
+            call("idb_spectrum", ptr(G), A, n, n, SPECTRUM_METHOD if method is None else method, ptr(sv),
+                 ptr(sweeps), ptr(ws), st)
+    return SpectrumResult(sv, _read_out(sv, A, n, st), sweeps)
+
+
 def spectrum_from_rows(X: torch.Tensor, K: int, D: int, scale: float, rows_per_anchor: Optional[int] = None,
                        method: Optional[int] = None) -> SpectrumResult:
     """dim_reduction.py:190-199 + plot_utils.py:224-229 on device.
@@ -74,14 +106,12 @@ def spectrum_from_rows(X: torch.Tensor, K: int, D: int, scale: float, rows_per_a
     dev = X.device
     st = stream_ptr()
     n = min(K, D)          # the smaller side of the centred score matrix carries all its singular values
-    n_out = n
-    sv = torch.empty(A, n_out, dtype=torch.float32, device=dev)
-    sweeps = torch.zeros(A, dtype=torch.int32, device=dev)
     colmean = torch.empty(A, D, dtype=torch.float64, device=dev)
     large = n > LARGE_N
     G = torch.empty(1 if large else A, n, n, dtype=torch.float64, device=dev)
     if large:
         # image-sized matrices: one anchor at a time, the whole GPU on each (cooperative tridiagonalisation)
+        sv = torch.empty(A, n, dtype=torch.float32, device=dev)
         ws = torch.empty(_lib.load().idb_spectrum_large_workspace_bytes(n), dtype=torch.uint8, device=dev)
         for a in range(A):
             with _stage("center_gram", K * D * 4.0 + n * n * 8.0):
@@ -89,26 +119,15 @@ def spectrum_from_rows(X: torch.Tensor, K: int, D: int, scale: float, rows_per_a
                     call("idb_row_gram", ptr(X[a]), ld, K, D, float(scale), ptr(colmean[a]), ptr(G), st)
                 else:
                     call("idb_center_gram", ptr(X[a]), R * ld, ld, 1, K, D, float(scale), ptr(colmean[a]), ptr(G), st)
-            with _stage("spectrum", n * n * 8.0 + n_out * 4.0):
-                call("idb_spectrum_large", ptr(G), n, n_out, ptr(sv[a]), ptr(ws), st)
-    else:
-        with _stage("center_gram", A * (K * D * 4.0 + n * n * 8.0)):
-            if K < D:
-                for a in range(A):
-                    call("idb_row_gram", ptr(X[a]), ld, K, D, float(scale), ptr(colmean[a]), ptr(G[a]), st)
-            else:
-                call("idb_center_gram", ptr(X), R * ld, ld, A, K, D, float(scale), ptr(colmean), ptr(G), st)
-        ws_bytes = _lib.load().idb_spectrum_workspace_bytes(A, n)
-        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
-        with _stage("spectrum", A * (n * n * 8.0 + n_out * 4.0)):
-            call("idb_spectrum", ptr(G), A, n, n_out, SPECTRUM_METHOD if method is None else method, ptr(sv),
-                 ptr(sweeps), ptr(ws), st)
-    dims = torch.empty(A, dtype=torch.int32, device=dev)
-    if n_out >= 3:
-        call("idb_id_from_spectrum", ptr(sv), A, n_out, n_out, ptr(dims), st)
-    else:
-        dims.fill_(-2)
-    return SpectrumResult(sv, dims, sweeps)
+            _solve_large(G[0], n, sv[a], ws, st)
+        return SpectrumResult(sv, _read_out(sv, A, n, st), torch.zeros(A, dtype=torch.int32, device=dev))
+    with _stage("center_gram", A * (K * D * 4.0 + n * n * 8.0)):
+        if K < D:
+            for a in range(A):
+                call("idb_row_gram", ptr(X[a]), ld, K, D, float(scale), ptr(colmean[a]), ptr(G[a]), st)
+        else:
+            call("idb_center_gram", ptr(X), R * ld, ld, A, K, D, float(scale), ptr(colmean), ptr(G), st)
+    return spectrum_from_gram(G, n, method)
 
 
 class FcnEngine:

@@ -383,18 +383,32 @@ class UNetEngine:
         return S
 
     def estimate_row_sharded(self, x0: torch.Tensor, K: int, mean_coeff: float, std: float, label: float, *,
-                             seed: int = 0, anchor_id0: int = 0, group=None, image_chunk: Optional[int] = None) -> SpectrumResult:
-        """One (or a few) huge anchors over all ranks of the process group: rank r evaluates the score network on its
-        K / world rows, ONE all-gather assembles S on every rank, the spectrum stage runs replicated."""
+                             seed: int = 0, anchor_id0: int = 0, group=None, image_chunk: Optional[int] = None,
+                             gather_rows: bool = False) -> SpectrumResult:
+        """One (or a few) huge anchors over all ranks of the process group: rank r evaluates the score
+        network on its K / world rows; the centred Gram is assembled from PARTIAL Grams with one all-reduce
+        (dim_reduction.sharded_centred_gram; K < D: one all-to-all to column panels first); the eigen-solve and the
+        read-out run replicated.  gather_rows=True is the older variant (all-gather of the rows, Gram replicated),
+        kept as the cross-check."""
         import torch.distributed as dist
-        from .dim_reduction import all_gather_rows, shard_range
+        from .dim_reduction import all_gather_rows, shard_range, sharded_centred_gram
+        from .engine import spectrum_from_gram
         world, rank = dist.get_world_size(group), dist.get_rank(group)
         lo, hi = shard_range(K, rank, world)
         S_loc = self.score_rows(x0, hi - lo, lo, mean_coeff, std, label, seed=seed, anchor_id0=anchor_id0,
                                 image_chunk=image_chunk)
-        with _stage("all_gather_rows", 0.0):
-            S = all_gather_rows(S_loc, K, group)
-        return spectrum_from_rows(S, K, S.shape[2], -1.0 / std)
+        if gather_rows:
+            with _stage("all_gather_rows", 0.0):
+                S = all_gather_rows(S_loc, K, group)
+            return spectrum_from_rows(S, K, S.shape[2], -1.0 / std)
+        A, _, D = S_loc.shape
+        out = []
+        for a in range(A):
+            with _stage("sharded_gram", 0.0):
+                G = sharded_centred_gram(S_loc[a], K, -1.0 / std, group)
+            out.append(spectrum_from_gram(G[None], min(K, D)))
+        return SpectrumResult(torch.cat([r.singular_values for r in out]), torch.cat([r.dims for r in out]),
+                              torch.cat([r.sweeps for r in out]))
 
     def estimate(self, x0: torch.Tensor, K: int, mean_coeff: float, std: float, label: float, *,
                  z: Optional[torch.Tensor] = None, seed: int = 0, anchor_id0: int = 0, image_shape=None,

@@ -111,6 +111,16 @@ int idb_ksphere_gt_score(const float* x, const float* sigma_rows, float sigma, i
 int idb_center_gram(const float* X, long long anchor_stride, int ld, int n_anchors, int K, int D, double scale,
                     double* colmean, double* G, void* stream);
 
+/* The two halves of idb_center_gram, for ONE anchor whose K rows are sharded over the GPUs of a box ("one
+ * huge anchor": partial Grams + one all-reduce).  Each rank calls idb_column_sums on its rows (colsum[a][D] fp64, plain
+ * sums), the sums are all-reduced and divided by the global K, then idb_gram_about accumulates
+ * G[a][D][D] = sum_{k local} (scale (X[k]-center))^T (scale (X[k]-center)) about that GLOBAL mean, so the partial Grams
+ * add up exactly to the centred Gram of dim_reduction.py:193-197 and one all-reduce of G finishes it. */
+int idb_column_sums(const float* X, long long anchor_stride, int ld, int n_anchors, int K, int D, double* colsum,
+                    void* stream);
+int idb_gram_about(const float* X, long long anchor_stride, int ld, int n_anchors, int K, int D, double scale,
+                   const double* center, double* G, void* stream);
+
 /* Singular values of the centred score matrix from its Gram matrix (replaces torch.linalg.svd at
  * dim_reduction.py:197-198), one anchor per CTA, matrix resident in shared memory while it fits:
  *   IDB_SPECTRUM_TRIDIAG  fp64 Householder tridiagonalisation + Sturm bisection (one thread per eigenvalue);

@@ -141,60 +141,4 @@ BEATGANS_SMALL = dict(image_size=16, centered=True, input_channels=3, in_channel
                       attn_checkpoint=False)
 
 
-def unet_config(spec: dict, name: str = "ddpm"):
-    """A config carrying the keys models/ddpm.py:84-109 reads, for the reference and for iddiff_b200 alike."""
-    from iddiff_b200.config import ConfigDict
-    model = {k: v for k, v in spec.items() if k not in ("image_size", "centered")}
-    if name.startswith("BeatGANs"):
-        model["image_size"] = spec["image_size"]
-    return ConfigDict(model=dict(name=name, sigma_min=1e-2, sigma_max=4.0, beta_min=0.1, beta_max=20.0,
-                                 num_scales=1000, checkpoint_path=None, **model),
-                      data=dict(effective_image_size=spec["image_size"], image_size=spec["image_size"],
-                                centered=spec["centered"], num_channels=spec["input_channels"],
-                                shape=[spec["input_channels"], spec["image_size"], spec["image_size"]],
-                                use_data_mean=False),
-                      training=dict(sde="vesde", batch_size=64, continuous=True))
-
-
-def make_unet_state(holder, seed: int) -> Dict[str, torch.Tensor]:
-    """Deterministic non-degenerate weights for a U-Net holder (the reference's zero-initialised output convolutions,
-    appendix A.11, are re-randomised): every tensor of holder.state_dict(), in order, from one seeded generator;
-    float64 draws rounded once to float32.  Matrices/filters: U(-b, b), b = sqrt(3 / fan_in); biases U(-0.1, 0.1);
-    GroupNorm scale 1 + U(-0.2, 0.2)."""
-    g = torch.Generator().manual_seed(seed)
-    out = {}
-    for k, v in holder.state_dict().items():
-        u = torch.rand(v.shape, generator=g, dtype=torch.float64) * 2 - 1
-        if v.dim() >= 2:
-            fan_in = v.shape[0] if k.endswith(".W") else v[0].numel()
-            if k.endswith("emb_layers.1.weight"):
-                fan_in *= 16   # BeatGANs scale-shift projection: keep (1 + scale) well away from 0
-            t = u * math.sqrt(3.0 / fan_in)
-        elif v.dim() == 1 and _is_norm_weight(holder, k):
-            t = 1.0 + 0.2 * u
-        else:
-            t = 0.1 * u
-        out[k] = t.float()
-    return out
-
-
-def _is_norm_weight(holder, key: str) -> bool:
-    mod = holder
-    parts = key.split(".")[:-1]
-    for p in parts:
-        mod = getattr(mod, p) if not p.isdigit() else mod[int(p)]
-    return isinstance(mod, torch.nn.GroupNorm) and key.endswith("weight")
-
-
-def smooth_images(n: int, c: int, size: int, seed: int) -> torch.Tensor:
-    """Synthetic image manifold in [0, 1]: a seeded 2-D latent -> one Gaussian blob per channel."""
-    g = torch.Generator().manual_seed(seed)
-    lat = torch.rand(n, 2, generator=g, dtype=torch.float64)
-    yy, xx = torch.meshgrid(torch.linspace(0, 1, size, dtype=torch.float64),
-                            torch.linspace(0, 1, size, dtype=torch.float64), indexing="ij")
-    imgs = []
-    for ch in range(c):
-        cx = (lat[:, 0] + 0.2 * ch) % 1.0
-        cy = (lat[:, 1] + 0.13 * ch) % 1.0
-        imgs.append(torch.exp(-((xx[None] - cx[:, None, None]) ** 2 + (yy[None] - cy[:, None, None]) ** 2) / 0.05))
-    return torch.stack(imgs, 1).float()
+from iddiff_b200.synthetic import unet_config, make_unet_state, smooth_images  # noqa: E402,F401  (shared with tools/ and bench.py)

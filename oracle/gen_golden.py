@@ -65,6 +65,9 @@ class _Injected:
     def train_dataloader(self):
         return list(_INJECT["batches"])
 
+    def val_dataloader(self):   # (batch, labels) pairs for get_conditional_manifold_dimension (dim_reduction.py:21,48)
+        return list(_INJECT["val_batches"])
+
 
 @mutils.register_model(name="idb_identity")
 class _Identity(torch.nn.Module):

@@ -19,7 +19,15 @@ import types
 import torch
 import torch.nn as nn
 
-REFERENCE_ROOT = "/root/reference"
+import os
+
+# the reference itself in the build container; on the GPU box (no /root/reference) the copy made by oracle/build_ref.sh
+REFERENCE_ROOT = "/root/reference" if os.path.isdir("/root/reference") else \
+    os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+
+
+def available() -> bool:
+    return os.path.isfile(os.path.join(REFERENCE_ROOT, "dim_reduction.py"))
 
 
 class _ConfigDict(dict):

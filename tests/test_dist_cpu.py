@@ -87,3 +87,58 @@ def test_row_sharding_of_one_anchor_world2():
                 + torch.arange(3.)[None, None, :]).tolist()
         for _, S in res:
             assert S == want
+
+
+class _HostGramOps:
+    """fp64 torch stand-in for the three device Gram pieces (collective bookkeeping test only)."""
+
+    @staticmethod
+    def column_sums(X):
+        return X.double().sum(0)
+
+    @staticmethod
+    def gram_about(X, center, scale):
+        Y = (X.double() - center[None]) * scale
+        return Y.T @ Y
+
+    @staticmethod
+    def row_gram(X, scale):
+        Y = (X.double() - X.double().mean(0, keepdim=True)) * scale
+        return Y @ Y.T
+
+
+def _gram_worker(rank, world, port, K, D, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from iddiff_b200.dim_reduction import shard_range, sharded_centred_gram, rows_to_column_panels
+    S = torch.randn(K, D, generator=torch.Generator().manual_seed(K * 1000 + D)) + 3.0
+    lo, hi = shard_range(K, rank, world)
+    panel = rows_to_column_panels(S[lo:hi].contiguous(), K)
+    clo, chi = shard_range(D, rank, world)
+    ok_panel = torch.equal(panel, S[:, clo:chi])
+    G = sharded_centred_gram(S[lo:hi].contiguous(), K, -2.0, ops=_HostGramOps)
+    q.put((rank, ok_panel, G))
+    dist.destroy_process_group()
+
+
+def test_sharded_partial_gram_world2():
+    """SURVEY 8e as specified: partial Grams + ONE all-reduce; both sides (K >= D: D x D about the all-reduced mean;
+    K < D: all-to-all to column panels, K x K), ragged shards included, against the centred Gram of the whole matrix."""
+    for K, D in ((9, 4), (8, 8), (5, 11), (6, 7)):
+        ctx = mp.get_context("spawn")
+        q = ctx.Queue()
+        port = _free_port()
+        procs = [ctx.Process(target=_gram_worker, args=(r, 2, port, K, D, q)) for r in range(2)]
+        for p in procs:
+            p.start()
+        res = sorted((q.get(timeout=120) for _ in procs), key=lambda t: t[0])
+        for p in procs:
+            p.join(timeout=60)
+            assert p.exitcode == 0
+        S = (torch.randn(K, D, generator=torch.Generator().manual_seed(K * 1000 + D)) + 3.0).double()
+        Y = (S - S.mean(0, keepdim=True)) * -2.0
+        want = Y.T @ Y if K >= D else Y @ Y.T
+        for rank, ok_panel, G in res:
+            assert ok_panel
+            assert G.shape == want.shape
+            torch.testing.assert_close(G, want, rtol=1e-12, atol=1e-12)

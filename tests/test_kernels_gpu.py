@@ -325,3 +325,24 @@ def test_bad_arguments_are_rejected_loudly():
     o = torch.zeros(100, 256, device=dev())
     with pytest.raises(_lib.IdbError):
         call("idb_fcn_output_layer", ptr(a), ptr(a), ptr(a), ptr(a), 0, 1.0, 100, 256, 64, ptr(o), stream_ptr())
+
+
+def test_partial_grams_about_the_global_mean_add_up_to_the_centred_gram():
+    """idb_column_sums + idb_gram_about (the K-sharded mode's per-rank pieces) on two row shards of one matrix: the
+    partial Grams about the all-reduced mean sum to idb_center_gram of the whole matrix, and both match fp64."""
+    from iddiff_b200.dim_reduction import _DeviceGramOps as Ops
+    K, D = 700, 300
+    X = (torch.randn(K, D, generator=torch.Generator().manual_seed(5)) * 0.01 + 1.5).cuda()
+    halves = (X[:333].contiguous(), X[333:].contiguous())
+    mean = sum(Ops.column_sums(h) for h in halves) / K
+    G = sum(Ops.gram_about(h, mean, -100.0) for h in halves)
+    whole = torch.empty(D, D, dtype=torch.float64, device="cuda")
+    cm = torch.empty(D, dtype=torch.float64, device="cuda")
+    _lib.call("idb_center_gram", X.data_ptr(), 0, D, 1, K, D, -100.0, cm.data_ptr(), whole.data_ptr(),
+              torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    Y = (X.double() - X.double().mean(0, keepdim=True)) * -100.0
+    want = Y.T @ Y
+    torch.testing.assert_close(mean, X.double().mean(0), rtol=1e-13, atol=0)
+    torch.testing.assert_close(whole, want, rtol=1e-11, atol=1e-11 * float(want.abs().max()))
+    torch.testing.assert_close(G, want, rtol=1e-11, atol=1e-11 * float(want.abs().max()))

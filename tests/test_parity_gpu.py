@@ -70,7 +70,7 @@ def test_fcn_small_golden(name):
     np.testing.assert_allclose(sv, truth, rtol=SV_RTOL)
     ref = g["singular_values"]
     floor = np.abs(ref - truth).max(axis=1, keepdims=True)
-    assert np.all(np.abs(sv - ref) <= SV_RTOL * ref + 2 * floor), np.abs(sv / ref - 1).max()
+    assert np.all(np.abs(sv - ref) <= SV_RTOL * ref + floor), np.abs(sv / ref - 1).max()
     assert res.dims.cpu().tolist() == g["dims"].tolist()
 
 
@@ -116,11 +116,20 @@ def test_ksphere_c1_golden():
     assert np.abs(sc[:, :16] - g["scores_head"]).max() < SCORE_TOL * scale
     sv = res.singular_values.cpu().numpy().astype(np.float64)
     np.testing.assert_allclose(sv, g["singular_values"], rtol=SV_RTOL)
-    # Appendix A.10 of SURVEY.md: the gap rule on this radial-only field is decided by noise in near-equal
-    # gaps, so the integer is compared against the oracle read-out of OUR spectrum (bit-exact rule), and
-    # against the reference integer only where the reference's own top gap is decisive.
+    # Appendix A.10 of SURVEY.md: the gap rule on this radial-only field is decided by near-equal gaps in a flat tail
+    # -- the reference's integers are asserted all the same (BASELINE: identical integer ID on every config); on a
+    # mismatch the message names the two competing gaps and their margin in the reference's own spectrum.
     got = res.dims.cpu().tolist()
     assert got == [O.id_from_spectrum(s) for s in res.singular_values.cpu().double().tolist()]
+    want = g["dims"].tolist()
+    for a in range(n):
+        if got[a] != want[a]:
+            s = g["singular_values"][a]
+            gaps = s[1:-1] - s[2:]
+            i_ref, i_got = len(gaps) - want[a], len(gaps) - got[a]
+            raise AssertionError(f"anchor {a}: ID {got[a]} != reference {want[a]}; reference gaps {gaps[i_ref]:.6g} "
+                                 f"(its argmax) vs {gaps[i_got]:.6g} (ours), margin {gaps[i_ref] - gaps[i_got]:.3g}, "
+                                 f"max |sv - ref| {np.abs(sv[a] - s).max():.3g}")
 
 
 def test_fused_philox_path_agrees_with_oracle_in_distribution():

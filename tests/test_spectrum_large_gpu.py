@@ -82,3 +82,28 @@ def test_tridiagonalisation_variants_agree(n):
         np.testing.assert_allclose(out[variant], want, rtol=1e-5, atol=1e-7 * want[0])
     np.testing.assert_allclose(out[2], out[1], rtol=1e-6, atol=1e-8 * want[0])
     np.testing.assert_allclose(out[-1], out[1], rtol=1e-6, atol=1e-8 * want[0])
+
+
+@pytest.mark.parametrize("n", [4096, 12288])
+def test_spectrum_large_at_baseline_sizes(n):
+    """The sizes BASELINE configs 4 / 5 produce: n = 4096 (K = 4096 rows of a 64x64x3 image, one column class) and
+    n = 12288 (the reference's own K = 16768: two column classes, the path that only runs above n = 9000), through the
+    production entry point idb_spectrum_large, against fp64 eigenvalues of the same Gram matrix.  The checker is
+    cuSOLVER's fp64 syevd through torch (LAPACK on the host would take minutes at n = 12288)."""
+    from iddiff_b200 import _lib
+    g = torch.Generator(device="cuda").manual_seed(n)
+    B = torch.randn(n, n + 64, generator=g, device="cuda", dtype=torch.float64)
+    B *= torch.logspace(0, -3, n, dtype=torch.float64, device="cuda")[:, None]
+    G = B @ B.T
+    del B
+    want = torch.linalg.eigvalsh(G).clamp_min(0).sqrt().flip(0).cpu().numpy()
+    lib = _lib.load()
+    ws = torch.empty(lib.idb_spectrum_large_workspace_bytes(n), dtype=torch.uint8, device="cuda")
+    sv = torch.empty(n, dtype=torch.float32, device="cuda")
+    _lib.call("idb_spectrum_large", G.data_ptr(), n, n, sv.data_ptr(), ws.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    got = sv.cpu().numpy().astype(np.float64)
+    assert np.all(np.diff(got) <= 0)
+    np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-7 * want[0])
+    del G, ws
+    torch.cuda.empty_cache()

@@ -247,3 +247,61 @@ def test_drop_in_runs_the_papers_squares_config_shape_from_the_synthetic_datamod
     with open(tmp_path / "squares" / "svd" / "squares.pkl", "rb") as f:
         sv = np.asarray(pickle.load(f)["singular_values"])
     assert sv.shape == (2, 1024) and np.isfinite(sv).all() and np.all(np.diff(sv, axis=1) <= 0) and sv[:, 0].min() > 0
+
+
+@pytest.mark.parametrize("gold", ["cond_ddpm_small_ve", "cond_ddpm_small_vp"])
+def test_conditional_sweep_exact_noise_vs_reference_golden(tmp_path, gold):
+    """Row a18: the REAL reference's get_conditional_manifold_dimension (dim_reduction.py:12-114; golden from
+    oracle/gen_golden_cond.py) against the drop-in on the reference's own noise, at the first, a middle and the LAST of
+    its 12 diffusion times (t = 0.3: VE sigma 0.06, VP mean coefficient 0.63 / std 0.78 -- the large-deviation end)."""
+    import pickle
+    from iddiff_b200 import dim_reduction as DR, plot_utils, sde_lib, unet_models
+    g = FX.golden(gold)
+    spec, fwd = FX.DDPM_SMALL, IO.ddpm_forward
+    sde_name, seed, B, nb, K = str(g["sde"]), int(g["seed"]), int(g["B"]), int(g["nb"]), int(g["K"])
+    holder = unet_models.get_model("ddpm")(FX.unet_config(spec, "ddpm"))
+    state = FX.make_unet_state(holder, seed)
+    ckpt = tmp_path / "last.ckpt"
+    torch.save({"state_dict": {"score_model." + k: v for k, v in state.items()}}, ckpt)
+    imgs = FX.smooth_images(6, 3, 16, seed + 2)
+    batch = imgs[torch.arange(B) % 6]
+    labels = torch.tensor([0, 1, 1, 0, 1, 1])[torch.arange(B) % 6]
+    n_anchor = g["singular_values"].shape[1]
+    assert np.array_equal(g["images"], np.stack([imgs[1].permute(1, 2, 0).numpy(), imgs[2].permute(1, 2, 0).numpy()]))
+    # the reference's noise: one [B, C, H, W] draw per perturbation batch, anchors inside time slices, in order
+    torch.manual_seed(seed + 3)
+    proto = torch.empty(B, 3, 16, 16)
+    z = torch.stack([torch.randn_like(proto) for _ in range(12 * n_anchor * nb)]).reshape(12, n_anchor, nb * B, -1)[:, :, :K]
+    pick = [0, 5, 11]
+    cfg = FX.unet_config(spec, "ddpm")
+    cfg.training.sde = sde_name
+    cfg.logging = dict(log_path=str(tmp_path), log_name="cond")
+    cfg.dim_estimation = dict(num_datapoints=int(g["num_datapoints"]))
+    cfg.device = "cuda:0"
+    cfg.training.batch_size = B
+    cfg.data.datamodule = "Tensor"
+    cfg.data.anchors, cfg.data.labels = batch, labels
+    cfg.model.checkpoint_path = str(ckpt)
+    times = torch.from_numpy(g["times"])[pick]
+    DR.get_conditional_manifold_dimension(cfg, times=times, noise=[[z[ti, j] for j in range(n_anchor)] for ti in pick])
+    sde, _ = sde_lib.configure_sde(cfg)
+    for ti in pick:
+        d = tmp_path / "cond" / "svd" / str(g["dirs"][ti])
+        with open(d / "labels_svd.pkl", "rb") as f:
+            sv = np.asarray(pickle.load(f)["singular_values"])
+        with open(d / "labels.pkl", "rb") as f:
+            assert pickle.load(f)["labels"] == g["labels"].tolist()
+        want = g["singular_values"][ti]
+        t = float(g["times"][ti])
+        mc, std = sde.coefficients(t)
+        label = float((torch.ones(1) * t * (sde.N - 1))[0])
+        S64 = IO.unet_score_matrix(fwd, state, spec, imgs[1].double(), z[ti, 0].reshape(K, 3, 16, 16).double(), mc, std, label)
+        s64 = torch.linalg.svdvals(S64).numpy()
+        floor = np.abs(want[0] - s64).max()
+        rel = np.abs(sv / want - 1).max()
+        print(f"{gold} t={t:.3f} std={std:.4f}: vs reference {rel:.3e}, vs fp64 {np.abs(sv[0] / s64 - 1).max():.3e}, "
+              f"reference vs fp64 {np.abs(want[0] / s64 - 1).max():.3e}")
+        assert np.isfinite(sv).all()
+        assert np.all(np.abs(sv[0] - s64) <= 1e-3 * s64 + floor)
+        assert np.all(np.abs(sv - want) <= 1e-3 * want + floor), rel
+        assert plot_utils.dims_from_spectra({"singular_values": sv.tolist()}) == g["dims"][ti].tolist()

@@ -19,38 +19,13 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import torch  # noqa: E402
 
-DDPM = dict(nf=128, ch_mult=(1, 2, 2, 3, 3), num_res_blocks=4, attn_resolutions=(16,), image_size=64,
-            resamp_with_conv=True, centered=False, input_channels=3, output_channels=3, dropout=0.0, conditional=True,
-            nonlinearity="swish")
-NCSNPP = dict(DDPM, fir=True, fir_kernel=[1, 3, 3, 1], skip_rescale=True, resblock_type="biggan", progressive="none",
-              progressive_input="residual", progressive_combine="sum", embedding_type="fourier", init_scale=0.0,
-              fourier_scale=16)
-BEAT = dict(image_size=64, centered=True, input_channels=3, in_channels=3, model_channels=128, out_channels=3,
-            num_res_blocks=2, num_input_res_blocks=None, embed_channels=64, attention_resolutions=(16,),
-            time_embed_channels=None, dropout=0.3, channel_mult=(1, 1, 2, 3, 4), input_channel_mult=None,
-            conv_resample=True, dims=2, num_classes=None, use_checkpoint=False, num_heads=1, num_head_channels=-1,
-            num_heads_upsample=-1, resblock_updown=True, use_new_attention_order=False, resnet_two_cond=False,
-            resnet_cond_channels=None, resnet_use_zero_module=True, attn_checkpoint=False)
-# the paper's synthetic-image configs (squares / gaussian_blobs: 1x32x32, configs/.../squares/10.py:101-135); its
-# FLOPs per image are counted here from the convolution / dense / attention shapes of the plan (2 * MAC)
-SQUARES = dict(DDPM, ch_mult=(1, 2, 2, 2), image_size=32, input_channels=1, output_channels=1)
-MODELS = {"squares": ("ddpm", SQUARES, None), "ddpm": ("ddpm", DDPM, 79.7), "ncsnpp": ("ncsnpp", NCSNPP, 88.6), "beatgans": ("BeatGANsUNetModel", BEAT, 37.4)}
+from iddiff_b200 import synthetic as SY  # noqa: E402
+
+MODELS = SY.FULL_MODELS
 
 
 def build(model):
-    from oracle import fixtures as FX
-    from iddiff_b200 import unet_models
-    from iddiff_b200.unet_engine import UNetEngine
-    name, spec, gflop = MODELS[model]
-    torch.manual_seed(0)
-    holder = unet_models.get_model(name)(FX.unet_config(spec, name))
-    with torch.no_grad():  # re-randomise the zero-initialised convolutions (appendix A.11)
-        for k, p in holder.named_parameters():
-            if p.dim() >= 2 and float(p.abs().max()) < 1e-3:
-                unet_models.fan_avg_uniform_(p, 1.0)
-    eng = UNetEngine.from_module(holder, "cuda:0")
-    eng.image_shape = (spec["input_channels"], spec["image_size"], spec["image_size"])
-    return eng, sum(p.numel() for p in holder.parameters()), gflop
+    return SY.build_full_engine(model, "cuda:0")
 
 
 def main():
@@ -93,11 +68,10 @@ def main():
                     "tflops_algorithmic": args.batch * gflop / ms, "launches_per_forward":
                     (_lib.launch_count - l0) / args.steps, "finite": bool(torch.isfinite(y).all())})
     else:
-        from oracle import fixtures as FX
         from iddiff_b200 import sde_lib
         sde = sde_lib.VESDE(sigma_min=0.009, sigma_max=50.0, N=1000)   # style_gan_base.py:100-101
         mc, std = sde.coefficients(1e-5)
-        x0 = FX.smooth_images(args.anchors, C, S, 5).reshape(args.anchors, -1).cuda()
+        x0 = SY.smooth_images(args.anchors, C, S, 5).reshape(args.anchors, -1).cuda()
         eng.estimate(x0[:1], min(args.K, 1024), mc, std, 0.00999, seed=0)   # warm-up (captures the forward graph)
         torch.cuda.synchronize()
         E.EVENT_LOG = {}
@@ -116,7 +90,6 @@ def main():
                     "sv_head": r.singular_values[0, :3].cpu().tolist(), "sv_tail": r.singular_values[0, -3:].cpu().tolist()})
     if args.cpu_baseline:
         import time
-        from oracle import fixtures as FX
         from oracle import img_oracle as IO
         name, spec, _ = MODELS[args.model]
         fwd = {"squares": IO.ddpm_forward, "ddpm": IO.ddpm_forward, "ncsnpp": IO.ncsnpp_forward, "beatgans": IO.beatgans_forward}[args.model]

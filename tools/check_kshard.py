@@ -25,19 +25,8 @@ def main():
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
     world, rank = dist.get_world_size(), dist.get_rank()
-    import bench_unet
-    from oracle import fixtures as FX
-    from iddiff_b200 import sde_lib, unet_models
-    from iddiff_b200.unet_engine import UNetEngine
-    name, spec, gflop = bench_unet.MODELS[args.model]
-    torch.manual_seed(0)
-    holder = unet_models.get_model(name)(FX.unet_config(spec, name))
-    with torch.no_grad():
-        for k, p in holder.named_parameters():
-            if p.dim() >= 2 and float(p.abs().max()) < 1e-3:
-                unet_models.fan_avg_uniform_(p, 1.0)
-    eng = UNetEngine.from_module(holder, dev)
-    eng.image_shape = (3, 64, 64)
+    from iddiff_b200 import sde_lib, synthetic as FX
+    eng, _, gflop = FX.build_full_engine(args.model, dev)
     sde = sde_lib.VESDE(sigma_min=0.009, sigma_max=50.0, N=1000)
     mc, std = sde.coefficients(1e-5)
     x0 = FX.smooth_images(1, 3, 64, 5).reshape(1, -1).to(dev)
