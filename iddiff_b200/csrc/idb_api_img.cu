@@ -95,6 +95,33 @@ EncodeTiledFn encode_tiled() {
 int idb_conv2d(const void* a_hi, const void* a_lo, int planes, int N, int Ha, int Wa, int H, int W, int Cp, const void* w_hi,
                const void* w_lo, int n_taps, const int* taps_host, int Np, int Cout, float acc_scale, float out_scale,
                const float* bias, const float* residual, int ld_res, float* out, int ldo, void* stream) {
+    return idb_conv2d_stats(a_hi, a_lo, planes, N, Ha, Wa, H, W, Cp, w_hi, w_lo, n_taps, taps_host, Np, Cout, acc_scale,
+                            out_scale, bias, residual, ld_res, out, ldo, nullptr, stream);
+}
+
+int idb_conv_stats_slots(int H, int W) {
+    if (H <= 0 || W <= 0) return 0;
+    const int BW = W < 128 ? W : 128;
+    const int BH = 128 / BW < H ? 128 / BW : H;
+    const int pimg = BW * BH;
+    if (pimg < 16 || (H * W) % (pimg < 32 ? pimg : 32)) return 0;
+    return (H * W) / (pimg < 32 ? pimg : 32);
+}
+
+int idb_groupnorm_from_conv_stats(const float* stats0, int C0, int slots0, const float* stats1, int C1, int slots1, int N,
+                                  int HW, int groups, double eps, float* mean_rstd, void* stream) {
+    if (!stats0 || !mean_rstd || N < 0 || HW <= 0 || groups <= 0 || C0 <= 0 || slots0 <= 0 || C1 < 0 ||
+        (C1 > 0 && (!stats1 || slots1 <= 0)) || (C0 + C1) % groups)
+        return api_fail("idb_groupnorm_from_conv_stats: bad argument");
+    return api_check(idb::launch_gn_from_partials(stats0, C0, slots0, C1 > 0 ? stats1 : nullptr, C1, slots1, N, HW,
+                                                  groups, eps, mean_rstd, static_cast<cudaStream_t>(stream)),
+                     "idb_groupnorm_from_conv_stats");
+}
+
+int idb_conv2d_stats(const void* a_hi, const void* a_lo, int planes, int N, int Ha, int Wa, int H, int W, int Cp,
+                     const void* w_hi, const void* w_lo, int n_taps, const int* taps_host, int Np, int Cout,
+                     float acc_scale, float out_scale, const float* bias, const float* residual, int ld_res, float* out,
+                     int ldo, float* stats, void* stream) {
     if (!a_hi || !a_lo || !w_hi || !w_lo || !out || !taps_host) return api_fail("idb_conv2d: null pointer");
     if (planes <= 0 || N <= 0 || H <= 0 || W <= 0 || Cp <= 0 || Cp % 64) return api_fail("idb_conv2d: bad shape (Cp % 64)");
     if (Ha < H || Wa < W) return api_fail("idb_conv2d: operand planes must be at least as large as the output (Ha >= H, Wa >= W)");
@@ -129,6 +156,9 @@ int idb_conv2d(const void* a_hi, const void* a_lo, int planes, int N, int Ha, in
     }
     p.Np = Np; p.Cout = Cout; p.acc_scale = acc_scale; p.out_scale = out_scale;
     p.bias = bias; p.residual = residual; p.ld_res = ld_res; p.out = out; p.ldo = ldo;
+    p.stats = stats;
+    if (stats && (idb_conv_stats_slots(H, W) == 0 || (reinterpret_cast<uintptr_t>(stats) & 15)))
+        return api_fail("idb_conv2d_stats: statistics need >= 16 pixels of an image per tile and a 16-byte aligned buffer");
     return api_check(idb::launch_conv(p, idb::api_num_sms(), static_cast<cudaStream_t>(stream)), "idb_conv2d");
 }
 

@@ -58,6 +58,24 @@ __device__ __forceinline__ void ld_global_nc_256(const float* src, float (&q)[8]
                  : "l"(src));
 }
 
+// Steps 8, 4, 2, 1 of the transposing butterfly over W live values per lane: after it a[0 .. W/16) hold the totals of
+// the channels this lane ends up owning (W = 16: channel `lane`; W = 32: channels 2 (lane & 15) + {0, 1}, summed over
+// the 16 lanes of the lane's half warp only).
+template <int W>
+__device__ __forceinline__ void stat_butterfly(float (&a)[32], float (&b)[32], int lane) {
+#pragma unroll
+    for (int m = 8, w = W; m >= 1; m >>= 1, w >>= 1) {
+        const bool up = lane & m;
+#pragma unroll
+        for (int i = 0; i < w / 2; ++i) {
+            const float ka = up ? a[i + w / 2] : a[i], sa = up ? a[i] : a[i + w / 2];
+            const float kb = up ? b[i + w / 2] : b[i], sb = up ? b[i] : b[i + w / 2];
+            a[i] = ka + __shfl_xor_sync(0xffffffffu, sa, m);
+            b[i] = kb + __shfl_xor_sync(0xffffffffu, sb, m);
+        }
+    }
+}
+
 template <int BN>
 __global__ void __launch_bounds__(C_THREADS, 1) conv_fp16x3_kernel(const __grid_constant__ ConvParams p) {
     using Cfg = ConvCfg<BN>;
@@ -160,6 +178,9 @@ __global__ void __launch_bounds__(C_THREADS, 1) conv_fp16x3_kernel(const __grid_
         const int cgroup = (warp - 2) >> 2;
         const int r = quarter * 32 + lane;  // row of the tile = TMEM lane = output pixel
         const bool ptrs32 = ((reinterpret_cast<uintptr_t>(p.out) | reinterpret_cast<uintptr_t>(p.residual)) & 31) == 0;
+        const int stat_pimg = p.BW * p.BH;                      // pixels of one image inside a tile
+        const int stat_ppw = stat_pimg < 32 ? stat_pimg : 32;   // pixels per warp that belong to one image (32 or 16)
+        const int stat_slots = (p.H * p.W) / stat_ppw;
         int it = 0;
         for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
             const int as = it & 1;
@@ -171,6 +192,10 @@ __global__ void __launch_bounds__(C_THREADS, 1) conv_fp16x3_kernel(const __grid_
             const int img = (mt / (tiles_w * tiles_h)) * p.BI + r / (p.BW * p.BH);
             const bool row_ok = img < p.N;
             const size_t pix = ((size_t)img * p.H + h) * p.W + w;
+            // statistics slot of this warp's 32 pixels inside their image (see the stats block below)
+            const int img_warp = (mt / (tiles_w * tiles_h)) * p.BI + (quarter * 32) / stat_pimg;
+            const bool row_ok_warp = img_warp < p.N;
+            const int stat_slot = (p.BI == 1 ? (mt % (tiles_w * tiles_h)) * 4 + quarter : ((quarter * 32) % stat_pimg) / 32);
             mbar_wait(&tfull[as], aphase);
             tc_fence_after();
             const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * BN;
@@ -181,52 +206,102 @@ __global__ void __launch_bounds__(C_THREADS, 1) conv_fp16x3_kernel(const __grid_
                 uint32_t v[32];
                 tmem_ld32(t_row + cc * 32, v);
                 tmem_ld_wait();
-                if (!row_ok) continue;
-                float* dst = p.out + pix * p.ldo + c0;
-                const float* res = p.residual ? p.residual + pix * p.ld_res + c0 : nullptr;
-                if (c0 + 32 <= p.Cout && (p.ldo & 7) == 0 && (!res || (p.ld_res & 7) == 0) && ptrs32) {
-                    // a thread owns 128 contiguous bytes of its pixel: 256-bit accesses move whole 32-byte sectors
+                if (row_ok) {
+                    float* dst = p.out + pix * p.ldo + c0;
+                    const float* res = p.residual ? p.residual + pix * p.ld_res + c0 : nullptr;
+                    if (c0 + 32 <= p.Cout && (p.ldo & 7) == 0 && (!res || (p.ld_res & 7) == 0) && ptrs32) {
+                        // a thread owns 128 contiguous bytes of its pixel: 256-bit accesses move whole 32-byte sectors
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        float o[8], q[8];
+                        for (int j = 0; j < 4; ++j) {
+                            float o[8], q[8];
 #pragma unroll
-                        for (int e = 0; e < 8; ++e) {
-                            const float b = p.bias ? __ldg(p.bias + c0 + 8 * j + e) : 0.f;
-                            o[e] = __uint_as_float(v[8 * j + e]) * p.acc_scale + b;
+                            for (int e = 0; e < 8; ++e) {
+                                const float b = p.bias ? __ldg(p.bias + c0 + 8 * j + e) : 0.f;
+                                o[e] = __uint_as_float(v[8 * j + e]) * p.acc_scale + b;
+                            }
+                            if (res) {
+                                ld_global_nc_256(res + 8 * j, q);
+#pragma unroll
+                                for (int e = 0; e < 8; ++e) o[e] += q[e];
+                            }
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) {
+                                o[e] *= p.out_scale;
+                                v[8 * j + e] = __float_as_uint(o[e]);
+                            }
+                            st_global_256f(dst + 8 * j, o);
                         }
-                        if (res) {
-                            ld_global_nc_256(res + 8 * j, q);
+                    } else if (c0 + 32 <= p.Cout && (p.ldo & 3) == 0 && (!res || (p.ld_res & 3) == 0)) {
 #pragma unroll
-                            for (int e = 0; e < 8; ++e) o[e] += q[e];
+                        for (int j = 0; j < 8; ++j) {
+                            float4 o;
+                            float4 b = p.bias ? __ldg(reinterpret_cast<const float4*>(p.bias + c0) + j)
+                                              : make_float4(0.f, 0.f, 0.f, 0.f);
+                            o.x = __uint_as_float(v[4 * j]) * p.acc_scale + b.x;
+                            o.y = __uint_as_float(v[4 * j + 1]) * p.acc_scale + b.y;
+                            o.z = __uint_as_float(v[4 * j + 2]) * p.acc_scale + b.z;
+                            o.w = __uint_as_float(v[4 * j + 3]) * p.acc_scale + b.w;
+                            if (res) {
+                                const float4 q = __ldg(reinterpret_cast<const float4*>(res) + j);
+                                o.x += q.x; o.y += q.y; o.z += q.z; o.w += q.w;
+                            }
+                            o.x *= p.out_scale; o.y *= p.out_scale; o.z *= p.out_scale; o.w *= p.out_scale;
+                            reinterpret_cast<float4*>(dst)[j] = o;
+                            v[4 * j] = __float_as_uint(o.x); v[4 * j + 1] = __float_as_uint(o.y);
+                            v[4 * j + 2] = __float_as_uint(o.z); v[4 * j + 3] = __float_as_uint(o.w);
                         }
+                    } else {
 #pragma unroll
-                        for (int e = 0; e < 8; ++e) o[e] *= p.out_scale;
-                        st_global_256f(dst + 8 * j, o);
+                        for (int j = 0; j < 32; ++j) {
+                            float o = 0.f;
+                            if (c0 + j < p.Cout) {
+                                o = __uint_as_float(v[j]) * p.acc_scale + (p.bias ? __ldg(p.bias + c0 + j) : 0.f);
+                                if (res) o += __ldg(res + j);
+                                o *= p.out_scale;
+                                dst[j] = o;
+                            }
+                            v[j] = __float_as_uint(o);
+                        }
                     }
-                } else if (c0 + 32 <= p.Cout && (p.ldo & 3) == 0 && (!res || (p.ld_res & 3) == 0)) {
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        float4 o;
-                        float4 b = p.bias ? __ldg(reinterpret_cast<const float4*>(p.bias + c0) + j)
-                                          : make_float4(0.f, 0.f, 0.f, 0.f);
-                        o.x = __uint_as_float(v[4 * j]) * p.acc_scale + b.x;
-                        o.y = __uint_as_float(v[4 * j + 1]) * p.acc_scale + b.y;
-                        o.z = __uint_as_float(v[4 * j + 2]) * p.acc_scale + b.z;
-                        o.w = __uint_as_float(v[4 * j + 3]) * p.acc_scale + b.w;
-                        if (res) {
-                            const float4 q = __ldg(reinterpret_cast<const float4*>(res) + j);
-                            o.x += q.x; o.y += q.y; o.z += q.z; o.w += q.w;
-                        }
-                        o.x *= p.out_scale; o.y *= p.out_scale; o.z *= p.out_scale; o.w *= p.out_scale;
-                        reinterpret_cast<float4*>(dst)[j] = o;
-                    }
-                } else {
+                }
+                if (p.stats) {
+                    // GroupNorm statistics of the tensor this convolution writes (layers.py:638,648: the NEXT block's
+                    // nn.GroupNorm), from the registers that already hold it: per (image, 32-pixel slot, channel) sums
+                    // of x and x^2.  A transposing butterfly leaves lane l with the total of channel c0 + l over the
+                    // warp's 32 pixels in 31 shuffles per quantity; fixed slots, no atomics -> bit-reproducible.
+                    float a[32], b2[32];
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
-                        if (c0 + j < p.Cout) {
-                            float o = __uint_as_float(v[j]) * p.acc_scale + (p.bias ? __ldg(p.bias + c0 + j) : 0.f);
-                            if (res) o += __ldg(res + j);
-                            dst[j] = o * p.out_scale;
+                        const float x = row_ok ? __uint_as_float(v[j]) : 0.f;
+                        a[j] = x;
+                        b2[j] = x * x;
+                    }
+                    const bool half_warp = stat_ppw == 16;   // 4x4 images: a warp holds two images of 16 pixels
+                    if (!half_warp) {
+                        const bool up = lane & 16;
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            const float ka = up ? a[i + 16] : a[i], sa = up ? a[i] : a[i + 16];
+                            const float kb = up ? b2[i + 16] : b2[i], sb = up ? b2[i] : b2[i + 16];
+                            a[i] = ka + __shfl_xor_sync(0xffffffffu, sa, 16);
+                            b2[i] = kb + __shfl_xor_sync(0xffffffffu, sb, 16);
+                        }
+                    }
+                    // remaining steps: masks 8, 4, 2, 1 on 16 (or, for half warps, 32) live values
+                    if (!half_warp) {
+                        stat_butterfly<16>(a, b2, lane);
+                        if (row_ok_warp && c0 + lane < p.Cout) {
+                            float2* dst2 = reinterpret_cast<float2*>(p.stats) +
+                                           ((size_t)img_warp * stat_slots + stat_slot) * p.Cout + c0 + lane;
+                            *dst2 = make_float2(a[0], b2[0]);
+                        }
+                    } else {
+                        stat_butterfly<32>(a, b2, lane);
+                        const int ch = c0 + 2 * (lane & 15);
+                        if (row_ok && ch < p.Cout) {   // lanes of one half share img
+                            float2* dst2 = reinterpret_cast<float2*>(p.stats) + (size_t)img * p.Cout + ch;
+                            dst2[0] = make_float2(a[0], b2[0]);
+                            if (ch + 1 < p.Cout) dst2[1] = make_float2(a[1], b2[1]);
                         }
                     }
                 }

@@ -104,6 +104,7 @@ struct alignas(64) ConvParams {
     int ld_res;
     float* out;                // [N][H][W][ldo]
     int ldo;
+    float* stats;              // optional [N][H*W / min(32, BW*BH)][Cout][2]: per-slot (sum, sum of squares) of `out`
 };
 cudaError_t launch_conv(const ConvParams& p, int num_sms, cudaStream_t stream);
 
@@ -127,6 +128,8 @@ struct PrepParams {
 };
 cudaError_t launch_conv_prep(const PrepParams& p, int num_sms, cudaStream_t stream);
 
+cudaError_t launch_gn_from_partials(const float* st0, int C0, int S0, const float* st1, int C1, int S1, int N, int HW,
+                                    int groups, double eps, float* mean_rstd, cudaStream_t stream);
 cudaError_t launch_gn_stats(const float* s0, int C0, const float* s1, int C1, int N, int HW, int groups, double eps,
                             double* sums, float* mean_rstd, int num_sms, cudaStream_t stream);
 

@@ -122,6 +122,55 @@ cudaError_t launch_gn_stats(const float* s0, int C0, const float* s1, int C1, in
     return cudaGetLastError();
 }
 
+// GroupNorm statistics from the per-(image, slot, channel) partial sums the convolution epilogue wrote
+// (idb_conv.cu, ConvParams::stats): one warp per (image, group) adds the (sum, sum of squares) pairs of the group's
+// channels over all slots in fp64, in a fixed order (bit-reproducible), over the virtual concat [st0 | st1].
+__global__ void __launch_bounds__(128) gn_from_partials_kernel(const float2* __restrict__ st0, int C0, int S0,
+                                                               const float2* __restrict__ st1, int C1, int S1, int N,
+                                                               int groups, double count, double eps,
+                                                               float* __restrict__ mr) {
+    const int wid = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (wid >= N * groups) return;
+    const int img = wid / groups, g = wid % groups;
+    const int cg = (C0 + C1) / groups;
+    double s = 0.0, q = 0.0;
+    for (int j = 0; j < cg; ++j) {
+        const int c = g * cg + j;
+        const float2* base;
+        int S, C, cc;
+        if (c < C0) { base = st0; S = S0; C = C0; cc = c; }
+        else { base = st1; S = S1; C = C1; cc = c - C0; }
+        const float2* ptr = base + (size_t)img * S * C + cc;
+        for (int k = lane; k < S; k += 32) {
+            const float2 v = __ldg(ptr + (size_t)k * C);
+            s += (double)v.x;
+            q += (double)v.y;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        s += __shfl_xor_sync(0xffffffffu, s, o);
+        q += __shfl_xor_sync(0xffffffffu, q, o);
+    }
+    if (lane == 0) {
+        const double m = s / count;
+        double var = q / count - m * m;
+        if (var < 0.0) var = 0.0;
+        mr[2 * wid] = (float)m;
+        mr[2 * wid + 1] = (float)(1.0 / sqrt(var + eps));
+    }
+}
+
+cudaError_t launch_gn_from_partials(const float* st0, int C0, int S0, const float* st1, int C1, int S1, int N, int HW,
+                                    int groups, double eps, float* mean_rstd, cudaStream_t stream) {
+    if (N <= 0) return cudaSuccess;
+    const int warps = N * groups;
+    gn_from_partials_kernel<<<(warps + 3) / 4, 128, 0, stream>>>(reinterpret_cast<const float2*>(st0), C0, S0,
+                                                                 reinterpret_cast<const float2*>(st1), C1, S1, N, groups,
+                                                                 (double)((C0 + C1) / groups) * HW, eps, mean_rstd);
+    return cudaGetLastError();
+}
+
 // ---------------------------------- operand preparation --------------------------------------
 // one thread = one output pixel x one 8-channel chunk (16 B of hi and 16 B of lo).  VEC: the chunk lies inside one NHWC
 // source and is 32-byte aligned -> two float4 loads; otherwise a scalar gather (NCHW network input, odd channel counts).

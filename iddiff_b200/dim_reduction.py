@@ -256,6 +256,13 @@ def estimate_anchors(engine, anchors: torch.Tensor, K: int, sde, t: float, *, se
     for k in out:
         host[k].copy_(out[k], non_blocking=True)
     torch.cuda.current_stream().synchronize()
+    if not bool(torch.isfinite(host["singular_values"]).all()):
+        # the fp16 hi/lo operand split is unsaturated: |deviation| or |activation| * 64 beyond the fp16 range (> ~1023)
+        # turns into inf - inf = NaN in the tensor-core chain and would otherwise be read out as a full-rank ID
+        bad = (~torch.isfinite(host["singular_values"]).all(dim=1)).nonzero().flatten().tolist()
+        raise _lib.IdbError(f"non-finite spectrum for anchors {bad[:8]}{'...' if len(bad) > 8 else ''}: an operand left "
+                            "the fp16-pair range (|value| > ~1023 after scaling); normalise the data or run the FCN "
+                            "engine with fmt=FMT_BF16")
     return host
 
 

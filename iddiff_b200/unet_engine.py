@@ -226,7 +226,7 @@ class UNetEngine:
             x0 = xr
         else:
             a = U.prep(x0, x1, mean_rstd=mr, groups=blk.groups0, gamma=blk.gn0[0], beta=blk.gn0[1], act=1)
-        h = U.conv(a, blk.conv0, bias=bias0)
+        h = U.conv(a, blk.conv0, bias=bias0, want_stats=True)
         mr = U.gn_stats(h, None, blk.groups1, self.EPS)
         a = U.prep(h, mean_rstd=mr, groups=blk.groups1, gamma=blk.gn1[0], beta=blk.gn1[1], act=1)
         if blk.short is not None:
@@ -235,7 +235,7 @@ class UNetEngine:
             raise _lib.IdbError("res-block with a concatenated input needs a shortcut projection")
         else:
             xs = x0
-        return U.conv(a, blk.conv1, residual=xs, out_scale=blk.out_scale)
+        return U.conv(a, blk.conv1, residual=xs, out_scale=blk.out_scale, want_stats=True)
 
     def _attn(self, blk: _Attn, x):
         mr = U.gn_stats(x, None, blk.groups, self.EPS)
@@ -243,13 +243,13 @@ class UNetEngine:
         qkv = U.conv(a, blk.qkv)
         c = blk.c
         o = U.attention(qkv, 1, c, 0, c, 2 * c, c, float(int(c) ** (-0.5)))
-        return U.conv(U.prep(o), blk.proj, residual=x, out_scale=blk.out_scale)
+        return U.conv(U.prep(o), blk.proj, residual=x, out_scale=blk.out_scale, want_stats=True)
 
     def _bres(self, blk: _BRes, affine1, x0, x1=None):
         mode = U.PREP_UP2 if blk.up else (U.PREP_AVGPOOL2 if blk.down else U.PREP_SAME)
         mr = U.gn_stats(x0, x1, blk.groups0, self.EPS)
         a = U.prep(x0, x1, mode=mode, mean_rstd=mr, groups=blk.groups0, gamma=blk.gn0[0], beta=blk.gn0[1], act=1)
-        h = U.conv(a, blk.conv0)
+        h = U.conv(a, blk.conv0, want_stats=True)
         mr = U.gn_stats(h, None, blk.groups1, self.EPS)
         a = U.prep(h, mean_rstd=mr, groups=blk.groups1, gamma=affine1[0], beta=affine1[1], act=1)
         if blk.up or blk.down:   # x_upd on the skip branch (BeatGANsblocks.py:199-204); channel count unchanged
@@ -261,7 +261,7 @@ class UNetEngine:
             raise _lib.IdbError("res-block with a lateral input needs a skip projection")
         else:
             xs = x0
-        return U.conv(a, blk.conv1, residual=xs)
+        return U.conv(a, blk.conv1, residual=xs, want_stats=True)
 
     def _battn(self, blk: _BAttn, x):
         mr = U.gn_stats(x, None, blk.groups, self.EPS)
@@ -270,7 +270,7 @@ class UNetEngine:
         dh = blk.c // blk.heads
         # legacy head layout: qkv.reshape(bs * heads, 3 * ch, T) -> head h owns channels [3 ch h, 3 ch (h + 1)) = q | k | v
         o = U.attention(qkv, blk.heads, dh, 0, dh, 2 * dh, 3 * dh, 1.0 / math.sqrt(dh))
-        return U.conv(U.prep(o), blk.proj, residual=x)
+        return U.conv(U.prep(o), blk.proj, residual=x, want_stats=True)
 
     def forward(self, x_nchw: torch.Tensor, label: float, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """x [B, C, H, W] fp32 (device) -> raw network output [B, H, W, Cout] fp32 NHWC (ddpm.py:149-213)."""
@@ -286,12 +286,12 @@ class UNetEngine:
                     a, pyramid = U.prep(x_nchw, nchw=True, gamma=ga, beta=be, want_f32=True)
                 else:
                     a = U.prep(x_nchw, nchw=True, gamma=ga, beta=be)
-                h = U.conv(a, blk)
+                h = U.conv(a, blk, want_stats=True)
             elif kind == "pyr_down":
                 # conv_downsample_2d (up_or_down_sampling.py:144-178) then (pyramid + h) / sqrt(2) (ncsnpp.py:300-304)
                 f = U.upfirdn2d_nhwc(pyramid, blk.fir, 1, 1, 2, 2)
                 h = U.conv(U.prep(f, mode=U.PREP_STRIDE2), blk.conv, residual=h, out_scale=self.rescale,
-                           out_hw=(h.shape[1], h.shape[2]))
+                           out_hw=(h.shape[1], h.shape[2]), want_stats=True)
                 pyramid = h
             elif kind == "push":
                 hs.append(h)
@@ -305,12 +305,12 @@ class UNetEngine:
                 h = self._attn(blk, h)
             elif kind == "down":
                 if blk is not None:
-                    h = U.conv(U.prep(h, mode=U.PREP_STRIDE2), blk)
+                    h = U.conv(U.prep(h, mode=U.PREP_STRIDE2), blk, want_stats=True)
                 else:
                     h = U.prep(h, mode=U.PREP_AVGPOOL2, want_operand=False, want_f32=True)[1]
             elif kind == "up":
                 if blk is not None:
-                    h = U.conv(U.prep(h, mode=U.PREP_UP2), blk)
+                    h = U.conv(U.prep(h, mode=U.PREP_UP2), blk, want_stats=True)
                 else:
                     h = U.prep(h, mode=U.PREP_UP2, want_operand=False, want_f32=True)[1]
             elif kind == "gn_out":

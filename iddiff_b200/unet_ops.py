@@ -77,10 +77,22 @@ def pack_conv(weight: torch.Tensor, bias: Optional[torch.Tensor], taps=None, pla
     return PackedConv(hi, lo, b, cin, cp, cout, np_, list(taps), w_scale, planes)
 
 
+FUSED_GN_STATS = True   # GroupNorm statistics from the producing convolution's epilogue (False: re-read the tensor)
+
+
 def gn_stats(x0: torch.Tensor, x1: Optional[torch.Tensor], groups: int, eps: float) -> torch.Tensor:
-    """x0 [N,H,W,C0] (+ x1 [N,H,W,C1] concatenated along C) -> mean_rstd [N, groups, 2] fp32."""
+    """x0 [N,H,W,C0] (+ x1 [N,H,W,C1] concatenated along C) -> mean_rstd [N, groups, 2] fp32.  When every input
+    carries the partial sums its convolution wrote (conv(..., want_stats=True)), they are folded by one small kernel;
+    otherwise the tensor is read once more (idb_groupnorm_stats)."""
     n, h, w, c0 = x0.shape
     c1 = x1.shape[3] if x1 is not None else 0
+    st0 = getattr(x0, "_idb_stats", None)
+    st1 = getattr(x1, "_idb_stats", None) if x1 is not None else None
+    if st0 is not None and (x1 is None or st1 is not None):
+        mr = torch.empty(n, groups, 2, dtype=torch.float32, device=x0.device)
+        _lib.call("idb_groupnorm_from_conv_stats", _lib.ptr(st0), c0, st0.shape[1], _lib.ptr(st1), c1,
+                  st1.shape[1] if st1 is not None else 0, n, h * w, groups, float(eps), _lib.ptr(mr), _lib.stream_ptr())
+        return mr
     sums = torch.empty(n, groups, 2, dtype=torch.float64, device=x0.device)
     mr = torch.empty(n, groups, 2, dtype=torch.float32, device=x0.device)
     _lib.call("idb_groupnorm_stats", _lib.ptr(x0), c0, _lib.ptr(x1), c1, n, h * w, groups, float(eps), _lib.ptr(sums),
@@ -128,9 +140,10 @@ def prep(x0: torch.Tensor, x1: Optional[torch.Tensor] = None, *, mode: int = PRE
 
 
 def conv(a: Operand, pc: PackedConv, *, bias: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None,
-         out_scale: float = 1.0, out: Optional[torch.Tensor] = None, out_hw=None) -> torch.Tensor:
+         out_scale: float = 1.0, out: Optional[torch.Tensor] = None, out_hw=None, want_stats: bool = False) -> torch.Tensor:
     """out [N,H,W,Cout] fp32 = out_scale * (conv(a, W) + bias + residual).  `bias` overrides pc.bias (the host folds
-    the time-embedding projection into it)."""
+    the time-embedding projection into it).  want_stats: the epilogue also writes the GroupNorm partial sums of `out`
+    (attached as out._idb_stats [N, slots, Cout, 2]; gn_stats picks them up)."""
     if a.cp != pc.cp or a.planes != pc.planes:
         raise _lib.IdbError(f"conv: operand (Cp={a.cp}, planes={a.planes}) does not match weights (Cp={pc.cp}, planes={pc.planes})")
     oh, ow = out_hw if out_hw is not None else (a.h, a.w)
@@ -138,9 +151,16 @@ def conv(a: Operand, pc: PackedConv, *, bias: Optional[torch.Tensor] = None, res
         out = torch.empty(a.n, oh, ow, pc.cout, dtype=torch.float32, device=a.hi.device)
     b = bias if bias is not None else pc.bias
     ld_res = residual.shape[-1] if residual is not None else 0
-    _lib.call("idb_conv2d", _lib.ptr(a.hi), _lib.ptr(a.lo), a.planes, a.n, a.h, a.w, oh, ow, a.cp, _lib.ptr(pc.w_hi),
+    stats = None
+    if want_stats and FUSED_GN_STATS:
+        slots = _lib.load().idb_conv_stats_slots(oh, ow)
+        if slots > 0:
+            stats = torch.empty(a.n, slots, pc.cout, 2, dtype=torch.float32, device=a.hi.device)
+    _lib.call("idb_conv2d_stats", _lib.ptr(a.hi), _lib.ptr(a.lo), a.planes, a.n, a.h, a.w, oh, ow, a.cp, _lib.ptr(pc.w_hi),
               _lib.ptr(pc.w_lo), len(pc.taps), pc.taps_c, pc.np_, pc.cout, 1.0 / (ACT_SCALE * pc.w_scale), float(out_scale),
-              _lib.ptr(b), _lib.ptr(residual), ld_res, _lib.ptr(out), out.shape[-1], _lib.stream_ptr())
+              _lib.ptr(b), _lib.ptr(residual), ld_res, _lib.ptr(out), out.shape[-1], _lib.ptr(stats), _lib.stream_ptr())
+    if stats is not None:
+        out._idb_stats = stats
     return out
 
 

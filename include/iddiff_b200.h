@@ -198,6 +198,21 @@ int idb_conv2d(const void* a_hi, const void* a_lo, int planes, int N, int Ha, in
                const void* w_lo, int n_taps, const int* taps_host, int Np, int Cout, float acc_scale, float out_scale,
                const float* bias, const float* residual, int ld_res, float* out, int ldo, void* stream);
 
+/* idb_conv2d that ALSO emits the GroupNorm statistics of the tensor it writes, from the epilogue registers (the fusion
+ * BASELINE.json asks for: "GroupNorm ... fused into their consumers" -- the next nn.GroupNorm, layers.py:638,648, no
+ * longer re-reads the activation): stats [N][slots][Cout][2] fp32 = per (image, 32-pixel slot, channel) sum and sum of
+ * squares of out, slots = idb_conv_stats_slots(H, W) (0: this shape cannot carry statistics, use idb_groupnorm_stats).
+ * Fixed slots, no atomics: bit-reproducible.  idb_groupnorm_from_conv_stats folds the partials of the (virtually
+ * concatenated) producers [stats0 | stats1] into mean_rstd [N][groups][2] in fp64, same result layout as
+ * idb_groupnorm_stats. */
+int idb_conv_stats_slots(int H, int W);
+int idb_conv2d_stats(const void* a_hi, const void* a_lo, int planes, int N, int Ha, int Wa, int H, int W, int Cp,
+                     const void* w_hi, const void* w_lo, int n_taps, const int* taps_host, int Np, int Cout,
+                     float acc_scale, float out_scale, const float* bias, const float* residual, int ld_res, float* out,
+                     int ldo, float* stats, void* stream);
+int idb_groupnorm_from_conv_stats(const float* stats0, int C0, int slots0, const float* stats1, int C1, int slots1, int N,
+                                  int HW, int groups, double eps, float* mean_rstd, void* stream);
+
 /* Self-attention over the T = H*W pixels of each image (layers.py:567-590 AttnBlock: 1 head, scale C^-1/2;
  * BeatGANsblocks.py:434-491 QKVAttentionLegacy: heads, scale dh^-1/2): out[n][i][h*dh+c] =
  * sum_j softmax_j(scale <q_i,k_j>) v[j][c], q/k/v of head h at channels q0/k0/v0 + h*head_stride of qkv [N][T][ld].

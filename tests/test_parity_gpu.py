@@ -402,3 +402,19 @@ def test_c3_shape_union_of_spheres_against_the_oracle():
         assert np.all(np.abs(sv[a] - s64[a]) <= SV_RTOL * s64[a] + floor)
         assert O.id_from_spectrum(want.tolist()) == rank
     assert res.dims.cpu().tolist() == [rank] * n
+
+
+def test_operand_overflow_is_reported_not_read_out():
+    """the fp16-pair split is unsaturated, so deviations beyond ~1023 / 64 used to turn into NaN spectra that
+    the read-out silently mapped to a full-rank ID.  The drop-in path now raises."""
+    from iddiff_b200 import _lib, sde_lib
+    from iddiff_b200.dim_reduction import estimate_anchors
+    g = FX.golden("fcn_small_ve")
+    D, L = int(g["D"]), int(g["L"])
+    ws, bs = FX.fcn_state_to_lists(FX.golden_fcn_state(g), L)
+    eng = FcnEngine([w.cuda() for w in ws], [b.cuda() for b in bs])
+    x0 = torch.from_numpy(g["x0"])[:2]
+    ok = estimate_anchors(eng, x0, 151, sde_lib.VESDE(sigma_min=1e-2, sigma_max=4.0, N=1000), 1e-5)
+    assert torch.isfinite(ok["singular_values"]).all()
+    with pytest.raises(_lib.IdbError, match="non-finite spectrum"):
+        estimate_anchors(eng, x0, 151, sde_lib.VESDE(sigma_min=3e4, sigma_max=4e4, N=1000), 1e-5)

@@ -120,3 +120,41 @@ def test_dense_silu():
     out = U.dense(x.cuda(), w.cuda(), b.cuda(), act_in=2)
     ref = F.linear(F.silu(x.double()), w.double(), b.double())
     np.testing.assert_allclose(out.cpu().numpy(), ref.numpy(), rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("n,cin,cout,h,w,groups", [(3, 64, 128, 64, 64, 32),    # BI = 1, 32 tiles per image, 128 slots
+                                                   (2, 128, 256, 16, 16, 32),   # two tiles per image
+                                                   (5, 64, 384, 8, 8, 32),      # 2 images per tile, ragged last tile, 12 channels per group
+                                                   (11, 128, 128, 4, 4, 32),    # 16-pixel images: half-warp reduction, ragged
+                                                   (2, 64, 96, 32, 32, 8)])     # Cout < Np: partial 32-channel chunk
+def test_groupnorm_statistics_from_the_conv_epilogue(n, cin, cout, h, w, groups):
+    """Row g1: the convolution's epilogue emits the per-(image, slot, channel) sums the NEXT GroupNorm needs; folded by
+    idb_groupnorm_from_conv_stats they equal the statistics of the written tensor (the re-reading kernel and fp64 torch),
+    alone and as the second half of a virtual concat; the result is bit-reproducible."""
+    from iddiff_b200 import unet_ops as U
+    torch.manual_seed(n * 100 + cout)
+    x = torch.randn(n, cin, h, w)
+    wt = torch.randn(cout, cin, 3, 3) / np.sqrt(9 * cin)
+    bias = torch.randn(cout)
+    res = nhwc(torch.randn(n, cout, h, w)).cuda()
+    pc = U.pack_conv(wt.cuda(), bias.cuda())
+    a = U.prep(nhwc(x).cuda())
+    y = U.conv(a, pc, residual=res, out_scale=0.7, want_stats=True)
+    assert hasattr(y, "_idb_stats") and y._idb_stats.shape == (n, max(1, h * w // 32), cout, 2)
+    y_plain = U.conv(a, pc, residual=res, out_scale=0.7)
+    assert torch.equal(y, y_plain) and not hasattr(y_plain, "_idb_stats")
+    mr_fused = U.gn_stats(y, None, groups, 1e-6)
+    mr_reread = U.gn_stats(y_plain, None, groups, 1e-6)
+    yd = y.double().permute(0, 3, 1, 2).reshape(n, groups, -1).cpu()
+    mean, rstd = yd.mean(-1), 1 / torch.sqrt(yd.var(-1, unbiased=False) + 1e-6)
+    np.testing.assert_allclose(mr_fused[..., 0].cpu().numpy(), mean.numpy(), rtol=2e-6, atol=2e-6)
+    np.testing.assert_allclose(mr_fused[..., 1].cpu().numpy(), rstd.numpy(), rtol=2e-6)
+    np.testing.assert_allclose(mr_fused.cpu().numpy(), mr_reread.cpu().numpy(), rtol=2e-6, atol=2e-6)
+    # virtual concat [other | y]: other carries no partial sums -> falls back to the re-reading kernel; both carry -> fused
+    y2 = U.conv(a, pc, want_stats=True)
+    cat_fused = U.gn_stats(y2, y, groups, 1e-6)
+    cd = torch.cat([y2, y], dim=3).double().permute(0, 3, 1, 2).reshape(n, groups, -1).cpu()
+    np.testing.assert_allclose(cat_fused[..., 0].cpu().numpy(), cd.mean(-1).numpy(), rtol=2e-6, atol=2e-6)
+    np.testing.assert_allclose(cat_fused[..., 1].cpu().numpy(), (1 / torch.sqrt(cd.var(-1, unbiased=False) + 1e-6)).numpy(), rtol=2e-6)
+    again = U.conv(a, pc, residual=res, out_scale=0.7, want_stats=True)
+    assert torch.equal(again._idb_stats, y._idb_stats)
