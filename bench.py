@@ -245,14 +245,13 @@ def run_ours(args):
             if self.done[b] is not None:
                 torch.cuda.current_stream().wait_event(self.done[b])   # the gather that last read this buffer
             out = self.packed[b]
-            ck = min(chunk, self.a)
-            for s in range(0, self.a, ck):
-                r = eng.estimate(self.dev[s:s + ck], K, mc, std, label, seed=step_idx, anchor_id0=rank * self.a + s,
-                                 defer=args.overlap)
-                if args.overlap:
-                    eng.join()
-                out[s:s + ck, :n_sv].copy_(r.singular_values)
-                out[s:s + ck, n_sv].copy_(r.dims.view(torch.float32))
+            # one call per step: one anchor chain, the GEMM chain in passes of `chunk` anchors, one spectrum stage
+            r = eng.estimate(self.dev, K, mc, std, label, seed=step_idx, anchor_id0=rank * self.a, chunk=chunk,
+                             defer=args.overlap)
+            if args.overlap:
+                eng.join()
+            out[:, :n_sv].copy_(r.singular_values)
+            out[:, n_sv].copy_(r.dims.view(torch.float32))
             self.sweeps = r.sweeps
             if world > 1:
                 ready = torch.cuda.Event()
@@ -317,8 +316,8 @@ def run_ours(args):
     grp = dist.group.WORLD if world > 1 else None
 
     def step_e2e(step_idx):
-        return estimate_anchors(eng, main_shard.host, K, sde, T_EPS, seed=step_idx, chunk=chunk, anchor_id0=rank * A,
-                                gather_group=grp, n_total=A * world)
+        return estimate_anchors(eng, main_shard.host, K, sde, T_EPS, seed=step_idx, gemm_chunk=chunk,
+                                anchor_id0=rank * A, gather_group=grp, n_total=A * world)
 
     step_e2e(0)
     barrier()
@@ -414,7 +413,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--anchors-per-gpu", type=int, default=512)
-    ap.add_argument("--chunk", type=int, default=128, help="anchors per device batch")
+    ap.add_argument("--chunk", type=int, default=256, help="anchors per pass of the tensor-core chain")
     ap.add_argument("--cpu-budget-s", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--short-train", type=int, default=0, help="untimed set-up: this many denoising-score-matching steps "

@@ -49,6 +49,8 @@ SIGNATURES = {
     "idb_fused_bias_act": (_i, [_vp, _vp, _vp, _i, _i, _f, _f, _ll, _i, _i, _vp, _vp]),
     "idb_groupnorm_stats": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _d, _vp, _vp, _vp]),
     "idb_conv_prep": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _i, _vp, _vp, _i, _f, _vp, _vp, _i, _vp, _vp]),
+    "idb_conv_prep_fir": (_i, [_vp, _i, _i, _i, _i, _vp, _i, _vp, _vp, _i, C.POINTER(C.c_float), _i, _i, _i, _i, _i, _i, _i, _f,
+                               _vp, _vp, _i, _vp, _vp]),
     "idb_conv2d": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, C.POINTER(C.c_int), _i, _i, _f, _f, _vp, _vp, _i,
                         _vp, _i, _vp]),
     "idb_conv_stats_slots": (_i, [_i, _i]),
@@ -89,7 +91,7 @@ def load():
 KERNELS_PER_CALL = {"idb_perturb": 1, "idb_perturb_rows": 1, "idb_pack_weight": 1, "idb_anchor_linear": 1, "idb_fcn_hidden_layer": 1,
                     "idb_fcn_output_layer": 1, "idb_fcn_anchor_layer": 1, "idb_fcn_scores": 1, "idb_ksphere_gt_score": 1, "idb_center_gram": 2, "idb_column_sums": 1, "idb_gram_about": 1,
                     "idb_spectrum": 2, "idb_id_from_spectrum": 1, "idb_upfirdn2d": 1, "idb_fused_bias_act": 1,
-                    "idb_groupnorm_stats": 2, "idb_conv_prep": 1, "idb_conv2d": 1, "idb_conv2d_stats": 1, "idb_groupnorm_from_conv_stats": 1, "idb_attention": 1,
+                    "idb_groupnorm_stats": 2, "idb_conv_prep": 1, "idb_conv_prep_fir": 1, "idb_conv2d": 1, "idb_conv2d_stats": 1, "idb_groupnorm_from_conv_stats": 1, "idb_attention": 1,
                     "idb_row_gram": 3, "idb_spectrum_large": 2, "idb_spectrum_large_variant": 2}
 launch_count = 0
 

@@ -64,6 +64,7 @@ int idb_conv_prep(const float* src0, int C0, const float* src1, int C1, int N, i
     idb::PrepParams p;
     p.src0 = src0; p.src1 = src1; p.C0 = C0; p.C1 = C1; p.N = N; p.Hs = Hs; p.Ws = Ws; p.src_nchw = src_nchw;
     p.mode = mode;
+    p.fir_kh = p.fir_kw = 0; p.fir_up = p.fir_down = 1; p.fir_pad0 = p.fir_planes = p.fir_hf = p.fir_wf = 0;
     p.planes = mode == 2 ? 4 : 1;
     p.Ho = mode == 1 ? 2 * Hs : (mode == 0 ? Hs : (mode == 2 ? (Hs + 1) / 2 : Hs / 2));
     p.Wo = mode == 1 ? 2 * Ws : (mode == 0 ? Ws : (mode == 2 ? (Ws + 1) / 2 : Ws / 2));
@@ -73,6 +74,41 @@ int idb_conv_prep(const float* src0, int C0, const float* src1, int C1, int N, i
     p.Cp = out_hi ? Cp : ((C + 7) & ~7);
     p.out_f32 = out_f32;
     return api_check(idb::launch_conv_prep(p, idb::api_num_sms(), static_cast<cudaStream_t>(stream)), "idb_conv_prep");
+}
+
+int idb_conv_prep_fir(const float* src0, int C0, int N, int Hs, int Ws, const float* mean_rstd, int groups,
+                      const float* gamma, const float* beta, int act, const float* kernel_host, int kh, int kw, int up,
+                      int down, int pad0, int pad1, int as_planes, float scale, void* out_hi, void* out_lo, int Cp,
+                      float* out_f32, void* stream) {
+    if (!src0 || !kernel_host || C0 <= 0 || N < 0 || Hs <= 0 || Ws <= 0) return api_fail("idb_conv_prep_fir: bad argument");
+    if (kh < 1 || kh > 4 || kw < 1 || kw > 4) return api_fail("idb_conv_prep_fir: FIR kernels up to 4 x 4");
+    if ((up != 1 && up != 2) || (down != 1 && down != 2) || (as_planes && down != 1) || pad0 < 0 || pad1 < 0)
+        return api_fail("idb_conv_prep_fir: up, down in {1, 2}, pads >= 0, as_planes needs down = 1");
+    if ((out_hi == nullptr) != (out_lo == nullptr)) return api_fail("idb_conv_prep_fir: out_hi/out_lo both or neither");
+    if (!out_hi && !out_f32) return api_fail("idb_conv_prep_fir: no output requested");
+    if (out_hi && (Cp % 64 || Cp < C0)) return api_fail("idb_conv_prep_fir: Cp must be a multiple of 64 and >= C");
+    if (mean_rstd && (groups <= 0 || C0 % groups)) return api_fail("idb_conv_prep_fir: bad groups");
+    if (act < 0 || act > 1) return api_fail("idb_conv_prep_fir: act must be 0 or 1");
+    if (out_hi && !(scale > 0.f)) return api_fail("idb_conv_prep_fir: scale must be positive");
+    const int hf = (Hs * up + pad0 + pad1 - kh) / down + 1, wf = (Ws * up + pad0 + pad1 - kw) / down + 1;
+    if (hf <= 0 || wf <= 0) return api_fail("idb_conv_prep_fir: empty output");
+    idb::PrepParams p;
+    p.src0 = src0; p.src1 = nullptr; p.C0 = C0; p.C1 = 0; p.N = N; p.Hs = Hs; p.Ws = Ws; p.src_nchw = 0;
+    p.mode = 4;
+    for (int a = 0; a < 4; ++a)
+        for (int b = 0; b < 4; ++b)   // the reference correlates with the FLIPPED kernel (upfirdn2d_kernel.cu:137)
+            p.fir[a * 4 + b] = (a < kh && b < kw) ? kernel_host[(kh - 1 - a) * kw + (kw - 1 - b)] : 0.f;
+    p.fir_kh = kh; p.fir_kw = kw; p.fir_up = up; p.fir_down = down; p.fir_pad0 = pad0; p.fir_planes = as_planes ? 1 : 0;
+    p.fir_hf = hf; p.fir_wf = wf;
+    p.planes = as_planes ? 4 : 1;
+    p.Ho = as_planes ? (hf + 1) / 2 : hf;
+    p.Wo = as_planes ? (wf + 1) / 2 : wf;
+    p.mean_rstd = mean_rstd; p.groups = mean_rstd ? groups : 1; p.cg = mean_rstd ? C0 / groups : C0;
+    p.gamma = gamma; p.beta = beta; p.act = act; p.scale = scale;
+    p.out_hi = static_cast<uint8_t*>(out_hi); p.out_lo = static_cast<uint8_t*>(out_lo);
+    p.Cp = out_hi ? Cp : ((C0 + 7) & ~7);
+    p.out_f32 = out_f32;
+    return api_check(idb::launch_conv_prep(p, idb::api_num_sms(), static_cast<cudaStream_t>(stream)), "idb_conv_prep_fir");
 }
 
 namespace {

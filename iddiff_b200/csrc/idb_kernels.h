@@ -112,7 +112,11 @@ struct PrepParams {
     const float* src0;  // NHWC [N][Hs][Ws][C0]  (NCHW [N][C0][Hs][Ws] when src_nchw)
     const float* src1;  // optional second tensor concatenated along C: [N][Hs][Ws][C1]
     int C0, C1, N, Hs, Ws, src_nchw;
-    int mode;           // 0 same size, 1 nearest x2 up, 2 stride-2 parity planes, 3 2x2 average pool
+    int mode;           // 0 same size, 1 nearest x2 up, 2 stride-2 parity planes, 3 2x2 average pool, 4 FIR resampling
+    // mode 4: upfirdn2d(transformed src, fir, up, down, pad) -- op/upfirdn2d_kernel.cu:107-207 folded into this pass
+    float fir[16];      // FLIPPED kernel, row-major [kh][4]
+    int fir_kh, fir_kw, fir_up, fir_down, fir_pad0, fir_planes;  // fir_planes: emit the 4 stride-2 parity planes of the
+    int fir_hf, fir_wf;                                          // (down = 1) result, whose size is fir_hf x fir_wf
     int planes, Ho, Wo;
     int wo_shift, ho_shift;  // log2 when Wo / Ho are powers of two, else -1 (filled by the launcher)
     const float* mean_rstd;  // [N][groups][2] or null

@@ -227,8 +227,9 @@ __device__ __forceinline__ void split2_fp16(float a, float b, uint32_t& hi, uint
     lo = *reinterpret_cast<const uint32_t*>(&l);
 }
 
-template <bool VEC, bool POOL>
-__global__ void __launch_bounds__(256, POOL ? 2 : 4) conv_prep_kernel(const PrepParams p) {
+template <bool VEC, int KIND>   // KIND 0: modes 0-2, 1: 2x2 average pool, 2: FIR resampling
+__global__ void __launch_bounds__(256, KIND ? 2 : 4) conv_prep_kernel(const PrepParams p) {
+    constexpr bool POOL = KIND == 1;
     // The launcher sizes the grid so that (gridDim.x * 256) % chunks == 0: a thread keeps ONE 8-channel chunk for its
     // whole grid-stride loop (per-channel parameters live in registers) and only the pixel index advances; all index
     // arithmetic is 32-bit, spatial sizes that are powers of two use shifts.
@@ -308,6 +309,35 @@ __global__ void __launch_bounds__(256, POOL ? 2 : 4) conv_prep_kernel(const Prep
                 } else {
 #pragma unroll
                     for (int j = 0; j < 8; ++j) v[j] = 0.f;
+                }
+            } else if (KIND == 2 && p.mode == 4) {
+                // upfirdn2d of the TRANSFORMED tensor (layerspp.py:244-257: FIR up/down-sampling of act(GN(x)) and of x;
+                // ncsnpp.py:297-304: FIR pad before the stride-2 convolution of the input pyramid), gathered per output
+                // pixel: out[y][x] = sum_ab fir[a][b] * U[y*down + a - pad0][x*down + b - pad0], U = zero-stuffed (up)
+                // transformed source, zero outside.  No intermediate tensor exists.
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] = 0.f;
+                const int yf = p.fir_planes ? 2 * yo + (plane >> 1) : yo, xf = p.fir_planes ? 2 * xo + (plane & 1) : xo;
+                if (yf < p.fir_hf && xf < p.fir_wf) {
+                    const int y0 = yf * p.fir_down - p.fir_pad0, x0 = xf * p.fir_down - p.fir_pad0;
+                    for (int a = 0; a < p.fir_kh; ++a) {
+                        int i = y0 + a;
+                        if (i < 0 || (p.fir_up == 2 && (i & 1))) continue;
+                        if (p.fir_up == 2) i >>= 1;
+                        if (i >= p.Hs) continue;
+                        for (int b = 0; b < p.fir_kw; ++b) {
+                            int jx = x0 + b;
+                            if (jx < 0 || (p.fir_up == 2 && (jx & 1))) continue;
+                            if (p.fir_up == 2) jx >>= 1;
+                            if (jx >= p.Ws) continue;
+                            float t[8];
+                            prep_load8<VEC>(p, n, i, jx, c0, C, t);
+                            prep_transform8<VEC>(p, k, c0, C, t);
+                            const float wgt = p.fir[a * 4 + b];
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) v[j] = fmaf(wgt, t[j], v[j]);
+                        }
+                    }
                 }
             }
         }
@@ -439,11 +469,14 @@ cudaError_t launch_conv_prep(const PrepParams& p_in, int num_sms, cudaStream_t s
         return cudaGetLastError();
     }
     if (p.mode == 3) {
-        if (vec) conv_prep_kernel<true, true><<<(unsigned)grid, 256, 0, stream>>>(p);
-        else conv_prep_kernel<false, true><<<(unsigned)grid, 256, 0, stream>>>(p);
+        if (vec) conv_prep_kernel<true, 1><<<(unsigned)grid, 256, 0, stream>>>(p);
+        else conv_prep_kernel<false, 1><<<(unsigned)grid, 256, 0, stream>>>(p);
+    } else if (p.mode == 4) {
+        if (vec) conv_prep_kernel<true, 2><<<(unsigned)grid, 256, 0, stream>>>(p);
+        else conv_prep_kernel<false, 2><<<(unsigned)grid, 256, 0, stream>>>(p);
     } else {
-        if (vec) conv_prep_kernel<true, false><<<(unsigned)grid, 256, 0, stream>>>(p);
-        else conv_prep_kernel<false, false><<<(unsigned)grid, 256, 0, stream>>>(p);
+        if (vec) conv_prep_kernel<true, 0><<<(unsigned)grid, 256, 0, stream>>>(p);
+        else conv_prep_kernel<false, 0><<<(unsigned)grid, 256, 0, stream>>>(p);
     }
     return cudaGetLastError();
 }

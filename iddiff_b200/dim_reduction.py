@@ -222,7 +222,7 @@ def sharded_centred_gram(S_loc: torch.Tensor, K: int, scale: float, group=None, 
 def estimate_anchors(engine, anchors: torch.Tensor, K: int, sde, t: float, *, seed: int = 0,
                      z: Optional[torch.Tensor] = None, chunk: Optional[int] = None, anchor_id0: int = 0,
                      mem_budget_bytes: int = 24 << 30, gather_group=None,
-                     n_total: Optional[int] = None) -> Dict[str, torch.Tensor]:
+                     n_total: Optional[int] = None, gemm_chunk: Optional[int] = None) -> Dict[str, torch.Tensor]:
     """anchors [N, D] (host or device) -> {'singular_values': [N, n] fp32, 'dims': [N] int32, 'sweeps'} on the
     HOST.  Host anchors are copied to the device chunk by chunk (pinned staging), results copied back once.
     With `gather_group` (anchors sharded over the ranks of a process group, `n_total` anchors in all) the spectra and
@@ -233,8 +233,14 @@ def estimate_anchors(engine, anchors: torch.Tensor, K: int, sde, t: float, *, se
     label = float((torch.ones(1, dtype=torch.float32) * t * (sde.N - 1))[0])
     if chunk is None:
         per = engine.bytes_per_anchor(K) if isinstance(engine, FcnEngine) else engine.bytes_per_anchor(K, D)
+        if isinstance(engine, FcnEngine):
+            mem_budget_bytes = max(mem_budget_bytes - engine.chain_bytes(K), per)
         if not isinstance(engine, (FcnEngine, KSphereEngine)):
             mem_budget_bytes = max(mem_budget_bytes, 96 << 30)  # image score matrices: size chunks for 180 GB HBM3e
+        # the budgets above are caps: on a shared or partly occupied device the chunk shrinks to what is actually free
+        # (60 % of it: the U-Net activation pool and the CUDA-graph private pools live beside the score matrices)
+        free_bytes, _ = torch.cuda.mem_get_info(dev)
+        mem_budget_bytes = min(mem_budget_bytes, int(free_bytes * 0.6))
         chunk = max(1, min(N, mem_budget_bytes // max(per, 1)))
     svs, dims, sweeps = [], [], []
     for s in range(0, N, chunk):
@@ -243,8 +249,9 @@ def estimate_anchors(engine, anchors: torch.Tensor, K: int, sde, t: float, *, se
             x0 = x0.contiguous().float()
             x0 = (x0 if x0.is_pinned() else x0.pin_memory()).to(dev, non_blocking=True)
         zc = None if z is None else z[s:s + chunk].to(dev, non_blocking=True).contiguous()
+        extra = {"chunk": gemm_chunk} if (gemm_chunk and isinstance(engine, FcnEngine)) else {}
         r: SpectrumResult = engine.estimate(x0.contiguous(), K, mc, std, label, z=zc, seed=seed,
-                                            anchor_id0=anchor_id0 + s)
+                                            anchor_id0=anchor_id0 + s, **extra)
         svs.append(r.singular_values)
         dims.append(r.dims)
         sweeps.append(r.sweeps)

@@ -188,13 +188,19 @@ class FcnEngine:
         return cls([m.weight.detach().to(device, torch.float32) for m in lin],
                    [m.bias.detach().to(device, torch.float32) for m in lin])
 
+    GEMM_CHUNK = 256   # anchors per pass of the tensor-core chain (activation ping-pong buffers: 2 x 3.2 GB at K = 1501)
+
     def rows_per_anchor(self, K: int) -> int:
         return _ceil(K, 128)
 
     def bytes_per_anchor(self, K: int) -> int:
+        """Per anchor of one estimate() call: fp32 deviations of the output layer, fp64 Gram + solver workspace; the
+        activation buffers of the GEMM chain are bounded by GEMM_CHUNK, not by the call."""
         Kp = self.rows_per_anchor(K)
-        act = max(self.Np[:-1]) * 2 * 2  # hi + lo, bf16
-        return Kp * (2 * act + self.Kc[0] * 4 + self.Np[-1] * 4) + self.D * self.D * 8 * 3
+        return Kp * (self.Kc[0] * 4 + self.Np[-1] * 4) + self.D * self.D * 8 * 3
+
+    def chain_bytes(self, K: int) -> int:
+        return self.GEMM_CHUNK * self.rows_per_anchor(K) * max(self.Np[:-1]) * 2 * 2 * 2
 
     def anchor_chain(self, x0: torch.Tensor, mean_coeff: float, label: float) -> List[torch.Tensor]:
         """Pre-activations of every layer at the un-perturbed anchors, fp32: list of [>= A, Np[l]].
@@ -243,8 +249,10 @@ class FcnEngine:
         return P
 
     def deviations(self, x0: torch.Tensor, K: int, mean_coeff: float, std: float, label: float,
-                   z: Optional[torch.Tensor] = None, seed: int = 0, anchor_id0: int = 0):
-        """Runs perturb + anchor chain + GEMM chain.  Returns (d_out [A, Kp, Np_last] fp32, a_out [A, Np_last])."""
+                   z: Optional[torch.Tensor] = None, seed: int = 0, anchor_id0: int = 0, P=None, d_out=None):
+        """Runs perturb + anchor chain + GEMM chain.  Returns (d_out [A, Kp, Np_last] fp32, a_out [A, Np_last]).
+        P: anchor pre-activations of these anchors when the caller already ran the anchor chain (one chain for all
+        the chunks of a call); d_out: where to write (a slice of the caller's buffer)."""
         _require_cuda(x0, "x0")
         A, D = x0.shape
         if D != self.D:
@@ -262,8 +270,9 @@ class FcnEngine:
         with _stage("perturb", 2.0 * M * self.Kc[0] * 2):
             call("idb_perturb", ptr(x0), ptr(z), A, K, D, Kp, self.Kc[0], float(mean_coeff), float(std), int(seed),
                  int(anchor_id0), None, self.fmt, self.a_scale, ptr(e_hi), ptr(e_lo), st)
-        with _stage("anchor_chain", sum(2.0 * A * i * o for i, o in zip(self.in_real, self.out_real))):
-            P = self.anchor_chain(x0, mean_coeff, label)
+        if P is None:
+            with _stage("anchor_chain", sum(2.0 * A * i * o for i, o in zip(self.in_real, self.out_real))):
+                P = self.anchor_chain(x0, mean_coeff, label)
         for l in range(self.n_layers - 1):
             o_hi = torch.empty(M * self.Np[l] * 2, dtype=torch.uint8, device=dev)
             o_lo = torch.empty(M * self.Np[l] * 2, dtype=torch.uint8, device=dev)
@@ -273,7 +282,8 @@ class FcnEngine:
                      ptr(o_hi), ptr(o_lo), st)
             e_hi, e_lo = o_hi, o_lo
         l = self.n_layers - 1
-        d_out = torch.empty(A, Kp, self.Np[l], dtype=torch.float32, device=dev)
+        if d_out is None:
+            d_out = torch.empty(A, Kp, self.Np[l], dtype=torch.float32, device=dev)
         with _stage("output", 2.0 * A * K * self.in_real[l] * self.out_real[l]):
             call("idb_fcn_output_layer", ptr(e_hi), ptr(e_lo), ptr(self.w_hi[l]), ptr(self.w_lo[l]), self.fmt,
                  self.w_inv_scale[l] / self.a_scale, M, self.Np[l], self.Kc[l], ptr(d_out), st)
@@ -286,11 +296,26 @@ class FcnEngine:
 
     def estimate(self, x0: torch.Tensor, K: int, mean_coeff: float, std: float, label: float,
                  z: Optional[torch.Tensor] = None, seed: int = 0, anchor_id0: int = 0,
-                 want_scores: bool = False, defer: bool = False) -> SpectrumResult:
-        """defer=True: the spectrum stage (fp64 Gram, eigen-solver, read-out: small latency-bound kernels) is enqueued
-        on a second CUDA stream so that it overlaps the tensor-core chain of the NEXT chunk; the caller must call
-        join() before reading the results on its own stream."""
-        d_out, a_out = self.deviations(x0, K, mean_coeff, std, label, z, seed, anchor_id0)
+                 want_scores: bool = False, defer: bool = False, chunk: Optional[int] = None) -> SpectrumResult:
+        """All anchors of x0 in one call: ONE anchor chain, the tensor-core chain in passes of `chunk` anchors
+        (default GEMM_CHUNK), then ONE centre/Gram + eigen-solve + read-out over all of them (the one-CTA-per-anchor
+        stages fill the SMs in ceil(A / 148) waves instead of one wave per chunk).
+        defer=True: the spectrum stage is enqueued on a second CUDA stream; the caller must call join() before
+        reading the results on its own stream."""
+        A = x0.shape[0]
+        ck = min(A, chunk or self.GEMM_CHUNK)
+        if A <= ck:
+            d_out, a_out = self.deviations(x0, K, mean_coeff, std, label, z, seed, anchor_id0)
+        else:
+            _require_cuda(x0, "x0")
+            with _stage("anchor_chain", sum(2.0 * A * i * o for i, o in zip(self.in_real, self.out_real))):
+                P = self.anchor_chain(x0, mean_coeff, label)
+            d_out = torch.empty(A, self.rows_per_anchor(K), self.Np[-1], dtype=torch.float32, device=self.dev)
+            for s in range(0, A, ck):
+                e = min(A, s + ck)
+                self.deviations(x0[s:e], K, mean_coeff, std, label, None if z is None else z[s:e], seed,
+                                anchor_id0 + s, P=[q[s:] for q in P], d_out=d_out[s:e])
+            a_out = P[-1]
         # centring removes the anchor part exactly: spectrum of (-(a + d)/std - mean) = spectrum of (d - mean(d))/std
         if defer and not want_scores:
             main = torch.cuda.current_stream(self.dev)

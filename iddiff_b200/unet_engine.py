@@ -62,6 +62,7 @@ class _Res:
                 raise NotImplementedError("BigGAN res-block resampling without FIR (naive_up/downsample) is not built")
             # upsample_2d: k * factor^2, up 2, pad (2, 1); downsample_2d: k, down 2, pad (1, 1)  (up_or_down_sampling.py:181-257)
             self.fir = U.fir_kernel(m.fir_kernel, 4.0 if self.up else 1.0, dev)
+            self.fir_host = U.fir_kernel_host(m.fir_kernel, 4.0 if self.up else 1.0)
 
 
 class _Attn:
@@ -85,6 +86,7 @@ class _PyrDown:
     def __init__(self, m, dev):
         self.conv = U.pack_conv(_f32(m.Conv2d_0.weight, dev), _f32(m.Conv2d_0.bias, dev), taps=U.TAPS_3x3_S2, planes=4)
         self.fir = U.fir_kernel(m.fir_kernel, 1.0, dev)
+        self.fir_host = U.fir_kernel_host(m.fir_kernel, 1.0)
 
 
 class _BRes:
@@ -216,6 +218,14 @@ class UNetEngine:
         if blk.up or blk.down:
             # layerspp.py:244-257: FIR resampling of BOTH act(GN(x)) and x before the convolutions
             assert x1 is None
+            if U.FUSED_FIR:
+                # one gathering pass per branch: act(GN(x)) -> FIR -> operand, and x -> FIR -> fp32; neither the
+                # normalised nor the filtered activation is materialised (no upfirdn2d launch)
+                updn = (2, 1, 2, 1) if blk.up else (1, 2, 1, 1)
+                a = U.prep_fir(x0, blk.fir_host, *updn, mean_rstd=mr, groups=blk.groups0, gamma=blk.gn0[0],
+                               beta=blk.gn0[1], act=1)
+                x0 = U.prep_fir(x0, blk.fir_host, *updn, want_operand=False, want_f32=True)[1]
+                return self._res_tail(blk, bias0, a, x0, None)
             _, hf = U.prep(x0, mean_rstd=mr, groups=blk.groups0, gamma=blk.gn0[0], beta=blk.gn0[1], act=1,
                            want_operand=False, want_f32=True)
             if blk.up:
@@ -226,6 +236,9 @@ class UNetEngine:
             x0 = xr
         else:
             a = U.prep(x0, x1, mean_rstd=mr, groups=blk.groups0, gamma=blk.gn0[0], beta=blk.gn0[1], act=1)
+        return self._res_tail(blk, bias0, a, x0, x1)
+
+    def _res_tail(self, blk: _Res, bias0, a, x0, x1):
         h = U.conv(a, blk.conv0, bias=bias0, want_stats=True)
         mr = U.gn_stats(h, None, blk.groups1, self.EPS)
         a = U.prep(h, mean_rstd=mr, groups=blk.groups1, gamma=blk.gn1[0], beta=blk.gn1[1], act=1)
@@ -289,8 +302,11 @@ class UNetEngine:
                 h = U.conv(a, blk, want_stats=True)
             elif kind == "pyr_down":
                 # conv_downsample_2d (up_or_down_sampling.py:144-178) then (pyramid + h) / sqrt(2) (ncsnpp.py:300-304)
-                f = U.upfirdn2d_nhwc(pyramid, blk.fir, 1, 1, 2, 2)
-                h = U.conv(U.prep(f, mode=U.PREP_STRIDE2), blk.conv, residual=h, out_scale=self.rescale,
+                if U.FUSED_FIR:
+                    a = U.prep_fir(pyramid, blk.fir_host, 1, 1, 2, 2, as_planes=True)
+                else:
+                    a = U.prep(U.upfirdn2d_nhwc(pyramid, blk.fir, 1, 1, 2, 2), mode=U.PREP_STRIDE2)
+                h = U.conv(a, blk.conv, residual=h, out_scale=self.rescale,
                            out_hw=(h.shape[1], h.shape[2]), want_stats=True)
                 pyramid = h
             elif kind == "push":

@@ -139,6 +139,47 @@ def prep(x0: torch.Tensor, x1: Optional[torch.Tensor] = None, *, mode: int = PRE
     return op
 
 
+FUSED_FIR = True   # FIR resampling folded into the operand-preparation pass (False: stand-alone idb_upfirdn2d launches)
+
+
+def fir_kernel_host(taps, gain: float):
+    """up_or_down_sampling._setup_kernel (:165-172) * gain as a contiguous numpy float32 [kh][kw] (host)."""
+    import numpy as np
+    k = np.asarray(taps, dtype=np.float32)
+    if k.ndim == 1:
+        k = np.outer(k, k)
+    k /= np.sum(k)
+    return np.ascontiguousarray(k * np.float32(gain), dtype=np.float32)
+
+
+def prep_fir(x0: torch.Tensor, k_host, up: int, down: int, pad0: int, pad1: int, *, as_planes: bool = False,
+             mean_rstd=None, groups: int = 0, gamma=None, beta=None, act: int = 0, want_operand: bool = True,
+             want_f32: bool = False):
+    """upfirdn2d(act(GN(x0)), k, up, down, (pad0, pad1)) written straight as the convolution operand and / or fp32 NHWC
+    (idb_conv_prep_fir); as_planes: the four stride-2 parity planes of the down = 1 result (conv_downsample_2d)."""
+    n, hs, ws, c = x0.shape
+    kh, kw = k_host.shape
+    hf = (hs * up + pad0 + pad1 - kh) // down + 1
+    wf = (ws * up + pad0 + pad1 - kw) // down + 1
+    planes = 4 if as_planes else 1
+    ho, wo = ((hf + 1) // 2, (wf + 1) // 2) if as_planes else (hf, wf)
+    cp = _ceil(c, 64)
+    dev = x0.device
+    hi = lo = None
+    if want_operand:
+        hi = torch.empty(planes, n, ho, wo, cp, dtype=torch.float16, device=dev)
+        lo = torch.empty_like(hi)
+    f32 = torch.empty(planes, n, ho, wo, c, dtype=torch.float32, device=dev) if want_f32 else None
+    kptr = k_host.ctypes.data_as(C.POINTER(C.c_float))
+    _lib.call("idb_conv_prep_fir", _lib.ptr(x0), c, n, hs, ws, _lib.ptr(mean_rstd), groups, _lib.ptr(gamma), _lib.ptr(beta),
+              act, kptr, kh, kw, up, down, pad0, pad1, int(as_planes), ACT_SCALE, _lib.ptr(hi), _lib.ptr(lo), cp,
+              _lib.ptr(f32), _lib.stream_ptr())
+    op = Operand(hi, lo, planes, n, ho, wo, cp) if want_operand else None
+    if want_f32:
+        return op, (f32[0] if planes == 1 else f32)
+    return op
+
+
 def conv(a: Operand, pc: PackedConv, *, bias: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None,
          out_scale: float = 1.0, out: Optional[torch.Tensor] = None, out_hw=None, want_stats: bool = False) -> torch.Tensor:
     """out [N,H,W,Cout] fp32 = out_scale * (conv(a, W) + bias + residual).  `bias` overrides pc.bias (the host folds

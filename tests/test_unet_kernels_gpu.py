@@ -158,3 +158,53 @@ def test_groupnorm_statistics_from_the_conv_epilogue(n, cin, cout, h, w, groups)
     np.testing.assert_allclose(cat_fused[..., 1].cpu().numpy(), (1 / torch.sqrt(cd.var(-1, unbiased=False) + 1e-6)).numpy(), rtol=2e-6)
     again = U.conv(a, pc, residual=res, out_scale=0.7, want_stats=True)
     assert torch.equal(again._idb_stats, y._idb_stats)
+
+
+@pytest.mark.parametrize("kind", ["down", "up", "pyramid"])
+@pytest.mark.parametrize("norm", [False, True])
+def test_fir_folded_into_operand_preparation(kind, norm):
+    """Row g1: idb_conv_prep_fir = upfirdn2d(act(GN(x))) gathered per output pixel, against (a) the oracle's numpy
+    upfirdn2d of the torch fp64 transform and (b) the unfused kernel sequence it replaces (prep -> idb_upfirdn2d -> prep):
+    layerspp.py:244-257 down (1, 2, pad 1 1) / up (kernel x 4, 2, 1, pad 2 1), and the input pyramid's pad-only FIR
+    (up_or_down_sampling.py:144-178) emitted as the four stride-2 parity planes."""
+    from iddiff_b200 import unet_ops as U
+    from oracle import img_oracle as IO
+    torch.manual_seed(7)
+    n, c, h, w, groups = 3, 48, 16, 16, 12
+    x = torch.randn(n, c, h, w) * 2 + 0.5
+    gamma, beta = torch.randn(c), torch.randn(c)
+    xg = nhwc(x).cuda()
+    gain = 4.0 if kind == "up" else 1.0
+    kh = U.fir_kernel_host([1, 3, 3, 1], gain)
+    kd = U.fir_kernel([1, 3, 3, 1], gain, "cuda")
+    up, down, p0, p1 = {"down": (1, 2, 1, 1), "up": (2, 1, 2, 1), "pyramid": (1, 1, 2, 2)}[kind]
+    kw = {}
+    t = x.double()
+    if norm:
+        mr = U.gn_stats(xg, None, groups, 1e-6)
+        kw = dict(mean_rstd=mr, groups=groups, gamma=gamma.cuda(), beta=beta.cuda(), act=1)
+        t = F.silu(F.group_norm(t, groups, gamma.double(), beta.double(), eps=1e-6))
+    op, f32 = U.prep_fir(xg, kh, up, down, p0, p1, as_planes=kind == "pyramid", want_f32=True, **kw)
+    # (a) oracle: numpy upfirdn2d on [major = N*C, H, W, minor = 1]
+    ref = IO.upfirdn2d_np(t.numpy().reshape(n * c, h, w, 1), kh.astype(np.float64), up, up, down, down, p0, p1, p0, p1)
+    ref = torch.from_numpy(ref.reshape(n, c, ref.shape[1], ref.shape[2]))
+    if kind == "pyramid":
+        refp = F.pad(ref, (0, 1, 0, 1))
+        ho = (ref.shape[2] + 1) // 2
+        ref_nhwc = torch.stack([nhwc(refp[:, :, py::2, px::2][:, :, :ho, :ho]) for py in (0, 1) for px in (0, 1)])
+        got = f32
+    else:
+        ref_nhwc, got = nhwc(ref)[None], f32[None]
+    assert got.shape == ref_nhwc.shape
+    np.testing.assert_allclose(got.cpu().numpy(), ref_nhwc.numpy(), rtol=2e-5, atol=2e-6)
+    rec = (op.hi.double() + op.lo.double()) / U.ACT_SCALE
+    np.testing.assert_allclose(rec[..., :c].cpu().numpy(), got.double().cpu().numpy(), rtol=1e-6, atol=1e-8)
+    assert float(rec[..., c:].abs().max()) == 0.0
+    # (b) the unfused sequence
+    tf = U.prep(xg, want_operand=False, want_f32=True, **kw)[1]
+    f = U.upfirdn2d_nhwc(tf, kd, up, down, p0, p1)
+    if kind == "pyramid":
+        old = U.prep(f, mode=U.PREP_STRIDE2, want_f32=True)[1]
+    else:
+        old = f[None]
+    np.testing.assert_allclose(got.cpu().numpy(), old.cpu().numpy(), rtol=2e-5, atol=2e-6)
