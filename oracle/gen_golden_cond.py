@@ -83,3 +83,17 @@ def gen_cond(name, sde, seed, B=64, num_datapoints=3):
 if __name__ == "__main__":
     gen_cond("cond_ddpm_small_ve", "vesde", seed=23)
     gen_cond("cond_ddpm_small_vp", "vpsde", seed=29)
+
+
+def gen_readout_tail():
+    """plot_utils.plot_distribution(svd, mode='all', tail=t) of the REAL reference on the readout.npz spectra."""
+    import plot_utils
+    plot_utils.plt = mock.MagicMock()
+    g = np.load(os.path.join(GG.GOLD, "readout.npz"))
+    spectra = [g["spectra"][i, :int(n)].tolist() for i, n in enumerate(g["lens"])]
+    out = {}
+    for t in (1, 3, 8, 50):
+        with mock.patch("builtins.print"):
+            out[f"tail_{t}"] = np.asarray(plot_utils.plot_distribution({"singular_values": spectra}, mode="all", tail=t))
+    np.savez_compressed(os.path.join(GG.GOLD, "readout_tail.npz"), **out)
+    print("readout_tail", {k: v.tolist() for k, v in out.items()})

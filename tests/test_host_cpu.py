@@ -199,3 +199,17 @@ def test_synthetic_image_manifolds_match_the_reference_generators():
     dm.setup()
     batch = next(iter(dm.train_dataloader()))
     assert tuple(batch.shape) == (8, 1, 32, 32) and len(dm.train_data) == 32 and len(dm.valid_data) == 4
+
+
+def test_plot_distribution_tail_truncates_the_softmax_like_the_reference():
+    """plot_utils.py:178-179: `tail` keeps the last entries of the SOFTMAX (not of the spectrum); golden from the real
+    reference's plot_distribution(mode='all', tail=t) on the readout fixtures."""
+    import numpy as np
+    from iddiff_b200 import plot_utils
+    from oracle import fixtures as FX
+    g, gt = FX.golden("readout"), FX.golden("readout_tail")
+    spectra = [g["spectra"][i, :int(n)].tolist() for i, n in enumerate(g["lens"])]
+    for t in (1, 3, 8, 50):
+        assert plot_utils.plot_distribution({"singular_values": spectra}, mode="all", tail=t) == gt[f"tail_{t}"].tolist()
+    assert plot_utils.plot_distribution({"singular_values": spectra}, mode="all") == g["dims"].tolist()
+    assert plot_utils.plot_dims({"singular_values": spectra})[1] == g["dims"].tolist()
