@@ -242,7 +242,7 @@ def estimate_anchors(engine, anchors: torch.Tensor, K: int, sde, t: float, *, se
         free_bytes, _ = torch.cuda.mem_get_info(dev)
         mem_budget_bytes = min(mem_budget_bytes, int(free_bytes * 0.6))
         chunk = max(1, min(N, mem_budget_bytes // max(per, 1)))
-    svs, dims, sweeps = [], [], []
+    svs, dims, sweeps, finite = [], [], [], []
     for s in range(0, N, chunk):
         x0 = anchors[s:s + chunk]
         if not x0.is_cuda:
@@ -255,6 +255,9 @@ def estimate_anchors(engine, anchors: torch.Tensor, K: int, sde, t: float, *, se
         svs.append(r.singular_values)
         dims.append(r.dims)
         sweeps.append(r.sweeps)
+        if r.finite is not None:
+            finite.append(r.finite)
+    ok_dev = torch.cat(finite).all() if finite else None
     out = {"singular_values": torch.cat(svs), "dims": torch.cat(dims), "sweeps": torch.cat(sweeps)}
     if gather_group is not None:
         out["singular_values"], out["dims"] = all_gather_spectra(out["singular_values"], out["dims"],
@@ -262,14 +265,18 @@ def estimate_anchors(engine, anchors: torch.Tensor, K: int, sde, t: float, *, se
     host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True) for k, v in out.items()}
     for k in out:
         host[k].copy_(out[k], non_blocking=True)
+    ok_host = None
+    if ok_dev is not None:
+        ok_host = torch.empty((), dtype=torch.bool, pin_memory=True)
+        ok_host.copy_(ok_dev, non_blocking=True)
     torch.cuda.current_stream().synchronize()
-    if not bool(torch.isfinite(host["singular_values"]).all()):
+    if (ok_host is not None and not bool(ok_host)) or not bool(torch.isfinite(host["singular_values"]).all()):
         # the fp16 hi/lo operand split is unsaturated: |deviation| or |activation| * 64 beyond the fp16 range (> ~1023)
-        # turns into inf - inf = NaN in the tensor-core chain and would otherwise be read out as a full-rank ID
-        bad = (~torch.isfinite(host["singular_values"]).all(dim=1)).nonzero().flatten().tolist()
-        raise _lib.IdbError(f"non-finite spectrum for anchors {bad[:8]}{'...' if len(bad) > 8 else ''}: an operand left "
-                            "the fp16-pair range (|value| > ~1023 after scaling); normalise the data or run the FCN "
-                            "engine with fmt=FMT_BF16")
+        # turns into inf - inf = NaN in the tensor-core chain; the bisection would return finite garbage for such a
+        # Gram matrix and the read-out a full-rank ID, so the Gram diagonal is checked on the device
+        raise _lib.IdbError("non-finite spectrum: the score matrix of at least one anchor holds NaN / inf -- an operand "
+                            "left the fp16-pair range (|value| > ~1023 after scaling); normalise the data or run the "
+                            "FCN engine with fmt=FMT_BF16")
     return host
 
 

@@ -57,6 +57,7 @@ class SpectrumResult:
     dims: torch.Tensor             # [A] int32 (device); -1 where the reference raises ZeroDivisionError
     sweeps: torch.Tensor           # [A] int32 Jacobi sweeps
     scores: Optional[torch.Tensor] = None  # [A, K, D] fp32 raw scores when requested
+    finite: Optional[torch.Tensor] = None  # [A] bool: the anchor's Gram diagonal (sums of squared scores) is finite
 
 
 LARGE_N = 1024  # above this, one Gram matrix is solved by the whole GPU (idb_spectrum_large)
@@ -77,10 +78,17 @@ def _read_out(sv: torch.Tensor, A: int, n: int, st) -> torch.Tensor:
     return dims
 
 
+def _gram_finite(G: torch.Tensor) -> torch.Tensor:
+    """Guard, not arithmetic of the path: a NaN / inf score (an operand that left the fp16-pair range) makes the sum of
+    squares on the Gram diagonal non-finite, while the bisection would still return finite garbage for it."""
+    return torch.isfinite(torch.diagonal(G, dim1=-2, dim2=-1)).all(dim=-1)
+
+
 def spectrum_from_gram(G: torch.Tensor, n: int, method: Optional[int] = None) -> SpectrumResult:
     """Singular values + IDs from centred Gram matrices G [A, n, n] fp64 (overwritten when n > LARGE_N)."""
     A = G.shape[0]
     dev, st = G.device, stream_ptr()
+    finite = _gram_finite(G)
     sv = torch.empty(A, n, dtype=torch.float32, device=dev)
     sweeps = torch.zeros(A, dtype=torch.int32, device=dev)
     if n > LARGE_N:
@@ -92,7 +100,7 @@ def spectrum_from_gram(G: torch.Tensor, n: int, method: Optional[int] = None) ->
         with _stage("spectrum", A * (n * n * 8.0 + n * 4.0)):
             call("idb_spectrum", ptr(G), A, n, n, SPECTRUM_METHOD if method is None else method, ptr(sv),
                  ptr(sweeps), ptr(ws), st)
-    return SpectrumResult(sv, _read_out(sv, A, n, st), sweeps)
+    return SpectrumResult(sv, _read_out(sv, A, n, st), sweeps, finite=finite)
 
 
 def spectrum_from_rows(X: torch.Tensor, K: int, D: int, scale: float, rows_per_anchor: Optional[int] = None,
@@ -112,6 +120,7 @@ def spectrum_from_rows(X: torch.Tensor, K: int, D: int, scale: float, rows_per_a
     if large:
         # image-sized matrices: one anchor at a time, the whole GPU on each (cooperative tridiagonalisation)
         sv = torch.empty(A, n, dtype=torch.float32, device=dev)
+        finite = torch.empty(A, dtype=torch.bool, device=dev)
         ws = torch.empty(_lib.load().idb_spectrum_large_workspace_bytes(n), dtype=torch.uint8, device=dev)
         for a in range(A):
             with _stage("center_gram", K * D * 4.0 + n * n * 8.0):
@@ -119,8 +128,9 @@ def spectrum_from_rows(X: torch.Tensor, K: int, D: int, scale: float, rows_per_a
                     call("idb_row_gram", ptr(X[a]), ld, K, D, float(scale), ptr(colmean[a]), ptr(G), st)
                 else:
                     call("idb_center_gram", ptr(X[a]), R * ld, ld, 1, K, D, float(scale), ptr(colmean[a]), ptr(G), st)
+            finite[a] = _gram_finite(G[0])
             _solve_large(G[0], n, sv[a], ws, st)
-        return SpectrumResult(sv, _read_out(sv, A, n, st), torch.zeros(A, dtype=torch.int32, device=dev))
+        return SpectrumResult(sv, _read_out(sv, A, n, st), torch.zeros(A, dtype=torch.int32, device=dev), finite=finite)
     with _stage("center_gram", A * (K * D * 4.0 + n * n * 8.0)):
         if K < D:
             for a in range(A):
@@ -325,7 +335,7 @@ class FcnEngine:
             with torch.cuda.stream(self._side):
                 res = spectrum_from_rows(d_out, K, self.D, 1.0 / std)
             d_out.record_stream(self._side)
-            for t in (res.singular_values, res.dims, res.sweeps):
+            for t in (res.singular_values, res.dims, res.sweeps, res.finite):
                 t.record_stream(main)
             return res
         res = spectrum_from_rows(d_out, K, self.D, 1.0 / std)

@@ -83,3 +83,23 @@ def test_unet_path_oracle_matches_reference_spectrum(model):
     s = torch.linalg.svdvals(S).double().numpy()
     np.testing.assert_allclose(s, g["singular_values"][a], rtol=1e-3)
     assert O.id_from_spectrum(s.tolist()) == int(g["dims"][a])
+
+
+@pytest.mark.parametrize("which", ["beatgans", "ddpm", "ncsnpp"])
+def test_oracle_forward_at_full_size_against_the_real_reference(which):
+    """The oracle restatement at the size BASELINE configs 4-5 name (64x64x3, 87-126 M parameters) against the output of
+    the REAL reference module stored in tests/golden/unet_*_full.npz (oracle/gen_golden_unet_full.py)."""
+    import numpy as np
+    import torch
+    from oracle import fixtures as FX, img_oracle as IO
+    from iddiff_b200 import synthetic as SY, unet_models
+    g = FX.golden(f"unet_{which}_full")
+    name, spec, _ = SY.FULL_MODELS[which]
+    holder = unet_models.get_model(name)(SY.unet_config(spec, name))
+    state = SY.make_unet_state(holder, int(g["seed"]))
+    fwd = {"ddpm": IO.ddpm_forward, "ncsnpp": IO.ncsnpp_forward, "beatgans": IO.beatgans_forward}[which]
+    x = torch.from_numpy(g["x"][:1])
+    with torch.no_grad():
+        y = fwd(state, spec, x, torch.full((1,), float(g["label"]))).numpy()
+    scale = np.abs(g["y"]).max()
+    assert np.abs(y - g["y"][:1]).max() < 1e-5 * scale
