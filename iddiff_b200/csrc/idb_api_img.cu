@@ -59,7 +59,7 @@ int idb_conv_prep(const float* src0, int C0, const float* src1, int C1, int N, i
     if (out_hi && (Cp % 64 || Cp < C)) return api_fail("idb_conv_prep: Cp must be a multiple of 64 and >= C");
     if (mean_rstd && (groups <= 0 || C % groups)) return api_fail("idb_conv_prep: bad groups");
     if (mode == 3 && ((Hs | Ws) & 1)) return api_fail("idb_conv_prep: average pool needs even H, W");
-    if (act < 0 || act > 1) return api_fail("idb_conv_prep: act must be 0 or 1");
+    if (act < 0 || act > 2) return api_fail("idb_conv_prep: act must be 0, 1 or 2");
     if (out_hi && !(scale > 0.f)) return api_fail("idb_conv_prep: scale must be positive");
     idb::PrepParams p;
     p.src0 = src0; p.src1 = src1; p.C0 = C0; p.C1 = C1; p.N = N; p.Hs = Hs; p.Ws = Ws; p.src_nchw = src_nchw;
@@ -88,7 +88,7 @@ int idb_conv_prep_fir(const float* src0, int C0, int N, int Hs, int Ws, const fl
     if (!out_hi && !out_f32) return api_fail("idb_conv_prep_fir: no output requested");
     if (out_hi && (Cp % 64 || Cp < C0)) return api_fail("idb_conv_prep_fir: Cp must be a multiple of 64 and >= C");
     if (mean_rstd && (groups <= 0 || C0 % groups)) return api_fail("idb_conv_prep_fir: bad groups");
-    if (act < 0 || act > 1) return api_fail("idb_conv_prep_fir: act must be 0 or 1");
+    if (act < 0 || act > 2) return api_fail("idb_conv_prep_fir: act must be 0, 1 or 2");
     if (out_hi && !(scale > 0.f)) return api_fail("idb_conv_prep_fir: scale must be positive");
     const int hf = (Hs * up + pad0 + pad1 - kh) / down + 1, wf = (Ws * up + pad0 + pad1 - kw) / down + 1;
     if (hf <= 0 || wf <= 0) return api_fail("idb_conv_prep_fir: empty output");

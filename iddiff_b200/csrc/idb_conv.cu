@@ -29,6 +29,7 @@ constexpr uint32_t CA_TILE = CBM * 128;  // 16 KB: 128 pixels x 64 fp16 channels
 constexpr int C_EPI_WARPS = 16;
 constexpr int C_EPI_THREADS = C_EPI_WARPS * 32;
 constexpr int C_THREADS = 64 + C_EPI_THREADS;
+constexpr int C_SEG = 8;   // k-blocks (512 product terms, 96 tcgen05.mma) accumulated in TMEM before a flush to registers
 
 template <int BN> struct ConvCfg {
     static constexpr uint32_t B_TILE = BN * 128;
@@ -58,20 +59,35 @@ __device__ __forceinline__ void ld_global_nc_256(const float* src, float (&q)[8]
                  : "l"(src));
 }
 
-// Steps 8, 4, 2, 1 of the transposing butterfly over W live values per lane: after it a[0 .. W/16) hold the totals of
-// the channels this lane ends up owning (W = 16: channel `lane`; W = 32: channels 2 (lane & 15) + {0, 1}, summed over
-// the 16 lanes of the lane's half warp only).
-template <int W>
-__device__ __forceinline__ void stat_butterfly(float (&a)[32], float (&b)[32], int lane) {
+// Transposing butterfly over the 32 per-lane values of one quantity: afterwards lane l holds in a[0] the total of value
+// index l over the warp's 32 lanes (full warp), or -- half_warp, two images of 16 pixels per warp -- in a[0], a[1] the
+// totals of indices 2 (l & 15) + {0, 1} over the 16 lanes of its half.  31 (30) shuffles instead of 160.
+__device__ __forceinline__ void stat_butterfly(float (&a)[32], int lane, bool half_warp) {
+    if (!half_warp) {
+        const bool up = lane & 16;
 #pragma unroll
-    for (int m = 8, w = W; m >= 1; m >>= 1, w >>= 1) {
-        const bool up = lane & m;
+        for (int i = 0; i < 16; ++i) {
+            const float keep = up ? a[i + 16] : a[i], send = up ? a[i] : a[i + 16];
+            a[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+        }
 #pragma unroll
-        for (int i = 0; i < w / 2; ++i) {
-            const float ka = up ? a[i + w / 2] : a[i], sa = up ? a[i] : a[i + w / 2];
-            const float kb = up ? b[i + w / 2] : b[i], sb = up ? b[i] : b[i + w / 2];
-            a[i] = ka + __shfl_xor_sync(0xffffffffu, sa, m);
-            b[i] = kb + __shfl_xor_sync(0xffffffffu, sb, m);
+        for (int m = 8, w = 16; m >= 1; m >>= 1, w >>= 1) {
+            const bool u = lane & m;
+#pragma unroll
+            for (int i = 0; i < w / 2; ++i) {
+                const float keep = u ? a[i + w / 2] : a[i], send = u ? a[i] : a[i + w / 2];
+                a[i] = keep + __shfl_xor_sync(0xffffffffu, send, m);
+            }
+        }
+    } else {
+#pragma unroll
+        for (int m = 8, w = 32; m >= 1; m >>= 1, w >>= 1) {
+            const bool u = lane & m;
+#pragma unroll
+            for (int i = 0; i < w / 2; ++i) {
+                const float keep = u ? a[i + w / 2] : a[i], send = u ? a[i] : a[i + w / 2];
+                a[i] = keep + __shfl_xor_sync(0xffffffffu, send, m);
+            }
         }
     }
 }
@@ -145,35 +161,39 @@ __global__ void __launch_bounds__(C_THREADS, 1) conv_fp16x3_kernel(const __grid_
             const uint32_t idesc = umma_idesc_f16(CBM, BN, 0u, 0u);  // fp16 x fp16 -> fp32
             int stage = 0;
             uint32_t phase = 0;
-            int it = 0;
-            for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
-                const int as = it & 1;
-                const uint32_t aphase = (it >> 1) & 1;
-                mbar_wait(&tempty[as], aphase ^ 1);
-                tc_fence_after();
-                const uint32_t d_tmem = tmem_base + as * BN;
-                for (int kb = 0; kb < n_kb; ++kb) {
-                    mbar_wait(&full[stage], phase);
+            int it = 0;   // counts (tile, K-segment) accumulation phases: TMEM buffer it & 1
+            for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+                for (int kb0 = 0; kb0 < n_kb; kb0 += C_SEG, ++it) {
+                    const int as = it & 1;
+                    const uint32_t aphase = (it >> 1) & 1;
+                    mbar_wait(&tempty[as], aphase ^ 1);
                     tc_fence_after();
-                    const uint32_t sa = smem_u32(smem + (size_t)stage * Cfg::STAGE);
-                    const uint64_t ah = umma_desc_sw128(sa);
-                    const uint64_t al = umma_desc_sw128(sa + CA_TILE);
-                    const uint64_t bh = umma_desc_sw128(sa + 2 * CA_TILE);
-                    const uint64_t bl = umma_desc_sw128(sa + 2 * CA_TILE + Cfg::B_TILE);
+                    const uint32_t d_tmem = tmem_base + as * BN;
+                    const int kb1 = kb0 + C_SEG < n_kb ? kb0 + C_SEG : n_kb;
+                    for (int kb = kb0; kb < kb1; ++kb) {
+                        mbar_wait(&full[stage], phase);
+                        tc_fence_after();
+                        const uint32_t sa = smem_u32(smem + (size_t)stage * Cfg::STAGE);
+                        const uint64_t ah = umma_desc_sw128(sa);
+                        const uint64_t al = umma_desc_sw128(sa + CA_TILE);
+                        const uint64_t bh = umma_desc_sw128(sa + 2 * CA_TILE);
+                        const uint64_t bl = umma_desc_sw128(sa + 2 * CA_TILE + Cfg::B_TILE);
 #pragma unroll
-                    for (int k = 0; k < CBK / 16; ++k) {
-                        const uint64_t adv = (uint64_t)((k * 32) >> 4);
-                        umma_bf16(d_tmem, al + adv, bh + adv, idesc, (kb | k) != 0);
-                        umma_bf16(d_tmem, ah + adv, bl + adv, idesc, 1);
-                        umma_bf16(d_tmem, ah + adv, bh + adv, idesc, 1);
+                        for (int k = 0; k < CBK / 16; ++k) {
+                            const uint64_t adv = (uint64_t)((k * 32) >> 4);
+                            umma_bf16(d_tmem, al + adv, bh + adv, idesc, ((kb - kb0) | k) != 0);
+                            umma_bf16(d_tmem, ah + adv, bl + adv, idesc, 1);
+                            umma_bf16(d_tmem, ah + adv, bh + adv, idesc, 1);
+                        }
+                        umma_commit(&empty[stage]);
+                        if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
                     }
-                    umma_commit(&empty[stage]);
-                    if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+                    umma_commit(&tfull[as]);
                 }
-                umma_commit(&tfull[as]);
             }
         }
     } else {
+        constexpr int NCH = BN / 128;   // 32-column chunks of the tile this warp owns: cc = cgroup + 4 * ci
         const int quarter = warp & 3;
         const int cgroup = (warp - 2) >> 2;
         const int r = quarter * 32 + lane;  // row of the tile = TMEM lane = output pixel
@@ -182,9 +202,7 @@ __global__ void __launch_bounds__(C_THREADS, 1) conv_fp16x3_kernel(const __grid_
         const int stat_ppw = stat_pimg < 32 ? stat_pimg : 32;   // pixels per warp that belong to one image (32 or 16)
         const int stat_slots = (p.H * p.W) / stat_ppw;
         int it = 0;
-        for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
-            const int as = it & 1;
-            const uint32_t aphase = (it >> 1) & 1;
+        for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
             const int mt = t / n_tiles_n;
             const int n0 = (t % n_tiles_n) * BN;
             const int w = (mt % tiles_w) * p.BW + r % p.BW;
@@ -196,16 +214,46 @@ __global__ void __launch_bounds__(C_THREADS, 1) conv_fp16x3_kernel(const __grid_
             const int img_warp = (mt / (tiles_w * tiles_h)) * p.BI + (quarter * 32) / stat_pimg;
             const bool row_ok_warp = img_warp < p.N;
             const int stat_slot = (p.BI == 1 ? (mt % (tiles_w * tiles_h)) * 4 + quarter : ((quarter * 32) % stat_pimg) / 32);
-            mbar_wait(&tfull[as], aphase);
-            tc_fence_after();
-            const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * BN;
-#pragma unroll 1
-            for (int cc = cgroup; cc < BN / 32; cc += C_EPI_WARPS / 4) {
+            // The tensor core adds into its fp32 accumulator with truncation, and the error of a long chain grows
+            // linearly with its length (measured: 3.6e-7 / 1.4e-6 / 6.0e-6 rms of the output scale at 576 / 2304 / 9216
+            // terms against 3e-7 for an fp32 FMA chain).  So a TMEM accumulator only ever holds C_SEG k-blocks; the
+            // partial sums are added here in registers with round-to-nearest, which keeps every convolution at the
+            // short-chain error whatever its depth.  The TMEM buffer is released as soon as it is in registers.
+            uint32_t acc[NCH][32];
+            for (int kb0 = 0; kb0 < n_kb; kb0 += C_SEG, ++it) {
+                const int as = it & 1;
+                const uint32_t aphase = (it >> 1) & 1;
+                mbar_wait(&tfull[as], aphase);
+                tc_fence_after();
+                const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * BN;
+#pragma unroll
+                for (int ci = 0; ci < NCH; ++ci) {
+                    const int cc = cgroup + 4 * ci;
+                    if (n0 + cc * 32 >= p.Cout) continue;  // warp-uniform: padded output channels
+                    if (kb0 == 0) {
+                        tmem_ld32(t_row + cc * 32, acc[ci]);
+                        tmem_ld_wait();
+                    } else {
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {   // 8 columns at a time: the partial sums never need 32 more registers
+                            uint32_t v[8];
+                            tmem_ld8(t_row + cc * 32 + q * 8, v);
+                            tmem_ld_wait();
+#pragma unroll
+                            for (int j = 0; j < 8; ++j)
+                                acc[ci][8 * q + j] = __float_as_uint(__uint_as_float(acc[ci][8 * q + j]) + __uint_as_float(v[j]));
+                        }
+                    }
+                }
+                tc_fence_before();
+                mbar_arrive(&tempty[as]);
+            }
+#pragma unroll
+            for (int ci = 0; ci < NCH; ++ci) {
+                const int cc = cgroup + 4 * ci;
                 const int c0 = n0 + cc * 32;
                 if (c0 >= p.Cout) continue;  // warp-uniform: padded output channels
-                uint32_t v[32];
-                tmem_ld32(t_row + cc * 32, v);
-                tmem_ld_wait();
+                uint32_t (&v)[32] = acc[ci];
                 if (row_ok) {
                     float* dst = p.out + pix * p.ldo + c0;
                     const float* res = p.residual ? p.residual + pix * p.ld_res + c0 : nullptr;
@@ -269,45 +317,41 @@ __global__ void __launch_bounds__(C_THREADS, 1) conv_fp16x3_kernel(const __grid_
                     // nn.GroupNorm), from the registers that already hold it: per (image, 32-pixel slot, channel) sums
                     // of x and x^2.  A transposing butterfly leaves lane l with the total of channel c0 + l over the
                     // warp's 32 pixels in 31 shuffles per quantity; fixed slots, no atomics -> bit-reproducible.
-                    float a[32], b2[32];
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        const float x = row_ok ? __uint_as_float(v[j]) : 0.f;
-                        a[j] = x;
-                        b2[j] = x * x;
-                    }
                     const bool half_warp = stat_ppw == 16;   // 4x4 images: a warp holds two images of 16 pixels
-                    if (!half_warp) {
-                        const bool up = lane & 16;
+                    float s0[2], q0[2];
+                    {
+                        float a[32];
 #pragma unroll
-                        for (int i = 0; i < 16; ++i) {
-                            const float ka = up ? a[i + 16] : a[i], sa = up ? a[i] : a[i + 16];
-                            const float kb = up ? b2[i + 16] : b2[i], sb = up ? b2[i] : b2[i + 16];
-                            a[i] = ka + __shfl_xor_sync(0xffffffffu, sa, 16);
-                            b2[i] = kb + __shfl_xor_sync(0xffffffffu, sb, 16);
-                        }
+                        for (int j = 0; j < 32; ++j) a[j] = row_ok ? __uint_as_float(v[j]) : 0.f;
+                        stat_butterfly(a, lane, half_warp);
+                        s0[0] = a[0]; s0[1] = a[1];
                     }
-                    // remaining steps: masks 8, 4, 2, 1 on 16 (or, for half warps, 32) live values
+                    {
+                        float a[32];
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            const float x = row_ok ? __uint_as_float(v[j]) : 0.f;
+                            a[j] = x * x;
+                        }
+                        stat_butterfly(a, lane, half_warp);
+                        q0[0] = a[0]; q0[1] = a[1];
+                    }
                     if (!half_warp) {
-                        stat_butterfly<16>(a, b2, lane);
                         if (row_ok_warp && c0 + lane < p.Cout) {
                             float2* dst2 = reinterpret_cast<float2*>(p.stats) +
                                            ((size_t)img_warp * stat_slots + stat_slot) * p.Cout + c0 + lane;
-                            *dst2 = make_float2(a[0], b2[0]);
+                            *dst2 = make_float2(s0[0], q0[0]);
                         }
                     } else {
-                        stat_butterfly<32>(a, b2, lane);
                         const int ch = c0 + 2 * (lane & 15);
                         if (row_ok && ch < p.Cout) {   // lanes of one half share img
                             float2* dst2 = reinterpret_cast<float2*>(p.stats) + (size_t)img * p.Cout + ch;
-                            dst2[0] = make_float2(a[0], b2[0]);
-                            if (ch + 1 < p.Cout) dst2[1] = make_float2(a[1], b2[1]);
+                            dst2[0] = make_float2(s0[0], q0[0]);
+                            if (ch + 1 < p.Cout) dst2[1] = make_float2(s0[1], q0[1]);
                         }
                     }
                 }
             }
-            tc_fence_before();
-            mbar_arrive(&tempty[as]);
         }
     }
 

@@ -214,6 +214,7 @@ __device__ __forceinline__ void prep_transform8(const PrepParams& p, const PrepC
         if (p.mean_rstd) o = (o - k.m[j]) * k.r[j];
         if (p.gamma) o = fmaf(o, k.g[j], k.b[j]);
         if (p.act == 1) o = __fdividef(o, 1.f + __expf(-o));
+        else if (p.act == 2) o = o / (1.f + expf(-o));   // IEEE divide + full-accuracy expf (accuracy experiments)
         v[j] = (VEC || c0 + j < C) ? o : 0.f;
     }
 }

@@ -77,6 +77,7 @@ def pack_conv(weight: torch.Tensor, bias: Optional[torch.Tensor], taps=None, pla
     return PackedConv(hi, lo, b, cin, cp, cout, np_, list(taps), w_scale, planes)
 
 
+SILU_ACT = 1            # 1: ex2.approx + approximate divide (|error| ~3e-7 relative); 2: expf + IEEE divide
 FUSED_GN_STATS = True   # GroupNorm statistics from the producing convolution's epilogue (False: re-read the tensor)
 
 
@@ -131,7 +132,7 @@ def prep(x0: torch.Tensor, x1: Optional[torch.Tensor] = None, *, mode: int = PRE
         lo = torch.empty_like(hi)
     f32 = torch.empty(planes, n, ho, wo, c, dtype=torch.float32, device=dev) if want_f32 else None
     _lib.call("idb_conv_prep", _lib.ptr(x0), c0, _lib.ptr(x1), c1, n, hs, ws, int(nchw), mode, _lib.ptr(mean_rstd),
-              groups, _lib.ptr(gamma), _lib.ptr(beta), act, ACT_SCALE, _lib.ptr(hi), _lib.ptr(lo), cp, _lib.ptr(f32),
+              groups, _lib.ptr(gamma), _lib.ptr(beta), act and SILU_ACT, ACT_SCALE, _lib.ptr(hi), _lib.ptr(lo), cp, _lib.ptr(f32),
               _lib.stream_ptr())
     op = Operand(hi, lo, planes, n, ho, wo, cp) if want_operand else None
     if want_f32:
@@ -172,7 +173,7 @@ def prep_fir(x0: torch.Tensor, k_host, up: int, down: int, pad0: int, pad1: int,
     f32 = torch.empty(planes, n, ho, wo, c, dtype=torch.float32, device=dev) if want_f32 else None
     kptr = k_host.ctypes.data_as(C.POINTER(C.c_float))
     _lib.call("idb_conv_prep_fir", _lib.ptr(x0), c, n, hs, ws, _lib.ptr(mean_rstd), groups, _lib.ptr(gamma), _lib.ptr(beta),
-              act, kptr, kh, kw, up, down, pad0, pad1, int(as_planes), ACT_SCALE, _lib.ptr(hi), _lib.ptr(lo), cp,
+              act and SILU_ACT, kptr, kh, kw, up, down, pad0, pad1, int(as_planes), ACT_SCALE, _lib.ptr(hi), _lib.ptr(lo), cp,
               _lib.ptr(f32), _lib.stream_ptr())
     op = Operand(hi, lo, planes, n, ho, wo, cp) if want_operand else None
     if want_f32:
