@@ -358,7 +358,7 @@ def run_ours(args):
                 extra["C5_beatgans"] = XW.image_config("beatgans", dev, peaks, K=4096)
             else:   # config 5 across GPUs: ONE anchor, its K rows sharded over the ranks (partial Grams + all-reduce)
                 extra["C5_beatgans_k_sharded"] = XW.image_config("beatgans", dev, peaks, K=4096, cpu_images=0,
-                                                                 group=dist.group.WORLD)
+                                                                 group=dist.group.WORLD, verify=True)
                 extra["C5_beatgans_k_sharded_K16768"] = XW.image_config("beatgans", dev, peaks, K=16768, cpu_images=0,
                                                                         group=dist.group.WORLD)
         except Exception as exc:   # the headline line must still be printed

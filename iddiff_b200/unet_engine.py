@@ -302,7 +302,7 @@ class UNetEngine:
                 h = U.conv(a, blk, want_stats=True)
             elif kind == "pyr_down":
                 # conv_downsample_2d (up_or_down_sampling.py:144-178) then (pyramid + h) / sqrt(2) (ncsnpp.py:300-304)
-                if U.FUSED_FIR:
+                if U.FUSED_FIR and pyramid.shape[-1] % 8 == 0:   # (the 3-channel image itself takes the scalar path: unfused is faster)
                     a = U.prep_fir(pyramid, blk.fir_host, 1, 1, 2, 2, as_planes=True)
                 else:
                     a = U.prep(U.upfirdn2d_nhwc(pyramid, blk.fir, 1, 1, 2, 2), mode=U.PREP_STRIDE2)

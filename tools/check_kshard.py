@@ -18,7 +18,7 @@ import torch.distributed as dist  # noqa: E402
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--model", default="beatgans")
-    ap.add_argument("--K", type=int, default=4096)
+    ap.add_argument("--K", default="4096", help="comma-separated list")
     args = ap.parse_args()
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
@@ -40,18 +40,28 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return r, float(t[0])
 
-    eng.estimate_row_sharded(x0, 256, mc, std, 0.00999, seed=0)                      # warm-up
-    r_sh, ms_sh = timed(lambda: eng.estimate_row_sharded(x0, args.K, mc, std, 0.00999, seed=1))
-    out = {"model": args.model, "K": args.K, "n_gpus": world, "ms_sharded": ms_sh,
-           "score_evals_per_s": args.K / ms_sh * 1e3}
-    if rank == 0:
-        S = eng.score_rows(x0, args.K, 0, mc, std, 0.00999, seed=1)
-        from iddiff_b200.engine import spectrum_from_rows
-        r_1 = spectrum_from_rows(S, args.K, S.shape[2], -1.0 / std)
-        a, b = r_sh.singular_values[0, :-1].double(), r_1.singular_values[0, :-1].double()
-        out["max_rel_diff_vs_single_gpu"] = float(((a - b).abs() / b).max())
-        out["dims_equal"] = r_sh.dims.cpu().tolist() == r_1.dims.cpu().tolist()
-        print(json.dumps(out), flush=True)
+    eng.estimate_row_sharded(x0, 256, mc, std, 0.00999, seed=0)                      # warm-up (K < D path)
+    from iddiff_b200 import engine as E
+    from iddiff_b200.engine import spectrum_from_rows
+    for K in [int(k) for k in str(args.K).split(",")]:
+        E.EVENT_LOG = {}
+        r_sh, ms_sh = timed(lambda: eng.estimate_row_sharded(x0, K, mc, std, 0.00999, seed=1))
+        stages = {k: sum(a.elapsed_time(b) for a, b, _ in v) for k, v in E.EVENT_LOG.items()}
+        E.EVENT_LOG = None
+        r_ag, ms_ag = timed(lambda: eng.estimate_row_sharded(x0, K, mc, std, 0.00999, seed=1, gather_rows=True))
+        out = {"model": args.model, "K": K, "n_gpus": world, "ms_partial_gram": ms_sh, "ms_gather_rows": ms_ag,
+               "stages_ms_rank0": stages, "score_evals_per_s": K / ms_sh * 1e3}
+        if rank == 0:
+            S = eng.score_rows(x0, K, 0, mc, std, 0.00999, seed=1)
+            r_1 = spectrum_from_rows(S, K, S.shape[2], -1.0 / std)
+            m = min(K, S.shape[2]) - (1 if K <= S.shape[2] else 0)
+            b1 = r_1.singular_values[0, :m].double()
+            out["max_rel_diff_vs_single_gpu"] = float(((r_sh.singular_values[0, :m].double() - b1).abs() / b1).max())
+            out["max_rel_diff_gather_rows_vs_single_gpu"] = float(((r_ag.singular_values[0, :m].double() - b1).abs() / b1).max())
+            out["dims_equal"] = r_sh.dims.cpu().tolist() == r_1.dims.cpu().tolist()
+            del S
+            print(json.dumps(out), flush=True)
+        dist.barrier()
     dist.barrier()
     dist.destroy_process_group()
 

@@ -103,7 +103,7 @@ _SDE = {"ncsnpp": (0.009, 50.0), "ddpm": (0.009, 50.0), "beatgans": (0.01, 50.0)
 _NAME = {"ncsnpp": "C4", "beatgans": "C5", "ddpm": "style_gan_base (DDPM)"}
 
 
-def image_config(which, dev, peaks, K=4096, cpu_images=8, group=None):
+def image_config(which, dev, peaks, K=4096, cpu_images=8, group=None, verify=False):
     """Whole path on ONE anchor (K x 12288 score matrix); with `group` (N > 1) the K rows are sharded over the ranks."""
     from iddiff_b200 import engine as E, sde_lib, synthetic as SY
     eng, n_params, gflop = SY.build_full_engine(which, dev)
@@ -145,6 +145,14 @@ def image_config(which, dev, peaks, K=4096, cpu_images=8, group=None):
                         "unit": "TFLOP/s", "frac": ach / peak,
                         "note": "ALGORITHMIC FLOPs of the reference forward (FlopCounterMode, SURVEY 6) per GPU over the "
                                 "CUDA-event time of the whole score-network stage; 3 tcgen05.mma per product"}}
+    if group is not None and verify:
+        # the sharded spectrum against the same anchor on ONE GPU (Philox rows are keyed globally, so only the summation
+        # order of the Gram differs): every rank runs it, rank 0's difference is reported
+        r1 = eng.estimate(x0, K, mc, std, label, seed=1)
+        m = min(K, D) - (1 if K <= D else 0)
+        a, b = r.singular_values[0, :m].double(), r1.singular_values[0, :m].double()
+        out["max_rel_diff_vs_single_gpu"] = float(((a - b).abs() / b).max())
+        out["dims_equal_single_gpu"] = r.dims.cpu().tolist() == r1.dims.cpu().tolist()
     if group is None and cpu_images:
         out["cpu_baseline"] = _cpu_forward_baseline(which, eng.h, cpu_images)
     del eng

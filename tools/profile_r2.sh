@@ -17,4 +17,11 @@ $UN > $O/r2_unet_plain.log 2>&1 || { echo "plain U-Net bench failed"; tail -5 $O
 ncu --metrics gpu__time_duration.sum --clock-control none -s 700 -c 800 --csv --log-file $O/r2_unet_launches.csv $UN > $O/r2_unet_ncu.log 2>&1
 ncu --set full --metrics $TM --clock-control none --import-source on -k regex:conv_fp16x3_kernel -s 170 -c 12 -o $O/r2_conv $UN > $O/r2_conv_ncu.log 2>&1
 ncu --set full --metrics $TM --clock-control none -k regex:"conv_prep|attention_kernel|gn_from_partials" -s 300 -c 8 -o $O/r2_unet_misc $UN > $O/r2_misc_ncu.log 2>&1
-ls -la $O/*.ncu-rep
+# the reports themselves exceed what gpurun copies back: keep their raw (all metrics per launch) and source pages as CSV
+for r in r2_gemm r2_fcn_tail r2_conv r2_unet_misc; do
+  [ -f $O/$r.ncu-rep ] || continue
+  ncu -i $O/$r.ncu-rep --page raw --csv > $O/${r}_raw.csv 2>/dev/null
+  case $r in r2_gemm|r2_conv) ncu -i $O/$r.ncu-rep --page source --csv > $O/${r}_source.csv 2>/dev/null; gzip -f $O/${r}_source.csv;; esac
+  rm -f $O/$r.ncu-rep
+done
+ls -la $O/
