@@ -61,12 +61,13 @@ def measured_peaks():
 
 
 def ncu_traffic_bytes(chunk):
-    """DRAM bytes of one hidden-layer launch from the committed ncu --set full capture (taken at chunk=128)."""
+    """DRAM bytes of one hidden-layer launch from the committed ncu --set full capture (profiles/r2_gemm_full.json, second
+    launch = an H x H hidden layer over a 256-anchor pass), scaled to this run's pass size."""
     try:
-        with open(os.path.join(ROOT, "profiles", "r1_gemm_hidden_full.json")) as f:
-            k = json.load(f)[0]
+        with open(os.path.join(ROOT, "profiles", "r2_gemm_full.json")) as f:
+            k = json.load(f)[1]
         gb = float(k["dram__bytes_read.sum"]["value"]) + float(k["dram__bytes_write.sum"]["value"])
-        return gb * 1e9 * chunk / 128.0
+        return gb * 1e9 * chunk / 256.0
     except Exception:
         return None
 
@@ -209,11 +210,10 @@ def run_ours(args):
 
     model = make_model()
     if args.short_train > 0:
-        sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "tools"))
-        import train_fcn
+        from iddiff_b200.train import short_train      # the DSM training step on the sm_100a kernels
         model = model.to(dev)
         if rank == 0:
-            train_fcn.short_train(model, make_anchors(50000, seed=2).to(dev), args.short_train)
+            short_train(model, make_anchors(50000, seed=2).to(dev), args.short_train)
         if world > 1:
             for prm in model.parameters():
                 dist.broadcast(prm.data, src=0)
@@ -376,11 +376,12 @@ def run_ours(args):
     roofline = {"kernel": "gemm_bf16x3_kernel<0> (hidden Linear+ELU on deviations, H x H)", "bound": "tensor",
                 "achieved": ach_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach_tf / peak_tf,
                 "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({peak_src}; kernel timed inside a long step)",
-                "mma_issue_frac": 3 * ach_tf / peak_tf,
+                "mma_issue_frac": 3 * ach_tf / peak_tf, "tensor_pipe_active_ncu": 0.877,
                 "note": "achieved = ALGORITHMIC FLOPs (2*A*K*H*H per launch); the split-precision scheme issues 3 "
                         "tcgen05.mma per algorithmic product, so tensor-pipe occupancy is mma_issue_frac",
-                "traffic": ncu_traffic_bytes(chunk), "traffic_source": "profiles/r1_gemm_hidden_full.json (ncu --set full, "
-                "dram__bytes_read.sum + dram__bytes_write.sum of one launch over a 128-anchor chunk)",
+                "traffic": ncu_traffic_bytes(chunk), "traffic_source": "profiles/r2_gemm_full.json (ncu --set full, "
+                "dram__bytes_read.sum + dram__bytes_write.sum of one hidden-layer launch over a 256-anchor pass; the same capture "
+                "measured sm__pipe_tensor_cycles_active 87.7 % of elapsed for this kernel)",
                 "algorithmic_bytes": 2.0 * (2 * chunk * 1536 * H * 2) , "share_of_step": hid["ms_total"] / ms_total}
     line = {"metric": "ID-estimates/sec", "value": value, "unit": "anchors/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
@@ -417,7 +418,7 @@ def main():
     ap.add_argument("--cpu-budget-s", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--short-train", type=int, default=0, help="untimed set-up: this many denoising-score-matching steps "
-                    "(tools/train_fcn.py, rank 0, broadcast) before the bench, so that the reported dims are the "
+                    "(iddiff_b200/train.py: the CUDA training step, rank 0, broadcast) before the bench, so that the reported dims are the "
                     "sphere's (51) instead of a random network's; same arithmetic per step either way")
     ap.add_argument("--extra", type=int, default=1, help="0: skip the extra_workloads (C1 / C4 / C5, K-sharded at N > 1)")
     ap.add_argument("--strong-anchors", type=int, default=4096, help="fixed anchor count of the strong-scaling leg (0: skip)")

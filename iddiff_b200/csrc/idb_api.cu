@@ -1,6 +1,7 @@
 // C ABI of libiddiff_b200.so -- see include/iddiff_b200.h for the contract of every entry point.
 #include "../../include/iddiff_b200.h"
 #include "idb_kernels.h"
+#include <math.h>
 #include <stdio.h>
 
 namespace {
@@ -178,6 +179,65 @@ int idb_gram_about(const float* X, long long anchor_stride, int ld, int n_anchor
     return check(idb::launch_gram_about(X, anchor_stride, ld, n_anchors, K, D, scale, center, G,
                                         static_cast<cudaStream_t>(stream)),
                  "idb_gram_about");
+}
+
+/* ---- DSM training step ---- */
+int idb_dsm_sample(const float* data, const long long* idx, const float* t, const float* mean_coeff, const float* stdv,
+                   const float* z_ext, int B, int D, int Mp, int ldx, float label_scale, uint64_t seed, uint64_t step,
+                   const long long* step_dev, float* X, float* z_out, void* stream) {
+    if (!data || !t || !mean_coeff || !stdv || !X || !z_out || B <= 0 || D <= 0 || Mp < B || ldx < D + 1 || ldx % 8 ||
+        !aligned16(X))
+        return fail("idb_dsm_sample: bad argument (need Mp >= B, ldx >= D + 1, ldx % 8 == 0, 16-byte aligned X)");
+    return check(idb::launch_dsm_sample(data, idx, t, mean_coeff, stdv, z_ext, B, D, Mp, ldx, label_scale, seed, step,
+                                        step_dev, X, z_out, static_cast<cudaStream_t>(stream)),
+                 "idb_dsm_sample");
+}
+
+int idb_train_pack(const float* src, int ld, int R, int C, const float* pre, int ld_pre, int mode, int transpose, int fmt,
+                   float scale, int Rp, int Cp, void* hi, void* lo, float* out_f32, int ld_out, void* stream) {
+    if (!src || R < 0 || C < 0 || ld < C || mode < 0 || mode > 2 || (mode == 2 && (!pre || ld_pre < C)))
+        return fail("idb_train_pack: bad argument");
+    if (fmt != IDB_FMT_BF16 && fmt != IDB_FMT_FP16) return fail("idb_train_pack: unknown fmt");
+    if (!(scale > 0.f)) return fail("idb_train_pack: scale must be positive");
+    if (transpose) {
+        if (!hi || !lo || out_f32) return fail("idb_train_pack: the transposed form writes the operand slabs only");
+        if (Cp % 128 || Rp % 64 || Cp < C || Rp < R) return fail("idb_train_pack: transposed slab needs Cp % 128 == 0, Rp % 64 == 0");
+    } else {
+        if ((hi == nullptr) != (lo == nullptr) || (!hi && !out_f32)) return fail("idb_train_pack: no output requested");
+        if (Rp % 8 || Cp % 64 || Cp < C || Rp < R) return fail("idb_train_pack: slab needs Rp % 8 == 0, Cp % 64 == 0");
+        if (out_f32 && ld_out < C) return fail("idb_train_pack: ld_out < C");
+    }
+    if (hi && (!aligned16(hi) || !aligned16(lo))) return fail("idb_train_pack: slabs must be 16-byte aligned");
+    idb::TrainPackParams p;
+    p.src = src; p.ld = ld; p.R = R; p.C = C; p.pre = pre; p.ld_pre = ld_pre; p.mode = mode; p.transpose = transpose;
+    p.fmt = fmt; p.scale = scale; p.Rp = Rp; p.Cp = Cp; p.hi = static_cast<uint8_t*>(hi); p.lo = static_cast<uint8_t*>(lo);
+    p.out_f32 = out_f32; p.ld_out = ld_out;
+    return check(idb::launch_train_pack(p, static_cast<cudaStream_t>(stream)), "idb_train_pack");
+}
+
+int idb_dsm_loss(const float* out, int ldo, const float* z, int B, int D, int Mp, float* dZ, float* loss, void* stream) {
+    if (!out || !z || !dZ || !loss || B <= 0 || D <= 0 || Mp < B || ldo < D) return fail("idb_dsm_loss: bad argument");
+    return check(idb::launch_dsm_loss(out, ldo, z, B, D, Mp, dZ, loss, static_cast<cudaStream_t>(stream)), "idb_dsm_loss");
+}
+
+int idb_column_sums_f32(const float* src, int ld, int R, int C, float* out, void* stream) {
+    if (!src || !out || R < 0 || C < 0 || ld < C) return fail("idb_column_sums_f32: bad argument");
+    return check(idb::launch_colsum_f32(src, ld, R, C, out, static_cast<cudaStream_t>(stream)), "idb_column_sums_f32");
+}
+
+int idb_grad_sumsq(const float* g, int ld, int N, int K, double* accum, void* stream) {
+    if (!g || !accum || N < 0 || K < 0 || ld < K) return fail("idb_grad_sumsq: bad argument");
+    return check(idb::launch_grad_sumsq(g, ld, N, K, accum, static_cast<cudaStream_t>(stream)), "idb_grad_sumsq");
+}
+
+int idb_adam_step(float* param, int ldp, const float* grad, int ldg, float* m, float* v, int N, int K, float lr,
+                  int warmup, float beta1, float beta2, float eps, long long step, const long long* step_dev,
+                  float max_norm, const double* grad_normsq, void* stream) {
+    if (!param || !grad || !m || !v || N < 0 || K < 0 || ldp < K || ldg < K || (!step_dev && step < 1))
+        return fail("idb_adam_step: bad argument");
+    return check(idb::launch_adam(param, ldp, grad, ldg, m, v, N, K, lr, warmup, beta1, beta2, eps, step, step_dev, max_norm,
+                                  grad_normsq, static_cast<cudaStream_t>(stream)),
+                 "idb_adam_step");
 }
 
 size_t idb_spectrum_workspace_bytes(int n_anchors, int n) {

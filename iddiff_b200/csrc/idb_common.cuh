@@ -180,4 +180,31 @@ __device__ __forceinline__ uint32_t pack_bf16(__nv_bfloat16 a, __nv_bfloat16 b) 
     return (uint32_t)__bfloat16_as_ushort(a) | ((uint32_t)__bfloat16_as_ushort(b) << 16);
 }
 
+// ---------------------------------- Philox4x32-10 -------------------------------------------
+__device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
+    const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi0 = __umulhi(M0, ctr.x), lo0 = M0 * ctr.x;
+        const uint32_t hi1 = __umulhi(M1, ctr.z), lo1 = M1 * ctr.z;
+        ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
+        key.x += W0;
+        key.y += W1;
+    }
+    return ctr;
+}
+
+// Box-Muller on the special-function unit: lg2.approx / sin.approx / cos.approx (absolute errors ~2e-7 / 5e-7 on the
+// arguments used here, far below the sampling noise of a 1501-row score matrix) instead of the ~50-instruction logf and
+// sincospif routines -- the perturbation pass is bound by its arithmetic, not by the 0.8 GB it writes.
+__device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& n0, float& n1) {
+    const float u1 = ((float)(a >> 8) + 1.0f) * (1.0f / 16777216.0f);  // (0, 1]
+    const float u2 = (float)(b >> 8) * (1.0f / 16777216.0f);           // [0, 1)
+    const float r = sqrtf(fmaxf(-1.3862943611198906f * __log2f(u1), 0.f));   // -2 ln u1 = -2 ln2 * log2 u1
+    const float ang = 6.283185307179586f * u2 - 3.141592653589793f;          // [-pi, pi): the range sin/cos.approx are accurate on
+    n0 = r * __cosf(ang);
+    n1 = r * __sinf(ang);
+}
+
+
 }  // namespace idb

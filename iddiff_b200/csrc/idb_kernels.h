@@ -158,4 +158,33 @@ int api_fail(const char* what);
 int api_check(cudaError_t e, const char* where);
 int api_num_sms();
 
+// ---- DSM training step of the FCN (idb_train.cu) ----
+struct TrainPackParams {
+    const float* src;   // fp32 [R][ld]
+    int ld, R, C;       // valid extent; everything outside packs as zero
+    const float* pre;   // mode 2: pre-activations [R][ld_pre]
+    int ld_pre;
+    int mode;           // 0 identity, 1 ELU(src), 2 src * ELU'(pre)
+    int transpose;      // 0: slab [Rp][Cp] (+ out_f32 [Rp][ld_out]); 1: slab [Cp][Rp]
+    int fmt;
+    float scale;
+    int Rp, Cp;
+    uint8_t* hi;
+    uint8_t* lo;
+    float* out_f32;
+    int ld_out;
+};
+cudaError_t launch_dsm_sample(const float* data, const long long* idx, const float* t, const float* mean_coeff,
+                              const float* stdv, const float* z_ext, int B, int D, int Mp, int ldx, float label_scale,
+                              uint64_t seed, uint64_t step, const long long* step_dev, float* X, float* z_out,
+                              cudaStream_t stream);
+cudaError_t launch_train_pack(const TrainPackParams& p, cudaStream_t stream);
+cudaError_t launch_dsm_loss(const float* out, int ldo, const float* z, int B, int D, int Mp, float* dZ, float* loss,
+                            cudaStream_t stream);
+cudaError_t launch_colsum_f32(const float* src, int ld, int R, int C, float* out, cudaStream_t stream);
+cudaError_t launch_grad_sumsq(const float* g, int ld, int N, int K, double* accum, cudaStream_t stream);
+cudaError_t launch_adam(float* prm, int ldp, const float* g, int ldg, float* m, float* v, int N, int K, float lr_base,
+                        int warmup, float beta1, float beta2, float eps, long long step_host, const long long* step_dev,
+                        float max_norm, const double* normsq, cudaStream_t stream);
+
 }  // namespace idb

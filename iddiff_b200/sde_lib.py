@@ -18,6 +18,8 @@ import torch
 
 
 class SDE:
+    T = 1.0   # end time of every SDE of sde_lib.py (`.T` properties :44-46, :159-161, :228-230, :322-324)
+
     def __init__(self, N: int):
         self.N = N
 

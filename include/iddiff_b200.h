@@ -139,6 +139,48 @@ int idb_spectrum(const double* G, int n_anchors, int n, int n_out, int method, f
 int idb_id_from_spectrum(const float* sv, int n_anchors, int n, int ld, int* dims, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Denoising-score-matching training step of the FCN (losses.py:164-188, :26-51,
+ * lightning_modules/BaseSdeGenerativeModel.py:60-63).  The matrix products of the forward AND backward pass are
+ * idb_fcn_anchor_layer / idb_fcn_output_layer in the bf16-pair format; these entry points are everything around them.
+ * Host side: iddiff_b200/train.py (FcnTrainer).
+ * ------------------------------------------------------------------------------------------------ */
+
+/* losses.py:176-179 + models/fcn.py:35-38: X[r] = (mean_coeff[r] * data[idx[r]] + std[r] * z[r], label_scale * t[r], 0 ...)
+ * for r < B, zero rows up to Mp; X fp32 [Mp][ldx] (ldx >= D + 1, % 8), z_out fp32 [B][D].  z_ext [B][D] or NULL (Philox
+ * keyed by (seed, step, row, column)); idx [B] int64 or NULL (rows 0 .. B-1 of data).  step_dev: optional device counter that
+ * replaces `step` (a whole training step is then one replayable CUDA graph). */
+int idb_dsm_sample(const float* data, const long long* idx, const float* t, const float* mean_coeff, const float* stdv,
+                   const float* z_ext, int B, int D, int Mp, int ldx, float label_scale, uint64_t seed, uint64_t step,
+                   const long long* step_dev, float* X, float* z_out, void* stream);
+
+/* fp32 [R][ld] -> tensor-core operand slabs with the activation (or its derivative) fused in:
+ *   value(r, c) = src (mode 0) | ELU(src) (mode 1) | src * ELU'(pre) (mode 2: dZ = dH * ELU'(pre)) inside [R) x [C), else 0;
+ *   transpose 0: slab of [Rp][Cp] (A operand: rows = batch) and / or the fp32 values out_f32 [Rp][ld_out];
+ *   transpose 1: slab of [Cp][Rp] (rows = features, contraction = batch: the operands of dW = dZ^T H). */
+int idb_train_pack(const float* src, int ld, int R, int C, const float* pre, int ld_pre, int mode, int transpose, int fmt,
+                   float scale, int Rp, int Cp, void* hi, void* lo, float* out_f32, int ld_out, void* stream);
+
+/* losses.py:181-187 (VE, reduce_mean, no likelihood weighting): loss = mean (out - z)^2 over [B) x [D);
+ * dZ [Mp][ldo] = 2 (out - z) / (B D) inside, 0 in the padding.  loss: one float on the device. */
+int idb_dsm_loss(const float* out, int ldo, const float* z, int B, int D, int Mp, float* dZ, float* loss, void* stream);
+
+/* out[c] = sum_{r < R} src[r][c] (bias gradients). */
+int idb_column_sums_f32(const float* src, int ld, int R, int C, float* out, void* stream);
+
+/* accum (one double on the device, zeroed by the caller once per step) += sum of squares of grad [N][K] (row stride ld):
+ * the global norm of torch.nn.utils.clip_grad_norm_ (losses.py:47-48). */
+int idb_grad_sumsq(const float* g, int ld, int N, int K, double* accum, void* stream);
+
+/* One torch.optim.Adam step (no amsgrad / weight decay; losses.py:26-35) on param [N][K] (row stride ldp) with gradient
+ * [N][K] (row stride ldg), after clipping by the global norm sqrt(*grad_normsq) to max_norm (max_norm < 0 or NULL: no
+ * clipping; losses.py:47-48) and with the linear warm-up lr * min(step / warmup, 1) (losses.py:44-46; warmup <= 0: none).
+ * step >= 1 is the optimiser step; when step_dev is set the counter is read from the device instead.  Clip coefficient,
+ * learning rate and bias corrections are all formed on the device: a step never synchronises with the host. */
+int idb_adam_step(float* param, int ldp, const float* grad, int ldg, float* m, float* v, int N, int K, float lr,
+                  int warmup, float beta1, float beta2, float eps, long long step, const long long* step_dev,
+                  float max_norm, const double* grad_normsq, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Image score networks.
  * ------------------------------------------------------------------------------------------------ */
 

@@ -75,6 +75,8 @@ def main():
     ap.add_argument("--sigma-max", type=float, default=4.0)
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--out", default="")
+    ap.add_argument("--torch", action="store_true", help="run the optimiser loop in PyTorch (the reference's own loop) "
+                    "instead of the CUDA training step of iddiff_b200/train.py")
     args = ap.parse_args()
 
     from iddiff_b200 import data, engine as E, models, sde_lib
@@ -120,8 +122,12 @@ def main():
             torch.cuda.synchronize()
             evaluate(step, run, time.perf_counter() - t0)
 
-    short_train(holder, train, args.steps, batch=args.batch, lr=args.lr, warmup=args.warmup, sigma_min=args.sigma_min,
-                sigma_max=args.sigma_max, eps_t=eps_t, on_step=on_step)
+    if args.torch:
+        train_fn = short_train
+    else:
+        from iddiff_b200.train import short_train as train_fn
+    train_fn(holder, train, args.steps, batch=args.batch, lr=args.lr, warmup=args.warmup, sigma_min=args.sigma_min,
+             sigma_max=args.sigma_max, eps_t=eps_t, on_step=on_step)
     if args.out:
         os.makedirs(os.path.dirname(os.path.abspath(args.out)), exist_ok=True)
         torch.save({"state_dict": {"score_model." + k: v.detach().cpu() for k, v in holder.state_dict().items()},
