@@ -44,7 +44,7 @@ SIGNATURES = {
     "idb_gram_about": (_i, [_vp, _ll, _i, _i, _i, _i, _d, _vp, _vp, _vp]),
     "idb_dsm_sample": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _u64, _u64, _vp, _vp, _vp, _vp]),
     "idb_train_pack": (_i, [_vp, _i, _i, _i, _vp, _i, _i, _i, _i, _f, _i, _i, _vp, _vp, _vp, _i, _vp]),
-    "idb_dsm_loss": (_i, [_vp, _i, _vp, _i, _i, _i, _vp, _vp, _vp]),
+    "idb_dsm_loss": (_i, [_vp, _i, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "idb_column_sums_f32": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "idb_grad_sumsq": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "idb_adam_step": (_i, [_vp, _i, _vp, _i, _vp, _vp, _i, _i, _f, _i, _f, _f, _f, _ll, _vp, _f, _vp, _vp]),
@@ -95,7 +95,7 @@ def load():
 
 # CUDA kernels each entry point enqueues (for bench.py's `gpu_launches` claim)
 KERNELS_PER_CALL = {"idb_perturb": 1, "idb_perturb_rows": 1, "idb_pack_weight": 1, "idb_anchor_linear": 1, "idb_fcn_hidden_layer": 1,
-                    "idb_fcn_output_layer": 1, "idb_fcn_anchor_layer": 1, "idb_fcn_scores": 1, "idb_ksphere_gt_score": 1, "idb_dsm_sample": 1, "idb_train_pack": 1, "idb_dsm_loss": 1, "idb_column_sums_f32": 1, "idb_grad_sumsq": 1,
+                    "idb_fcn_output_layer": 1, "idb_fcn_anchor_layer": 1, "idb_fcn_scores": 1, "idb_ksphere_gt_score": 1, "idb_dsm_sample": 1, "idb_train_pack": 1, "idb_dsm_loss": 2, "idb_column_sums_f32": 1, "idb_grad_sumsq": 1,
                     "idb_adam_step": 1, "idb_center_gram": 2, "idb_column_sums": 1, "idb_gram_about": 1,
                     "idb_spectrum": 2, "idb_id_from_spectrum": 1, "idb_upfirdn2d": 1, "idb_fused_bias_act": 1,
                     "idb_groupnorm_stats": 2, "idb_conv_prep": 1, "idb_conv_prep_fir": 1, "idb_conv2d": 1, "idb_conv2d_stats": 1, "idb_groupnorm_from_conv_stats": 1, "idb_attention": 1,

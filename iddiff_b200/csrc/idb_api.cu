@@ -215,9 +215,12 @@ int idb_train_pack(const float* src, int ld, int R, int C, const float* pre, int
     return check(idb::launch_train_pack(p, static_cast<cudaStream_t>(stream)), "idb_train_pack");
 }
 
-int idb_dsm_loss(const float* out, int ldo, const float* z, int B, int D, int Mp, float* dZ, float* loss, void* stream) {
-    if (!out || !z || !dZ || !loss || B <= 0 || D <= 0 || Mp < B || ldo < D) return fail("idb_dsm_loss: bad argument");
-    return check(idb::launch_dsm_loss(out, ldo, z, B, D, Mp, dZ, loss, static_cast<cudaStream_t>(stream)), "idb_dsm_loss");
+int idb_dsm_loss(const float* out, int ldo, const float* z, int B, int D, int Mp, float* dZ, float* loss, double* scratch,
+                 void* stream) {
+    if (!out || !z || !dZ || !loss || !scratch || B <= 0 || D <= 0 || Mp < B || ldo < D)
+        return fail("idb_dsm_loss: bad argument");
+    return check(idb::launch_dsm_loss(out, ldo, z, B, D, Mp, dZ, loss, scratch, static_cast<cudaStream_t>(stream)),
+                 "idb_dsm_loss");
 }
 
 int idb_column_sums_f32(const float* src, int ld, int R, int C, float* out, void* stream) {

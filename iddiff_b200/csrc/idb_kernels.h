@@ -180,7 +180,7 @@ cudaError_t launch_dsm_sample(const float* data, const long long* idx, const flo
                               cudaStream_t stream);
 cudaError_t launch_train_pack(const TrainPackParams& p, cudaStream_t stream);
 cudaError_t launch_dsm_loss(const float* out, int ldo, const float* z, int B, int D, int Mp, float* dZ, float* loss,
-                            cudaStream_t stream);
+                            double* partial, cudaStream_t stream);
 cudaError_t launch_colsum_f32(const float* src, int ld, int R, int C, float* out, cudaStream_t stream);
 cudaError_t launch_grad_sumsq(const float* g, int ld, int N, int K, double* accum, cudaStream_t stream);
 cudaError_t launch_adam(float* prm, int ldp, const float* g, int ldg, float* m, float* v, int N, int K, float lr_base,

@@ -149,13 +149,15 @@ cudaError_t launch_train_pack(const TrainPackParams& p, cudaStream_t stream) {
 // ---------------------------------- loss and its gradient -----------------------------------
 // loss = mean_{r < B, c < D} (out[r][c] - z[r][c])^2 (losses.py:173-185 with reduce_mean, VE, no likelihood weighting);
 // dZ[r][c] = 2 (out - z) / (B D) inside, 0 in the padding.  One CTA: the sum is formed in a fixed order (reproducible).
-__global__ void __launch_bounds__(1024) dsm_loss_kernel(const float* __restrict__ out, int ldo, const float* __restrict__ z,
-                                                        int B, int D, int Mp, float* __restrict__ dZ, float* __restrict__ loss) {
-    __shared__ double red[32];
+constexpr int LOSS_BLOCKS = 64;
+__global__ void __launch_bounds__(256) dsm_loss_kernel(const float* __restrict__ out, int ldo, const float* __restrict__ z,
+                                                       int B, int D, int Mp, float* __restrict__ dZ,
+                                                       double* __restrict__ partial) {
+    __shared__ double red[8];
     const double inv = 1.0 / ((double)B * (double)D);
     double acc = 0.0;
     const long long total = (long long)Mp * ldo;
-    for (long long i = threadIdx.x; i < total; i += 1024) {
+    for (long long i = blockIdx.x * 256LL + threadIdx.x; i < total; i += (long long)LOSS_BLOCKS * 256) {
         const int r = (int)(i / ldo), c = (int)(i % ldo);
         float g = 0.f;
         if (r < B && c < D) {
@@ -171,31 +173,46 @@ __global__ void __launch_bounds__(1024) dsm_loss_kernel(const float* __restrict_
     __syncthreads();
     if (threadIdx.x == 0) {
         double s = 0.0;
-        for (int w = 0; w < 32; ++w) s += red[w];
-        *loss = (float)(s * inv);
+        for (int w = 0; w < 8; ++w) s += red[w];
+        partial[blockIdx.x] = s;
     }
+}
+// second stage: the block partials in a fixed order (bit-reproducible loss)
+__global__ void dsm_loss_final_kernel(const double* __restrict__ partial, double inv, float* __restrict__ loss) {
+    double s = 0.0;
+    for (int i = 0; i < LOSS_BLOCKS; ++i) s += partial[i];
+    *loss = (float)(s * inv);
 }
 
 cudaError_t launch_dsm_loss(const float* out, int ldo, const float* z, int B, int D, int Mp, float* dZ, float* loss,
-                            cudaStream_t stream) {
-    dsm_loss_kernel<<<1, 1024, 0, stream>>>(out, ldo, z, B, D, Mp, dZ, loss);
+                            double* partial, cudaStream_t stream) {
+    dsm_loss_kernel<<<LOSS_BLOCKS, 256, 0, stream>>>(out, ldo, z, B, D, Mp, dZ, partial);
+    dsm_loss_final_kernel<<<1, 1, 0, stream>>>(partial, 1.0 / ((double)B * (double)D), loss);
     return cudaGetLastError();
 }
 
 // ---------------------------------- bias gradient -------------------------------------------
 // out[c] = sum_{r < R} src[r][c]: one thread per column, rows in order (reproducible); coalesced across the warp.
-__global__ void __launch_bounds__(128) colsum_f32_kernel(const float* __restrict__ src, int ld, int R, int C,
+__global__ void __launch_bounds__(256) colsum_f32_kernel(const float* __restrict__ src, int ld, int R, int C,
                                                          float* __restrict__ out) {
-    const int c = blockIdx.x * 128 + threadIdx.x;
-    if (c >= C) return;
+    __shared__ float part[8][33];
+    const int c = blockIdx.x * 32 + (threadIdx.x & 31), rg = threadIdx.x >> 5;
     float a = 0.f;
-    for (int r = 0; r < R; ++r) a += src[(size_t)r * ld + c];
-    out[c] = a;
+    if (c < C)
+        for (int r = rg; r < R; r += 8) a += src[(size_t)r * ld + c];
+    part[rg][threadIdx.x & 31] = a;
+    __syncthreads();
+    if (rg == 0 && c < C) {
+        float t = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) t += part[i][threadIdx.x];
+        out[c] = t;
+    }
 }
 
 cudaError_t launch_colsum_f32(const float* src, int ld, int R, int C, float* out, cudaStream_t stream) {
     if (C <= 0) return cudaSuccess;
-    colsum_f32_kernel<<<(C + 127) / 128, 128, 0, stream>>>(src, ld, R, C, out);
+    colsum_f32_kernel<<<(C + 31) / 32, 256, 0, stream>>>(src, ld, R, C, out);
     return cudaGetLastError();
 }
 
@@ -205,10 +222,11 @@ __global__ void __launch_bounds__(256) grad_sumsq_kernel(const float* __restrict
                                                          double* __restrict__ accum) {
     __shared__ double red[8];
     double a = 0.0;
-    const long long total = (long long)N * K;
-    for (long long i = blockIdx.x * 256LL + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
-        const float v = g[(size_t)(i / K) * ld + (i % K)];
-        a += (double)v * (double)v;
+    for (int n = blockIdx.x; n < N; n += gridDim.x) {      // one row per block iteration: no per-element division
+        const float* row = g + (size_t)n * ld;
+        float f = 0.f;
+        for (int k = threadIdx.x; k < K; k += 256) f = fmaf(row[k], row[k], f);
+        a += (double)f;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
@@ -222,12 +240,9 @@ __global__ void __launch_bounds__(256) grad_sumsq_kernel(const float* __restrict
 }
 
 cudaError_t launch_grad_sumsq(const float* g, int ld, int N, int K, double* accum, cudaStream_t stream) {
-    const long long total = (long long)N * K;
-    if (total <= 0) return cudaSuccess;
-    long long blocks = (total + 256 * 8 - 1) / (256 * 8);
-    if (blocks > 296) blocks = 296;
-    if (blocks < 1) blocks = 1;
-    grad_sumsq_kernel<<<(int)blocks, 256, 0, stream>>>(g, ld, N, K, accum);
+    if (N <= 0 || K <= 0) return cudaSuccess;
+    const int blocks = N < 592 ? N : 592;
+    grad_sumsq_kernel<<<blocks, 256, 0, stream>>>(g, ld, N, K, accum);
     return cudaGetLastError();
 }
 

@@ -43,8 +43,14 @@ class VESDE(SDE):
         self.sigma_min, self.sigma_max, self.data_mean = sigma_min, sigma_max, data_mean
 
     def marginal_prob(self, x, t):
-        smin = torch.tensor(self.sigma_min).type_as(t)
-        smax = torch.tensor(self.sigma_max).type_as(t)
+        # the two constants as tensors of t's type (same float32 arithmetic as before), cached per (device, dtype) so that
+        # a captured training step (train.FcnTrainer.step_graph) performs no host-to-device copy
+        key = (t.device, t.dtype)
+        c = getattr(self, "_consts", {}).get(key)
+        if c is None:
+            c = (torch.tensor(self.sigma_min).type_as(t), torch.tensor(self.sigma_max).type_as(t))
+            self.__dict__.setdefault("_consts", {})[key] = c
+        smin, smax = c
         return x, smin * (smax / smin) ** t
 
 

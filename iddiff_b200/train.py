@@ -80,6 +80,7 @@ class FcnTrainer:
         self.v_b = [z(self.n_out[l]) for l in range(L)]
         self.normsq = z(1, dtype=torch.float64)
         self.loss = z(1)
+        self.loss_scratch = z(64, dtype=torch.float64)
         self.step_count = 0                                   # host mirror of the device counter below
         self.step_dev = z(1, dtype=torch.int64)               # optimiser step, read by the sampling and Adam kernels
         self._graph = None
@@ -119,7 +120,7 @@ class FcnTrainer:
         st = stream_ptr()
         L = len(self.lin)
         call("idb_dsm_loss", ptr(self.pre[-1]), self.Pout[-1], ptr(self.zbuf), self.B, self.D, self.Mp, ptr(self.dZ[-1]),
-             ptr(self.loss), st)
+             ptr(self.loss), ptr(self.loss_scratch), st)
         for l in range(L - 1, -1, -1):
             dz = self.dZ[l]
             # operands of this layer's two products: dZ_l as [batch][features] and as [features][batch]

@@ -161,8 +161,10 @@ int idb_train_pack(const float* src, int ld, int R, int C, const float* pre, int
                    float scale, int Rp, int Cp, void* hi, void* lo, float* out_f32, int ld_out, void* stream);
 
 /* losses.py:181-187 (VE, reduce_mean, no likelihood weighting): loss = mean (out - z)^2 over [B) x [D);
- * dZ [Mp][ldo] = 2 (out - z) / (B D) inside, 0 in the padding.  loss: one float on the device. */
-int idb_dsm_loss(const float* out, int ldo, const float* z, int B, int D, int Mp, float* dZ, float* loss, void* stream);
+ * dZ [Mp][ldo] = 2 (out - z) / (B D) inside, 0 in the padding.  loss: one float on the device; scratch: 64 doubles (block
+ * partial sums, added in a fixed order: the loss is bit-reproducible). */
+int idb_dsm_loss(const float* out, int ldo, const float* z, int B, int D, int Mp, float* dZ, float* loss, double* scratch,
+                 void* stream);
 
 /* out[c] = sum_{r < R} src[r][c] (bias gradients). */
 int idb_column_sums_f32(const float* src, int ld, int R, int C, float* out, void* stream);
