@@ -34,7 +34,7 @@ SIGNATURES = {
     "idb_perturb_rows": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _f, _f, _u64, _u64, C.c_uint32, _vp, _i, _f, _vp, _vp, _vp]),
     "idb_pack_weight": (_i, [_vp, _i, _i, _i, _i, _i, _i, _f, _vp, _vp, _vp]),
     "idb_anchor_linear": (_i, [_vp, _i, _i, _f, _vp, _i, _vp, _vp, _i, _f, _vp, _i, _i, _i, _i, _vp]),
-    "idb_fcn_hidden_layer": (_i, [_vp, _vp, _vp, _vp, _i, _f, _f, _i, _i, _i, _vp, _i, _vp, _vp, _vp]),
+    "idb_fcn_hidden_layer": (_i, [_vp, _vp, _vp, _vp, _i, _f, _f, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp]),
     "idb_fcn_output_layer": (_i, [_vp, _vp, _vp, _vp, _i, _f, _i, _i, _i, _vp, _vp]),
     "idb_fcn_anchor_layer": (_i, [_vp, _vp, _vp, _vp, _i, _f, _f, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "idb_fcn_scores": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _f, _vp, _vp]),

@@ -53,8 +53,8 @@ int idb_perturb_rows(const float* x0, const float* z, int n_anchors, int K, int 
     if (d_hi && fmt != IDB_FMT_BF16 && fmt != IDB_FMT_FP16) return fail("idb_perturb: unknown fmt");
     if (d_hi && !(d_scale > 0.f)) return fail("idb_perturb: d_scale must be positive");
     if ((d_hi == nullptr) != (d_lo == nullptr)) return fail("idb_perturb: d_hi and d_lo must both be set or both NULL");
-    if (d_hi && (Kp % 128 || Dp % 64 || Kp < K || Dp < D || !aligned16(d_hi) || !aligned16(d_lo)))
-        return fail("idb_perturb: need Kp % 128 == 0, Dp % 64 == 0, Kp >= K, Dp >= D, 16-byte aligned slabs");
+    if (d_hi && (Dp % 64 || Kp < K || Dp < D || !aligned16(d_hi) || !aligned16(d_lo)))
+        return fail("idb_perturb: need Dp % 64 == 0, Kp >= K, Dp >= D, 16-byte aligned slabs");
     if (!d_hi && !x_out) return fail("idb_perturb: no output requested");
     idb::PerturbParams p;
     p.x0 = x0; p.z = z; p.n_anchors = n_anchors; p.K = K; p.D = D;
@@ -91,7 +91,8 @@ int idb_anchor_linear(const float* in, int ld_in, int apply_elu, float in_scale,
 }
 
 static int gemm_common(int mode, const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, int w_fmt,
-                       float w_inv_scale, float out_scale, int M, int Np, int Kc, const float* a0, int rows_per_anchor, void* out_hi, void* out_lo, float* out_f32,
+                       float w_inv_scale, float out_scale, int M, int Np, int Kc, const float* a0, int rows_per_anchor,
+                       int n_anchors, void* out_hi, void* out_lo, float* out_f32,
                        void* stream, const char* name) {
     if (!a_hi || !a_lo || !w_hi || !w_lo) return fail("idb_fcn_*_layer: NULL operand");
     if (w_fmt != IDB_FMT_BF16 && w_fmt != IDB_FMT_FP16) return fail("idb_fcn_*_layer: unknown fmt");
@@ -105,7 +106,7 @@ static int gemm_common(int mode, const void* a_hi, const void* a_lo, const void*
     p.b_hi = static_cast<const uint8_t*>(w_hi); p.b_lo = static_cast<const uint8_t*>(w_lo);
     p.M = M; p.Np = Np; p.Kc = Kc;
     p.fmt = w_fmt; p.acc_scale = w_inv_scale; p.out_scale = out_scale;
-    p.a0 = a0; p.rows_per_anchor = rows_per_anchor;
+    p.a0 = a0; p.rows_per_anchor = rows_per_anchor; p.n_anchors = n_anchors;
     p.out_hi = static_cast<uint8_t*>(out_hi); p.out_lo = static_cast<uint8_t*>(out_lo);
     p.out_f32 = out_f32;
     return check(idb::launch_gemm_bf16x3(mode, p, num_sms(), static_cast<cudaStream_t>(stream)), name);
@@ -113,18 +114,20 @@ static int gemm_common(int mode, const void* a_hi, const void* a_lo, const void*
 
 int idb_fcn_hidden_layer(const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, int w_fmt,
                          float w_inv_scale, float out_scale, int M, int Np, int Kc, const float* a0,
-                         int rows_per_anchor, void* out_hi, void* out_lo, void* stream) {
-    if (!a0 || !out_hi || !out_lo || rows_per_anchor <= 0 || rows_per_anchor % 128 || M % rows_per_anchor)
-        return fail("idb_fcn_hidden_layer: need a0, outputs, rows_per_anchor % 128 == 0 and M % rows_per_anchor == 0");
+                         int rows_per_anchor, int n_anchors, void* out_hi, void* out_lo, void* stream) {
+    if (!a0 || !out_hi || !out_lo || rows_per_anchor < 128 || n_anchors <= 0 ||
+        (long long)n_anchors * rows_per_anchor > (long long)M)
+        return fail("idb_fcn_hidden_layer: need a0, outputs, rows_per_anchor >= 128 and n_anchors * rows_per_anchor <= M");
     if (!aligned16(out_hi) || !aligned16(out_lo)) return fail("idb_fcn_hidden_layer: outputs must be 16-byte aligned");
-    return gemm_common(0, a_hi, a_lo, w_hi, w_lo, w_fmt, w_inv_scale, out_scale, M, Np, Kc, a0, rows_per_anchor, out_hi, out_lo, nullptr, stream,
+    return gemm_common(0, a_hi, a_lo, w_hi, w_lo, w_fmt, w_inv_scale, out_scale, M, Np, Kc, a0, rows_per_anchor, n_anchors,
+                       out_hi, out_lo, nullptr, stream,
                        "idb_fcn_hidden_layer");
 }
 
 int idb_fcn_output_layer(const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, int w_fmt,
                          float w_inv_scale, int M, int Np, int Kc, float* out_f32, void* stream) {
     if (!out_f32 || !aligned16(out_f32)) return fail("idb_fcn_output_layer: out_f32 must be set and 16-byte aligned");
-    return gemm_common(1, a_hi, a_lo, w_hi, w_lo, w_fmt, w_inv_scale, 1.0f, M, Np, Kc, nullptr, 128, nullptr, nullptr, out_f32, stream,
+    return gemm_common(1, a_hi, a_lo, w_hi, w_lo, w_fmt, w_inv_scale, 1.0f, M, Np, Kc, nullptr, 128, 1, nullptr, nullptr, out_f32, stream,
                        "idb_fcn_output_layer");
 }
 
@@ -134,7 +137,7 @@ int idb_fcn_anchor_layer(const void* a_hi, const void* a_lo, const void* w_hi, c
     if (!out_f32 || !aligned16(out_f32)) return fail("idb_fcn_anchor_layer: out_f32 must be set and 16-byte aligned");
     if ((out_hi == nullptr) != (out_lo == nullptr) || !aligned16(out_hi) || !aligned16(out_lo))
         return fail("idb_fcn_anchor_layer: out_hi/out_lo must both be set (16-byte aligned) or both NULL");
-    return gemm_common(2, a_hi, a_lo, w_hi, w_lo, fmt, acc_scale, out_scale, M, Np, Kc, bias, 128, out_hi, out_lo,
+    return gemm_common(2, a_hi, a_lo, w_hi, w_lo, fmt, acc_scale, out_scale, M, Np, Kc, bias, 128, 1, out_hi, out_lo,
                        out_f32, stream, "idb_fcn_anchor_layer");
 }
 

@@ -9,8 +9,9 @@ namespace idb {
 // One thread = one 16-byte output chunk = 8 consecutive columns of one perturbation row.
 __global__ void __launch_bounds__(256) perturb_kernel(const PerturbParams p) {
     const int chunks = p.Dp >> 3;
-    const long long total = (long long)p.n_anchors * p.Kp * chunks;
-    const long long Mtot = (long long)p.n_anchors * p.Kp;
+    // slab rows: anchor-major, Kp rows per anchor (Kp = K: densely packed), padded with zero rows to a multiple of 128
+    const long long Mtot = p.d_hi ? (((long long)p.n_anchors * p.Kp + 127) / 128) * 128 : (long long)p.n_anchors * p.Kp;
+    const long long total = Mtot * chunks;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
          i += (long long)gridDim.x * blockDim.x) {
         const int ch = (int)(i % chunks);
@@ -21,7 +22,7 @@ __global__ void __launch_bounds__(256) perturb_kernel(const PerturbParams p) {
         float dev[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) dev[j] = 0.f;
-        if (k < p.K && c0 < p.D) {
+        if (a < p.n_anchors && k < p.K && c0 < p.D) {
             float zz[8];
             if (p.z != nullptr) {
                 const float* zr = p.z + ((size_t)a * p.K + k) * p.D;
@@ -64,7 +65,8 @@ __global__ void __launch_bounds__(256) perturb_kernel(const PerturbParams p) {
 }
 
 cudaError_t launch_perturb(const PerturbParams& p, cudaStream_t stream) {
-    const long long total = (long long)p.n_anchors * p.Kp * (p.Dp >> 3);
+    const long long rows = p.d_hi ? (((long long)p.n_anchors * p.Kp + 127) / 128) * 128 : (long long)p.n_anchors * p.Kp;
+    const long long total = rows * (p.Dp >> 3);
     if (total <= 0) return cudaSuccess;
     long long blocks = (total + 255) / 256;
     if (blocks > 148LL * 64) blocks = 148LL * 64;

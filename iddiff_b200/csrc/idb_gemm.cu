@@ -29,7 +29,7 @@ constexpr uint32_t STAGE_BYTES = 2 * A_TILE_BYTES + 2 * B_TILE_BYTES;
 constexpr int EPI_WARPS = 16;  // 4 per scheduler: the epilogue is issue-latency bound with fewer
 constexpr int EPI_THREADS = EPI_WARPS * 32;
 constexpr int GEMM_THREADS = 64 + EPI_THREADS;
-constexpr size_t GEMM_SMEM = 1024 /*align slack*/ + (size_t)STAGES * STAGE_BYTES + 2 * 2 * BN * sizeof(float) + 256;
+constexpr size_t GEMM_SMEM = 1024 /*align slack*/ + (size_t)STAGES * STAGE_BYTES + 2 * 4 * BN * sizeof(float) + 256;
 
 
 // 32-byte store of two 16-byte halves (first -> lower address); dst 32-byte aligned
@@ -65,9 +65,9 @@ template <int kMode>
 __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_bf16x3_kernel(const GemmParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    float* s_a0 = reinterpret_cast<float*>(smem + (size_t)STAGES * STAGE_BYTES);  // [2][BN]
-    float* s_em1 = s_a0 + 2 * BN;                                                 // [2][BN]
-    uint64_t* bars = reinterpret_cast<uint64_t*>(s_em1 + 2 * BN);
+    float* s_a0 = reinterpret_cast<float*>(smem + (size_t)STAGES * STAGE_BYTES);  // [2 TMEM buffers][2 anchors][BN]
+    float* s_em1 = s_a0 + 4 * BN;                                                 // same shape
+    uint64_t* bars = reinterpret_cast<uint64_t*>(s_em1 + 4 * BN);
     uint64_t* full = bars;                  // [STAGES]
     uint64_t* empty = bars + STAGES;        // [STAGES]
     uint64_t* tfull = bars + 2 * STAGES;    // [2]
@@ -163,17 +163,21 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_bf16x3_kernel(const Gemm
             const uint32_t aphase = (it >> 1) & 1;
             const size_t m0 = (size_t)(t / n_tiles_n) * BM;
             const size_t n0 = (size_t)(t % n_tiles_n) * BN;
+            int anchor = 0;
             if (kMode == 0) {
-                const int anchor = (int)(m0 / (size_t)p.rows_per_anchor);
-                const float* a0 = p.a0 + (size_t)anchor * p.Np + n0;
-                for (int c = et; c < BN; c += EPI_THREADS) {
-                    const float a = __ldg(a0 + c);
-                    s_a0[as * BN + c] = a;
-                    s_em1[as * BN + c] = expm1f(fminf(a, 0.f));
+                // rows are packed densely, anchor-major: this tile's 128 rows belong to `anchor` and, past the boundary,
+                // to `anchor + 1` (rows_per_anchor >= 128); both anchors' pre-activations are staged, each row picks its own
+                anchor = (int)(m0 / (size_t)p.rows_per_anchor);
+                for (int c = et; c < 2 * BN; c += EPI_THREADS) {
+                    const int w = c / BN, col = c % BN;
+                    const int an = min(anchor + w, p.n_anchors - 1);
+                    const float a = __ldg(p.a0 + (size_t)an * p.Np + n0 + col);
+                    s_a0[(as * 2 + w) * BN + col] = a;
+                    s_em1[(as * 2 + w) * BN + col] = expm1f(fminf(a, 0.f));
                 }
                 asm volatile("bar.sync 1, %0;" ::"n"(EPI_THREADS) : "memory");
             } else if (kMode == 2) {  // anchor layer: p.a0 is the bias vector [Np] (may be null)
-                for (int c = et; c < BN; c += EPI_THREADS) s_a0[as * BN + c] = p.a0 ? __ldg(p.a0 + n0 + c) : 0.f;
+                for (int c = et; c < BN; c += EPI_THREADS) s_a0[as * 2 * BN + c] = p.a0 ? __ldg(p.a0 + n0 + c) : 0.f;
                 asm volatile("bar.sync 1, %0;" ::"n"(EPI_THREADS) : "memory");
             }
             mbar_wait(&tfull[as], aphase);
@@ -188,7 +192,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_bf16x3_kernel(const Gemm
 #pragma unroll
                 for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) * p.acc_scale);
                 if (kMode == 2) {  // pre-activation = acc + bias, kept in fp32 for the hidden-layer epilogues
-                    const float* sb = s_a0 + as * BN + cc * 32;
+                    const float* sb = s_a0 + as * 2 * BN + cc * 32;
 #pragma unroll
                     for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + sb[j]);
                 }
@@ -200,8 +204,9 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_bf16x3_kernel(const Gemm
                                              __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
                 }
                 if (kMode == 0 || (kMode == 2 && p.out_hi != nullptr)) {
-                    const float* sa = s_a0 + as * BN + cc * 32;
-                    const float* se = s_em1 + as * BN + cc * 32;
+                    const int sel = (kMode == 0 && m >= (size_t)(anchor + 1) * (size_t)p.rows_per_anchor) ? 1 : 0;
+                    const float* sa = s_a0 + (as * 2 + sel) * BN + cc * 32;
+                    const float* se = s_em1 + (as * 2 + sel) * BN + cc * 32;
                     const size_t n = n0 + cc * 32;  // 32 columns = half of one 64-wide output slab
                     uint8_t* row_hi = p.out_hi + ((n >> 6) * (size_t)p.M + m) * 128;
                     uint8_t* row_lo = p.out_lo + ((n >> 6) * (size_t)p.M + m) * 128;

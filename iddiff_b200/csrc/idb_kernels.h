@@ -17,7 +17,8 @@ struct GemmParams {
     float out_scale;  // mode 0: deviations are multiplied by this before the hi/lo split (a_scale of the next layer)
     // mode 0 (hidden layer): anchor pre-activations in, slab-layout deviations out
     const float* a0;  // [n_anchors][Np]
-    int rows_per_anchor;
+    int rows_per_anchor;  // rows of A per anchor, anchor-major and DENSE (>= 128; a 128-row tile spans at most two anchors)
+    int n_anchors;        // rows past n_anchors * rows_per_anchor are padding (zero deviations)
     uint8_t* out_hi;  // slab [Np/64][M][128 B]
     uint8_t* out_lo;
     // mode 1 (last layer): fp32 row-major [M][Np]

@@ -201,7 +201,10 @@ class FcnEngine:
     GEMM_CHUNK = 256   # anchors per pass of the tensor-core chain (activation ping-pong buffers: 2 x 3.2 GB at K = 1501)
 
     def rows_per_anchor(self, K: int) -> int:
-        return _ceil(K, 128)
+        """Rows of the operand slabs per anchor: the K perturbations packed DENSELY (a 128-row GEMM tile then spans at
+        most two anchors and its epilogue looks the anchor up per row; no zero rows are multiplied: K = 1501 used to pad
+        to 1536).  Below 128 rows an anchor is padded to one tile."""
+        return max(int(K), 128)
 
     def bytes_per_anchor(self, K: int) -> int:
         """Per anchor of one estimate() call: fp32 deviations of the output layer, fp64 Gram + solver workspace; the
@@ -272,7 +275,7 @@ class FcnEngine:
             if tuple(z.shape) != (A, K, D):
                 raise _lib.IdbError("z must be [A, K, D]")
         Kp = self.rows_per_anchor(K)
-        M = A * Kp
+        M = _ceil(A * Kp, 128)          # slab rows: anchors back to back, zero rows up to the tile boundary
         st = stream_ptr()
         dev = self.dev
         e_hi = torch.empty(M * self.Kc[0] * 2, dtype=torch.uint8, device=dev)
@@ -288,16 +291,18 @@ class FcnEngine:
             o_lo = torch.empty(M * self.Np[l] * 2, dtype=torch.uint8, device=dev)
             with _stage("hidden_first" if l == 0 else "hidden", 2.0 * A * K * self.in_real[l] * self.out_real[l]):
                 call("idb_fcn_hidden_layer", ptr(e_hi), ptr(e_lo), ptr(self.w_hi[l]), ptr(self.w_lo[l]), self.fmt,
-                     self.w_inv_scale[l] / self.a_scale, self.a_scale, M, self.Np[l], self.Kc[l], ptr(P[l]), Kp,
+                     self.w_inv_scale[l] / self.a_scale, self.a_scale, M, self.Np[l], self.Kc[l], ptr(P[l]), Kp, A,
                      ptr(o_hi), ptr(o_lo), st)
             e_hi, e_lo = o_hi, o_lo
         l = self.n_layers - 1
         if d_out is None:
-            d_out = torch.empty(A, Kp, self.Np[l], dtype=torch.float32, device=dev)
+            d_out = torch.empty(M, self.Np[l], dtype=torch.float32, device=dev)
+        elif tuple(d_out.shape) != (M, self.Np[l]) or not d_out.is_contiguous():
+            raise _lib.IdbError("deviations: d_out must be a contiguous [ceil128(A * rows_per_anchor), Np] buffer")
         with _stage("output", 2.0 * A * K * self.in_real[l] * self.out_real[l]):
             call("idb_fcn_output_layer", ptr(e_hi), ptr(e_lo), ptr(self.w_hi[l]), ptr(self.w_lo[l]), self.fmt,
                  self.w_inv_scale[l] / self.a_scale, M, self.Np[l], self.Kc[l], ptr(d_out), st)
-        return d_out, P[-1]
+        return d_out[:A * Kp].view(A, Kp, self.Np[l]), P[-1]
 
     def join(self):
         """Makes the current stream wait for every spectrum stage deferred with estimate(..., defer=True)."""
@@ -320,11 +325,15 @@ class FcnEngine:
             _require_cuda(x0, "x0")
             with _stage("anchor_chain", sum(2.0 * A * i * o for i, o in zip(self.in_real, self.out_real))):
                 P = self.anchor_chain(x0, mean_coeff, label)
-            d_out = torch.empty(A, self.rows_per_anchor(K), self.Np[-1], dtype=torch.float32, device=self.dev)
+            Kp = self.rows_per_anchor(K)
+            # one flat buffer for all passes: a pass writes whole 128-row tiles, so its zero tail rows spill into the next
+            # pass's region and are overwritten by it (same stream, in order); 128 rows of slack close the last one
+            flat = torch.empty(_ceil(A * Kp, 128) + 128, self.Np[-1], dtype=torch.float32, device=self.dev)
             for s in range(0, A, ck):
                 e = min(A, s + ck)
                 self.deviations(x0[s:e], K, mean_coeff, std, label, None if z is None else z[s:e], seed,
-                                anchor_id0 + s, P=[q[s:] for q in P], d_out=d_out[s:e])
+                                anchor_id0 + s, P=[q[s:] for q in P], d_out=flat[s * Kp:s * Kp + _ceil((e - s) * Kp, 128)])
+            d_out = flat[:A * Kp].view(A, Kp, self.Np[-1])
             a_out = P[-1]
         # centring removes the anchor part exactly: spectrum of (-(a + d)/std - mean) = spectrum of (d - mean(d))/std
         if defer and not want_scores:

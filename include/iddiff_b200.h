@@ -35,8 +35,9 @@ const char* idb_last_error(void);
  *   x0 [n_anchors][D] fp32;  z [n_anchors][K][D] fp32 or NULL -> fused Philox4x32-10 + Box-Muller keyed by
  *   (seed, anchor_id0 + a, row, column), so results do not depend on sharding or chunking.
  * Outputs (either may be NULL): x_out [n_anchors][K][D] fp32 = fl(fl(mean_coeff*x0) + fl(std*z));
- *   d_hi/d_lo slab layout [Dp/64][n_anchors*Kp][128B] = hi/lo pair (format fmt) of d_scale*(x - mean), rows >= K
- *   and columns >= D zero.  Kp % 128 == 0, Dp % 64 == 0. */
+ *   d_hi/d_lo slab layout [Dp/64][M][128B], M = ceil128(n_anchors*Kp) = hi/lo pair (format fmt) of d_scale*(x - mean):
+ *   anchor a owns rows [a*Kp, a*Kp + K) (Kp >= K; Kp = K packs the anchors densely), all other rows and columns >= D zero.
+ *   Dp % 64 == 0. */
 int idb_perturb(const float* x0, const float* z, int n_anchors, int K, int D, int Kp, int Dp, float mean_coeff,
                 float std, uint64_t seed, uint64_t anchor_id0, float* x_out, int fmt, float d_scale, void* d_hi,
                 void* d_lo, void* stream);
@@ -75,11 +76,13 @@ int idb_anchor_linear(const float* in, int ld_in, int apply_elu, float in_scale,
 /* Hidden nn.Linear + ELU on the deviations (tcgen05 kind::f16, 3 MMAs per product, fp32 accumulate in TMEM):
  *   acc = acc_scale * A (hi+lo) . W^T (hi+lo);  e = ELU(a0 + acc) - ELU(a0);  out = hi/lo pair of out_scale * e in
  *   slabs [Np/64][M][128B].  acc_scale = 1 / (scale of A * scale of W); out_scale = scale the next layer expects.
- * a0 [M/rows_per_anchor][Np] fp32 = anchor pre-activations of this layer.  M % 128 == 0, Np % 256 == 0,
- * Kc % 64 == 0, rows_per_anchor % 128 == 0. */
+ * a0 [n_anchors][Np] fp32 = anchor pre-activations of this layer.  Rows of A are anchor-major and DENSE: anchor a owns rows
+ * [a * rows_per_anchor, (a + 1) * rows_per_anchor) (rows_per_anchor = K >= 128: a 128-row tile spans at most two anchors and
+ * every row looks up its own), rows from n_anchors * rows_per_anchor to M are zero padding.  M % 128 == 0, Np % 256 == 0,
+ * Kc % 64 == 0. */
 int idb_fcn_hidden_layer(const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, int fmt,
                          float acc_scale, float out_scale, int M, int Np, int Kc, const float* a0,
-                         int rows_per_anchor, void* out_hi, void* out_lo, void* stream);
+                         int rows_per_anchor, int n_anchors, void* out_hi, void* out_lo, void* stream);
 
 /* Last nn.Linear on the deviations: out_f32 [M][Np] fp32 row-major = acc_scale * A (hi+lo) . W^T (hi+lo). */
 int idb_fcn_output_layer(const void* a_hi, const void* a_lo, const void* w_hi, const void* w_lo, int fmt,

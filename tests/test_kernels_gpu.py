@@ -100,10 +100,12 @@ def _elu(x):
 
 
 @pytest.mark.parametrize("fmt", [_lib.FMT_BF16, _lib.FMT_FP16])
-@pytest.mark.parametrize("A,Kp,Np,Kc", [(1, 128, 256, 64), (3, 256, 512, 192), (2, 128, 2048, 2048)])
+@pytest.mark.parametrize("A,Kp,Np,Kc", [(1, 128, 256, 64), (3, 256, 512, 192), (2, 128, 2048, 2048),
+                                        (3, 151, 256, 64), (5, 333, 512, 128)])   # dense packing: tiles straddle anchors
 def test_hidden_layer_gemm_elu_deviation(A, Kp, Np, Kc, fmt):
-    M = A * Kp
+    M = (A * Kp + 127) // 128 * 128
     a = _rand(M, Kc, seed=4, scale=0.02)
+    a[A * Kp:] = 0                                   # rows past the last anchor are padding
     w = _rand(Np, Kc, seed=5, scale=1 / math.sqrt(Kc))
     a0 = _rand(A, Np, seed=6, scale=0.5)
     a_hi, a_lo, a64, asc = _slabs(a, fmt)
@@ -111,13 +113,14 @@ def test_hidden_layer_gemm_elu_deviation(A, Kp, Np, Kc, fmt):
     o_hi = torch.zeros(M * Np * 2, dtype=torch.uint8, device=dev())
     o_lo = torch.zeros_like(o_hi)
     call("idb_fcn_hidden_layer", ptr(a_hi), ptr(a_lo), ptr(w_hi), ptr(w_lo), fmt, inv / asc, asc, M, Np, Kc, ptr(a0),
-         Kp, ptr(o_hi), ptr(o_lo), stream_ptr())
+         Kp, A, ptr(o_hi), ptr(o_lo), stream_ptr())
     torch.cuda.synchronize()
     dt = torch.float16 if fmt == _lib.FMT_FP16 else torch.bfloat16
     got = (layout.from_slab(o_hi, M, Np).view(dt).double() + layout.from_slab(o_lo, M, Np).view(dt).double()) / asc
     d = a64 @ w64.T
-    base = a0.double().repeat_interleave(Kp, dim=0)
+    base = torch.cat([a0.double().repeat_interleave(Kp, dim=0), a0[-1:].double().expand(M - A * Kp, Np)])
     ref = _elu(base + d) - _elu(base)
+    assert float(got[A * Kp:].abs().max() if M > A * Kp else 0.0) == 0.0
     err = (got - ref).abs().max().item()
     scale = ref.abs().max().item()
     assert err < (5e-5 if fmt == _lib.FMT_BF16 else 2e-5) * scale, (err, scale)
