@@ -56,7 +56,7 @@ SIGNATURES = {
     "idb_groupnorm_stats": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _d, _vp, _vp, _vp]),
     "idb_conv_prep": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _i, _vp, _vp, _i, _f, _vp, _vp, _i, _vp, _vp]),
     "idb_conv_prep_fir": (_i, [_vp, _i, _i, _i, _i, _vp, _i, _vp, _vp, _i, C.POINTER(C.c_float), _i, _i, _i, _i, _i, _i, _i, _f,
-                               _vp, _vp, _i, _vp, _vp]),
+                               _vp, _vp, _i, _vp, _vp, _vp]),
     "idb_conv2d": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, C.POINTER(C.c_int), _i, _i, _f, _f, _vp, _vp, _i,
                         _vp, _i, _vp]),
     "idb_conv_stats_slots": (_i, [_i, _i]),

@@ -72,20 +72,20 @@ int idb_conv_prep(const float* src0, int C0, const float* src1, int C1, int N, i
     p.gamma = gamma; p.beta = beta; p.act = act; p.scale = scale;
     p.out_hi = static_cast<uint8_t*>(out_hi); p.out_lo = static_cast<uint8_t*>(out_lo);
     p.Cp = out_hi ? Cp : ((C + 7) & ~7);
-    p.out_f32 = out_f32;
+    p.out_f32 = out_f32; p.out_raw = nullptr;
     return api_check(idb::launch_conv_prep(p, idb::api_num_sms(), static_cast<cudaStream_t>(stream)), "idb_conv_prep");
 }
 
 int idb_conv_prep_fir(const float* src0, int C0, int N, int Hs, int Ws, const float* mean_rstd, int groups,
                       const float* gamma, const float* beta, int act, const float* kernel_host, int kh, int kw, int up,
                       int down, int pad0, int pad1, int as_planes, float scale, void* out_hi, void* out_lo, int Cp,
-                      float* out_f32, void* stream) {
+                      float* out_f32, float* out_raw, void* stream) {
     if (!src0 || !kernel_host || C0 <= 0 || N < 0 || Hs <= 0 || Ws <= 0) return api_fail("idb_conv_prep_fir: bad argument");
     if (kh < 1 || kh > 4 || kw < 1 || kw > 4) return api_fail("idb_conv_prep_fir: FIR kernels up to 4 x 4");
     if ((up != 1 && up != 2) || (down != 1 && down != 2) || (as_planes && down != 1) || pad0 < 0 || pad1 < 0)
         return api_fail("idb_conv_prep_fir: up, down in {1, 2}, pads >= 0, as_planes needs down = 1");
     if ((out_hi == nullptr) != (out_lo == nullptr)) return api_fail("idb_conv_prep_fir: out_hi/out_lo both or neither");
-    if (!out_hi && !out_f32) return api_fail("idb_conv_prep_fir: no output requested");
+    if (!out_hi && !out_f32 && !out_raw) return api_fail("idb_conv_prep_fir: no output requested");
     if (out_hi && (Cp % 64 || Cp < C0)) return api_fail("idb_conv_prep_fir: Cp must be a multiple of 64 and >= C");
     if (mean_rstd && (groups <= 0 || C0 % groups)) return api_fail("idb_conv_prep_fir: bad groups");
     if (act < 0 || act > 2) return api_fail("idb_conv_prep_fir: act must be 0, 1 or 2");
@@ -107,7 +107,7 @@ int idb_conv_prep_fir(const float* src0, int C0, int N, int Hs, int Ws, const fl
     p.gamma = gamma; p.beta = beta; p.act = act; p.scale = scale;
     p.out_hi = static_cast<uint8_t*>(out_hi); p.out_lo = static_cast<uint8_t*>(out_lo);
     p.Cp = out_hi ? Cp : ((C0 + 7) & ~7);
-    p.out_f32 = out_f32;
+    p.out_f32 = out_f32; p.out_raw = out_raw;
     return api_check(idb::launch_conv_prep(p, idb::api_num_sms(), static_cast<cudaStream_t>(stream)), "idb_conv_prep_fir");
 }
 

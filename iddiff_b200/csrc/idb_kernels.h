@@ -130,6 +130,7 @@ struct PrepParams {
     uint8_t* out_lo;
     int Cp;
     float* out_f32;          // optional fp32 [planes][N][Ho][Wo][C] copy of the transformed tensor
+    float* out_raw;          // mode 4 only, optional: the same FIR applied to the UNtransformed source, fp32 [planes][N][Ho][Wo][C]
 };
 cudaError_t launch_conv_prep(const PrepParams& p, int num_sms, cudaStream_t stream);
 

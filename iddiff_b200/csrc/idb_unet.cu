@@ -315,9 +315,12 @@ __global__ void __launch_bounds__(256, KIND ? 2 : 4) conv_prep_kernel(const Prep
                 // upfirdn2d of the TRANSFORMED tensor (layerspp.py:244-257: FIR up/down-sampling of act(GN(x)) and of x;
                 // ncsnpp.py:297-304: FIR pad before the stride-2 convolution of the input pyramid), gathered per output
                 // pixel: out[y][x] = sum_ab fir[a][b] * U[y*down + a - pad0][x*down + b - pad0], U = zero-stuffed (up)
-                // transformed source, zero outside.  No intermediate tensor exists.
+                // transformed source, zero outside.  No intermediate tensor exists.  With out_raw the SAME gather also
+                // filters the untransformed source (the res-block's skip branch, layerspp.py:246-248,253-255): one read
+                // of the activation serves both branches.
+                float raw[8];
 #pragma unroll
-                for (int j = 0; j < 8; ++j) v[j] = 0.f;
+                for (int j = 0; j < 8; ++j) { v[j] = 0.f; raw[j] = 0.f; }
                 const int yf = p.fir_planes ? 2 * yo + (plane >> 1) : yo, xf = p.fir_planes ? 2 * xo + (plane & 1) : xo;
                 if (yf < p.fir_hf && xf < p.fir_wf) {
                     const int y0 = yf * p.fir_down - p.fir_pad0, x0 = xf * p.fir_down - p.fir_pad0;
@@ -333,11 +336,26 @@ __global__ void __launch_bounds__(256, KIND ? 2 : 4) conv_prep_kernel(const Prep
                             if (jx >= p.Ws) continue;
                             float t[8];
                             prep_load8<VEC>(p, n, i, jx, c0, C, t);
-                            prep_transform8<VEC>(p, k, c0, C, t);
                             const float wgt = p.fir[a * 4 + b];
+                            if (p.out_raw) {
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) raw[j] = fmaf(wgt, t[j], raw[j]);
+                            }
+                            prep_transform8<VEC>(p, k, c0, C, t);
 #pragma unroll
                             for (int j = 0; j < 8; ++j) v[j] = fmaf(wgt, t[j], v[j]);
                         }
+                    }
+                }
+                if (p.out_raw) {
+                    if (VEC) {
+                        float4* dst = reinterpret_cast<float4*>(p.out_raw + (size_t)pix * C + c0);
+                        dst[0] = make_float4(raw[0], raw[1], raw[2], raw[3]);
+                        dst[1] = make_float4(raw[4], raw[5], raw[6], raw[7]);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j)
+                            if (c0 + j < C) p.out_raw[(size_t)pix * C + c0 + j] = raw[j];
                     }
                 }
             }

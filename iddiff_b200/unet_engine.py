@@ -219,12 +219,11 @@ class UNetEngine:
             # layerspp.py:244-257: FIR resampling of BOTH act(GN(x)) and x before the convolutions
             assert x1 is None
             if U.FUSED_FIR:
-                # one gathering pass per branch: act(GN(x)) -> FIR -> operand, and x -> FIR -> fp32; neither the
+                # ONE gathering pass for both branches: act(GN(x)) -> FIR -> operand, and x -> FIR -> fp32; neither the
                 # normalised nor the filtered activation is materialised (no upfirdn2d launch)
                 updn = (2, 1, 2, 1) if blk.up else (1, 2, 1, 1)
-                a = U.prep_fir(x0, blk.fir_host, *updn, mean_rstd=mr, groups=blk.groups0, gamma=blk.gn0[0],
-                               beta=blk.gn0[1], act=1)
-                x0 = U.prep_fir(x0, blk.fir_host, *updn, want_operand=False, want_f32=True)[1]
+                a, x0 = U.prep_fir(x0, blk.fir_host, *updn, mean_rstd=mr, groups=blk.groups0, gamma=blk.gn0[0],
+                                   beta=blk.gn0[1], act=1, want_raw=True)
                 return self._res_tail(blk, bias0, a, x0, None)
             _, hf = U.prep(x0, mean_rstd=mr, groups=blk.groups0, gamma=blk.gn0[0], beta=blk.gn0[1], act=1,
                            want_operand=False, want_f32=True)

@@ -155,7 +155,7 @@ def fir_kernel_host(taps, gain: float):
 
 def prep_fir(x0: torch.Tensor, k_host, up: int, down: int, pad0: int, pad1: int, *, as_planes: bool = False,
              mean_rstd=None, groups: int = 0, gamma=None, beta=None, act: int = 0, want_operand: bool = True,
-             want_f32: bool = False):
+             want_f32: bool = False, want_raw: bool = False):
     """upfirdn2d(act(GN(x0)), k, up, down, (pad0, pad1)) written straight as the convolution operand and / or fp32 NHWC
     (idb_conv_prep_fir); as_planes: the four stride-2 parity planes of the down = 1 result (conv_downsample_2d)."""
     n, hs, ws, c = x0.shape
@@ -171,14 +171,18 @@ def prep_fir(x0: torch.Tensor, k_host, up: int, down: int, pad0: int, pad1: int,
         hi = torch.empty(planes, n, ho, wo, cp, dtype=torch.float16, device=dev)
         lo = torch.empty_like(hi)
     f32 = torch.empty(planes, n, ho, wo, c, dtype=torch.float32, device=dev) if want_f32 else None
+    raw = torch.empty(planes, n, ho, wo, c, dtype=torch.float32, device=dev) if want_raw else None
     kptr = k_host.ctypes.data_as(C.POINTER(C.c_float))
     _lib.call("idb_conv_prep_fir", _lib.ptr(x0), c, n, hs, ws, _lib.ptr(mean_rstd), groups, _lib.ptr(gamma), _lib.ptr(beta),
               act and SILU_ACT, kptr, kh, kw, up, down, pad0, pad1, int(as_planes), ACT_SCALE, _lib.ptr(hi), _lib.ptr(lo), cp,
-              _lib.ptr(f32), _lib.stream_ptr())
+              _lib.ptr(f32), _lib.ptr(raw), _lib.stream_ptr())
     op = Operand(hi, lo, planes, n, ho, wo, cp) if want_operand else None
+    out = [op]
     if want_f32:
-        return op, (f32[0] if planes == 1 else f32)
-    return op
+        out.append(f32[0] if planes == 1 else f32)
+    if want_raw:
+        out.append(raw[0] if planes == 1 else raw)
+    return out[0] if len(out) == 1 else tuple(out)
 
 
 def conv(a: Operand, pc: PackedConv, *, bias: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None,

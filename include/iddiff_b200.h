@@ -236,11 +236,13 @@ int idb_conv_prep(const float* src0, int C0, const float* src1, int C1, int N, i
  * normalised, activated and the filtered tensors are never materialised.  Covers layerspp.py:244-257 (BigGAN res-block:
  * downsample_2d = up 1, down 2, pad (1, 1); upsample_2d = kernel * 4, up 2, down 1, pad (2, 1)) and, with as_planes,
  * up_or_down_sampling.py:144-178 conv_downsample_2d: FIR pad (2, 2) at down = 1 followed by a stride-2 convolution,
- * emitted directly as the four stride-2 parity planes idb_conv2d reads.  kernel_host: HOST array [kh][kw]. */
+ * emitted directly as the four stride-2 parity planes idb_conv2d reads.  kernel_host: HOST array [kh][kw].
+ * out_raw (optional, fp32): the same filter applied to the UNtransformed src0 in the same gather -- the res-block's skip
+ * branch upfirdn2d(x) (layerspp.py:246-248,253-255) costs no second read of the activation. */
 int idb_conv_prep_fir(const float* src0, int C0, int N, int Hs, int Ws, const float* mean_rstd, int groups,
                       const float* gamma, const float* beta, int act, const float* kernel_host, int kh, int kw, int up,
                       int down, int pad0, int pad1, int as_planes, float scale, void* out_hi, void* out_lo, int Cp,
-                      float* out_f32, void* stream);
+                      float* out_f32, float* out_raw, void* stream);
 
 /* nn.Conv2d / NIN as an implicit GEMM on tcgen05 (3 MMAs per product on fp16 hi/lo pairs, fp32 accumulate in TMEM):
  *   out[n,h,w,co] = out_scale * (acc_scale * sum_{t,ci} A[plane_t][n, h+dy_t, w+dx_t, ci] * Wt[co][t][ci]

@@ -184,7 +184,12 @@ def test_fir_folded_into_operand_preparation(kind, norm):
         mr = U.gn_stats(xg, None, groups, 1e-6)
         kw = dict(mean_rstd=mr, groups=groups, gamma=gamma.cuda(), beta=beta.cuda(), act=1)
         t = F.silu(F.group_norm(t, groups, gamma.double(), beta.double(), eps=1e-6))
-    op, f32 = U.prep_fir(xg, kh, up, down, p0, p1, as_planes=kind == "pyramid", want_f32=True, **kw)
+    op, f32, raw = U.prep_fir(xg, kh, up, down, p0, p1, as_planes=kind == "pyramid", want_f32=True, want_raw=True, **kw)
+    # the skip branch from the same gather: the filter on the untransformed tensor
+    plain = U.prep_fir(xg, kh, up, down, p0, p1, as_planes=kind == "pyramid", want_operand=False, want_f32=True)[1]
+    assert torch.equal(raw, plain)
+    if not norm:
+        assert torch.equal(raw, f32)
     # (a) oracle: numpy upfirdn2d on [major = N*C, H, W, minor = 1]
     ref = IO.upfirdn2d_np(t.numpy().reshape(n * c, h, w, 1), kh.astype(np.float64), up, up, down, down, p0, p1, p0, p1)
     ref = torch.from_numpy(ref.reshape(n, c, ref.shape[1], ref.shape[2]))
