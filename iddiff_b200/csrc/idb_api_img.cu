@@ -154,10 +154,64 @@ int idb_groupnorm_from_conv_stats(const float* stats0, int C0, int slots0, const
                      "idb_groupnorm_from_conv_stats");
 }
 
+static int conv2d_impl(const void* a_hi, const void* a_lo, int planes, int N, int Ha, int Wa, int H, int W, int Cp,
+                       const void* w_hi, const void* w_lo, int n_taps, const int* taps_host, int Np, int Cout,
+                       float acc_scale, float out_scale, const float* bias, const float* residual, int ld_res, float* out,
+                       int ldo, float* stats, long long w_img_stride, void* stream);
+
 int idb_conv2d_stats(const void* a_hi, const void* a_lo, int planes, int N, int Ha, int Wa, int H, int W, int Cp,
                      const void* w_hi, const void* w_lo, int n_taps, const int* taps_host, int Np, int Cout,
                      float acc_scale, float out_scale, const float* bias, const float* residual, int ld_res, float* out,
                      int ldo, float* stats, void* stream) {
+    return conv2d_impl(a_hi, a_lo, planes, N, Ha, Wa, H, W, Cp, w_hi, w_lo, n_taps, taps_host, Np, Cout, acc_scale, out_scale,
+                       bias, residual, ld_res, out, ldo, stats, 0, stream);
+}
+
+size_t idb_attention_tc_workspace_bytes(int N, int T, int dh) {
+    if (N <= 0 || T <= 0 || dh <= 0) return 256;
+    const size_t op = (size_t)N * T * dh * 2;          // one fp16 plane of Q / K / V^T
+    return 6 * op + (size_t)N * T * T * 4 + 2 * (size_t)N * T * T * 2 + 1024;
+}
+
+int idb_attention_tc(const float* qkv, int N, int H, int W, int ld, int dh, int q0, int k0, int v0, float scale,
+                     void* workspace, float* out, int ld_out, void* stream) {
+    const int T = H * W;
+    if (!qkv || !workspace || !out || N <= 0 || H <= 0 || W <= 0 || ld_out < dh)
+        return api_fail("idb_attention_tc: bad argument");
+    if (T < 128 || T % 128 || dh % 64 || dh > 256 * 4 || T > 1024)
+        return api_fail("idb_attention_tc: needs T = H*W a multiple of 128 (one image per 128-pixel tile) and dh % 64 == 0; "
+                        "use idb_attention otherwise");
+    if ((reinterpret_cast<uintptr_t>(workspace) & 1023) || (reinterpret_cast<uintptr_t>(qkv) & 15))
+        return api_fail("idb_attention_tc: workspace must be 1024-byte aligned, qkv 16-byte aligned");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const size_t op = (size_t)N * T * dh * 2;
+    uint8_t* ws = static_cast<uint8_t*>(workspace);
+    uint8_t *q_hi = ws, *q_lo = ws + op, *k_hi = ws + 2 * op, *k_lo = ws + 3 * op, *vt_hi = ws + 4 * op, *vt_lo = ws + 5 * op;
+    float* S = reinterpret_cast<float*>(ws + 6 * op);
+    uint8_t* p_hi = reinterpret_cast<uint8_t*>(S) + (size_t)N * T * T * 4;
+    uint8_t* p_lo = p_hi + (size_t)N * T * T * 2;
+    const float OPS = 64.f, PS = 4096.f;     // operand scales: activations x 2^6 (as every convolution), probabilities x 2^12
+    int rc = api_check(idb::launch_attn_pack(qkv, N, T, ld, dh, q0, k0, v0, OPS, q_hi, q_lo, k_hi, k_lo, vt_hi, vt_lo, st),
+                       "idb_attention_tc(pack)");
+    if (rc) return rc;
+    const int tap[3] = {0, 0, 0};
+    // S[n][query][key] = scale * sum_c Q[n][query][c] K[n][key][c]: "1x1 convolution" with the image's own K as weights
+    rc = conv2d_impl(q_hi, q_lo, 1, N, H, W, H, W, dh, k_hi, k_lo, 1, tap, T, T, scale / (OPS * OPS), 1.f, nullptr, nullptr, 0,
+                     S, T, nullptr, (long long)T * dh * 2, st);
+    if (rc) return rc;
+    rc = api_check(idb::launch_attn_softmax(S, N * T, T, PS, p_hi, p_lo, st), "idb_attention_tc(softmax)");
+    if (rc) return rc;
+    // O[n][query][c] = sum_key P[n][query][key] V[n][key][c]: weights = the image's own V^T
+    const int Np = (dh + 127) / 128 * 128;
+    if (Np != dh) return api_fail("idb_attention_tc: dh must be a multiple of 128");
+    return conv2d_impl(p_hi, p_lo, 1, N, H, W, H, W, T, vt_hi, vt_lo, 1, tap, Np, dh, 1.f / (PS * OPS), 1.f, nullptr, nullptr, 0,
+                       out, ld_out, nullptr, (long long)T * dh * 2, st);
+}
+
+static int conv2d_impl(const void* a_hi, const void* a_lo, int planes, int N, int Ha, int Wa, int H, int W, int Cp,
+                       const void* w_hi, const void* w_lo, int n_taps, const int* taps_host, int Np, int Cout,
+                       float acc_scale, float out_scale, const float* bias, const float* residual, int ld_res, float* out,
+                       int ldo, float* stats, long long w_img_stride, void* stream) {
     if (!a_hi || !a_lo || !w_hi || !w_lo || !out || !taps_host) return api_fail("idb_conv2d: null pointer");
     if (planes <= 0 || N <= 0 || H <= 0 || W <= 0 || Cp <= 0 || Cp % 64) return api_fail("idb_conv2d: bad shape (Cp % 64)");
     if (Ha < H || Wa < W) return api_fail("idb_conv2d: operand planes must be at least as large as the output (Ha >= H, Wa >= W)");
@@ -193,6 +247,8 @@ int idb_conv2d_stats(const void* a_hi, const void* a_lo, int planes, int N, int 
     p.Np = Np; p.Cout = Cout; p.acc_scale = acc_scale; p.out_scale = out_scale;
     p.bias = bias; p.residual = residual; p.ld_res = ld_res; p.out = out; p.ldo = ldo;
     p.stats = stats;
+    p.w_img_stride = w_img_stride;
+    if (w_img_stride && p.BI != 1) return api_fail("idb_conv2d: per-image weights need one image per 128-pixel tile");
     if (stats && (idb_conv_stats_slots(H, W) == 0 || (reinterpret_cast<uintptr_t>(stats) & 15)))
         return api_fail("idb_conv2d_stats: statistics need >= 16 pixels of an image per tile and a 16-byte aligned buffer");
     return api_check(idb::launch_conv(p, idb::api_num_sms(), static_cast<cudaStream_t>(stream)), "idb_conv2d");

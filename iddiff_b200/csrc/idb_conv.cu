@@ -149,7 +149,7 @@ __global__ void __launch_bounds__(C_THREADS, 1) conv_fp16x3_kernel(const __grid_
                     const int cw = w0 + p.tap_dx[tap], ch = h0 + p.tap_dy[tap], cp = p.tap_plane[tap];
                     tma_tensor5d_g2s(st, &p.tm_hi, c0, cw, ch, i0, cp, &full[stage]);
                     tma_tensor5d_g2s(st + CA_TILE, &p.tm_lo, c0, cw, ch, i0, cp, &full[stage]);
-                    const size_t b_off = ((size_t)kb * p.Np + n0) * 128;
+                    const size_t b_off = ((size_t)kb * p.Np + n0) * 128 + (size_t)i0 * (size_t)p.w_img_stride;
                     tma_bulk_g2s(st + 2 * CA_TILE, p.w_hi + b_off, Cfg::B_TILE, &full[stage]);
                     tma_bulk_g2s(st + 2 * CA_TILE + Cfg::B_TILE, p.w_lo + b_off, Cfg::B_TILE, &full[stage]);
                     if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }

@@ -106,6 +106,8 @@ struct alignas(64) ConvParams {
     float* out;                // [N][H][W][ldo]
     int ldo;
     float* stats;              // optional [N][H*W / min(32, BW*BH)][Cout][2]: per-slot (sum, sum of squares) of `out`
+    long long w_img_stride;    // bytes between the weight slabs of consecutive images (0: one weight matrix for all) --
+                               // attention's Q K^T and P V are convolutions whose "weights" are per-image (BI == 1 only)
 };
 cudaError_t launch_conv(const ConvParams& p, int num_sms, cudaStream_t stream);
 
@@ -188,5 +190,12 @@ cudaError_t launch_grad_sumsq(const float* g, int ld, int N, int K, double* accu
 cudaError_t launch_adam(float* prm, int ldp, const float* g, int ldg, float* m, float* v, int N, int K, float lr_base,
                         int warmup, float beta1, float beta2, float eps, long long step_host, const long long* step_dev,
                         float max_norm, const double* normsq, cudaStream_t stream);
+
+// ---- attention on the tensor cores: operand packing + softmax around two per-image-weight convolutions (idb_unet.cu) ----
+cudaError_t launch_attn_pack(const float* qkv, int N, int T, int ld, int dh, int q0, int k0, int v0, float scale,
+                             uint8_t* q_hi, uint8_t* q_lo, uint8_t* k_hi, uint8_t* k_lo, uint8_t* vt_hi, uint8_t* vt_lo,
+                             cudaStream_t stream);
+cudaError_t launch_attn_softmax(const float* S, int rows, int T, float scale, uint8_t* p_hi, uint8_t* p_lo,
+                                cudaStream_t stream);
 
 }  // namespace idb

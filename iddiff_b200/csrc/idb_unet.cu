@@ -613,4 +613,109 @@ cudaError_t launch_attention(const AttnParams& p, cudaStream_t stream) {
     return cudaGetLastError();
 }
 
+// ---------------------------------- attention on the tensor cores ------------------------------
+// layers.py:577-587 / BeatGANsblocks.py:480-491 for one head of T >= 128 tokens: S = scale Q K^T and O = softmax(S) V are
+// run by conv_fp16x3_kernel as 1x1 convolutions whose weight matrix differs per image (ConvParams::w_img_stride): the
+// "pixels" are the queries, the "output channels" the keys (then the value channels).  These two kernels build the
+// operands: Q as the NHWC activation operand, K as a per-image weight slab [dh/64][T][128 B] (rows = keys), V^T as a
+// per-image weight slab [T/64][dh][128 B] (rows = value channels, contraction = keys), and the softmax that turns the
+// fp32 scores into the P operand.  All operands are fp16 hi/lo pairs of value * scale, like every other convolution.
+__global__ void __launch_bounds__(256) attn_pack_kernel(const float* __restrict__ qkv, int N, int T, int ld, int dh, int q0,
+                                                        int k0, int v0, float scale, uint8_t* __restrict__ q_hi,
+                                                        uint8_t* __restrict__ q_lo, uint8_t* __restrict__ k_hi,
+                                                        uint8_t* __restrict__ k_lo, uint8_t* __restrict__ vt_hi,
+                                                        uint8_t* __restrict__ vt_lo) {
+    const int chunks = dh >> 3;
+    const long long plain = (long long)N * T * chunks;          // phase 1: (n, t, 8 channels) -> Q operand and K slab
+    const long long trans = (long long)N * dh * (T >> 3);       // phase 2: (n, c, 8 tokens)   -> V^T slab
+    for (long long i = blockIdx.x * 256LL + threadIdx.x; i < plain + trans; i += (long long)gridDim.x * 256) {
+        float v[8];
+        uint32_t h[4], l[4];
+        if (i < plain) {
+            const int ch = (int)(i % chunks), t = (int)((i / chunks) % T), n = (int)(i / ((long long)chunks * T));
+            const float* row = qkv + ((size_t)n * T + t) * ld;
+            const int c0 = ch << 3;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = __ldg(row + q0 + c0 + j);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) split2_fp16(v[2 * j] * scale, v[2 * j + 1] * scale, h[j], l[j]);
+            const size_t qo = (((size_t)n * T + t) * dh + c0) * 2;
+            *reinterpret_cast<uint4*>(q_hi + qo) = make_uint4(h[0], h[1], h[2], h[3]);
+            *reinterpret_cast<uint4*>(q_lo + qo) = make_uint4(l[0], l[1], l[2], l[3]);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = __ldg(row + k0 + c0 + j);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) split2_fp16(v[2 * j] * scale, v[2 * j + 1] * scale, h[j], l[j]);
+            const size_t ko = (size_t)n * T * dh * 2 + slab_offset_bytes((size_t)T, (size_t)t, (size_t)c0);
+            *reinterpret_cast<uint4*>(k_hi + ko) = make_uint4(h[0], h[1], h[2], h[3]);
+            *reinterpret_cast<uint4*>(k_lo + ko) = make_uint4(l[0], l[1], l[2], l[3]);
+        } else {
+            const long long r = i - plain;
+            const int c = (int)(r % dh), t0 = (int)((r / dh) % (T >> 3)) << 3, n = (int)(r / ((long long)dh * (T >> 3)));
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = __ldg(qkv + ((size_t)n * T + t0 + j) * ld + v0 + c);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) split2_fp16(v[2 * j] * scale, v[2 * j + 1] * scale, h[j], l[j]);
+            const size_t vo = (size_t)n * T * dh * 2 + slab_offset_bytes((size_t)dh, (size_t)c, (size_t)t0);
+            *reinterpret_cast<uint4*>(vt_hi + vo) = make_uint4(h[0], h[1], h[2], h[3]);
+            *reinterpret_cast<uint4*>(vt_lo + vo) = make_uint4(l[0], l[1], l[2], l[3]);
+        }
+    }
+}
+
+cudaError_t launch_attn_pack(const float* qkv, int N, int T, int ld, int dh, int q0, int k0, int v0, float scale,
+                             uint8_t* q_hi, uint8_t* q_lo, uint8_t* k_hi, uint8_t* k_lo, uint8_t* vt_hi, uint8_t* vt_lo,
+                             cudaStream_t stream) {
+    const long long total = (long long)N * T * (dh >> 3) * 2;
+    if (total <= 0) return cudaSuccess;
+    long long blocks = (total + 255) / 256;
+    if (blocks > 148LL * 32) blocks = 148LL * 32;
+    attn_pack_kernel<<<(int)blocks, 256, 0, stream>>>(qkv, N, T, ld, dh, q0, k0, v0, scale, q_hi, q_lo, k_hi, k_lo, vt_hi, vt_lo);
+    return cudaGetLastError();
+}
+
+// F.softmax over the keys of one query row (layers.py:584), one warp per row, the reference's order of operations
+// (max, exp, sum, divide); writes the probabilities as the hi/lo operand [rows][T] of P * scale.
+__global__ void __launch_bounds__(256) attn_softmax_kernel(const float* __restrict__ S, long long rows, int T, float scale,
+                                                           uint8_t* __restrict__ p_hi, uint8_t* __restrict__ p_lo) {
+    const long long row = blockIdx.x * 8LL + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (row >= rows) return;
+    const float* s = S + row * T;
+    float m = -INFINITY;
+    for (int c = lane * 8; c < T; c += 256) {
+        const float4 a = __ldg(reinterpret_cast<const float4*>(s + c)), b = __ldg(reinterpret_cast<const float4*>(s + c) + 1);
+        m = fmaxf(m, fmaxf(fmaxf(fmaxf(a.x, a.y), fmaxf(a.z, a.w)), fmaxf(fmaxf(b.x, b.y), fmaxf(b.z, b.w))));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    float sum = 0.f;
+    for (int c = lane * 8; c < T; c += 256) {
+        const float4 a = __ldg(reinterpret_cast<const float4*>(s + c)), b = __ldg(reinterpret_cast<const float4*>(s + c) + 1);
+        sum += expf(a.x - m) + expf(a.y - m) + expf(a.z - m) + expf(a.w - m) + expf(b.x - m) + expf(b.y - m) + expf(b.z - m) +
+               expf(b.w - m);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    const float inv = 1.f / sum;
+    for (int c = lane * 8; c < T; c += 256) {
+        const float4 a = __ldg(reinterpret_cast<const float4*>(s + c)), b = __ldg(reinterpret_cast<const float4*>(s + c) + 1);
+        const float v[8] = {expf(a.x - m) * inv, expf(a.y - m) * inv, expf(a.z - m) * inv, expf(a.w - m) * inv,
+                            expf(b.x - m) * inv, expf(b.y - m) * inv, expf(b.z - m) * inv, expf(b.w - m) * inv};
+        uint32_t h[4], l[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) split2_fp16(v[2 * j] * scale, v[2 * j + 1] * scale, h[j], l[j]);
+        const size_t off = ((size_t)row * T + c) * 2;
+        *reinterpret_cast<uint4*>(p_hi + off) = make_uint4(h[0], h[1], h[2], h[3]);
+        *reinterpret_cast<uint4*>(p_lo + off) = make_uint4(l[0], l[1], l[2], l[3]);
+    }
+}
+
+cudaError_t launch_attn_softmax(const float* S, int rows, int T, float scale, uint8_t* p_hi, uint8_t* p_lo,
+                                cudaStream_t stream) {
+    if (rows <= 0) return cudaSuccess;
+    attn_softmax_kernel<<<(rows + 7) / 8, 256, 0, stream>>>(S, rows, T, scale, p_hi, p_lo);
+    return cudaGetLastError();
+}
+
 }  // namespace idb

@@ -210,11 +210,21 @@ def conv(a: Operand, pc: PackedConv, *, bias: Optional[torch.Tensor] = None, res
     return out
 
 
+TC_ATTENTION = True   # one-head attention over >= 128 tokens on the tensor cores (False: the fp32 CUDA-core kernel)
+
+
 def attention(qkv: torch.Tensor, heads: int, dh: int, q0: int, k0: int, v0: int, head_stride: int,
               scale: float) -> torch.Tensor:
     """qkv [N,H,W,ld] fp32 -> [N,H,W,heads*dh] fp32."""
     n, h, w, ld = qkv.shape
     out = torch.empty(n, h, w, heads * dh, dtype=torch.float32, device=qkv.device)
+    t = h * w
+    if TC_ATTENTION and heads == 1 and t >= 128 and t % 128 == 0 and t <= 1024 and dh % 128 == 0:
+        ws = torch.empty(_lib.load().idb_attention_tc_workspace_bytes(n, t, dh) + 1024, dtype=torch.uint8, device=qkv.device)
+        base = (ws.data_ptr() + 1023) // 1024 * 1024
+        _lib.call("idb_attention_tc", _lib.ptr(qkv), n, h, w, ld, dh, q0, k0, v0, float(scale), base, _lib.ptr(out), dh,
+                  _lib.stream_ptr())
+        return out
     _lib.call("idb_attention", _lib.ptr(qkv), n, h * w, ld, heads, dh, q0, k0, v0, head_stride, float(scale),
               _lib.ptr(out), heads * dh, _lib.stream_ptr())
     return out

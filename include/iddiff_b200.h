@@ -281,6 +281,16 @@ int idb_groupnorm_from_conv_stats(const float* stats0, int C0, int slots0, const
 int idb_attention(const float* qkv, int N, int T, int ld, int heads, int dh, int q0, int k0, int v0, int head_stride,
                   float scale, float* out, int ld_out, void* stream);
 
+/* The same attention on the TENSOR CORES for one head of T = H*W >= 128 tokens (T % 128 == 0, dh % 128 == 0: the 16x16
+ * attention blocks of the 64x64 networks, 256 tokens x 256 channels): S = scale Q K^T and O = softmax(S) V run on
+ * conv_fp16x3_kernel (tcgen05, 3 MMAs per product) as 1x1 convolutions whose weight matrix is the image's own K (then
+ * V^T); Q / K / V^T are packed as fp16 hi/lo operands and the softmax (the reference's max / exp / sum / divide order)
+ * writes P as the second convolution's operand.  workspace: idb_attention_tc_workspace_bytes(N, T, dh), 1024-byte aligned.
+ * Other shapes (4x4 mid-block, multi-head reduced-width nets): idb_attention. */
+size_t idb_attention_tc_workspace_bytes(int N, int T, int dh);
+int idb_attention_tc(const float* qkv, int N, int H, int W, int ld, int dh, int q0, int k0, int v0, float scale,
+                     void* workspace, float* out, int ld_out, void* stream);
+
 /* Row-side centred Gram for one anchor when K < D (image shapes: K = 4096 perturbations, D = 12288 pixels):
  * colmean[D] (fp64) and G[K][K] = (scale (X - mean)) (scale (X - mean))^T in fp64; its eigenvalues are the squared
  * singular values of the centred K x D score matrix, the same ones the D-side Gram of idb_center_gram has

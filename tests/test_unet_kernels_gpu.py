@@ -213,3 +213,28 @@ def test_fir_folded_into_operand_preparation(kind, norm):
     else:
         old = f[None]
     np.testing.assert_allclose(got.cpu().numpy(), old.cpu().numpy(), rtol=2e-5, atol=2e-6)
+
+
+@pytest.mark.parametrize("n,hh,ww,c", [(3, 16, 16, 256), (2, 8, 16, 128), (5, 16, 16, 384)])
+def test_tensor_core_attention_vs_cuda_core_and_fp64(n, hh, ww, c):
+    """The 16x16 attention blocks of the 64x64 networks (layers.py:577-587: one head, 256 tokens x 256 channels) on the
+    tensor cores -- Q K^T and P V as per-image-weight 1x1 convolutions on conv_fp16x3_kernel -- against the fp32 CUDA-core
+    kernel and torch fp64."""
+    from iddiff_b200 import unet_ops as U
+    torch.manual_seed(8)
+    T = hh * ww
+    qkv = (torch.randn(n, T, 3 * c) * 1.5).reshape(n, hh, ww, 3 * c).cuda()
+    assert U.TC_ATTENTION
+    got = U.attention(qkv, 1, c, 0, c, 2 * c, c, float(c) ** -0.5)
+    U.TC_ATTENTION = False
+    try:
+        old = U.attention(qkv, 1, c, 0, c, 2 * c, c, float(c) ** -0.5)
+    finally:
+        U.TC_ATTENTION = True
+    q, k, v = (qkv.reshape(n, T, 3 * c)[..., i * c:(i + 1) * c].double().cpu() for i in range(3))
+    ref = torch.softmax(q @ k.transpose(-1, -2) * float(c) ** -0.5, -1) @ v
+    sc = float(ref.abs().max())
+    e_tc, e_cc = float((got.reshape(n, T, c).double().cpu() - ref).abs().max()), float((old.reshape(n, T, c).double().cpu() - ref).abs().max())
+    print(f"T={T} C={c}: tensor-core error {e_tc / sc:.2e}, CUDA-core error {e_cc / sc:.2e} of the output scale")
+    # the scores carry the 22-bit operand rounding times |S| ~ 10 into the softmax exponent: ~4e-6 of the output scale
+    assert e_tc < 1e-5 * sc and e_cc < 3e-6 * sc
