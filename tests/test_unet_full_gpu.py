@@ -91,3 +91,54 @@ def test_full_size_path_k256_vs_reference(which):
 def test_release_engines():
     _CACHE.clear()
     torch.cuda.empty_cache()
+
+
+def test_config5_true_size_whole_path_vs_the_reference_driver():
+    """BASELINE config 5 at its TRUE size through the reference's own driver: golden = the REAL
+    dim_reduction.get_manifold_dimension (oracle/gen_golden_c5_full.py; full-size BeatGANs, loader batch 128 -> the
+    reference's K schedule gives K = 16768, a 16768 x 12288 score matrix, LAPACK full SVD, ~40 min on 8 cores).  Here:
+    the drop-in path on the reference's own noise -- perturb, 16768 forwards, D-side fp64 Gram, the n = 12288 whole-GPU
+    eigen-solver (two column classes), read-out.  All 12288 singular values rtol 1e-3 (+ 1e-6 s_0: no fp64 oracle of this
+    size exists to measure the reference's own floor), integer ID exact."""
+    import os
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "c5_beatgans_k16768.npz")
+    if not os.path.exists(path):
+        pytest.skip("tests/golden/c5_beatgans_k16768.npz not generated")
+    from iddiff_b200 import unet_models
+    from iddiff_b200.unet_engine import UNetEngine
+    _CACHE.clear()
+    torch.cuda.empty_cache()
+    g = np.load(path)
+    name, spec, _ = SY.FULL_MODELS["beatgans"]
+    holder = unet_models.get_model(name)(SY.unet_config(spec, name))
+    state = SY.make_unet_state(holder, int(g["seed"]))
+    wsum = sum(v.double().abs().sum().item() for v in state.values())
+    assert abs(wsum - float(g["w_checksum"])) <= 1e-9 * float(g["w_checksum"])
+    holder.load_state_dict(state, strict=True)
+    eng = UNetEngine.from_module(holder, "cuda:0")
+    eng.image_shape = (3, 64, 64)
+    K, B, draws = int(g["K"]), int(g["B"]), int(g["draws"])
+    assert K == 16768 and draws == 132
+    x0 = torch.from_numpy(g["x0"])
+    torch.manual_seed(int(g["seed"]) + 3)
+    proto = torch.empty(B, *x0.shape)
+    z = torch.empty(K, x0.numel())
+    for i in range(draws):                       # the last batch is drawn and discarded by the reference (SURVEY A.2)
+        zi = torch.randn_like(proto)
+        if (i + 1) * B <= K:
+            z[i * B:(i + 1) * B] = zi.reshape(B, -1)
+    from iddiff_b200 import sde_lib
+    sde = sde_lib.VESDE(sigma_min=float(g["sigma_min"]), sigma_max=float(g["sigma_max"]), N=1000)
+    mc, std = sde.coefficients(1e-5)
+    label = float((torch.ones(1) * 1e-5 * 999)[0])
+    res = eng.estimate(x0.reshape(1, -1).cuda(), K, mc, std, label, z=z.reshape(1, K, -1).cuda())
+    torch.cuda.synchronize()
+    sv = res.singular_values[0].cpu().numpy().astype(np.float64)
+    want = g["singular_values"].astype(np.float64)
+    rel = np.abs(sv / want - 1)
+    print(f"config 5 true size: n = {sv.size}, max relative difference {rel.max():.3e} (median {np.median(rel):.2e}), "
+          f"s0 {want[0]:.2f} s_last {want[-1]:.4f}, ID {res.dims.cpu().tolist()} vs {g['dims'].tolist()}")
+    assert np.all(np.abs(sv - want) <= 1e-3 * want + 1e-6 * want[0])
+    assert res.dims.cpu().tolist() == g["dims"].tolist()
+    del eng
+    torch.cuda.empty_cache()
