@@ -31,10 +31,15 @@ constexpr int C_EPI_THREADS = C_EPI_WARPS * 32;
 constexpr int C_THREADS = 64 + C_EPI_THREADS;
 constexpr int C_SEG = 8;   // k-blocks (512 product terms, 96 tcgen05.mma) accumulated in TMEM before a flush to registers
 
-template <int BN> struct ConvCfg {
+// BN output channels x (MT x 128) output pixels per CTA tile.  MT = 2 ("two M-subtiles share one weight tile") is the
+// shape for Cout = 128 layers: a 128 x 128 tile moves 64 KB per k-block for 12 MMAs of N = 128 (85 B per tensor-pipe cycle,
+// more than the L2 feeds: ncu 68 % pipe activity), a 256 x 128 tile moves 96 KB for 24 (62 B per cycle, like 128 x 256).
+template <int BN, int MT> struct ConvCfg {
     static constexpr uint32_t B_TILE = BN * 128;
-    static constexpr uint32_t STAGE = 2 * CA_TILE + 2 * B_TILE;
-    static constexpr int STAGES = BN == 256 ? 2 : 3;
+    static constexpr uint32_t A_BYTES = MT * 2 * CA_TILE;
+    static constexpr uint32_t STAGE = A_BYTES + 2 * B_TILE;
+    static constexpr int STAGES = STAGE >= 96 * 1024 ? 2 : 3;
+    static constexpr int TCOLS = MT * BN;                      // fp32 accumulator columns of one TMEM buffer
     static constexpr size_t SMEM = 1024 + (size_t)STAGES * STAGE + 256;
 };
 
@@ -92,9 +97,9 @@ __device__ __forceinline__ void stat_butterfly(float (&a)[32], int lane, bool ha
     }
 }
 
-template <int BN>
+template <int BN, int MT>
 __global__ void __launch_bounds__(C_THREADS, 1) conv_fp16x3_kernel(const __grid_constant__ ConvParams p) {
-    using Cfg = ConvCfg<BN>;
+    using Cfg = ConvCfg<BN, MT>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)Cfg::STAGES * Cfg::STAGE);
@@ -110,7 +115,7 @@ __global__ void __launch_bounds__(C_THREADS, 1) conv_fp16x3_kernel(const __grid_
     const int tiles_img = (p.N + p.BI - 1) / p.BI;
     const int m_tiles = tiles_w * tiles_h * tiles_img;
     const int n_tiles_n = p.Np / BN;
-    const int n_tiles = m_tiles * n_tiles_n;
+    const int n_tiles = ((m_tiles + MT - 1) / MT) * n_tiles_n;   // a CTA tile = MT consecutive 128-pixel tiles x BN channels
     const int kc = p.Cp / CBK;          // 64-channel chunks per tap
     const int n_kb = p.n_taps * kc;
 
@@ -125,7 +130,7 @@ __global__ void __launch_bounds__(C_THREADS, 1) conv_fp16x3_kernel(const __grid_
         }
         fence_barrier_init();
     }
-    if (warp == 1) tmem_alloc(tmem_slot, 2 * BN);
+    if (warp == 1) tmem_alloc(tmem_slot, 2 * Cfg::TCOLS);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -136,22 +141,29 @@ __global__ void __launch_bounds__(C_THREADS, 1) conv_fp16x3_kernel(const __grid_
             int stage = 0;
             uint32_t phase = 0;
             for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-                const int mt = t / n_tiles_n;
+                const int mt0 = (t / n_tiles_n) * MT;
                 const size_t n0 = (size_t)(t % n_tiles_n) * BN;
-                const int w0 = (mt % tiles_w) * p.BW;
-                const int h0 = ((mt / tiles_w) % tiles_h) * p.BH;
-                const int i0 = (mt / (tiles_w * tiles_h)) * p.BI;
                 for (int kb = 0; kb < n_kb; ++kb) {
                     const int tap = kb / kc, c0 = (kb % kc) * CBK;
                     mbar_wait(&empty[stage], phase ^ 1);
                     uint8_t* st = smem + (size_t)stage * Cfg::STAGE;
                     mbar_arrive_expect_tx(&full[stage], Cfg::STAGE);
-                    const int cw = w0 + p.tap_dx[tap], ch = h0 + p.tap_dy[tap], cp = p.tap_plane[tap];
-                    tma_tensor5d_g2s(st, &p.tm_hi, c0, cw, ch, i0, cp, &full[stage]);
-                    tma_tensor5d_g2s(st + CA_TILE, &p.tm_lo, c0, cw, ch, i0, cp, &full[stage]);
-                    const size_t b_off = ((size_t)kb * p.Np + n0) * 128 + (size_t)i0 * (size_t)p.w_img_stride;
-                    tma_bulk_g2s(st + 2 * CA_TILE, p.w_hi + b_off, Cfg::B_TILE, &full[stage]);
-                    tma_bulk_g2s(st + 2 * CA_TILE + Cfg::B_TILE, p.w_lo + b_off, Cfg::B_TILE, &full[stage]);
+                    int i_first = 0;
+#pragma unroll
+                    for (int sub = 0; sub < MT; ++sub) {
+                        // a sub-tile past the last one (odd tile count) reads image indices >= N: TMA fills zeros
+                        const int mt = mt0 + sub;
+                        const int w0 = (mt % tiles_w) * p.BW;
+                        const int h0 = ((mt / tiles_w) % tiles_h) * p.BH;
+                        const int i0 = (mt / (tiles_w * tiles_h)) * p.BI;
+                        if (sub == 0) i_first = i0;
+                        const int cw = w0 + p.tap_dx[tap], ch = h0 + p.tap_dy[tap], cp = p.tap_plane[tap];
+                        tma_tensor5d_g2s(st + sub * 2 * CA_TILE, &p.tm_hi, c0, cw, ch, i0, cp, &full[stage]);
+                        tma_tensor5d_g2s(st + sub * 2 * CA_TILE + CA_TILE, &p.tm_lo, c0, cw, ch, i0, cp, &full[stage]);
+                    }
+                    const size_t b_off = ((size_t)kb * p.Np + n0) * 128 + (size_t)i_first * (size_t)p.w_img_stride;
+                    tma_bulk_g2s(st + Cfg::A_BYTES, p.w_hi + b_off, Cfg::B_TILE, &full[stage]);
+                    tma_bulk_g2s(st + Cfg::A_BYTES + Cfg::B_TILE, p.w_lo + b_off, Cfg::B_TILE, &full[stage]);
                     if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
                 }
             }
@@ -168,22 +180,25 @@ __global__ void __launch_bounds__(C_THREADS, 1) conv_fp16x3_kernel(const __grid_
                     const uint32_t aphase = (it >> 1) & 1;
                     mbar_wait(&tempty[as], aphase ^ 1);
                     tc_fence_after();
-                    const uint32_t d_tmem = tmem_base + as * BN;
+                    const uint32_t d_tmem = tmem_base + as * Cfg::TCOLS;
                     const int kb1 = kb0 + C_SEG < n_kb ? kb0 + C_SEG : n_kb;
                     for (int kb = kb0; kb < kb1; ++kb) {
                         mbar_wait(&full[stage], phase);
                         tc_fence_after();
                         const uint32_t sa = smem_u32(smem + (size_t)stage * Cfg::STAGE);
-                        const uint64_t ah = umma_desc_sw128(sa);
-                        const uint64_t al = umma_desc_sw128(sa + CA_TILE);
-                        const uint64_t bh = umma_desc_sw128(sa + 2 * CA_TILE);
-                        const uint64_t bl = umma_desc_sw128(sa + 2 * CA_TILE + Cfg::B_TILE);
+                        const uint64_t bh = umma_desc_sw128(sa + Cfg::A_BYTES);
+                        const uint64_t bl = umma_desc_sw128(sa + Cfg::A_BYTES + Cfg::B_TILE);
 #pragma unroll
-                        for (int k = 0; k < CBK / 16; ++k) {
-                            const uint64_t adv = (uint64_t)((k * 32) >> 4);
-                            umma_bf16(d_tmem, al + adv, bh + adv, idesc, ((kb - kb0) | k) != 0);
-                            umma_bf16(d_tmem, ah + adv, bl + adv, idesc, 1);
-                            umma_bf16(d_tmem, ah + adv, bh + adv, idesc, 1);
+                        for (int sub = 0; sub < MT; ++sub) {     // the sub-tiles share the weight tile of this k-block
+                            const uint64_t ah = umma_desc_sw128(sa + sub * 2 * CA_TILE);
+                            const uint64_t al = umma_desc_sw128(sa + sub * 2 * CA_TILE + CA_TILE);
+#pragma unroll
+                            for (int k = 0; k < CBK / 16; ++k) {
+                                const uint64_t adv = (uint64_t)((k * 32) >> 4);
+                                umma_bf16(d_tmem + sub * BN, al + adv, bh + adv, idesc, ((kb - kb0) | k) != 0);
+                                umma_bf16(d_tmem + sub * BN, ah + adv, bl + adv, idesc, 1);
+                                umma_bf16(d_tmem + sub * BN, ah + adv, bh + adv, idesc, 1);
+                            }
                         }
                         umma_commit(&empty[stage]);
                         if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
@@ -193,27 +208,20 @@ __global__ void __launch_bounds__(C_THREADS, 1) conv_fp16x3_kernel(const __grid_
             }
         }
     } else {
-        constexpr int NCH = BN / 128;   // 32-column chunks of the tile this warp owns: cc = cgroup + 4 * ci
+        // the 32-column chunks of the CTA tile this warp owns: MT = 1: columns cc = cgroup + 4 ci of the one sub-tile;
+        // MT = 2 (BN = 128): column chunk cgroup of sub-tile ci
+        constexpr int NCH = MT * BN / 128;
         const int quarter = warp & 3;
         const int cgroup = (warp - 2) >> 2;
-        const int r = quarter * 32 + lane;  // row of the tile = TMEM lane = output pixel
+        const int r = quarter * 32 + lane;  // row of a sub-tile = TMEM lane = output pixel
         const bool ptrs32 = ((reinterpret_cast<uintptr_t>(p.out) | reinterpret_cast<uintptr_t>(p.residual)) & 31) == 0;
         const int stat_pimg = p.BW * p.BH;                      // pixels of one image inside a tile
         const int stat_ppw = stat_pimg < 32 ? stat_pimg : 32;   // pixels per warp that belong to one image (32 or 16)
         const int stat_slots = (p.H * p.W) / stat_ppw;
         int it = 0;
         for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-            const int mt = t / n_tiles_n;
+            const int mt0 = (t / n_tiles_n) * MT;
             const int n0 = (t % n_tiles_n) * BN;
-            const int w = (mt % tiles_w) * p.BW + r % p.BW;
-            const int h = ((mt / tiles_w) % tiles_h) * p.BH + (r / p.BW) % p.BH;
-            const int img = (mt / (tiles_w * tiles_h)) * p.BI + r / (p.BW * p.BH);
-            const bool row_ok = img < p.N;
-            const size_t pix = ((size_t)img * p.H + h) * p.W + w;
-            // statistics slot of this warp's 32 pixels inside their image (see the stats block below)
-            const int img_warp = (mt / (tiles_w * tiles_h)) * p.BI + (quarter * 32) / stat_pimg;
-            const bool row_ok_warp = img_warp < p.N;
-            const int stat_slot = (p.BI == 1 ? (mt % (tiles_w * tiles_h)) * 4 + quarter : ((quarter * 32) % stat_pimg) / 32);
             // The tensor core adds into its fp32 accumulator with truncation, and the error of a long chain grows
             // linearly with its length (measured: 3.6e-7 / 1.4e-6 / 6.0e-6 rms of the output scale at 576 / 2304 / 9216
             // terms against 3e-7 for an fp32 FMA chain).  So a TMEM accumulator only ever holds C_SEG k-blocks; the
@@ -225,11 +233,11 @@ __global__ void __launch_bounds__(C_THREADS, 1) conv_fp16x3_kernel(const __grid_
                 const uint32_t aphase = (it >> 1) & 1;
                 mbar_wait(&tfull[as], aphase);
                 tc_fence_after();
-                const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * BN;
+                const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * Cfg::TCOLS;
 #pragma unroll
                 for (int ci = 0; ci < NCH; ++ci) {
-                    const int cc = cgroup + 4 * ci;
-                    if (n0 + cc * 32 >= p.Cout) continue;  // warp-uniform: padded output channels
+                    const int cc = MT == 2 ? cgroup + (BN / 32) * ci : cgroup + 4 * ci;   // column chunk inside the TMEM buffer
+                    if (n0 + (MT == 2 ? cgroup : cc) * 32 >= p.Cout) continue;  // warp-uniform: padded output channels
                     if (kb0 == 0) {
                         tmem_ld32(t_row + cc * 32, acc[ci]);
                         tmem_ld_wait();
@@ -250,10 +258,20 @@ __global__ void __launch_bounds__(C_THREADS, 1) conv_fp16x3_kernel(const __grid_
             }
 #pragma unroll
             for (int ci = 0; ci < NCH; ++ci) {
-                const int cc = cgroup + 4 * ci;
-                const int c0 = n0 + cc * 32;
+                const int c0 = n0 + (MT == 2 ? cgroup : cgroup + 4 * ci) * 32;
                 if (c0 >= p.Cout) continue;  // warp-uniform: padded output channels
                 uint32_t (&v)[32] = acc[ci];
+                // output pixel of this thread in sub-tile mt (MT = 2: sub-tile ci; one past the end holds images >= N)
+                const int mt = mt0 + (MT == 2 ? ci : 0);
+                const int w = (mt % tiles_w) * p.BW + r % p.BW;
+                const int h = ((mt / tiles_w) % tiles_h) * p.BH + (r / p.BW) % p.BH;
+                const int img = (mt / (tiles_w * tiles_h)) * p.BI + r / (p.BW * p.BH);
+                const bool row_ok = img < p.N;
+                const size_t pix = ((size_t)img * p.H + h) * p.W + w;
+                // statistics slot of this warp's 32 pixels inside their image (see the stats block below)
+                const int img_warp = (mt / (tiles_w * tiles_h)) * p.BI + (quarter * 32) / stat_pimg;
+                const bool row_ok_warp = img_warp < p.N;
+                const int stat_slot = (p.BI == 1 ? (mt % (tiles_w * tiles_h)) * 4 + quarter : ((quarter * 32) % stat_pimg) / 32);
                 if (row_ok) {
                     float* dst = p.out + pix * p.ldo + c0;
                     const float* res = p.residual ? p.residual + pix * p.ld_res + c0 : nullptr;
@@ -357,26 +375,30 @@ __global__ void __launch_bounds__(C_THREADS, 1) conv_fp16x3_kernel(const __grid_
 
     tc_fence_before();
     __syncthreads();
-    if (warp == 1) tmem_dealloc(tmem_base, 2 * BN);
+    if (warp == 1) tmem_dealloc(tmem_base, 2 * Cfg::TCOLS);
 }
 
-template <int BN>
+template <int BN, int MT>
 static cudaError_t launch_conv_bn(const ConvParams& p, int num_sms, cudaStream_t stream) {
-    using Cfg = ConvCfg<BN>;
+    using Cfg = ConvCfg<BN, MT>;
     const int m_tiles = (p.W / p.BW) * (p.H / p.BH) * ((p.N + p.BI - 1) / p.BI);
-    const int n_tiles = m_tiles * (p.Np / BN);
+    const int n_tiles = ((m_tiles + MT - 1) / MT) * (p.Np / BN);
     const int grid = n_tiles < num_sms ? n_tiles : num_sms;
     if (grid <= 0) return cudaSuccess;
     cudaError_t e =
-        cudaFuncSetAttribute(conv_fp16x3_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM);
+        cudaFuncSetAttribute(conv_fp16x3_kernel<BN, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM);
     if (e != cudaSuccess) return e;
-    conv_fp16x3_kernel<BN><<<grid, C_THREADS, Cfg::SMEM, stream>>>(p);
+    conv_fp16x3_kernel<BN, MT><<<grid, C_THREADS, Cfg::SMEM, stream>>>(p);
     return cudaGetLastError();
 }
 
 cudaError_t launch_conv(const ConvParams& p, int num_sms, cudaStream_t stream) {
-    if (p.Np % 256 == 0) return launch_conv_bn<256>(p, num_sms, stream);
-    return launch_conv_bn<128>(p, num_sms, stream);
+    if (p.Np % 256 == 0) return launch_conv_bn<256, 1>(p, num_sms, stream);
+    // Cout = 128 (384) layers: pair two pixel tiles on one weight tile when there are enough tiles to keep every SM busy
+    // (and the weights are shared by all images)
+    const int m_tiles = (p.W / p.BW) * (p.H / p.BH) * ((p.N + p.BI - 1) / p.BI);
+    if (p.w_img_stride == 0 && (long long)(m_tiles / 2) * (p.Np / 128) >= 2LL * num_sms) return launch_conv_bn<128, 2>(p, num_sms, stream);
+    return launch_conv_bn<128, 1>(p, num_sms, stream);
 }
 
 }  // namespace idb

@@ -238,3 +238,33 @@ def test_tensor_core_attention_vs_cuda_core_and_fp64(n, hh, ww, c):
     print(f"T={T} C={c}: tensor-core error {e_tc / sc:.2e}, CUDA-core error {e_cc / sc:.2e} of the output scale")
     # the scores carry the 22-bit operand rounding times |S| ~ 10 into the softmax exponent: ~4e-6 of the output scale
     assert e_tc < 1e-5 * sc and e_cc < 3e-6 * sc
+
+
+@pytest.mark.parametrize("n,cin,cout,h,w", [(20, 64, 128, 64, 64),      # 640 pixel tiles -> paired (256 x 128 CTA tiles)
+                                            (1185, 64, 128, 8, 8),      # odd tile count (593): the last CTA tile has a phantom half
+                                            (200, 128, 384, 16, 16)])   # Np = 384: three channel tiles per pixel-tile pair
+def test_paired_pixel_tiles_share_one_weight_tile(n, cin, cout, h, w):
+    """conv_fp16x3_kernel<128, 2>: the Cout = 128 / 384 layers run two 128-pixel sub-tiles per CTA on one weight tile.
+    Against torch fp64, with bias + residual + GroupNorm statistics, bit-identical to the unpaired kernel (forced by a
+    batch small enough to fall under the pairing threshold)."""
+    from iddiff_b200 import unet_ops as U
+    torch.manual_seed(n + cout)
+    x = torch.randn(n, cin, h, w)
+    wt = torch.randn(cout, cin, 3, 3) / np.sqrt(9 * cin)
+    bias = torch.randn(cout)
+    res = nhwc(torch.randn(n, cout, h, w)).cuda()
+    pc = U.pack_conv(wt.cuda(), bias.cuda())
+    a = U.prep(nhwc(x).cuda())
+    y = U.conv(a, pc, residual=res, out_scale=0.5, want_stats=True)
+    ref = 0.5 * (F.conv2d(x.double(), wt.double(), bias.double(), padding=1) + res.cpu().double().permute(0, 3, 1, 2))
+    assert rel_err(y.permute(0, 3, 1, 2), ref) < 1e-5
+    # the same images in small batches take the unpaired kernel: identical bits
+    step = max(1, n // 16)
+    for s in range(0, n, step):
+        e = min(n, s + step)
+        part = U.conv(U.prep(nhwc(x[s:e]).cuda()), pc, residual=res[s:e].contiguous(), out_scale=0.5, want_stats=True)
+        assert torch.equal(part, y[s:e])
+        assert torch.equal(part._idb_stats, y._idb_stats[s:e])
+    mr = U.gn_stats(y, None, 32, 1e-6)
+    yd = y.double().permute(0, 3, 1, 2).reshape(n, 32, -1).cpu()
+    np.testing.assert_allclose(mr[..., 0].cpu().numpy(), yd.mean(-1).numpy(), rtol=2e-6, atol=2e-6)
