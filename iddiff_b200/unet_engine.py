@@ -209,7 +209,13 @@ class UNetEngine:
                 _lib.call("idb_fused_bias_act", _lib.ptr(proj), _lib.ptr(blk.conv0.bias), None, 1, 0, 0.0, 1.0,
                           proj.numel(), 1, proj.numel(), _lib.ptr(eff), _lib.stream_ptr())
                 out[idx] = eff.reshape(-1)
-        self._label_cache[key] = out   # kept for the engine's lifetime: captured graphs reference these vectors
+        self._label_cache[key] = out   # captured graphs reference these vectors: an entry lives as long as a graph of its label
+        # a t-sweep visits many labels (12 per call of get_conditional_manifold_dimension): keep the cache bounded, never
+        # dropping a label a live graph was captured with
+        if len(self._label_cache) > self.LABEL_CACHE:
+            pinned = {k[1] for k in self._graphs}
+            for old in [k for k in self._label_cache if k not in pinned and k != key][:len(self._label_cache) - self.LABEL_CACHE]:
+                del self._label_cache[old]
         return out
 
     # ---- blocks --------------------------------------------------------------------------------
@@ -340,6 +346,7 @@ class UNetEngine:
     def bytes_per_anchor(self, K: int, D: int) -> int:
         return K * D * 4 * 2 + D * D * 8
 
+    LABEL_CACHE = 16    # per-label constant sets kept (time-embedding biases / GroupNorm affines), besides those graphs pin
     IMAGE_CHUNK = 1024  # images per forward: fills the 148 SMs at the 8x8 / 4x4 levels too (measured +7 % at 512 over 128, +2 % more at 1024)
     USE_GRAPH = True    # replay one captured CUDA graph per full chunk (494-594 launches per forward; measured +5 %)
 
