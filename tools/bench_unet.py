@@ -72,7 +72,7 @@ def main():
         sde = sde_lib.VESDE(sigma_min=0.009, sigma_max=50.0, N=1000)   # style_gan_base.py:100-101
         mc, std = sde.coefficients(1e-5)
         x0 = SY.smooth_images(args.anchors, C, S, 5).reshape(args.anchors, -1).cuda()
-        eng.estimate(x0[:1], min(args.K, 1024), mc, std, 0.00999, seed=0)   # warm-up (captures the forward graph)
+        eng.estimate(x0[:1], min(args.K, 2 * eng.IMAGE_CHUNK), mc, std, 0.00999, seed=0)   # warm-up (captures the forward graph)
         torch.cuda.synchronize()
         E.EVENT_LOG = {}
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

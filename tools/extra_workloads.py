@@ -117,7 +117,7 @@ def image_config(which, dev, peaks, K=4096, cpu_images=8, group=None, verify=Fal
         run = lambda seed, k: eng.estimate(x0, k, mc, std, label, seed=seed)
     else:
         run = lambda seed, k: eng.estimate_row_sharded(x0, k, mc, std, label, seed=seed, group=group)
-    run(0, min(K, 1024 if group is None else K))   # warm-up (captures the forward graph of a full image chunk)
+    run(0, min(K, 2 * eng.IMAGE_CHUNK if group is None else K))   # warm-up: two full image chunks, so the forward graph is captured here
     E.EVENT_LOG = {}
     r, ms = _timed(lambda: run(1, K))
     stages = {k: sum(a.elapsed_time(b) for a, b, _ in v) for k, v in E.EVENT_LOG.items()}
