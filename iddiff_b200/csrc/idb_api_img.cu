@@ -276,7 +276,7 @@ size_t idb_spectrum_large_workspace_bytes(int n) { return idb::spectrum_large_wo
 int idb_spectrum_large_variant(double* G, int n, int n_out, float* sv, void* workspace, int variant, void* stream) {
     if (!G || !sv || !workspace || n <= 0 || n_out <= 0 || n_out > n) return api_fail("idb_spectrum_large: bad argument");
     if (n > 14000) return api_fail("idb_spectrum_large: n <= 14000 (d and e^2 of the bisection in shared memory)");
-    if (variant < -1 || variant > 2) return api_fail("idb_spectrum_large_variant: variant in {-1, 0, 1, 2}");
+    if (variant < -1 || variant > 3) return api_fail("idb_spectrum_large_variant: variant in {-1, 0, 1, 2, 3}");
     return api_check(idb::launch_spectrum_large(G, n, n_out, sv, workspace, idb::api_num_sms(),
                                                 static_cast<cudaStream_t>(stream), variant),
                      "idb_spectrum_large");

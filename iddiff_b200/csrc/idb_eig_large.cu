@@ -242,6 +242,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tridiag_coop_kernel(double* __r
 // applied on the fly when its reflector is formed.  (v, w, u) must sit in shared memory for the sweep: three
 // n-vectors fit one SM up to n = TCF_MAX_N; above that
 constexpr int TCF_MAX_N = 9000;
+constexpr bool PANEL_DEFAULT = false;   // the automatic choice takes the panel kernel (variant 3) once it is measured faster
 // the 64-wide column chunks of the trailing block are dealt round-robin over C classes of CTAs, a CTA of class c keeps
 // only ITS chunks of (v, w, u) in shared memory (3 n / C doubles) and produces the partial products p_c[i]; the full
 // reflector of every step lives in a double-buffered global copy (ubuf, written by CTA 0, L2-resident) and w is
@@ -491,7 +492,14 @@ __global__ void __launch_bounds__(256) bisect_large_kernel(const double* __restr
 }
 
 // d[n], e[n], partial products [2][classes <= 2][n], reflectors [2][n]
-size_t spectrum_large_workspace_bytes(int n) { return (size_t)8 * n * sizeof(double) + 256; }
+size_t tridiag_panel_workspace_doubles(int n, int grid);
+cudaError_t launch_tridiag_panel(double* G, int n, double* d, double* e, double* ws, int num_sms, cudaStream_t stream);
+
+// d, e, then the larger of the fused kernels' 6 n doubles and the panel kernel's buffers (sized for up to 192 CTAs)
+size_t spectrum_large_workspace_bytes(int n) {
+    const size_t panel = tridiag_panel_workspace_doubles(n, 192), fused = (size_t)6 * n;
+    return ((size_t)2 * n + (panel > fused ? panel : fused)) * sizeof(double) + 256;
+}
 
 template <int C>
 static cudaError_t launch_tridiag_cls(double* G, int n, double* d, double* e, double* p, double* u, int num_sms,
@@ -516,8 +524,8 @@ static cudaError_t launch_tridiag_cls(double* G, int n, double* d, double* e, do
                                        dim3(TC_THREADS), args, tsmem, stream);
 }
 
-// classes: 0 = choose (1 up to TCF_MAX_N, 2 above), 1 = one-class fused kernel, 2 = two column classes,
-// -1 = the unfused two-pass kernel (kept as the cross-check of the fused ones)
+// classes: 0 = choose, 1 = one-class fused kernel, 2 = two column classes, 3 = panel kernel with deferred updates
+// (idb_eig_panel.cu; even n), -1 = the unfused two-pass kernel (kept as the cross-check of the others)
 cudaError_t launch_spectrum_large(double* G, int n, int n_out, float* sv, void* workspace, int num_sms,
                                   cudaStream_t stream, int classes) {
     if (n <= 0) return cudaSuccess;
@@ -525,9 +533,12 @@ cudaError_t launch_spectrum_large(double* G, int n, int n_out, float* sv, void* 
     double* e = d + n;
     double* p = e + n;
     double* u = p + (size_t)4 * n;
-    if (classes == 0) classes = n <= TCF_MAX_N ? 1 : 2;
+    if (classes == 0) classes = PANEL_DEFAULT && (n % 2 == 0) && n >= 2048 && num_sms <= 192 ? 3 : (n <= TCF_MAX_N ? 1 : 2);
     cudaError_t err;
-    if (classes == 2) {
+    if (classes == 3) {
+        err = launch_tridiag_panel(G, n, d, e, p, num_sms, stream);
+        if (err != cudaSuccess) return err;
+    } else if (classes == 2) {
         err = launch_tridiag_cls<2>(G, n, d, e, p, u, num_sms, stream);
         if (err != cudaSuccess) return err;
     } else if (classes == 1) {

@@ -305,7 +305,8 @@ size_t idb_spectrum_large_workspace_bytes(int n);
 int idb_spectrum_large(double* G, int n, int n_out, float* sv, void* workspace, void* stream);
 /* Same, with the tridiagonalisation kernel chosen by the caller (cross-checks and tuning): 0 = automatic (what
  * idb_spectrum_large runs), 1 = fused one-pass kernel (n <= 9000), 2 = fused kernel with two column classes
- * (n <= 14000; the automatic choice above 9000), -1 = unfused two-pass kernel. */
+ * (n <= 14000; the automatic choice above 9000), 3 = panel kernel with deferred rank-2 updates (even n; (8 + 8/NB) m^2
+ * bytes per column instead of 16), -1 = unfused two-pass kernel. */
 int idb_spectrum_large_variant(double* G, int n, int n_out, float* sv, void* workspace, int variant, void* stream);
 
 #ifdef __cplusplus

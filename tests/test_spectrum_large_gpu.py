@@ -73,7 +73,7 @@ def test_tridiagonalisation_variants_agree(n):
     ws = torch.empty(lib.idb_spectrum_large_workspace_bytes(n), dtype=torch.uint8, device="cuda")
     st = torch.cuda.current_stream().cuda_stream
     out = {}
-    for variant in (-1, 1, 2):
+    for variant in (-1, 1, 2) + ((3,) if n % 2 == 0 else ()):     # 3: the panel kernel with deferred updates (even n)
         A = G.clone()
         sv = torch.empty(n, dtype=torch.float32, device="cuda")
         _lib.call("idb_spectrum_large_variant", A.data_ptr(), n, n, sv.data_ptr(), ws.data_ptr(), variant, st)
@@ -82,6 +82,8 @@ def test_tridiagonalisation_variants_agree(n):
         np.testing.assert_allclose(out[variant], want, rtol=1e-5, atol=1e-7 * want[0])
     np.testing.assert_allclose(out[2], out[1], rtol=1e-6, atol=1e-8 * want[0])
     np.testing.assert_allclose(out[-1], out[1], rtol=1e-6, atol=1e-8 * want[0])
+    if 3 in out:
+        np.testing.assert_allclose(out[3], out[1], rtol=1e-6, atol=1e-8 * want[0])
 
 
 @pytest.mark.parametrize("n", [4096, 12288])
@@ -99,11 +101,19 @@ def test_spectrum_large_at_baseline_sizes(n):
     want = torch.linalg.eigvalsh(G).clamp_min(0).sqrt().flip(0).cpu().numpy()
     lib = _lib.load()
     ws = torch.empty(lib.idb_spectrum_large_workspace_bytes(n), dtype=torch.uint8, device="cuda")
-    sv = torch.empty(n, dtype=torch.float32, device="cuda")
-    _lib.call("idb_spectrum_large", G.data_ptr(), n, n, sv.data_ptr(), ws.data_ptr(), torch.cuda.current_stream().cuda_stream)
-    torch.cuda.synchronize()
-    got = sv.cpu().numpy().astype(np.float64)
-    assert np.all(np.diff(got) <= 0)
-    np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-7 * want[0])
+    st = torch.cuda.current_stream().cuda_stream
+    for variant in (0, 3, 2 if n > 9000 else 1):       # production choice, panel kernel, fused kernel
+        A = G.clone()
+        sv = torch.empty(n, dtype=torch.float32, device="cuda")
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        _lib.call("idb_spectrum_large_variant", A.data_ptr(), n, n, sv.data_ptr(), ws.data_ptr(), variant, st)
+        b.record()
+        torch.cuda.synchronize()
+        got = sv.cpu().numpy().astype(np.float64)
+        print(f"n = {n}, variant {variant}: {a.elapsed_time(b):.1f} ms, max rel err {np.abs(got / np.maximum(want, 1e-7 * want[0]) - 1).max():.2e}")
+        assert np.all(np.diff(got) <= 0)
+        np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-7 * want[0])
+        del A
     del G, ws
     torch.cuda.empty_cache()
