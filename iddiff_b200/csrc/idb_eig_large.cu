@@ -242,7 +242,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tridiag_coop_kernel(double* __r
 // applied on the fly when its reflector is formed.  (v, w, u) must sit in shared memory for the sweep: three
 // n-vectors fit one SM up to n = TCF_MAX_N; above that
 constexpr int TCF_MAX_N = 9000;
-constexpr bool PANEL_DEFAULT = false;   // the automatic choice takes the panel kernel (variant 3) once it is measured faster
+constexpr int PANEL_MIN_N = 6144;   // the automatic choice takes the panel kernel (variant 3) from here on: measured 286 ms vs 300
+                                    // at n = 6144, 536 vs 645 at 8192, 1.39 s vs 1.91 at 12288 (126 vs 107 ms at 4096: fused stays)
 // the 64-wide column chunks of the trailing block are dealt round-robin over C classes of CTAs, a CTA of class c keeps
 // only ITS chunks of (v, w, u) in shared memory (3 n / C doubles) and produces the partial products p_c[i]; the full
 // reflector of every step lives in a double-buffered global copy (ubuf, written by CTA 0, L2-resident) and w is
@@ -494,6 +495,7 @@ __global__ void __launch_bounds__(256) bisect_large_kernel(const double* __restr
 // d[n], e[n], partial products [2][classes <= 2][n], reflectors [2][n]
 size_t tridiag_panel_workspace_doubles(int n, int grid);
 cudaError_t launch_tridiag_panel(double* G, int n, double* d, double* e, double* ws, int num_sms, cudaStream_t stream);
+bool tridiag_panel_supported(int n, int num_sms);
 
 // d, e, then the larger of the fused kernels' 6 n doubles and the panel kernel's buffers (sized for up to 192 CTAs)
 size_t spectrum_large_workspace_bytes(int n) {
@@ -533,7 +535,7 @@ cudaError_t launch_spectrum_large(double* G, int n, int n_out, float* sv, void* 
     double* e = d + n;
     double* p = e + n;
     double* u = p + (size_t)4 * n;
-    if (classes == 0) classes = PANEL_DEFAULT && (n % 2 == 0) && n >= 2048 && num_sms <= 192 ? 3 : (n <= TCF_MAX_N ? 1 : 2);
+    if (classes == 0) classes = (n >= PANEL_MIN_N && tridiag_panel_supported(n, num_sms)) ? 3 : (n <= TCF_MAX_N ? 1 : 2);
     cudaError_t err;
     if (classes == 3) {
         err = launch_tridiag_panel(G, n, d, e, p, num_sms, stream);

@@ -8,15 +8,19 @@
 //     A_true u = A_stale u - sum_p (v_p (w_p.u) + w_p (v_p.u)),
 // and only every NB-th column's sweep applies all pending pairs and writes the block back: (8 + 8 / NB) m^2 bytes per column
 // instead of 16 -- 9 at NB = 8.  Replaces torch.linalg.svd at dim_reduction.py:197-198 for image-sized score matrices
-// (same role as tridiag_fused_cls_kernel; selected by launch_spectrum_large for even n >= 2048).
+// (same role as tridiag_fused_cls_kernel; selected by launch_spectrum_large for even n >= 8192).
 //
-// Work split per column k (cooperative launch, one CTA per SM, three grid synchronisations):
+// Work split per column k (cooperative launch, one CTA per SM, TWO grid synchronisations):
 //   phase A  every CTA owns a cyclic SLICE of the indices j > k: finalises the previous column's w there
-//            (w = tau (A_stale u - corrections) + kk u), forms its slice of row k of A_true and the partial norm;
-//   phase B  norm -> (tau, beta), reflector slice u -> global;
-//   sweep    rows are owned by fixed warps (row i -> warp i mod #warps); columns are walked in blocks of LB whose vectors
-//            (u, and on a flush all pending v_p, w_p) sit in shared memory, each loaded vector element serves all of the
-//            warp's rows; the sweep also accumulates the dot products the next phase A needs (pc.u, w_p.u, v_p.u).
+//            (w = tau (A_stale u - corrections) + kk u) and writes its slice of row k of A_true;        -> grid sync
+//   phase B  every CTA pulls the whole row into shared memory with one bulk copy, forms the norm, (tau, beta) and the
+//            reflector u redundantly (u lives in shared memory only: 8 n bytes);
+//   sweep    rows are owned by fixed warps (row i -> CTA i mod G, warp (i / G) mod 8).  Seven sweeps of eight only READ the
+//            stale block: every warp streams its rows through a private ring of 1-D bulk copies (cp.async.bulk + mbarrier
+//            transaction counts, 6 x 2 KB per warp = 96 KB in flight per SM with no register cost) and dots them with u.
+//            The eighth stages the pending pairs' column sides per block of LB columns, applies them to all of the warp's
+//            rows in registers and writes the block back.  Every sweep also accumulates the dot products the next phase A
+//            needs (pc.u, w_p.u, v_p.u).                                                                -> grid sync
 #include "idb_common.cuh"
 #include "idb_kernels.h"
 #include <cooperative_groups.h>
@@ -27,12 +31,16 @@ namespace cg = cooperative_groups;
 namespace idb {
 
 namespace {
-constexpr int TP_THREADS = 512;
+constexpr int TP_THREADS = 256;
 constexpr int TP_WARPS = TP_THREADS / 32;
 constexpr int TP_NB = 8;       // pending reflector pairs before a flush
-constexpr int TP_LB = 1024;    // columns per shared-memory block
-constexpr int TP_RMAX = 8;     // rows of the trailing block per warp (n <= TP_RMAX * gridDim.x * TP_WARPS)
+constexpr int TP_LB = 512;     // columns per shared-memory block of a flush sweep (the pairs' column sides)
+constexpr int TP_RMAX = 11;    // rows of the trailing block per warp (n <= TP_RMAX * gridDim.x * TP_WARPS = 13024 on 148 SMs)
+constexpr int TP_CH = 256;     // doubles per bulk copy of a read-only sweep (one ring stage = 2 KB of one row)
+constexpr int TP_S = 6;        // ring stages per warp: 8 warps x 6 x 2 KB = 96 KB in flight per SM
 constexpr int TP_NDOT = 2 * TP_NB + 1;
+constexpr int TP_DC = (TP_NDOT + TP_WARPS - 1) / TP_WARPS;   // dot-product columns per warp in phase A
+constexpr int TP_GL = 5;       // CTAs per lane there (grid <= 160)
 
 __device__ __forceinline__ double tp_warp_sum(double v) {
 #pragma unroll
@@ -49,255 +57,385 @@ __device__ __forceinline__ double tp_block_sum(double v, double* red) {
     for (int w = 0; w < TP_WARPS; ++w) t += red[w];
     return t;
 }
+constexpr size_t tp_smem_doubles(int n) {
+    return (size_t)((n + 63) & ~63) + (size_t)TP_WARPS * TP_S * TP_CH + (size_t)TP_WARPS * TP_RMAX * 2 * TP_NB;
+}
 }  // namespace
 
 size_t tridiag_panel_workspace_doubles(int n, int grid) {
-    return (size_t)(2 * TP_NB + 2) * n + (size_t)grid * (TP_NDOT + 1) + 64;
+    return (size_t)(2 * TP_NB + 2) * n + (size_t)grid * TP_NDOT + 64;
 }
+
+#ifdef TP_PROFILE   // phase timers of CTA 0 (tools/panel_profile.sh), written behind part_dot
+#define TP_TICK_START() long long tp_t = clock64()
+#define TP_TICK(i) do { long long tp_n = clock64(); tp_acc[i] += tp_n - tp_t; tp_t = tp_n; } while (0)
+#else
+#define TP_TICK_START() do {} while (0)
+#define TP_TICK(i) do {} while (0)
+#endif
 
 __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __restrict__ A, int n, double* __restrict__ d,
                                                                       double* __restrict__ e, double* __restrict__ ws) {
     cg::grid_group grid = cg::this_grid();
-    extern __shared__ __align__(16) double tp_smem[];
-    double* ub = tp_smem;                                   // [LB]
-    double* vb = ub + TP_LB;                                // [NB][LB]
-    double* wb = vb + TP_NB * TP_LB;                        // [NB][LB]
-    double* rowsc = wb + TP_NB * TP_LB;                     // [WARPS][RMAX][2 NB]: v_p[i], w_p[i] of the warp's rows
+    extern __shared__ __align__(128) double tp_smem[];
+    const int nu = (n + 63) & ~63;
+    double* us = tp_smem;                                   // [nu] the WHOLE reflector of the current column (0 for j <= k)
+    double* ring = us + nu;                                 // [WARPS][S][CH] bulk-copy ring of the read-only sweeps ...
+    double* vb = ring;                                      // ... aliased by [NB][LB] + [NB][LB] of the flush sweeps
+    double* wb = vb + TP_NB * TP_LB;
+    double* rowsc = ring + TP_WARPS * TP_S * TP_CH;         // [WARPS][RMAX][2 NB]: v_p[i], w_p[i] of the warp's rows
+    __shared__ __align__(8) uint64_t full[TP_WARPS * TP_S];
+    __shared__ __align__(8) uint64_t xbar;
     __shared__ double red[TP_WARPS];
     __shared__ double s_dot[TP_NDOT];                       // pc.u, (w_p.u)_p, (v_p.u)_p of the previous sweep
     __shared__ double s_vk[TP_NB + 1], s_wk[TP_NB + 1];     // v_p[k], w_p[k]
-    __shared__ double s_sc[4];
+    __shared__ double s_part[TP_WARPS * TP_NDOT];
 
     const int G = gridDim.x, b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int n_gw = G * TP_WARPS, gw = b * TP_WARPS + warp;
+    const int n_gw = G * TP_WARPS, gw = warp * G + b;       // rows cyclic over the CTAs first: a short tail still uses every SM
     double* Vbuf = ws;                                      // [NB][n]
     double* Wbuf = Vbuf + (size_t)TP_NB * n;                // [NB][n]
-    double* uc = Wbuf + (size_t)TP_NB * n;                  // [n] reflector of the current column
-    double* pc = uc + n;                                    // [n] A u of the current column (stale or true, unscaled)
-    double* part_ss = pc + n;                               // [G]
-    double* part_dot = part_ss + G;                         // [G][NDOT]
-    double* alpha_g = part_dot + (size_t)G * TP_NDOT;       // [1]
+    double* xbuf = Wbuf + (size_t)TP_NB * n;                // [n] row k of A_true, written in slices
+    double* pc = xbuf + n;                                  // [n] A u of the current column (stale or true, unscaled)
+    double* part_dot = pc + n;                              // [NDOT][G]
+
+    for (int q = tid; q < nu; q += TP_THREADS) us[q] = 0.0;
+    if (tid == 0) {
+        for (int q = 0; q < TP_WARPS * TP_S; ++q) mbar_init(&full[q], 1);
+        mbar_init(&xbar, 1);
+        fence_barrier_init();
+    }
+    fence_proxy_async();
+    __syncthreads();
+    double* ring_w = ring + (size_t)warp * TP_S * TP_CH;
+    uint64_t* full_w = full + warp * TP_S;
+    int stage = 0;             // the warp's ring position and phase bit run on across sweeps (strict round-robin)
+    uint32_t phase = 0, xphase = 0;
 
     // replicated scalar state (identical in every CTA)
     int r = 0;                 // pending pairs whose w is final (slots 0 .. r-1)
-    bool have_prev = false;    // the previous column produced a reflector whose w still has to be finalised in slot r
+    bool have_prev = false;    // the previous column produced a reflector (still in `us`) whose w goes to slot r now
     bool prev_flushed = false; // ... and its sweep applied the pending pairs (its A u is already the true one)
-    int r_prev = 0;            // pending pairs that were outstanding during the previous sweep
     double tau_prev = 0.0;
 
+#ifdef TP_PROFILE
+    long long tp_acc[7] = {0, 0, 0, 0, 0, 0, 0};
+#endif
     for (int k = 0; k + 1 < n; ++k) {
+        TP_TICK_START();
         const bool last = (k + 2 >= n);                     // k = n - 2: only finalise + read the last 2 x 2 block
-        // ---------------- phase A ----------------
-        // (a) scalars of the previous column from the sweep's partial dot products
-        double kk = 0.0;
-        if (have_prev) {
-            for (int c = warp; c < TP_NDOT; c += TP_WARPS) {
-                double t = 0.0;
-                for (int q = lane; q < G; q += 32) t += part_dot[(size_t)q * TP_NDOT + c];
-                t = tp_warp_sum(t);
-                if (lane == 0) s_dot[c] = t;
+        // ---------------- phase A: this CTA's slice of the indices j > k ----------------
+        const int j = k + 1 + tid * G + b;
+        const bool mine = j < n;
+        // every global load of the phase is issued up front: ONE L2 round trip.  (The pairs outstanding during the previous
+        // sweep are exactly the r final ones unless that sweep flushed them, so w_new and x share the same loads.)
+        double pd[TP_DC][TP_GL];                             // the CTAs' partial dot products of the previous sweep
+#pragma unroll
+        for (int ci = 0; ci < TP_DC; ++ci)
+#pragma unroll
+            for (int i = 0; i < TP_GL; ++i) {
+                const int c = warp + TP_WARPS * ci, q = lane + 32 * i;
+                pd[ci][i] = (have_prev && c < TP_NDOT && q < G) ? part_dot[(size_t)c * G + q] : 0.0;
             }
-            __syncthreads();
-            double corr = 0.0;
-            if (!prev_flushed)
-                for (int p = 0; p < r_prev; ++p) corr += s_dot[1 + p] * s_dot[1 + TP_NB + p];
-            const double pv = tau_prev * (s_dot[0] - 2.0 * corr);
-            kk = -0.5 * tau_prev * pv;
+        double akj = 0.0, pcj = 0.0, upj = 0.0, pck = 0.0, vj[TP_NB], wj[TP_NB];
+#pragma unroll
+        for (int p = 0; p < TP_NB; ++p) { vj[p] = 0.0; wj[p] = 0.0; }
+        if (mine) {
+            akj = A[(size_t)k * n + j];
+            if (have_prev) { pcj = pc[j]; upj = us[j]; }
+#pragma unroll
+            for (int p = 0; p < TP_NB; ++p)
+                if (p < r) { vj[p] = Vbuf[(size_t)p * n + j]; wj[p] = Wbuf[(size_t)p * n + j]; }
         }
-        const int slot = r;                                 // where the previous column's pair goes
-        // w_new[j] of the previous column (only meaningful when have_prev)
-        auto w_new_at = [&](int j) {
-            double base = pc[j];
-            if (!prev_flushed)
-                for (int p = 0; p < r_prev; ++p)
-                    base -= Vbuf[(size_t)p * n + j] * s_dot[1 + p] + Wbuf[(size_t)p * n + j] * s_dot[1 + TP_NB + p];
-            return fma(kk, uc[j], tau_prev * base);
-        };
-        // (b) v_p[k], w_p[k] of every pending pair (the newest: v[k] = u_prev[k] = 1, w[k] computed here)
-        if (tid <= r) {
-            if (tid < r) { s_vk[tid] = Vbuf[(size_t)tid * n + k]; s_wk[tid] = Wbuf[(size_t)tid * n + k]; }
-            else if (have_prev) { s_vk[tid] = uc[k]; s_wk[tid] = w_new_at(k); }
+        if (have_prev) pck = pc[k];
+        if (tid < r) { s_vk[tid] = Vbuf[(size_t)tid * n + k]; s_wk[tid] = Wbuf[(size_t)tid * n + k]; }
+        if (have_prev) {
+#pragma unroll
+            for (int ci = 0; ci < TP_DC; ++ci) {
+                double t = 0.0;
+#pragma unroll
+                for (int i = 0; i < TP_GL; ++i) t += pd[ci][i];
+                t = tp_warp_sum(t);
+                if (lane == 0 && warp + TP_WARPS * ci < TP_NDOT) s_dot[warp + TP_WARPS * ci] = t;
+            }
         }
         __syncthreads();
+        double kk = 0.0, wk_new = 0.0;
+        const double upk = have_prev ? us[k] : 0.0;          // = 1: the previous reflector's leading element
+        if (have_prev) {
+            double corr = 0.0;
+            if (!prev_flushed)
+                for (int p = 0; p < r; ++p) corr += s_dot[1 + p] * s_dot[1 + TP_NB + p];
+            kk = -0.5 * tau_prev * tau_prev * (s_dot[0] - 2.0 * corr);
+            // w_new[k] of the previous column: tau (A_true u)[k] + kk u[k], redundantly in every thread
+            double base = pck;
+            if (!prev_flushed)
+                for (int p = 0; p < r; ++p) base -= s_vk[p] * s_dot[1 + p] + s_wk[p] * s_dot[1 + TP_NB + p];
+            wk_new = fma(kk, upk, tau_prev * base);
+        }
+        const int slot = r;
         const int r_now = r + (have_prev ? 1 : 0);
-        // (c) this CTA's slice of j in (k, n): finalise w_new there, then row k of A_true
-        const int j = k + 1 + tid * G + b;
-        double x = 0.0;
-        if (j < n) {
-            double vj_new = 0.0, wj_new = 0.0;
+        double x = 0.0, wj_new = 0.0;
+        if (mine) {
             if (have_prev) {
-                vj_new = uc[j];
-                wj_new = w_new_at(j);
-                Vbuf[(size_t)slot * n + j] = vj_new;
+                double base = pcj;
+                if (!prev_flushed) {
+#pragma unroll
+                    for (int p = 0; p < TP_NB; ++p)
+                        if (p < r) base -= vj[p] * s_dot[1 + p] + wj[p] * s_dot[1 + TP_NB + p];
+                }
+                wj_new = fma(kk, upj, tau_prev * base);
+                Vbuf[(size_t)slot * n + j] = upj;
                 Wbuf[(size_t)slot * n + j] = wj_new;
             }
-            x = A[(size_t)k * n + j];
-            for (int p = 0; p < r; ++p) x -= s_vk[p] * Wbuf[(size_t)p * n + j] + s_wk[p] * Vbuf[(size_t)p * n + j];
-            if (have_prev) x -= s_vk[r] * wj_new + s_wk[r] * vj_new;
+            x = akj;
+#pragma unroll
+            for (int p = 0; p < TP_NB; ++p)
+                if (p < r) x -= s_vk[p] * wj[p] + s_wk[p] * vj[p];
+            if (have_prev) x -= upk * wj_new + wk_new * upj;
+            xbuf[j] = x;
+            fence_proxy_async();                             // read by the other CTAs' bulk copies after the grid sync
         }
         if (b == 0 && tid == 0) {
             double dk = A[(size_t)k * n + k];
-            for (int p = 0; p < r_now; ++p) dk -= 2.0 * s_vk[p] * s_wk[p];
+            for (int p = 0; p < r; ++p) dk -= 2.0 * s_vk[p] * s_wk[p];
+            if (have_prev) dk -= 2.0 * upk * wk_new;
             d[k] = dk;
         }
         if (last) {
-            // x (thread 0 of the CTA owning j = n - 1) is A_true[n-2][n-1]; the last diagonal entry needs the pairs too
-            if (j == n - 1) {
+            if (j == n - 1) {                                // thread 0 of CTA 0: x = A_true[n-2][n-1]
                 e[n - 2] = x;
                 e[n - 1] = 0.0;
                 double dl = A[(size_t)(n - 1) * n + (n - 1)];
-                for (int p = 0; p < r; ++p) dl -= 2.0 * Vbuf[(size_t)p * n + j] * Wbuf[(size_t)p * n + j];
-                if (have_prev) dl -= 2.0 * uc[j] * w_new_at(j);
+#pragma unroll
+                for (int p = 0; p < TP_NB; ++p)
+                    if (p < r) dl -= 2.0 * vj[p] * wj[p];
+                if (have_prev) dl -= 2.0 * upj * wj_new;
                 d[n - 1] = dl;
             }
             break;
         }
-        if (j == k + 1) *alpha_g = x;
-        const double ss_part = tp_block_sum((j < n && j >= k + 2) ? x * x : 0.0, red);
-        if (tid == 0) part_ss[b] = ss_part;
+        r = r_now;                                          // the previous pair is final now (slots 0 .. r-1)
+        TP_TICK(0);
         grid.sync();
-        // ---------------- phase B ----------------
-        if (warp == 0) {
-            double t = 0.0;
-            for (int q = lane; q < G; q += 32) t += part_ss[q];
-            t = tp_warp_sum(t);
-            if (lane == 0) { s_sc[0] = t; s_sc[1] = *alpha_g; }
+        TP_TICK(1);
+        // ---------------- phase B: the whole row -> norm -> reflector, redundantly in every CTA ----------------
+        int first = gw;
+        if (first < k + 1) first += ((k + 1 - first + n_gw - 1) / n_gw) * n_gw;
+        int nrows = 0;
+        if (first < n) nrows = (n - 1 - first) / n_gw + 1;
+        double* rs = rowsc + (size_t)warp * TP_RMAX * 2 * TP_NB;
+        const int rs_cnt = nrows * 2 * r;
+        // the row x: ONE bulk copy straight into `us` (from the even index at or below k + 1)
+        const int xs0 = (k + 1) & ~1;
+        if (tid == 0) {
+            const uint32_t bytes = (uint32_t)(n - xs0) * 8u;
+            mbar_arrive_expect_tx(&xbar, bytes);
+            tma_bulk_g2s(us + xs0, xbuf + xs0, bytes, &xbar);
         }
-        __syncthreads();
-        const double ss = s_sc[0], alpha = s_sc[1];
+        // the row sides v_p[i], w_p[i] of this warp's rows, under the latency of that copy
+        constexpr int RSL = (TP_RMAX * 2 * TP_NB + 31) / 32;
+        double rs_val[RSL];
+#pragma unroll
+        for (int qq = 0; qq < RSL; ++qq) {
+            const int q = lane + 32 * qq;
+            rs_val[qq] = 0.0;
+            if (q < rs_cnt) {
+                const int t = q / (2 * r), c = q % (2 * r);
+                const int i = first + t * n_gw;
+                rs_val[qq] = c < r ? Vbuf[(size_t)c * n + i] : Wbuf[(size_t)(c - r) * n + i];
+            }
+        }
+#pragma unroll
+        for (int qq = 0; qq < RSL; ++qq) {
+            const int q = lane + 32 * qq;
+            if (q < rs_cnt) {
+                const int t = q / (2 * r), c = q % (2 * r);
+                rs[t * 2 * TP_NB + (c < r ? c : TP_NB + (c - r))] = rs_val[qq];      // v_p[i] at [p], w_p[i] at [NB + p]
+            }
+        }
+        mbar_wait(&xbar, xphase);
+        xphase ^= 1u;
+        double ssp = 0.0;
+        for (int q = k + 2 + tid; q < n; q += TP_THREADS) {
+            const double xv = us[q];
+            ssp = fma(xv, xv, ssp);
+        }
+        const double alpha = us[k + 1];
+        const double ss = tp_block_sum(ssp, red);            // (its barriers also publish `rs`)
+        if (tid == 0) us[k] = 0.0;                           // u is zero up to k
         double tau = 0.0, beta = alpha;
         if (ss > 0.0) {
             const double nrm = sqrt(fma(alpha, alpha, ss));
             beta = alpha >= 0.0 ? -nrm : nrm;
             tau = (beta - alpha) / beta;
             const double inv = 1.0 / (alpha - beta);
-            if (j < n) uc[j] = (j == k + 1) ? 1.0 : x * inv;
+            for (int q = k + 1 + tid; q < n; q += TP_THREADS) us[q] = (q == k + 1) ? 1.0 : us[q] * inv;
         }
         if (b == 0 && tid == 0) e[k] = beta;
-        r = r_now;                                          // the previous pair is final now (slots 0 .. r-1)
-        grid.sync();
+        fence_proxy_async();                                 // the next column's bulk copy overwrites these generic writes
+        __syncthreads();
+        TP_TICK(2);
         // ---------------- sweep ----------------
         const bool flush = (r == TP_NB);
         if (tau != 0.0) {
-            // rows of this warp: i_t = first + t n_gw >= k + 1
-            int first = gw;
-            if (first < k + 1) first += ((k + 1 - first + n_gw - 1) / n_gw) * n_gw;
-            int nrows = 0;
-            if (first < n) nrows = (n - 1 - first) / n_gw + 1;
-            double* rs = rowsc + (size_t)warp * TP_RMAX * 2 * TP_NB;
-            for (int q = lane; q < nrows * 2 * r; q += 32) {
-                const int t = q / (2 * r), c = q % (2 * r);
+            const int cb0 = (k + 1) & ~63;
+            double dot0 = 0.0;   // sum_i (A u)[i] u[i] over the warp's rows (identical in every lane)
+            double dotl = 0.0;   // lane c < 2 NB: sum_i rs[.][c] u[i]  (v_p.u at c = p, w_p.u at c = NB + p)
+            const bool dot_lane = lane < 2 * TP_NB && (lane & (TP_NB - 1)) < r;
+            auto row_result = [&](int t, double st) {
                 const int i = first + t * n_gw;
-                if (c < r) rs[t * 2 * TP_NB + c] = Vbuf[(size_t)c * n + i];                         // v_p[i] at [p]
-                else rs[t * 2 * TP_NB + TP_NB + (c - r)] = Wbuf[(size_t)(c - r) * n + i];          // w_p[i] at [NB + p]
-            }
-            double s[TP_RMAX];
-#pragma unroll
-            for (int t = 0; t < TP_RMAX; ++t) s[t] = 0.0;
-            const int cb0 = ((k + 1) / TP_LB) * TP_LB;
-            for (int c0 = cb0; c0 < n; c0 += TP_LB) {
-                __syncthreads();
-                for (int q = tid; q < TP_LB; q += TP_THREADS) {
-                    const int jj = c0 + q;
-                    ub[q] = (jj >= k + 1 && jj < n) ? uc[jj] : 0.0;
+                const double ui = us[i];
+                if (lane == 0) pc[i] = st;
+                dot0 = fma(st, ui, dot0);
+                if (!flush && dot_lane) dotl = fma(rs[t * 2 * TP_NB + lane], ui, dotl);
+            };
+            if (!flush) {
+                // read-only sweep over the stale block: each warp streams its rows through its own ring of bulk copies
+                // (lane 0 issues, the mbarrier's transaction count completes the stage), row after row, 2 KB per stage;
+                // a stage is refilled as soon as the warp has read it, so S x 2 KB per warp stay in flight throughout
+                const int nch = (n - cb0 + TP_CH - 1) / TP_CH;
+                const int total = nrows * nch;
+                int pt = 0, pc_i = 0, issued = 0;            // producer cursor (row, chunk), lane 0 only
+                auto issue = [&](int st_i) {
+                    const int col = cb0 + pc_i * TP_CH;
+                    const uint32_t bytes = (uint32_t)min(TP_CH, n - col) * 8u;
+                    mbar_arrive_expect_tx(&full_w[st_i], bytes);
+                    tma_bulk_g2s(ring_w + st_i * TP_CH, A + (size_t)(first + pt * n_gw) * n + col, bytes, &full_w[st_i]);
+                    if (++pc_i == nch) { pc_i = 0; ++pt; }
+                    ++issued;
+                };
+                if (lane == 0) {
+                    int st_i = stage;
+                    for (int q = 0; q < TP_S && q < total; ++q) {
+                        issue(st_i);
+                        if (++st_i == TP_S) st_i = 0;
+                    }
                 }
-                if (flush) {
+                for (int t = 0; t < nrows; ++t) {
+                    double acc = 0.0;
+                    for (int ci = 0; ci < nch; ++ci) {
+                        mbar_wait(&full_w[stage], phase);
+                        const double* src = ring_w + stage * TP_CH;
+                        const int c = cb0 + ci * TP_CH;
+#pragma unroll
+                        for (int q = 0; q < TP_CH / 64; ++q) {
+                            const int pos = 2 * lane + 64 * q;
+                            if (c + pos < n) {
+                                const double2 av = *reinterpret_cast<const double2*>(src + pos);
+                                const double2 uj = *reinterpret_cast<const double2*>(us + c + pos);
+                                acc = fma(av.y, uj.y, fma(av.x, uj.x, acc));
+                            }
+                        }
+                        __syncwarp();
+                        if (lane == 0 && issued < total) issue(stage);
+                        if (++stage == TP_S) { stage = 0; phase ^= 1u; }
+                    }
+                    row_result(t, tp_warp_sum(acc));
+                }
+            } else {
+                // flush: apply the NB pending pairs, write the block back, dot the TRUE rows with u; the pairs' column
+                // sides are staged per block of LB columns (in the ring's shared memory, idle during a flush)
+                double s[TP_RMAX];
+#pragma unroll
+                for (int t = 0; t < TP_RMAX; ++t) s[t] = 0.0;
+                for (int c0 = cb0; c0 < n; c0 += TP_LB) {
+                    __syncthreads();
                     for (int q = tid; q < TP_NB * TP_LB; q += TP_THREADS) {
                         const int p = q / TP_LB, jj = c0 + q % TP_LB;
                         const bool ok = jj < n;
                         vb[q] = ok ? Vbuf[(size_t)p * n + jj] : 0.0;
                         wb[q] = ok ? Wbuf[(size_t)p * n + jj] : 0.0;
                     }
-                }
-                __syncthreads();
-                const int cend = min(TP_LB, n - c0);
-                for (int q0 = 2 * lane; q0 < cend; q0 += 64) {
-                    double2 a[TP_RMAX];
+                    __syncthreads();
+                    const int cend = min(TP_LB, n - c0);
+                    for (int q0 = 2 * lane; q0 < cend; q0 += 128) {
+                        double2 a[2][TP_RMAX];
 #pragma unroll
-                    for (int t = 0; t < TP_RMAX; ++t)
-                        if (t < nrows) a[t] = *reinterpret_cast<const double2*>(A + (size_t)(first + t * n_gw) * n + c0 + q0);
-                    if (flush) {
+                        for (int uu = 0; uu < 2; ++uu)
 #pragma unroll
-                        for (int p = 0; p < TP_NB; ++p) {
-                            const double2 vj = *reinterpret_cast<const double2*>(vb + p * TP_LB + q0);
-                            const double2 wj = *reinterpret_cast<const double2*>(wb + p * TP_LB + q0);
+                            for (int t = 0; t < TP_RMAX; ++t)
+                                if (t < nrows && q0 + 64 * uu < cend)
+                                    a[uu][t] = *reinterpret_cast<const double2*>(A + (size_t)(first + t * n_gw) * n + c0 + q0 + 64 * uu);
 #pragma unroll
-                            for (int t = 0; t < TP_RMAX; ++t) {
-                                if (t < nrows) {
-                                    const double vi = rs[t * 2 * TP_NB + p], wi = rs[t * 2 * TP_NB + TP_NB + p];
-                                    a[t].x = a[t].x - vi * wj.x - wi * vj.x;
-                                    a[t].y = a[t].y - vi * wj.y - wi * vj.y;
+                        for (int uu = 0; uu < 2; ++uu) {
+                            if (q0 + 64 * uu < cend) {
+                                const int qq = q0 + 64 * uu;
+#pragma unroll
+                                for (int p = 0; p < TP_NB; ++p) {
+                                    const double2 vj = *reinterpret_cast<const double2*>(vb + p * TP_LB + qq);
+                                    const double2 wj = *reinterpret_cast<const double2*>(wb + p * TP_LB + qq);
+#pragma unroll
+                                    for (int t = 0; t < TP_RMAX; ++t) {
+                                        if (t < nrows) {
+                                            const double vi = rs[t * 2 * TP_NB + p], wi = rs[t * 2 * TP_NB + TP_NB + p];
+                                            a[uu][t].x = a[uu][t].x - vi * wj.x - wi * vj.x;
+                                            a[uu][t].y = a[uu][t].y - vi * wj.y - wi * vj.y;
+                                        }
+                                    }
+                                }
+                                const double2 uj = *reinterpret_cast<const double2*>(us + c0 + qq);
+#pragma unroll
+                                for (int t = 0; t < TP_RMAX; ++t) {
+                                    if (t < nrows) {
+                                        *reinterpret_cast<double2*>(A + (size_t)(first + t * n_gw) * n + c0 + qq) = a[uu][t];
+                                        s[t] = fma(a[uu][t].y, uj.y, fma(a[uu][t].x, uj.x, s[t]));
+                                    }
                                 }
                             }
                         }
-#pragma unroll
-                        for (int t = 0; t < TP_RMAX; ++t)
-                            if (t < nrows) *reinterpret_cast<double2*>(A + (size_t)(first + t * n_gw) * n + c0 + q0) = a[t];
-                    }
-                    const double2 uj = *reinterpret_cast<const double2*>(ub + q0);
-#pragma unroll
-                    for (int t = 0; t < TP_RMAX; ++t)
-                        if (t < nrows) s[t] = fma(a[t].y, uj.y, fma(a[t].x, uj.x, s[t]));
-                }
-            }
-            // row results + the dot products of the next phase A
-            double dots[TP_NDOT];
-#pragma unroll
-            for (int c = 0; c < TP_NDOT; ++c) dots[c] = 0.0;
-#pragma unroll
-            for (int t = 0; t < TP_RMAX; ++t) {
-                if (t < nrows) {
-                    const double st = tp_warp_sum(s[t]);
-                    if (lane == 0) {
-                        const int i = first + t * n_gw;
-                        const double ui = uc[i];
-                        pc[i] = st;
-                        dots[0] = fma(st, ui, dots[0]);
-                        if (!flush) {
-                            for (int p = 0; p < r; ++p) {
-                                dots[1 + p] = fma(rs[t * 2 * TP_NB + TP_NB + p], ui, dots[1 + p]);      // w_p[i] u[i]
-                                dots[1 + TP_NB + p] = fma(rs[t * 2 * TP_NB + p], ui, dots[1 + TP_NB + p]);  // v_p[i] u[i]
-                            }
-                        }
                     }
                 }
+                fence_proxy_async();                         // the next bulk copies overwrite what this sweep staged / read what it wrote
+#pragma unroll
+                for (int t = 0; t < TP_RMAX; ++t)
+                    if (t < nrows) row_result(t, tp_warp_sum(s[t]));
             }
-            // CTA partial sums (lane 0 of every warp holds its share)
-            __syncthreads();
-            double* scratch = ub;                              // [WARPS][NDOT] reuse
-            if (lane == 0)
-                for (int c = 0; c < TP_NDOT; ++c) scratch[warp * TP_NDOT + c] = dots[c];
+            TP_TICK(flush ? 6 : 3);
+            // the dot products of the next phase A: pc.u, (w_p.u)_p at [1 + p], (v_p.u)_p at [1 + NB + p]
+            if (lane == 0) s_part[warp * TP_NDOT] = dot0;
+            if (lane < 2 * TP_NB) s_part[warp * TP_NDOT + 1 + (lane < TP_NB ? TP_NB + lane : lane - TP_NB)] = dotl;
             __syncthreads();
             if (tid < TP_NDOT) {
                 double t = 0.0;
-                for (int w2 = 0; w2 < TP_WARPS; ++w2) t += scratch[w2 * TP_NDOT + tid];
-                part_dot[(size_t)b * TP_NDOT + tid] = t;
+                for (int w2 = 0; w2 < TP_WARPS; ++w2) t += s_part[w2 * TP_NDOT + tid];
+                part_dot[(size_t)tid * G + b] = t;
             }
             have_prev = true;
             prev_flushed = flush;
-            r_prev = r;
             tau_prev = tau;
             if (flush) r = 0;
         } else {
             have_prev = false;
         }
+        TP_TICK(4);
         grid.sync();
+        TP_TICK(5);
     }
+#ifdef TP_PROFILE
+    if (b == 0 && tid == 0)
+        for (int i = 0; i < 7; ++i) part_dot[(size_t)G * TP_NDOT + i] = (double)tp_acc[i];
+#endif
+}
+
+// even n (16-byte bulk copies), every row owned (RMAX rows per warp), one slice element and <= GL partial sums per thread
+bool tridiag_panel_supported(int n, int num_sms) {
+    return n >= 4 && (n & 1) == 0 && (long long)n <= (long long)TP_RMAX * num_sms * TP_WARPS &&
+           (n + num_sms - 1) / num_sms <= TP_THREADS && num_sms <= 32 * TP_GL && tp_smem_doubles(n) * sizeof(double) <= 225 * 1024;
 }
 
 cudaError_t launch_tridiag_panel(double* G, int n, double* d, double* e, double* ws, int num_sms, cudaStream_t stream) {
-    const size_t smem = ((size_t)(1 + 2 * TP_NB) * TP_LB + (size_t)TP_WARPS * TP_RMAX * 2 * TP_NB) * sizeof(double);
+    static_assert(TP_WARPS * TP_S * TP_CH >= 2 * TP_NB * TP_LB, "the flush staging buffers alias the ring");
+    if (!tridiag_panel_supported(n, num_sms)) return cudaErrorInvalidValue;
+    const size_t smem = tp_smem_doubles(n) * sizeof(double);
     cudaError_t err = cudaFuncSetAttribute(tridiag_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
     int per_sm = 0;
     err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tridiag_panel_kernel, TP_THREADS, smem);
     if (err != cudaSuccess) return err;
     if (per_sm < 1) return cudaErrorInvalidValue;
-    int grid = num_sms;
-    if ((n & 1) || (long long)n > (long long)TP_RMAX * grid * TP_WARPS || (n + grid - 1) / grid > TP_THREADS)
-        return cudaErrorInvalidValue;
     void* args[] = {&G, &n, &d, &e, &ws};
-    return cudaLaunchCooperativeKernel(reinterpret_cast<void*>(tridiag_panel_kernel), dim3(grid), dim3(TP_THREADS), args, smem,
+    return cudaLaunchCooperativeKernel(reinterpret_cast<void*>(tridiag_panel_kernel), dim3(num_sms), dim3(TP_THREADS), args, smem,
                                        stream);
 }
 
