@@ -67,6 +67,8 @@ SIGNATURES = {
     "idb_spectrum_large_workspace_bytes": (C.c_size_t, [_i]),
     "idb_spectrum_large": (_i, [_vp, _i, _i, _vp, _vp, _vp]),
     "idb_spectrum_large_variant": (_i, [_vp, _i, _i, _vp, _vp, _i, _vp]),
+    "idb_spectrum_large_static_max_n": (_i, []),
+    "idb_spectrum_large_static": (_i, [_vp, _i, _i, _vp, _vp]),
     "idb_attention_tc_workspace_bytes": (C.c_size_t, [_i, _i, _i]),
     "idb_attention_tc": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _i, _f, _vp, _vp, _i, _vp]),
     "idb_attention": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _f, _vp, _i, _vp]),
@@ -101,7 +103,8 @@ KERNELS_PER_CALL = {"idb_perturb": 1, "idb_perturb_rows": 1, "idb_pack_weight": 
                     "idb_adam_step": 1, "idb_center_gram": 2, "idb_column_sums": 1, "idb_gram_about": 1,
                     "idb_spectrum": 2, "idb_id_from_spectrum": 1, "idb_upfirdn2d": 1, "idb_fused_bias_act": 1,
                     "idb_groupnorm_stats": 2, "idb_conv_prep": 1, "idb_conv_prep_fir": 1, "idb_conv2d": 1, "idb_conv2d_stats": 1, "idb_groupnorm_from_conv_stats": 1, "idb_attention": 1, "idb_attention_tc": 4,
-                    "idb_row_gram": 3, "idb_spectrum_large": 2, "idb_spectrum_large_variant": 2}
+                    "idb_row_gram": 3, "idb_spectrum_large": 2, "idb_spectrum_large_variant": 2,
+                    "idb_spectrum_large_static": 2}
 launch_count = 0
 
 

@@ -309,6 +309,18 @@ int idb_spectrum_large(double* G, int n, int n_out, float* sv, void* workspace, 
  * bytes per column instead of 16), -1 = unfused two-pass kernel. */
 int idb_spectrum_large_variant(double* G, int n, int n_out, float* sv, void* workspace, int variant, void* stream);
 
+/* idb_spectrum_large WITHOUT a workspace argument and without any allocation: the workspace is a file-scope device array
+ * inside the library (768 KB, held by every GPU that loads the library until the process exits), so the call is usable
+ * where cudaMalloc is not (under CUDA graph capture, in tight serving loops, in harnesses that forbid it).  It has no
+ * counterpart in the reference.  Limit: n <= 4096
+ * (idb_spectrum_large_static_max_n()); a larger n is rejected with an error, use idb_spectrum_large there.  Same
+ * arguments, output and kernels as idb_spectrum_large otherwise (G [n][n] fp64 is overwritten; sv [n_out] fp32
+ * descending).  Every call on a device shares the one array: calls that overlap on the GPU race -- serialise them.  Nothing
+ * needs clearing between calls (every workspace word is written before it is read). */
+#define IDB_SPECTRUM_STATIC_MAX_N 4096
+int idb_spectrum_large_static_max_n(void);
+int idb_spectrum_large_static(double* G, int n, int n_out, float* sv, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
