@@ -34,7 +34,7 @@ namespace {
 constexpr int TP_THREADS = 256;
 constexpr int TP_WARPS = TP_THREADS / 32;
 constexpr int TP_NB = 8;       // pending reflector pairs before a flush
-constexpr int TP_LB = 512;     // columns per shared-memory block of a flush sweep (the pairs' column sides)
+constexpr int TP_LB = 256;     // columns per staged block of a flush sweep (the pairs' column sides: 2 NB LB doubles = 32 KB)
 constexpr int TP_RMAX = 11;    // rows of the trailing block per warp (n <= TP_RMAX * gridDim.x * TP_WARPS = 13024 on 148 SMs)
 constexpr int TP_CH = 256;     // doubles per bulk copy of a read-only sweep (one ring stage = 2 KB of one row)
 constexpr int TP_S = 6;        // ring stages per warp: 8 warps x 6 x 2 KB = 96 KB in flight per SM
@@ -81,11 +81,11 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
     const int nu = (n + 63) & ~63;
     double* us = tp_smem;                                   // [nu] the WHOLE reflector of the current column (0 for j <= k)
     double* ring = us + nu;                                 // [WARPS][S][CH] bulk-copy ring of the read-only sweeps ...
-    double* vb = ring;                                      // ... aliased by [NB][LB] + [NB][LB] of the flush sweeps
-    double* wb = vb + TP_NB * TP_LB;
+                                                            // ... aliased by 3 stages of [2 NB][LB] in the flush sweeps
     double* rowsc = ring + TP_WARPS * TP_S * TP_CH;         // [WARPS][RMAX][2 NB]: v_p[i], w_p[i] of the warp's rows
     __shared__ __align__(8) uint64_t full[TP_WARPS * TP_S];
     __shared__ __align__(8) uint64_t xbar;
+    __shared__ __align__(8) uint64_t fbar[3];
     __shared__ double red[TP_WARPS];
     __shared__ double s_dot[TP_NDOT];                       // pc.u, (w_p.u)_p, (v_p.u)_p of the previous sweep
     __shared__ double s_vk[TP_NB + 1], s_wk[TP_NB + 1];     // v_p[k], w_p[k]
@@ -103,6 +103,7 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
     if (tid == 0) {
         for (int q = 0; q < TP_WARPS * TP_S; ++q) mbar_init(&full[q], 1);
         mbar_init(&xbar, 1);
+        for (int q = 0; q < 3; ++q) mbar_init(&fbar[q], 1);
         fence_barrier_init();
     }
     fence_proxy_async();
@@ -111,6 +112,7 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
     uint64_t* full_w = full + warp * TP_S;
     int stage = 0;             // the warp's ring position and phase bit run on across sweeps (strict round-robin)
     uint32_t phase = 0, xphase = 0;
+    int fcnt = 0;              // staged blocks consumed so far by the flush sweeps: stage fcnt % 3, phase (fcnt / 3) & 1
 
     // replicated scalar state (identical in every CTA)
     int r = 0;                 // pending pairs whose w is final (slots 0 .. r-1)
@@ -334,57 +336,86 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
                     row_result(t, tp_warp_sum(acc));
                 }
             } else {
-                // flush: apply the NB pending pairs, write the block back, dot the TRUE rows with u; the pairs' column
-                // sides are staged per block of LB columns (in the ring's shared memory, idle during a flush)
+                // flush: apply the NB pending pairs, write the block back, dot the TRUE rows with u.  The pairs' column sides
+                // are staged per block of LB columns by bulk copies, two blocks ahead (three stages in the ring's shared
+                // memory, idle during a flush); a warp's rows are walked in 64-column chunks, the loads of chunk c + 1 in
+                // flight while chunk c is updated and stored
                 double s[TP_RMAX];
 #pragma unroll
                 for (int t = 0; t < TP_RMAX; ++t) s[t] = 0.0;
-                for (int c0 = cb0; c0 < n; c0 += TP_LB) {
-                    __syncthreads();
-                    for (int q = tid; q < TP_NB * TP_LB; q += TP_THREADS) {
-                        const int p = q / TP_LB, jj = c0 + q % TP_LB;
-                        const bool ok = jj < n;
-                        vb[q] = ok ? Vbuf[(size_t)p * n + jj] : 0.0;
-                        wb[q] = ok ? Wbuf[(size_t)p * n + jj] : 0.0;
+                constexpr int CPB = TP_LB / 64;              // chunks per staged block
+                const int nchunk = (n - cb0 + 63) >> 6;
+                const int nblk = (nchunk + CPB - 1) / CPB;
+                const size_t rstride = (size_t)n_gw * n;
+                double* Arow = A + (size_t)first * n + cb0 + 2 * lane;   // (not dereferenced when the warp owns no row)
+                auto stage_block = [&](int blk, int cnt) {   // thread 0: V, W columns of block blk -> stage cnt % 3
+                    const int c0 = cb0 + blk * TP_LB;
+                    const uint32_t bytes = (uint32_t)min(TP_LB, n - c0) * 8u;
+                    const int st_i = cnt % 3;
+                    double* dst = ring + (size_t)st_i * 2 * TP_NB * TP_LB;
+                    mbar_arrive_expect_tx(&fbar[st_i], 2 * TP_NB * bytes);
+                    for (int p = 0; p < TP_NB; ++p) {
+                        tma_bulk_g2s(dst + p * TP_LB, Vbuf + (size_t)p * n + c0, bytes, &fbar[st_i]);
+                        tma_bulk_g2s(dst + (TP_NB + p) * TP_LB, Wbuf + (size_t)p * n + c0, bytes, &fbar[st_i]);
                     }
-                    __syncthreads();
-                    const int cend = min(TP_LB, n - c0);
-                    for (int q0 = 2 * lane; q0 < cend; q0 += 128) {
-                        double2 a[2][TP_RMAX];
+                };
+                auto load = [&](double2 (&a)[TP_RMAX], int c) {
 #pragma unroll
-                        for (int uu = 0; uu < 2; ++uu)
+                    for (int t = 0; t < TP_RMAX; ++t)
+                        if (t < nrows && cb0 + 64 * c + 2 * lane < n)
+                            a[t] = *reinterpret_cast<const double2*>(Arow + t * rstride + 64 * c);
+                };
+                auto process = [&](double2 (&a)[TP_RMAX], int c) {
+                    const int blk = c / CPB, within = c % CPB;
+                    if (within == 0) {
+                        __syncthreads();                     // every warp is done with block blk - 1: its stage is free
+                        if (tid == 0 && blk + 2 < nblk) stage_block(blk + 2, fcnt + 2);
+                        mbar_wait(&fbar[fcnt % 3], (uint32_t)(fcnt / 3) & 1u);
+                    }
+                    const double* vbs = ring + (size_t)(fcnt % 3) * 2 * TP_NB * TP_LB;
+                    const double* wbs = vbs + TP_NB * TP_LB;
+                    const int qq = within * 64 + 2 * lane;
+                    if (cb0 + 64 * c + 2 * lane < n) {
+#ifdef TP_EXP_PAIRS
+                        constexpr int NPAIR = TP_EXP_PAIRS;   // timing experiment only (wrong results)
+#else
+                        constexpr int NPAIR = TP_NB;
+#endif
 #pragma unroll
-                            for (int t = 0; t < TP_RMAX; ++t)
-                                if (t < nrows && q0 + 64 * uu < cend)
-                                    a[uu][t] = *reinterpret_cast<const double2*>(A + (size_t)(first + t * n_gw) * n + c0 + q0 + 64 * uu);
+                        for (int p = 0; p < NPAIR; ++p) {
+                            const double2 vj = *reinterpret_cast<const double2*>(vbs + p * TP_LB + qq);
+                            const double2 wj = *reinterpret_cast<const double2*>(wbs + p * TP_LB + qq);
 #pragma unroll
-                        for (int uu = 0; uu < 2; ++uu) {
-                            if (q0 + 64 * uu < cend) {
-                                const int qq = q0 + 64 * uu;
-#pragma unroll
-                                for (int p = 0; p < TP_NB; ++p) {
-                                    const double2 vj = *reinterpret_cast<const double2*>(vb + p * TP_LB + qq);
-                                    const double2 wj = *reinterpret_cast<const double2*>(wb + p * TP_LB + qq);
-#pragma unroll
-                                    for (int t = 0; t < TP_RMAX; ++t) {
-                                        if (t < nrows) {
-                                            const double vi = rs[t * 2 * TP_NB + p], wi = rs[t * 2 * TP_NB + TP_NB + p];
-                                            a[uu][t].x = a[uu][t].x - vi * wj.x - wi * vj.x;
-                                            a[uu][t].y = a[uu][t].y - vi * wj.y - wi * vj.y;
-                                        }
-                                    }
-                                }
-                                const double2 uj = *reinterpret_cast<const double2*>(us + c0 + qq);
-#pragma unroll
-                                for (int t = 0; t < TP_RMAX; ++t) {
-                                    if (t < nrows) {
-                                        *reinterpret_cast<double2*>(A + (size_t)(first + t * n_gw) * n + c0 + qq) = a[uu][t];
-                                        s[t] = fma(a[uu][t].y, uj.y, fma(a[uu][t].x, uj.x, s[t]));
-                                    }
+                            for (int t = 0; t < TP_RMAX; ++t) {
+                                if (t < nrows) {
+                                    const double vi = rs[t * 2 * TP_NB + p], wi = rs[t * 2 * TP_NB + TP_NB + p];
+                                    a[t].x = a[t].x - vi * wj.x - wi * vj.x;
+                                    a[t].y = a[t].y - vi * wj.y - wi * vj.y;
                                 }
                             }
                         }
+                        const double2 uj = *reinterpret_cast<const double2*>(us + cb0 + 64 * c + 2 * lane);
+#pragma unroll
+                        for (int t = 0; t < TP_RMAX; ++t) {
+                            if (t < nrows) {
+                                *reinterpret_cast<double2*>(Arow + t * rstride + 64 * c) = a[t];
+                                s[t] = fma(a[t].y, uj.y, fma(a[t].x, uj.x, s[t]));
+                            }
+                        }
                     }
+                    if (within == CPB - 1 || c == nchunk - 1) ++fcnt;
+                };
+                if (tid == 0) {
+                    stage_block(0, fcnt);
+                    if (nblk > 1) stage_block(1, fcnt + 1);
+                }
+                double2 a0[TP_RMAX], a1[TP_RMAX];
+                load(a0, 0);
+                for (int c = 0; c < nchunk; c += 2) {
+                    if (c + 1 < nchunk) load(a1, c + 1);
+                    process(a0, c);
+                    if (c + 2 < nchunk) load(a0, c + 2);
+                    if (c + 1 < nchunk) process(a1, c + 1);
                 }
                 fence_proxy_async();                         // the next bulk copies overwrite what this sweep staged / read what it wrote
 #pragma unroll
@@ -425,7 +456,7 @@ bool tridiag_panel_supported(int n, int num_sms) {
 }
 
 cudaError_t launch_tridiag_panel(double* G, int n, double* d, double* e, double* ws, int num_sms, cudaStream_t stream) {
-    static_assert(TP_WARPS * TP_S * TP_CH >= 2 * TP_NB * TP_LB, "the flush staging buffers alias the ring");
+    static_assert(TP_WARPS * TP_S * TP_CH >= 3 * 2 * TP_NB * TP_LB, "the flush staging buffers alias the ring");
     if (!tridiag_panel_supported(n, num_sms)) return cudaErrorInvalidValue;
     const size_t smem = tp_smem_doubles(n) * sizeof(double);
     cudaError_t err = cudaFuncSetAttribute(tridiag_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
