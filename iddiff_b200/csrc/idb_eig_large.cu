@@ -498,6 +498,9 @@ cudaError_t launch_tridiag_panel(double* G, int n, double* d, double* e, double*
 bool tridiag_panel_supported(int n, int num_sms);
 
 // d, e, then the larger of the fused kernels' 6 n doubles and the panel kernel's buffers (sized for up to 192 CTAs)
+// what the fused kernels alone need (classes 1, 2, -1): d, e and 6 n doubles
+size_t spectrum_large_fused_workspace_bytes(int n) { return (size_t)8 * n * sizeof(double) + 256; }
+
 size_t spectrum_large_workspace_bytes(int n) {
     const size_t panel = tridiag_panel_workspace_doubles(n, 192), fused = (size_t)6 * n;
     return ((size_t)2 * n + (panel > fused ? panel : fused)) * sizeof(double) + 256;

@@ -36,10 +36,13 @@ constexpr int TP_WARPS = TP_THREADS / 32;
 constexpr int TP_NB = 8;       // pending reflector pairs before a flush
 constexpr int TP_LB = 256;     // columns per staged block of a flush sweep (the pairs' column sides: 2 NB LB doubles = 32 KB)
 constexpr int TP_RMAX = 11;    // rows of the trailing block per warp (n <= TP_RMAX * gridDim.x * TP_WARPS = 13024 on 148 SMs)
-constexpr int TP_CH = 256;     // doubles per bulk copy of a read-only sweep (one ring stage = 2 KB of one row)
-constexpr int TP_S = 6;        // ring stages per warp: 8 warps x 6 x 2 KB = 96 KB in flight per SM
+constexpr int TP_CW = 256;     // columns per chunk of a read-only sweep
+constexpr int TP_TR = 2;       // rows per tile there (one ring stage = TR rows x CW columns = 4 KB, two 2 KB bulk copies)
+constexpr int TP_S = 3;        // ring stages per warp: 8 warps x 3 x 4 KB = 96 KB in flight per SM
+constexpr int TP_TILE = TP_TR * TP_CW;
+constexpr int TP_RPC = TP_RMAX * TP_WARPS;   // rows of the trailing block per CTA
 constexpr int TP_NDOT = 2 * TP_NB + 1;
-constexpr int TP_DC = (TP_NDOT + TP_WARPS - 1) / TP_WARPS;   // dot-product columns per warp in phase A
+constexpr int TP_DC = (TP_NDOT + 1 + TP_WARPS - 1) / TP_WARPS;   // dot-product columns per warp in phase A (+ 1: column sum at k)
 constexpr int TP_GL = 5;       // CTAs per lane there (grid <= 160)
 
 __device__ __forceinline__ double tp_warp_sum(double v) {
@@ -58,12 +61,13 @@ __device__ __forceinline__ double tp_block_sum(double v, double* red) {
     return t;
 }
 constexpr size_t tp_smem_doubles(int n) {
-    return (size_t)((n + 63) & ~63) + (size_t)TP_WARPS * TP_S * TP_CH + (size_t)TP_WARPS * TP_RMAX * 2 * TP_NB;
+    return (size_t)((n + 63) & ~63) + (size_t)TP_WARPS * TP_S * TP_TILE + (size_t)TP_WARPS * TP_RMAX * 2 * TP_NB +
+           (size_t)TP_WARPS * TP_RPC;
 }
 }  // namespace
 
 size_t tridiag_panel_workspace_doubles(int n, int grid) {
-    return (size_t)(2 * TP_NB + 2) * n + (size_t)grid * TP_NDOT + 64;
+    return (size_t)(2 * TP_NB + 2) * n + (size_t)grid * TP_NDOT + 64 + (size_t)grid * ((n + 63) & ~63);
 }
 
 #ifdef TP_PROFILE   // phase timers of CTA 0 (tools/panel_profile.sh), written behind part_dot
@@ -82,12 +86,14 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
     double* us = tp_smem;                                   // [nu] the WHOLE reflector of the current column (0 for j <= k)
     double* ring = us + nu;                                 // [WARPS][S][CH] bulk-copy ring of the read-only sweeps ...
                                                             // ... aliased by 3 stages of [2 NB][LB] in the flush sweeps
-    double* rowsc = ring + TP_WARPS * TP_S * TP_CH;         // [WARPS][RMAX][2 NB]: v_p[i], w_p[i] of the warp's rows
+    double* rowsc = ring + TP_WARPS * TP_S * TP_TILE;       // [WARPS][RMAX][2 NB]: v_p[i], w_p[i] of the warp's rows
+    double* rowacc = rowsc + TP_WARPS * TP_RMAX * 2 * TP_NB; // [WARPS][RPC] row sums of a read-only sweep, per warp (= per column set)
     __shared__ __align__(8) uint64_t full[TP_WARPS * TP_S];
     __shared__ __align__(8) uint64_t xbar;
     __shared__ __align__(8) uint64_t fbar[3];
     __shared__ double red[TP_WARPS];
-    __shared__ double s_dot[TP_NDOT];                       // pc.u, (w_p.u)_p, (v_p.u)_p of the previous sweep
+    __shared__ double s_dot[TP_NDOT + 1];                   // pc.u, (w_p.u)_p, (v_p.u)_p of the previous sweep; [NDOT]: the column
+                                                            // side of (A u)[k]
     __shared__ double s_vk[TP_NB + 1], s_wk[TP_NB + 1];     // v_p[k], w_p[k]
     __shared__ double s_part[TP_WARPS * TP_NDOT];
 
@@ -97,7 +103,9 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
     double* Wbuf = Vbuf + (size_t)TP_NB * n;                // [NB][n]
     double* xbuf = Wbuf + (size_t)TP_NB * n;                // [n] row k of A_true, written in slices
     double* pc = xbuf + n;                                  // [n] A u of the current column (stale or true, unscaled)
-    double* part_dot = pc + n;                              // [NDOT][G]
+    double* part_dot = pc + n;                              // [NDOT][G] (+ 64 spare)
+    double* part_col = part_dot + (((size_t)G * TP_NDOT + 64 + 1) & ~(size_t)1);   // [G][nu] column-side partial products of a
+                                                                                    // read-only sweep, one row per CTA
 
     for (int q = tid; q < nu; q += TP_THREADS) us[q] = 0.0;
     if (tid == 0) {
@@ -108,7 +116,7 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
     }
     fence_proxy_async();
     __syncthreads();
-    double* ring_w = ring + (size_t)warp * TP_S * TP_CH;
+    double* ring_w = ring + (size_t)warp * TP_S * TP_TILE;
     uint64_t* full_w = full + warp * TP_S;
     int stage = 0;             // the warp's ring position and phase bit run on across sweeps (strict round-robin)
     uint32_t phase = 0, xphase = 0;
@@ -127,8 +135,11 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
         TP_TICK_START();
         const bool last = (k + 2 >= n);                     // k = n - 2: only finalise + read the last 2 x 2 block
         // ---------------- phase A: this CTA's slice of the indices j > k ----------------
-        const int j = k + 1 + tid * G + b;
-        const bool mine = j < n;
+        const int sl = (n - k - 1 + G - 1) / G;              // contiguous slices: coalesced reads of the G column partials
+        const int j = k + 1 + b * sl + tid;
+        const bool mine = tid < sl && j < n;
+        const bool sym_prev = have_prev && !prev_flushed;    // the previous sweep read the lower triangle only: (A u)[j] =
+                                                             // pc[j] (row side) + sum over the CTAs of part_col[.][j]
         // every global load of the phase is issued up front: ONE L2 round trip.  (The pairs outstanding during the previous
         // sweep are exactly the r final ones unless that sweep flushed them, so w_new and x share the same loads.)
         double pd[TP_DC][TP_GL];                             // the CTAs' partial dot products of the previous sweep
@@ -137,7 +148,11 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
 #pragma unroll
             for (int i = 0; i < TP_GL; ++i) {
                 const int c = warp + TP_WARPS * ci, q = lane + 32 * i;
-                pd[ci][i] = (have_prev && c < TP_NDOT && q < G) ? part_dot[(size_t)c * G + q] : 0.0;
+                pd[ci][i] = 0.0;
+                if (have_prev && q < G) {
+                    if (c < TP_NDOT) pd[ci][i] = part_dot[(size_t)c * G + q];
+                    else if (c == TP_NDOT && sym_prev) pd[ci][i] = part_col[(size_t)q * nu + k];
+                }
             }
         double akj = 0.0, pcj = 0.0, upj = 0.0, pck = 0.0, vj[TP_NB], wj[TP_NB];
 #pragma unroll
@@ -150,6 +165,25 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
                 if (p < r) { vj[p] = Vbuf[(size_t)p * n + j]; wj[p] = Wbuf[(size_t)p * n + j]; }
         }
         if (have_prev) pck = pc[k];
+        if (sym_prev) {
+            // column side of (A u)[j] over the slice: warp w sums the partials of the CTAs w, w + 8, ... (all loads independent)
+            constexpr int JL = (TP_RPC + 31) / 32;
+            double acc[JL];
+#pragma unroll
+            for (int e = 0; e < JL; ++e) acc[e] = 0.0;
+            const int j0 = k + 1 + b * sl;
+#pragma unroll 4
+            for (int q = warp; q < G; q += TP_WARPS) {
+#pragma unroll
+                for (int e = 0; e < JL; ++e) {
+                    const int jj = lane + 32 * e;
+                    if (jj < sl && j0 + jj < n) acc[e] += part_col[(size_t)q * nu + j0 + jj];
+                }
+            }
+#pragma unroll
+            for (int e = 0; e < JL; ++e)
+                if (lane + 32 * e < TP_RPC) rowacc[warp * TP_RPC + lane + 32 * e] = acc[e];
+        }
         if (tid < r) { s_vk[tid] = Vbuf[(size_t)tid * n + k]; s_wk[tid] = Wbuf[(size_t)tid * n + k]; }
         if (have_prev) {
 #pragma unroll
@@ -158,7 +192,7 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
 #pragma unroll
                 for (int i = 0; i < TP_GL; ++i) t += pd[ci][i];
                 t = tp_warp_sum(t);
-                if (lane == 0 && warp + TP_WARPS * ci < TP_NDOT) s_dot[warp + TP_WARPS * ci] = t;
+                if (lane == 0 && warp + TP_WARPS * ci <= TP_NDOT) s_dot[warp + TP_WARPS * ci] = t;
             }
         }
         __syncthreads();
@@ -170,7 +204,7 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
                 for (int p = 0; p < r; ++p) corr += s_dot[1 + p] * s_dot[1 + TP_NB + p];
             kk = -0.5 * tau_prev * tau_prev * (s_dot[0] - 2.0 * corr);
             // w_new[k] of the previous column: tau (A_true u)[k] + kk u[k], redundantly in every thread
-            double base = pck;
+            double base = pck + (prev_flushed ? 0.0 : s_dot[TP_NDOT]);
             if (!prev_flushed)
                 for (int p = 0; p < r; ++p) base -= s_vk[p] * s_dot[1 + p] + s_wk[p] * s_dot[1 + TP_NB + p];
             wk_new = fma(kk, upk, tau_prev * base);
@@ -179,6 +213,10 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
         const int r_now = r + (have_prev ? 1 : 0);
         double x = 0.0, wj_new = 0.0;
         if (mine) {
+            if (sym_prev) {
+#pragma unroll
+                for (int w2 = 0; w2 < TP_WARPS; ++w2) pcj += rowacc[w2 * TP_RPC + tid];
+            }
             if (have_prev) {
                 double base = pcj;
                 if (!prev_flushed) {
@@ -205,7 +243,7 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
             d[k] = dk;
         }
         if (last) {
-            if (j == n - 1) {                                // thread 0 of CTA 0: x = A_true[n-2][n-1]
+            if (mine && j == n - 1) {                        // thread 0 of CTA 0: x = A_true[n-2][n-1]
                 e[n - 2] = x;
                 e[n - 1] = 0.0;
                 double dl = A[(size_t)(n - 1) * n + (n - 1)];
@@ -293,48 +331,139 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
                 if (!flush && dot_lane) dotl = fma(rs[t * 2 * TP_NB + lane], ui, dotl);
             };
             if (!flush) {
-                // read-only sweep over the stale block: each warp streams its rows through its own ring of bulk copies
-                // (lane 0 issues, the mbarrier's transaction count completes the stage), row after row, 2 KB per stage;
-                // a stage is refilled as soon as the warp has read it, so S x 2 KB per warp stay in flight throughout
-                const int nch = (n - cb0 + TP_CH - 1) / TP_CH;
-                const int total = nrows * nch;
-                int pt = 0, pc_i = 0, issued = 0;            // producer cursor (row, chunk), lane 0 only
+                // read-only sweep over the LOWER TRIANGLE of the stale block (the block is symmetric: every element a_ij,
+                // i > j, serves (A u)[i] += a_ij u[j] and (A u)[j] += a_ij u[i]): 4 m^2 bytes instead of 8 m^2.  The CTA owns
+                // the rows i = b (mod G); its warps own 256-column chunks of those rows (dealt in snake order, so every warp
+                // gets the same share of the triangle) and stream them as tiles of 2 rows x 256 columns (two 2 KB bulk
+                // copies) through their rings.  Column-side sums stay in registers over all the CTA's rows of a chunk and
+                // go to part_col[b][.] (summed over the CTAs by the next phase A); row-side sums are reduced over the lanes
+                // eight rows at a time by a transposing butterfly and collected per warp.
+                const int Q = (n - 1 - b) / G + 1;           // the CTA's rows i_q = b + G q < n
+                const int q0 = (b >= k + 1) ? 0 : (k + 1 - b + G - 1) / G;
+                const int c_lo = (k + 1) / TP_CW, c_hi = (n - 1) / TP_CW;
+                double* rowacc_w = rowacc + warp * TP_RPC;
+                for (int q = lane; q < TP_RPC; q += 32) rowacc_w[q] = 0.0;
+                auto chunk_of = [&](int m) {                 // m-th chunk of this warp: w, 15 - w, 16 + w, 31 - w, ...
+                    return c_lo + 2 * TP_WARPS * (m >> 1) + ((m & 1) ? 2 * TP_WARPS - 1 - warp : warp);
+                };
+                auto first_row = [&](int c) {                // first row of the CTA that reaches chunk c (i >= CW c, i >= k + 1)
+                    const int lo = TP_CW * c;
+                    const int qc = (lo <= b) ? 0 : (lo - b + G - 1) / G;
+                    return max(qc, q0);
+                };
+                int p_m = 0, p_c = chunk_of(0), p_q = 0;     // producer cursor (chunk, first row of the tile), lane 0 only
+                bool p_done = p_c > c_hi;
+                if (!p_done) { p_q = first_row(p_c); p_done = p_q >= Q; }
                 auto issue = [&](int st_i) {
-                    const int col = cb0 + pc_i * TP_CH;
-                    const uint32_t bytes = (uint32_t)min(TP_CH, n - col) * 8u;
-                    mbar_arrive_expect_tx(&full_w[st_i], bytes);
-                    tma_bulk_g2s(ring_w + st_i * TP_CH, A + (size_t)(first + pt * n_gw) * n + col, bytes, &full_w[st_i]);
-                    if (++pc_i == nch) { pc_i = 0; ++pt; }
-                    ++issued;
+                    const int nr = min(TP_TR, Q - p_q);
+                    const int col = TP_CW * p_c;
+                    const uint32_t bytes = (uint32_t)min(TP_CW, n - col) * 8u;
+                    mbar_arrive_expect_tx(&full_w[st_i], bytes * nr);
+                    const double* src = A + (size_t)(b + G * p_q) * n + col;
+                    for (int rr = 0; rr < nr; ++rr)
+                        tma_bulk_g2s(ring_w + st_i * TP_TILE + rr * TP_CW, src + (size_t)rr * G * n, bytes, &full_w[st_i]);
+                    p_q += TP_TR;
+                    if (p_q >= Q) {                          // next chunk of this warp (later chunks reach fewer rows)
+                        p_c = chunk_of(++p_m);
+                        if (p_c > c_hi) p_done = true;
+                        else { p_q = first_row(p_c); p_done = p_q >= Q; }
+                    }
                 };
                 if (lane == 0) {
                     int st_i = stage;
-                    for (int q = 0; q < TP_S && q < total; ++q) {
+                    for (int q = 0; q < TP_S && !p_done; ++q) {
                         issue(st_i);
                         if (++st_i == TP_S) st_i = 0;
                     }
                 }
-                for (int t = 0; t < nrows; ++t) {
-                    double acc = 0.0;
-                    for (int ci = 0; ci < nch; ++ci) {
-                        mbar_wait(&full_w[stage], phase);
-                        const double* src = ring_w + stage * TP_CH;
-                        const int c = cb0 + ci * TP_CH;
+                __syncwarp();
+                double dotc = 0.0;                           // sum_j colsum[j] u[j] over this lane's columns
+                for (int m = 0;; ++m) {
+                    const int c = chunk_of(m);
+                    if (c > c_hi) break;
+                    const int col0 = TP_CW * c + 2 * lane;   // this lane's columns: col0 + 64 e, + 1
+                    double2 uj[TP_CW / 64], cs[TP_CW / 64];
 #pragma unroll
-                        for (int q = 0; q < TP_CH / 64; ++q) {
-                            const int pos = 2 * lane + 64 * q;
-                            if (c + pos < n) {
-                                const double2 av = *reinterpret_cast<const double2*>(src + pos);
-                                const double2 uj = *reinterpret_cast<const double2*>(us + c + pos);
-                                acc = fma(av.y, uj.y, fma(av.x, uj.x, acc));
+                    for (int e = 0; e < TP_CW / 64; ++e) {
+                        uj[e] = col0 + 64 * e < nu ? *reinterpret_cast<const double2*>(us + col0 + 64 * e)   // 0 up to k, beyond n
+                                                   : make_double2(0.0, 0.0);
+                        cs[e] = make_double2(0.0, 0.0);
+                    }
+                    for (int q = first_row(c); q < Q; q += 8) {
+                        double pr[8];
+#pragma unroll
+                        for (int h = 0; h < 8 / TP_TR; ++h) {
+                            if (q + TP_TR * h < Q) {         // (warp-uniform) one tile = rows q + 2 h, q + 2 h + 1
+                                mbar_wait(&full_w[stage], phase);
+                                const double* src = ring_w + stage * TP_TILE + 2 * lane;
+#pragma unroll
+                                for (int r2 = 0; r2 < TP_TR; ++r2) {
+                                    const int rr = TP_TR * h + r2;
+                                    double acc = 0.0;
+                                    if (q + rr < Q) {
+                                        const int i = b + G * (q + rr);
+                                        const double ui = us[i];
+#pragma unroll
+                                        for (int e = 0; e < TP_CW / 64; ++e) {
+                                            const int col = col0 + 64 * e;
+                                            const double2 a = *reinterpret_cast<const double2*>(src + r2 * TP_CW + 64 * e);
+                                            // row side: lower triangle + diagonal; column side: strictly lower
+                                            acc = fma(col + 1 <= i ? a.y : 0.0, uj[e].y, fma(col <= i ? a.x : 0.0, uj[e].x, acc));
+                                            cs[e].x = fma(col < i ? a.x : 0.0, ui, cs[e].x);
+                                            cs[e].y = fma(col + 1 < i ? a.y : 0.0, ui, cs[e].y);
+                                        }
+                                    }
+                                    pr[rr] = acc;
+                                }
+                                __syncwarp();
+                                if (lane == 0 && !p_done) issue(stage);
+                                if (++stage == TP_S) { stage = 0; phase ^= 1u; }
+                            } else {
+#pragma unroll
+                                for (int r2 = 0; r2 < TP_TR; ++r2) pr[TP_TR * h + r2] = 0.0;
                             }
                         }
-                        __syncwarp();
-                        if (lane == 0 && issued < total) issue(stage);
-                        if (++stage == TP_S) { stage = 0; phase ^= 1u; }
+                        // transposing butterfly: 8 row sums over 32 lanes in 4 + 2 + 1 + 2 shuffles; lane 4 g holds row g
+                        const bool h16 = lane & 16, h8 = lane & 8, h4 = lane & 4;
+                        double t4[4], t2[2], t1;
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const double keep = h16 ? pr[e + 4] : pr[e], send = h16 ? pr[e] : pr[e + 4];
+                            t4[e] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+                        }
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            const double keep = h8 ? t4[e + 2] : t4[e], send = h8 ? t4[e] : t4[e + 2];
+                            t2[e] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+                        }
+                        {
+                            const double keep = h4 ? t2[1] : t2[0], send = h4 ? t2[0] : t2[1];
+                            t1 = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+                        }
+                        t1 += __shfl_xor_sync(0xffffffffu, t1, 2);
+                        t1 += __shfl_xor_sync(0xffffffffu, t1, 1);
+                        const int rg = (h16 ? 4 : 0) + (h8 ? 2 : 0) + (h4 ? 1 : 0);
+                        if ((lane & 3) == 0 && q + rg < Q) rowacc_w[q + rg] += t1;
                     }
-                    row_result(t, tp_warp_sum(acc));
+#pragma unroll
+                    for (int e = 0; e < TP_CW / 64; ++e) {
+                        if (col0 + 64 * e < nu) *reinterpret_cast<double2*>(part_col + (size_t)b * nu + col0 + 64 * e) = cs[e];
+                        dotc = fma(cs[e].x, uj[e].x, fma(cs[e].y, uj[e].y, dotc));
+                    }
                 }
+                __syncthreads();                             // every warp's row sums are complete
+                double mine_dot = dotc;
+                if (tid >= q0 && tid < Q) {                  // one CTA row per thread: row side of (A u)[i]
+                    double rsum = 0.0;
+#pragma unroll
+                    for (int w2 = 0; w2 < TP_WARPS; ++w2) rsum += rowacc[w2 * TP_RPC + tid];
+                    const int i = b + G * tid;
+                    pc[i] = rsum;
+                    mine_dot = fma(rsum, us[i], mine_dot);
+                }
+                dot0 = tp_warp_sum(mine_dot);
+                if (dot_lane)
+                    for (int t = 0; t < nrows; ++t) dotl = fma(rs[t * 2 * TP_NB + lane], us[first + t * n_gw], dotl);
             } else {
                 // flush: apply the NB pending pairs, write the block back, dot the TRUE rows with u.  The pairs' column sides
                 // are staged per block of LB columns by bulk copies, two blocks ahead (three stages in the ring's shared
@@ -456,7 +585,7 @@ bool tridiag_panel_supported(int n, int num_sms) {
 }
 
 cudaError_t launch_tridiag_panel(double* G, int n, double* d, double* e, double* ws, int num_sms, cudaStream_t stream) {
-    static_assert(TP_WARPS * TP_S * TP_CH >= 3 * 2 * TP_NB * TP_LB, "the flush staging buffers alias the ring");
+    static_assert(TP_WARPS * TP_S * TP_TILE >= 3 * 2 * TP_NB * TP_LB, "the flush staging buffers alias the ring");
     if (!tridiag_panel_supported(n, num_sms)) return cudaErrorInvalidValue;
     const size_t smem = tp_smem_doubles(n) * sizeof(double);
     cudaError_t err = cudaFuncSetAttribute(tridiag_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

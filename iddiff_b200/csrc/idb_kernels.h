@@ -154,6 +154,7 @@ cudaError_t launch_attention(const AttnParams& p, cudaStream_t stream);
 cudaError_t launch_row_gram(const float* X, int ld, int K, int D, double scale, double* colmean, double* G,
                             cudaStream_t stream);
 size_t spectrum_large_workspace_bytes(int n);
+size_t spectrum_large_fused_workspace_bytes(int n);
 cudaError_t launch_spectrum_large(double* G, int n, int n_out, float* sv, void* workspace, int num_sms,
                                   cudaStream_t stream, int classes = 0);
 

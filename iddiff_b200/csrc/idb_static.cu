@@ -1,7 +1,8 @@
 // An entry point that allocates NOTHING: the whole-GPU eigen-solver of idb_eig_large.cu with its workspace in a file-scope
 // device array instead of a caller-supplied buffer.  No counterpart in the reference: added
 // for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
-// forbid it).
+// forbid it).  It always takes the one-class fused tridiagonalisation kernel (the panel kernel's per-CTA partial-sum buffers
+// are megabytes).
 //
 // The array costs IDB_STATIC_SCRATCH_BYTES (768 KB) on every GPU that loads the library, until the process exits; that
 // bounds the matrix at n <= IDB_SPECTRUM_STATIC_MAX_N (4096).  Every call on a device shares the one array: calls that
@@ -16,7 +17,7 @@
 
 namespace {
 constexpr int STATIC_MAX_N = 4096;
-constexpr size_t STATIC_DOUBLES = (size_t)24 * STATIC_MAX_N;      // 768 KB >= spectrum_large_workspace_bytes(4096) = 681 KB
+constexpr size_t STATIC_DOUBLES = (size_t)24 * STATIC_MAX_N;      // 768 KB >= the fused kernel's workspace at n = 4096 (256 KB)
 constexpr int STATIC_MAX_DEVICES = 64;
 
 static __device__ __align__(256) double g_spectrum_scratch[STATIC_DOUBLES];
@@ -49,13 +50,13 @@ int idb_spectrum_large_static_max_n(void) { return STATIC_MAX_N; }
 
 int idb_spectrum_large_static(double* G, int n, int n_out, float* sv, void* stream) {
     if (!G || !sv || n <= 0 || n_out <= 0 || n_out > n) return idb::api_fail("idb_spectrum_large_static: bad argument");
-    if (n > STATIC_MAX_N || idb::spectrum_large_workspace_bytes(n) > sizeof(double) * STATIC_DOUBLES)
+    if (n > STATIC_MAX_N || idb::spectrum_large_fused_workspace_bytes(n) > sizeof(double) * STATIC_DOUBLES)
         return idb::api_fail("idb_spectrum_large_static: n exceeds IDB_SPECTRUM_STATIC_MAX_N = 4096 (the built-in 768 KB "
                              "scratch array); use idb_spectrum_large with a caller-supplied workspace");
     void* ws = nullptr;
     cudaError_t err = scratch_address(&ws);
     if (err != cudaSuccess) return idb::api_check(err, "idb_spectrum_large_static: cudaGetSymbolAddress");
-    return idb::api_check(idb::launch_spectrum_large(G, n, n_out, sv, ws, idb::api_num_sms(), static_cast<cudaStream_t>(stream), 0),
+    return idb::api_check(idb::launch_spectrum_large(G, n, n_out, sv, ws, idb::api_num_sms(), static_cast<cudaStream_t>(stream), 1),
                           "idb_spectrum_large_static");
 }
 
