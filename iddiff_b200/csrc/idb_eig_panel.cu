@@ -25,6 +25,7 @@
 #include "idb_kernels.h"
 #include <cooperative_groups.h>
 #include <math.h>
+#include <type_traits>
 
 namespace cg = cooperative_groups;
 
@@ -34,7 +35,6 @@ namespace {
 constexpr int TP_THREADS = 256;
 constexpr int TP_WARPS = TP_THREADS / 32;
 constexpr int TP_NB = 8;       // pending reflector pairs before a flush
-constexpr int TP_LB = 256;     // columns per staged block of a flush sweep (the pairs' column sides: 2 NB LB doubles = 32 KB)
 constexpr int TP_RMAX = 11;    // rows of the trailing block per warp (n <= TP_RMAX * gridDim.x * TP_WARPS = 13024 on 148 SMs)
 constexpr int TP_CW = 256;     // columns per chunk of a read-only sweep
 constexpr int TP_TR = 2;       // rows per tile there (one ring stage = TR rows x CW columns = 4 KB, two 2 KB bulk copies)
@@ -90,7 +90,6 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
     double* rowacc = rowsc + TP_WARPS * TP_RMAX * 2 * TP_NB; // [WARPS][RPC] row sums of a read-only sweep, per warp (= per column set)
     __shared__ __align__(8) uint64_t full[TP_WARPS * TP_S];
     __shared__ __align__(8) uint64_t xbar;
-    __shared__ __align__(8) uint64_t fbar[3];
     __shared__ double red[TP_WARPS];
     __shared__ double s_dot[TP_NDOT + 1];                   // pc.u, (w_p.u)_p, (v_p.u)_p of the previous sweep; [NDOT]: the column
                                                             // side of (A u)[k]
@@ -111,7 +110,6 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
     if (tid == 0) {
         for (int q = 0; q < TP_WARPS * TP_S; ++q) mbar_init(&full[q], 1);
         mbar_init(&xbar, 1);
-        for (int q = 0; q < 3; ++q) mbar_init(&fbar[q], 1);
         fence_barrier_init();
     }
     fence_proxy_async();
@@ -120,7 +118,6 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
     uint64_t* full_w = full + warp * TP_S;
     int stage = 0;             // the warp's ring position and phase bit run on across sweeps (strict round-robin)
     uint32_t phase = 0, xphase = 0;
-    int fcnt = 0;              // staged blocks consumed so far by the flush sweeps: stage fcnt % 3, phase (fcnt / 3) & 1
 
     // replicated scalar state (identical in every CTA)
     int r = 0;                 // pending pairs whose w is final (slots 0 .. r-1)
@@ -138,7 +135,7 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
         const int sl = (n - k - 1 + G - 1) / G;              // contiguous slices: coalesced reads of the G column partials
         const int j = k + 1 + b * sl + tid;
         const bool mine = tid < sl && j < n;
-        const bool sym_prev = have_prev && !prev_flushed;    // the previous sweep read the lower triangle only: (A u)[j] =
+        const bool sym_prev = have_prev;                     // every sweep walks the lower triangle only: (A u)[j] =
                                                              // pc[j] (row side) + sum over the CTAs of part_col[.][j]
         // every global load of the phase is issued up front: ONE L2 round trip.  (The pairs outstanding during the previous
         // sweep are exactly the r final ones unless that sweep flushed them, so w_new and x share the same loads.)
@@ -158,7 +155,7 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
 #pragma unroll
         for (int p = 0; p < TP_NB; ++p) { vj[p] = 0.0; wj[p] = 0.0; }
         if (mine) {
-            akj = A[(size_t)k * n + j];
+            akj = A[(size_t)j * n + k];                      // column k of the lower triangle (the only one kept up to date)
             if (have_prev) { pcj = pc[j]; upj = us[j]; }
 #pragma unroll
             for (int p = 0; p < TP_NB; ++p)
@@ -204,7 +201,7 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
                 for (int p = 0; p < r; ++p) corr += s_dot[1 + p] * s_dot[1 + TP_NB + p];
             kk = -0.5 * tau_prev * tau_prev * (s_dot[0] - 2.0 * corr);
             // w_new[k] of the previous column: tau (A_true u)[k] + kk u[k], redundantly in every thread
-            double base = pck + (prev_flushed ? 0.0 : s_dot[TP_NDOT]);
+            double base = pck + s_dot[TP_NDOT];
             if (!prev_flushed)
                 for (int p = 0; p < r; ++p) base -= s_vk[p] * s_dot[1 + p] + s_wk[p] * s_dot[1 + TP_NB + p];
             wk_new = fma(kk, upk, tau_prev * base);
@@ -319,35 +316,33 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
         // ---------------- sweep ----------------
         const bool flush = (r == TP_NB);
         if (tau != 0.0) {
-            const int cb0 = (k + 1) & ~63;
             double dot0 = 0.0;   // sum_i (A u)[i] u[i] over the warp's rows (identical in every lane)
             double dotl = 0.0;   // lane c < 2 NB: sum_i rs[.][c] u[i]  (v_p.u at c = p, w_p.u at c = NB + p)
             const bool dot_lane = lane < 2 * TP_NB && (lane & (TP_NB - 1)) < r;
-            auto row_result = [&](int t, double st) {
-                const int i = first + t * n_gw;
-                const double ui = us[i];
-                if (lane == 0) pc[i] = st;
-                dot0 = fma(st, ui, dot0);
-                if (!flush && dot_lane) dotl = fma(rs[t * 2 * TP_NB + lane], ui, dotl);
-            };
-            if (!flush) {
-                // read-only sweep over the LOWER TRIANGLE of the stale block (the block is symmetric: every element a_ij,
-                // i > j, serves (A u)[i] += a_ij u[j] and (A u)[j] += a_ij u[i]): 4 m^2 bytes instead of 8 m^2.  The CTA owns
-                // the rows i = b (mod G); its warps own 256-column chunks of those rows (dealt in snake order, so every warp
-                // gets the same share of the triangle) and stream them as tiles of 2 rows x 256 columns (two 2 KB bulk
-                // copies) through their rings.  Column-side sums stay in registers over all the CTA's rows of a chunk and
-                // go to part_col[b][.] (summed over the CTAs by the next phase A); row-side sums are reduced over the lanes
-                // eight rows at a time by a transposing butterfly and collected per warp.
+            // One sweep over the LOWER TRIANGLE of the trailing block (the block is symmetric: every element a_ij, i > j,
+            // serves (A u)[i] += a_ij u[j] and (A u)[j] += a_ij u[i]): 4 m^2 bytes read instead of 8 m^2, and only that
+            // triangle is ever kept up to date.  The CTA owns the rows i = b (mod G); its warps own CW-column chunks of those
+            // rows (dealt in snake order, so every warp gets the same share of the triangle) and stream them as 4 KB tiles
+            // (TR rows x CW columns, one bulk copy per row) through their rings.  Column-side sums stay in registers over all
+            // the CTA's rows of a chunk and go to part_col[b][.] (summed over the CTAs by the next phase A); row-side sums
+            // are reduced over the lanes eight rows at a time by a transposing butterfly and collected per warp.
+            //   read-only sweep (seven of eight): CW = 256, the stale block is only read;
+            //   flush sweep: CW = 128, the pending pairs' column sides of the chunk sit in registers, their row sides in
+            //   shared memory; every tile is brought up to date, written back from registers, and then used.
+            auto sweep = [&](auto cw_tag, auto flush_tag) {
+                constexpr int CW = decltype(cw_tag)::value;
+                constexpr bool FL = decltype(flush_tag)::value;
+                constexpr int TR = TP_TILE / CW, NE = CW / 64;
                 const int Q = (n - 1 - b) / G + 1;           // the CTA's rows i_q = b + G q < n
                 const int q0 = (b >= k + 1) ? 0 : (k + 1 - b + G - 1) / G;
-                const int c_lo = (k + 1) / TP_CW, c_hi = (n - 1) / TP_CW;
+                const int c_lo = (k + 1) / CW, c_hi = (n - 1) / CW;
                 double* rowacc_w = rowacc + warp * TP_RPC;
                 for (int q = lane; q < TP_RPC; q += 32) rowacc_w[q] = 0.0;
                 auto chunk_of = [&](int m) {                 // m-th chunk of this warp: w, 15 - w, 16 + w, 31 - w, ...
                     return c_lo + 2 * TP_WARPS * (m >> 1) + ((m & 1) ? 2 * TP_WARPS - 1 - warp : warp);
                 };
                 auto first_row = [&](int c) {                // first row of the CTA that reaches chunk c (i >= CW c, i >= k + 1)
-                    const int lo = TP_CW * c;
+                    const int lo = CW * c;
                     const int qc = (lo <= b) ? 0 : (lo - b + G - 1) / G;
                     return max(qc, q0);
                 };
@@ -355,14 +350,14 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
                 bool p_done = p_c > c_hi;
                 if (!p_done) { p_q = first_row(p_c); p_done = p_q >= Q; }
                 auto issue = [&](int st_i) {
-                    const int nr = min(TP_TR, Q - p_q);
-                    const int col = TP_CW * p_c;
-                    const uint32_t bytes = (uint32_t)min(TP_CW, n - col) * 8u;
+                    const int nr = min(TR, Q - p_q);
+                    const int col = CW * p_c;
+                    const uint32_t bytes = (uint32_t)min(CW, n - col) * 8u;
                     mbar_arrive_expect_tx(&full_w[st_i], bytes * nr);
                     const double* src = A + (size_t)(b + G * p_q) * n + col;
                     for (int rr = 0; rr < nr; ++rr)
-                        tma_bulk_g2s(ring_w + st_i * TP_TILE + rr * TP_CW, src + (size_t)rr * G * n, bytes, &full_w[st_i]);
-                    p_q += TP_TR;
+                        tma_bulk_g2s(ring_w + st_i * TP_TILE + rr * CW, src + (size_t)rr * G * n, bytes, &full_w[st_i]);
+                    p_q += TR;
                     if (p_q >= Q) {                          // next chunk of this warp (later chunks reach fewer rows)
                         p_c = chunk_of(++p_m);
                         if (p_c > c_hi) p_done = true;
@@ -381,36 +376,64 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
                 for (int m = 0;; ++m) {
                     const int c = chunk_of(m);
                     if (c > c_hi) break;
-                    const int col0 = TP_CW * c + 2 * lane;   // this lane's columns: col0 + 64 e, + 1
-                    double2 uj[TP_CW / 64], cs[TP_CW / 64];
+                    const int col0 = CW * c + 2 * lane;      // this lane's columns: col0 + 64 e, + 1
+                    const int q_first = first_row(c);
+                    double2 uj[NE], cs[NE];
+                    double2 vj[FL ? TP_NB : 1][NE], wj[FL ? TP_NB : 1][NE];   // flush: the pairs' column sides of this chunk
 #pragma unroll
-                    for (int e = 0; e < TP_CW / 64; ++e) {
-                        uj[e] = col0 + 64 * e < nu ? *reinterpret_cast<const double2*>(us + col0 + 64 * e)   // 0 up to k, beyond n
-                                                   : make_double2(0.0, 0.0);
+                    for (int e = 0; e < NE; ++e) {
+                        const bool in = col0 + 64 * e < nu;
+                        uj[e] = in ? *reinterpret_cast<const double2*>(us + col0 + 64 * e) : make_double2(0.0, 0.0);   // 0 up to k, beyond n
                         cs[e] = make_double2(0.0, 0.0);
+                        if (FL) {
+#pragma unroll
+                            for (int p = 0; p < TP_NB; ++p) {
+                                const bool ld = q_first < Q && col0 + 64 * e < n;
+                                vj[p][e] = ld ? *reinterpret_cast<const double2*>(Vbuf + (size_t)p * n + col0 + 64 * e) : make_double2(0.0, 0.0);
+                                wj[p][e] = ld ? *reinterpret_cast<const double2*>(Wbuf + (size_t)p * n + col0 + 64 * e) : make_double2(0.0, 0.0);
+                            }
+                        }
                     }
-                    for (int q = first_row(c); q < Q; q += 8) {
+                    for (int q = q_first; q < Q; q += 8) {
                         double pr[8];
 #pragma unroll
-                        for (int h = 0; h < 8 / TP_TR; ++h) {
-                            if (q + TP_TR * h < Q) {         // (warp-uniform) one tile = rows q + 2 h, q + 2 h + 1
+                        for (int h = 0; h < 8 / TR; ++h) {
+                            if (q + TR * h < Q) {            // (warp-uniform) one tile = rows q + TR h ... + TR - 1
                                 mbar_wait(&full_w[stage], phase);
                                 const double* src = ring_w + stage * TP_TILE + 2 * lane;
 #pragma unroll
-                                for (int r2 = 0; r2 < TP_TR; ++r2) {
-                                    const int rr = TP_TR * h + r2;
+                                for (int r2 = 0; r2 < TR; ++r2) {
+                                    const int rr = TR * h + r2;
                                     double acc = 0.0;
                                     if (q + rr < Q) {
                                         const int i = b + G * (q + rr);
                                         const double ui = us[i];
+                                        double2 a[NE];
 #pragma unroll
-                                        for (int e = 0; e < TP_CW / 64; ++e) {
+                                        for (int e = 0; e < NE; ++e) a[e] = *reinterpret_cast<const double2*>(src + r2 * CW + 64 * e);
+                                        if (FL) {
+                                            // row sides of CTA row q + rr: warp (q + rr) mod 8 loaded them in phase B at its slot (q + rr - q0) / 8
+                                            const double* rsq = rowsc + (((q + rr) & (TP_WARPS - 1)) * TP_RMAX + ((q + rr - q0) >> 3)) * 2 * TP_NB;
+#pragma unroll
+                                            for (int p = 0; p < TP_NB; ++p) {
+                                                const double vi = rsq[p], wi = rsq[TP_NB + p];
+#pragma unroll
+                                                for (int e = 0; e < NE; ++e) {
+                                                    a[e].x = a[e].x - vi * wj[p][e].x - wi * vj[p][e].x;
+                                                    a[e].y = a[e].y - vi * wj[p][e].y - wi * vj[p][e].y;
+                                                }
+                                            }
+#pragma unroll
+                                            for (int e = 0; e < NE; ++e)
+                                                if (col0 + 64 * e < n) *reinterpret_cast<double2*>(A + (size_t)i * n + col0 + 64 * e) = a[e];
+                                        }
+#pragma unroll
+                                        for (int e = 0; e < NE; ++e) {
                                             const int col = col0 + 64 * e;
-                                            const double2 a = *reinterpret_cast<const double2*>(src + r2 * TP_CW + 64 * e);
                                             // row side: lower triangle + diagonal; column side: strictly lower
-                                            acc = fma(col + 1 <= i ? a.y : 0.0, uj[e].y, fma(col <= i ? a.x : 0.0, uj[e].x, acc));
-                                            cs[e].x = fma(col < i ? a.x : 0.0, ui, cs[e].x);
-                                            cs[e].y = fma(col + 1 < i ? a.y : 0.0, ui, cs[e].y);
+                                            acc = fma(col + 1 <= i ? a[e].y : 0.0, uj[e].y, fma(col <= i ? a[e].x : 0.0, uj[e].x, acc));
+                                            cs[e].x = fma(col < i ? a[e].x : 0.0, ui, cs[e].x);
+                                            cs[e].y = fma(col + 1 < i ? a[e].y : 0.0, ui, cs[e].y);
                                         }
                                     }
                                     pr[rr] = acc;
@@ -420,7 +443,7 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
                                 if (++stage == TP_S) { stage = 0; phase ^= 1u; }
                             } else {
 #pragma unroll
-                                for (int r2 = 0; r2 < TP_TR; ++r2) pr[TP_TR * h + r2] = 0.0;
+                                for (int r2 = 0; r2 < TR; ++r2) pr[TR * h + r2] = 0.0;
                             }
                         }
                         // transposing butterfly: 8 row sums over 32 lanes in 4 + 2 + 1 + 2 shuffles; lane 4 g holds row g
@@ -446,11 +469,12 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
                         if ((lane & 3) == 0 && q + rg < Q) rowacc_w[q + rg] += t1;
                     }
 #pragma unroll
-                    for (int e = 0; e < TP_CW / 64; ++e) {
+                    for (int e = 0; e < NE; ++e) {
                         if (col0 + 64 * e < nu) *reinterpret_cast<double2*>(part_col + (size_t)b * nu + col0 + 64 * e) = cs[e];
                         dotc = fma(cs[e].x, uj[e].x, fma(cs[e].y, uj[e].y, dotc));
                     }
                 }
+                if (FL) fence_proxy_async();                 // the next sweeps' bulk copies read what this one stored
                 __syncthreads();                             // every warp's row sums are complete
                 double mine_dot = dotc;
                 if (tid >= q0 && tid < Q) {                  // one CTA row per thread: row side of (A u)[i]
@@ -462,94 +486,13 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
                     mine_dot = fma(rsum, us[i], mine_dot);
                 }
                 dot0 = tp_warp_sum(mine_dot);
+            };
+            if (!flush) {
+                sweep(std::integral_constant<int, 256>{}, std::false_type{});
                 if (dot_lane)
                     for (int t = 0; t < nrows; ++t) dotl = fma(rs[t * 2 * TP_NB + lane], us[first + t * n_gw], dotl);
             } else {
-                // flush: apply the NB pending pairs, write the block back, dot the TRUE rows with u.  The pairs' column sides
-                // are staged per block of LB columns by bulk copies, two blocks ahead (three stages in the ring's shared
-                // memory, idle during a flush); a warp's rows are walked in 64-column chunks, the loads of chunk c + 1 in
-                // flight while chunk c is updated and stored
-                double s[TP_RMAX];
-#pragma unroll
-                for (int t = 0; t < TP_RMAX; ++t) s[t] = 0.0;
-                constexpr int CPB = TP_LB / 64;              // chunks per staged block
-                const int nchunk = (n - cb0 + 63) >> 6;
-                const int nblk = (nchunk + CPB - 1) / CPB;
-                const size_t rstride = (size_t)n_gw * n;
-                double* Arow = A + (size_t)first * n + cb0 + 2 * lane;   // (not dereferenced when the warp owns no row)
-                auto stage_block = [&](int blk, int cnt) {   // thread 0: V, W columns of block blk -> stage cnt % 3
-                    const int c0 = cb0 + blk * TP_LB;
-                    const uint32_t bytes = (uint32_t)min(TP_LB, n - c0) * 8u;
-                    const int st_i = cnt % 3;
-                    double* dst = ring + (size_t)st_i * 2 * TP_NB * TP_LB;
-                    mbar_arrive_expect_tx(&fbar[st_i], 2 * TP_NB * bytes);
-                    for (int p = 0; p < TP_NB; ++p) {
-                        tma_bulk_g2s(dst + p * TP_LB, Vbuf + (size_t)p * n + c0, bytes, &fbar[st_i]);
-                        tma_bulk_g2s(dst + (TP_NB + p) * TP_LB, Wbuf + (size_t)p * n + c0, bytes, &fbar[st_i]);
-                    }
-                };
-                auto load = [&](double2 (&a)[TP_RMAX], int c) {
-#pragma unroll
-                    for (int t = 0; t < TP_RMAX; ++t)
-                        if (t < nrows && cb0 + 64 * c + 2 * lane < n)
-                            a[t] = *reinterpret_cast<const double2*>(Arow + t * rstride + 64 * c);
-                };
-                auto process = [&](double2 (&a)[TP_RMAX], int c) {
-                    const int blk = c / CPB, within = c % CPB;
-                    if (within == 0) {
-                        __syncthreads();                     // every warp is done with block blk - 1: its stage is free
-                        if (tid == 0 && blk + 2 < nblk) stage_block(blk + 2, fcnt + 2);
-                        mbar_wait(&fbar[fcnt % 3], (uint32_t)(fcnt / 3) & 1u);
-                    }
-                    const double* vbs = ring + (size_t)(fcnt % 3) * 2 * TP_NB * TP_LB;
-                    const double* wbs = vbs + TP_NB * TP_LB;
-                    const int qq = within * 64 + 2 * lane;
-                    if (cb0 + 64 * c + 2 * lane < n) {
-#ifdef TP_EXP_PAIRS
-                        constexpr int NPAIR = TP_EXP_PAIRS;   // timing experiment only (wrong results)
-#else
-                        constexpr int NPAIR = TP_NB;
-#endif
-#pragma unroll
-                        for (int p = 0; p < NPAIR; ++p) {
-                            const double2 vj = *reinterpret_cast<const double2*>(vbs + p * TP_LB + qq);
-                            const double2 wj = *reinterpret_cast<const double2*>(wbs + p * TP_LB + qq);
-#pragma unroll
-                            for (int t = 0; t < TP_RMAX; ++t) {
-                                if (t < nrows) {
-                                    const double vi = rs[t * 2 * TP_NB + p], wi = rs[t * 2 * TP_NB + TP_NB + p];
-                                    a[t].x = a[t].x - vi * wj.x - wi * vj.x;
-                                    a[t].y = a[t].y - vi * wj.y - wi * vj.y;
-                                }
-                            }
-                        }
-                        const double2 uj = *reinterpret_cast<const double2*>(us + cb0 + 64 * c + 2 * lane);
-#pragma unroll
-                        for (int t = 0; t < TP_RMAX; ++t) {
-                            if (t < nrows) {
-                                *reinterpret_cast<double2*>(Arow + t * rstride + 64 * c) = a[t];
-                                s[t] = fma(a[t].y, uj.y, fma(a[t].x, uj.x, s[t]));
-                            }
-                        }
-                    }
-                    if (within == CPB - 1 || c == nchunk - 1) ++fcnt;
-                };
-                if (tid == 0) {
-                    stage_block(0, fcnt);
-                    if (nblk > 1) stage_block(1, fcnt + 1);
-                }
-                double2 a0[TP_RMAX], a1[TP_RMAX];
-                load(a0, 0);
-                for (int c = 0; c < nchunk; c += 2) {
-                    if (c + 1 < nchunk) load(a1, c + 1);
-                    process(a0, c);
-                    if (c + 2 < nchunk) load(a0, c + 2);
-                    if (c + 1 < nchunk) process(a1, c + 1);
-                }
-                fence_proxy_async();                         // the next bulk copies overwrite what this sweep staged / read what it wrote
-#pragma unroll
-                for (int t = 0; t < TP_RMAX; ++t)
-                    if (t < nrows) row_result(t, tp_warp_sum(s[t]));
+                sweep(std::integral_constant<int, 128>{}, std::true_type{});
             }
             TP_TICK(flush ? 6 : 3);
             // the dot products of the next phase A: pc.u, (w_p.u)_p at [1 + p], (v_p.u)_p at [1 + NB + p]
@@ -585,7 +528,6 @@ bool tridiag_panel_supported(int n, int num_sms) {
 }
 
 cudaError_t launch_tridiag_panel(double* G, int n, double* d, double* e, double* ws, int num_sms, cudaStream_t stream) {
-    static_assert(TP_WARPS * TP_S * TP_TILE >= 3 * 2 * TP_NB * TP_LB, "the flush staging buffers alias the ring");
     if (!tridiag_panel_supported(n, num_sms)) return cudaErrorInvalidValue;
     const size_t smem = tp_smem_doubles(n) * sizeof(double);
     cudaError_t err = cudaFuncSetAttribute(tridiag_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
