@@ -242,8 +242,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tridiag_coop_kernel(double* __r
 // applied on the fly when its reflector is formed.  (v, w, u) must sit in shared memory for the sweep: three
 // n-vectors fit one SM up to n = TCF_MAX_N; above that
 constexpr int TCF_MAX_N = 9000;
-constexpr int PANEL_MIN_N = 6144;   // the automatic choice takes the panel kernel (variant 3) from here on: measured 286 ms vs 300
-                                    // at n = 6144, 536 vs 645 at 8192, 1.39 s vs 1.91 at 12288 (126 vs 107 ms at 4096: fused stays)
+constexpr int PANEL_MIN_N = 3584;   // the automatic choice takes the panel kernel (variant 3, idb_eig_panel.cu) from here on; measured
+                                    // fused / panel: n = 3072 59 / 63 ms, 4096 106 / 92, 6144 298 / 181, 8192 645 / 302 (tridiag. only),
+                                    // 12288 1916 / 778 ms
 // the 64-wide column chunks of the trailing block are dealt round-robin over C classes of CTAs, a CTA of class c keeps
 // only ITS chunks of (v, w, u) in shared memory (3 n / C doubles) and produces the partial products p_c[i]; the full
 // reflector of every step lives in a double-buffered global copy (ubuf, written by CTA 0, L2-resident) and w is

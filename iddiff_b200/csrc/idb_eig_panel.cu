@@ -1,26 +1,33 @@
 // Panel (deferred-update) Householder tridiagonalisation of ONE large symmetric fp64 matrix by the whole GPU.
 //
-// The fused kernel of idb_eig_large.cu reads AND writes the trailing block once per eliminated column (16 m^2 bytes): it is
-// a level-2 algorithm at its HBM roofline (5.1 TB/s at n = 12288).  This kernel defers the rank-2 updates the way LAPACK's
-// dlatrd does: the reflector pairs (v_p, w_p) of up to NB columns stay PENDING while the trailing block in HBM is stale,
-//     A_true = A_stale - sum_p (v_p w_p^T + w_p v_p^T),
-// a column's symmetric product is taken with the stale block and corrected with 2 NB dot products,
-//     A_true u = A_stale u - sum_p (v_p (w_p.u) + w_p (v_p.u)),
-// and only every NB-th column's sweep applies all pending pairs and writes the block back: (8 + 8 / NB) m^2 bytes per column
-// instead of 16 -- 9 at NB = 8.  Replaces torch.linalg.svd at dim_reduction.py:197-198 for image-sized score matrices
-// (same role as tridiag_fused_cls_kernel; selected by launch_spectrum_large for even n >= 8192).
+// The fused kernel of idb_eig_large.cu reads AND writes the whole trailing block once per eliminated column (16 m^2 bytes): a
+// level-2 algorithm at its HBM roofline (5.1 TB/s at n = 12288).  This kernel cuts the traffic to 4.5 m^2 bytes per column:
+//   * deferred updates, the way LAPACK's dlatrd does: the reflector pairs (v_p, w_p) of up to NB = 8 columns stay PENDING while
+//     the trailing block in HBM is stale,  A_true = A_stale - sum_p (v_p w_p^T + w_p v_p^T);  a column's symmetric product is
+//     taken with the stale block and corrected with 2 NB dot products,
+//         A_true u = A_stale u - sum_p (v_p (w_p.u) + w_p (v_p.u)),
+//     and only every NB-th column's sweep applies the pending pairs and writes the block back;
+//   * symmetry: only the LOWER TRIANGLE is ever read or kept up to date.  Every element a_ij, i > j, serves both
+//     (A u)[i] += a_ij u[j] (row side) and (A u)[j] += a_ij u[i] (column side) from one load.
+// Per column: 7/8 x 4 m^2 (read-only sweeps) + 1/8 x 8 m^2 (flush sweeps: read + write) = 4.5 m^2 bytes.  Replaces
+// torch.linalg.svd at dim_reduction.py:197-198 for image-sized score matrices (same role as tridiag_fused_cls_kernel; taken
+// by launch_spectrum_large for even n >= 3584).  Measured (B200): n = 12288 0.69 s (fused kernel 1.83 s), 8192 0.30 s, 4096 77 ms.
 //
-// Work split per column k (cooperative launch, one CTA per SM, TWO grid synchronisations):
-//   phase A  every CTA owns a cyclic SLICE of the indices j > k: finalises the previous column's w there
-//            (w = tau (A_stale u - corrections) + kk u) and writes its slice of row k of A_true;        -> grid sync
+// Work split per column k (cooperative launch, one CTA per SM, 8 warps, TWO grid synchronisations):
+//   phase A  every CTA owns a contiguous SLICE of the indices j > k: sums the CTAs' column-side partials of the previous
+//            sweep, finalises the previous column's w there (w = tau (A_stale u - corrections) + kk u) and writes its slice
+//            of row k of A_true (read as column k of the lower triangle);                                -> grid sync
 //   phase B  every CTA pulls the whole row into shared memory with one bulk copy, forms the norm, (tau, beta) and the
 //            reflector u redundantly (u lives in shared memory only: 8 n bytes);
-//   sweep    rows are owned by fixed warps (row i -> CTA i mod G, warp (i / G) mod 8).  Seven sweeps of eight only READ the
-//            stale block: every warp streams its rows through a private ring of 1-D bulk copies (cp.async.bulk + mbarrier
-//            transaction counts, 6 x 2 KB per warp = 96 KB in flight per SM with no register cost) and dots them with u.
-//            The eighth stages the pending pairs' column sides per block of LB columns, applies them to all of the warp's
-//            rows in registers and writes the block back.  Every sweep also accumulates the dot products the next phase A
-//            needs (pc.u, w_p.u, v_p.u).                                                                -> grid sync
+//   sweep    the CTA owns the rows i = b (mod G); its warps own column chunks of those rows (dealt in snake order so every
+//            warp gets the same share of the triangle) and stream them as 4 KB tiles through private rings of 1-D bulk copies
+//            (cp.async.bulk + mbarrier transaction counts, 3 stages per warp = 96 KB in flight per SM at no register cost).
+//            Column-side sums stay in registers over all the CTA's rows of a chunk and go to part_col[b][.]; row-side sums
+//            are reduced over the lanes eight rows at a time by a transposing butterfly.  A flush sweep additionally holds
+//            the pending pairs' column sides of its chunk in registers (row sides in shared memory), brings every tile up
+//            to date before using it and writes it back from registers.  Every sweep also produces the dot products the
+//            next phase A needs (u.(A u), w_p.u, v_p.u).                                                 -> grid sync
+// tools/panel_profile.sh builds the kernel with per-phase clock64 timers (-DTP_PROFILE).
 #include "idb_common.cuh"
 #include "idb_kernels.h"
 #include <cooperative_groups.h>
