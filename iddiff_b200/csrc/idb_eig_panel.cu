@@ -176,13 +176,19 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tridiag_panel_kernel(double* __
 #pragma unroll
             for (int e = 0; e < JL; ++e) acc[e] = 0.0;
             const int j0 = k + 1 + b * sl;
-#pragma unroll 4
-            for (int q = warp; q < G; q += TP_WARPS) {
+            constexpr int QL = (32 * TP_GL) / TP_WARPS;      // CTAs per warp
+            double pv[QL][JL];                               // every load is issued before the first add (clamped addresses,
+#pragma unroll                                               // masked values): one L2 round trip
+            for (int qi = 0; qi < QL; ++qi) {
+                const int q = min(warp + TP_WARPS * qi, G - 1);
 #pragma unroll
-                for (int e = 0; e < JL; ++e) {
-                    const int jj = lane + 32 * e;
-                    if (jj < sl && j0 + jj < n) acc[e] += part_col[(size_t)q * nu + j0 + jj];
-                }
+                for (int e = 0; e < JL; ++e) pv[qi][e] = part_col[(size_t)q * nu + min(j0 + lane + 32 * e, n - 1)];
+            }
+#pragma unroll
+            for (int qi = 0; qi < QL; ++qi) {
+                const bool qok = warp + TP_WARPS * qi < G;
+#pragma unroll
+                for (int e = 0; e < JL; ++e) acc[e] += (qok && lane + 32 * e < sl) ? pv[qi][e] : 0.0;
             }
 #pragma unroll
             for (int e = 0; e < JL; ++e)
