@@ -163,11 +163,12 @@ __device__ __forceinline__ uint32_t pack_fp16(__half a, __half b) {
 // Two consecutive values -> (hi pair, lo pair) 32-bit words in the operand format fmt (0 = bf16, 1 = fp16).
 __device__ __forceinline__ void split_pair16(float v0, float v1, int fmt, uint32_t& hi, uint32_t& lo) {
     if (fmt) {
-        __half h0, l0, h1, l1;
-        split_fp16(v0, h0, l0);
-        split_fp16(v1, h1, l1);
-        hi = pack_fp16(h0, h1);
-        lo = pack_fp16(l0, l1);
+        // packed conversions (one F2FP per pair instead of two F2F); same round-to-nearest results as split_fp16
+        const __half2 h = __floats2half2_rn(v0, v1);
+        const float2 hf = __half22float2(h);
+        const __half2 l = __floats2half2_rn(v0 - hf.x, v1 - hf.y);
+        hi = *reinterpret_cast<const uint32_t*>(&h);
+        lo = *reinterpret_cast<const uint32_t*>(&l);
     } else {
         const __nv_bfloat16 h0 = __float2bfloat16_rn(v0), h1 = __float2bfloat16_rn(v1);
         const __nv_bfloat16 l0 = __float2bfloat16_rn(v0 - __bfloat162float(h0));

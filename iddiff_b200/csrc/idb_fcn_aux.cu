@@ -7,17 +7,18 @@
 namespace idb {
 
 // One thread = one 16-byte output chunk = 8 consecutive columns of one perturbation row.
+// IDX = uint32_t when the chunk count fits 31 bits (every case benched): 32-bit divisions instead of three 64-bit ones.
+template <typename IDX>
 __global__ void __launch_bounds__(256) perturb_kernel(const PerturbParams p) {
-    const int chunks = p.Dp >> 3;
+    const IDX chunks = (IDX)(p.Dp >> 3);
     // slab rows: anchor-major, Kp rows per anchor (Kp = K: densely packed), padded with zero rows to a multiple of 128
     const long long Mtot = p.d_hi ? (((long long)p.n_anchors * p.Kp + 127) / 128) * 128 : (long long)p.n_anchors * p.Kp;
-    const long long total = Mtot * chunks;
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
-         i += (long long)gridDim.x * blockDim.x) {
+    const IDX total = (IDX)(Mtot * (long long)chunks);
+    for (IDX i = (IDX)blockIdx.x * (IDX)blockDim.x + threadIdx.x; i < total; i += (IDX)gridDim.x * (IDX)blockDim.x) {
         const int ch = (int)(i % chunks);
-        const long long m = i / chunks;
-        const int k = (int)(m % p.Kp);
-        const int a = (int)(m / p.Kp);
+        const IDX m = i / chunks;
+        const int k = (int)(m % (IDX)p.Kp);
+        const int a = (int)(m / (IDX)p.Kp);
         const int c0 = ch << 3;
         float dev[8];
 #pragma unroll
@@ -70,7 +71,8 @@ cudaError_t launch_perturb(const PerturbParams& p, cudaStream_t stream) {
     if (total <= 0) return cudaSuccess;
     long long blocks = (total + 255) / 256;
     if (blocks > 148LL * 64) blocks = 148LL * 64;
-    perturb_kernel<<<(int)blocks, 256, 0, stream>>>(p);
+    if (total + blocks * 256 < 0x7fffffffLL) perturb_kernel<uint32_t><<<(int)blocks, 256, 0, stream>>>(p);
+    else perturb_kernel<unsigned long long><<<(int)blocks, 256, 0, stream>>>(p);
     return cudaGetLastError();
 }
 
