@@ -117,3 +117,34 @@ def test_spectrum_large_at_baseline_sizes(n):
         del A
     del G, ws
     torch.cuda.empty_cache()
+
+
+@pytest.mark.parametrize("n", [3586, 5002, 9002])
+def test_panel_kernel_at_ragged_sizes(n):
+    """The production entry point takes the panel kernel for every even n >= 3584: sizes that are not multiples of the
+    64-column chunk, of the 128 / 256-column tiles or of the CTA count (ragged last chunk, ragged row ownership), and one
+    above the fused kernel's one-class limit, against cuSOLVER fp64 eigenvalues; n_out < n returns the leading values.
+    Rank-deficient on purpose (K = n - 40 rows): the trailing 40 singular values are structural zeros."""
+    from iddiff_b200 import _lib
+    g = torch.Generator(device="cuda").manual_seed(n)
+    B = torch.randn(n, n - 40, generator=g, device="cuda", dtype=torch.float64)
+    B *= torch.logspace(0, -2, n, dtype=torch.float64, device="cuda")[:, None]
+    G = B @ B.T
+    del B
+    want = torch.linalg.eigvalsh(G).clamp_min(0).sqrt().flip(0).cpu().numpy()
+    lib = _lib.load()
+    ws = torch.empty(lib.idb_spectrum_large_workspace_bytes(n), dtype=torch.uint8, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    n_out = n - 41
+    out = {}
+    for variant in (0, 3):
+        A = G.clone()
+        sv = torch.full((n_out,), -1.0, dtype=torch.float32, device="cuda")
+        _lib.call("idb_spectrum_large_variant", A.data_ptr(), n, n_out, sv.data_ptr(), ws.data_ptr(), variant, st)
+        torch.cuda.synchronize()
+        out[variant] = sv.cpu().numpy().astype(np.float64)
+        assert np.all(np.diff(out[variant]) <= 0)
+        np.testing.assert_allclose(out[variant], want[:n_out], rtol=1e-5, atol=1e-7 * want[0])
+    assert np.array_equal(out[0], out[3])               # the automatic choice IS the panel kernel at these sizes
+    del G, ws
+    torch.cuda.empty_cache()
