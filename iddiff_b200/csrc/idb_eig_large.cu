@@ -5,7 +5,7 @@
 //                          (north_star: "S.S^T or S^T.S, whichever side is smaller")
 //   tridiag_coop_kernel    Householder tridiagonalisation of ONE n x n fp64 matrix by the whole GPU: a cooperative
 //                          (grid-synchronised) kernel, trailing block streamed from L2/HBM by every SM
-//   bisect_large_kernel    Sturm bisection, 256 eigenvalues per CTA, d / e^2 in shared memory
+//   bisect_large_kernel    Sturm multisection, one warp per eigenvalue (32 probes per round), d / e^2 in shared memory
 //
 // Replaces torch.linalg.svd at dim_reduction.py:197-198 (LAPACK gesdd of the K x D matrix on the host: 16 s at
 // 4096 x 12288).  Roofline: memory-bound -- per eliminated column the trailing m x m block is read once
@@ -451,46 +451,60 @@ __device__ __forceinline__ int sturm_count_l(const double* __restrict__ d, const
     return cnt;
 }
 
-// ---------------------------------- bisection over many CTAs --------------------------------
-__global__ void __launch_bounds__(256) bisect_large_kernel(const double* __restrict__ dg, const double* __restrict__ eg,
-                                                           int n, int n_out, float* __restrict__ sv) {
+// ---------------------------------- multisection over many CTAs -----------------------------
+// One WARP per eigenvalue: every round the 32 lanes evaluate the Sturm count at 32 interior points of the current interval
+// and the interval shrinks 33-fold (5 bits per round instead of the 1 bit of a bisection step: ~8 rounds of n dependent
+// steps from the Gershgorin interval to fp32 resolution instead of ~40-60).  The recurrence is sequential in i, so the time
+// of this stage is rounds x n x (latency of one step); the extra evaluations ride on parallelism the one-thread-per-
+// eigenvalue version left idle (n = 4096: 16 CTAs on 148 SMs).  d / e^2 in shared memory, 32 eigenvalues per CTA.
+constexpr int BL_THREADS = 1024;
+constexpr int BL_WARPS = BL_THREADS / 32;
+
+__global__ void __launch_bounds__(BL_THREADS, 1) bisect_large_kernel(const double* __restrict__ dg, const double* __restrict__ eg,
+                                                                     int n, int n_out, float* __restrict__ sv) {
     extern __shared__ __align__(16) double bl_smem[];
     double* d = bl_smem;
     double* e2 = bl_smem + n;
-    __shared__ double s_lo[8], s_hi[8], s_em[8];
-    double lo = 1e300, hi = -1e300, em = 0.0;
-    for (int i = threadIdx.x; i < n; i += 256) {
+    __shared__ double s_lo[BL_WARPS], s_hi[BL_WARPS];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double lo = 1e300, hi = -1e300;
+    for (int i = threadIdx.x; i < n; i += BL_THREADS) {
         const double di = dg[i], ei = eg[i];
         d[i] = di;
         e2[i] = ei * ei;
         const double el = i > 0 ? fabs(eg[i - 1]) : 0.0, er = i + 1 < n ? fabs(ei) : 0.0;
         lo = fmin(lo, di - el - er);
         hi = fmax(hi, di + el + er);
-        em = fmax(em, ei * ei);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         lo = fmin(lo, __shfl_xor_sync(0xffffffffu, lo, o));
         hi = fmax(hi, __shfl_xor_sync(0xffffffffu, hi, o));
-        em = fmax(em, __shfl_xor_sync(0xffffffffu, em, o));
     }
-    if ((threadIdx.x & 31) == 0) { s_lo[threadIdx.x >> 5] = lo; s_hi[threadIdx.x >> 5] = hi; s_em[threadIdx.x >> 5] = em; }
+    if (lane == 0) { s_lo[warp] = lo; s_hi[warp] = hi; }
     __syncthreads();
-    for (int q = 0; q < 8; ++q) { lo = fmin(lo, s_lo[q]); hi = fmax(hi, s_hi[q]); em = fmax(em, s_em[q]); }
+    for (int q = 0; q < BL_WARPS; ++q) { lo = fmin(lo, s_lo[q]); hi = fmax(hi, s_hi[q]); }
     const double span = fmax(fabs(lo), fabs(hi));
     lo = lo - 1e-14 * span - 1e-300;
     hi = hi + 1e-14 * span + 1e-300;
-    const int k = blockIdx.x * 256 + threadIdx.x;   // k-th smallest eigenvalue
-    if (k >= n || n - 1 - k >= n_out) return;
+    const int k = n - 1 - (blockIdx.x * BL_WARPS + warp);   // this warp's eigenvalue: the k-th smallest (largest ones first)
+    if (k < 0 || n - 1 - k >= n_out) return;
     const double atol = 1e-17 * fmax(fabs(lo), fabs(hi));
-    for (int it = 0; it < 200; ++it) {
-        const double mid = 0.5 * (lo + hi);
+    for (int it = 0; it < 64; ++it) {
         // the result is rounded to fp32 after a square root: 4e-10 relative on lambda is 3e-3 ulp of sqrt(lambda)
-        if (hi - lo <= fmax(atol, 4e-10 * fmax(fabs(lo), fabs(hi))) || mid <= lo || mid >= hi) break;
-        const int cnt = sturm_count_l(d, e2, n, mid);
-        if (cnt > k) hi = mid; else lo = mid;
+        if (hi - lo <= fmax(atol, 4e-10 * fmax(fabs(lo), fabs(hi)))) break;
+        const double x = fma((hi - lo) * (1.0 / 33.0), (double)(lane + 1), lo);   // lo < x_0 < ... < x_31 < hi (up to rounding)
+        const bool above = sturm_count_l(d, e2, n, x) > k;   // x is above the k-th eigenvalue
+        const unsigned m = __ballot_sync(0xffffffffu, above);
+        const int f = m ? __ffs(m) - 1 : 32;                  // first probe above it
+        const double x_hi = __shfl_sync(0xffffffffu, x, f < 32 ? f : 31);
+        const double x_lo = __shfl_sync(0xffffffffu, x, f > 0 ? f - 1 : 0);
+        const double nlo = f > 0 ? fmax(x_lo, lo) : lo, nhi = f < 32 ? fmin(x_hi, hi) : hi;
+        if (!(nhi - nlo < hi - lo)) break;                    // no progress: the interval is at the resolution of fp64
+        lo = nlo;
+        hi = nhi;
     }
-    sv[n - 1 - k] = (float)sqrt(fmax(0.5 * (lo + hi), 0.0));
+    if (lane == 0) sv[n - 1 - k] = (float)sqrt(fmax(0.5 * (lo + hi), 0.0));
 }
 
 // d[n], e[n], partial products [2][classes <= 2][n], reflectors [2][n]
@@ -570,7 +584,7 @@ cudaError_t launch_spectrum_large(double* G, int n, int n_out, float* sv, void* 
     const size_t smem = (size_t)2 * n * sizeof(double);
     err = cudaFuncSetAttribute(bisect_large_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
-    bisect_large_kernel<<<(n + 255) / 256, 256, smem, stream>>>(d, e, n, n_out, sv);
+    bisect_large_kernel<<<(n_out + BL_WARPS - 1) / BL_WARPS, BL_THREADS, smem, stream>>>(d, e, n, n_out, sv);
     return cudaGetLastError();
 }
 
