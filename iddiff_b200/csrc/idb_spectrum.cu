@@ -154,20 +154,28 @@ __global__ void __launch_bounds__(160) center_gram40_kernel(const float* __restr
         mua[q] = ca < D ? mu[ca] : 0.0;
         mub[q] = cb < D ? mu[cb] : 0.0;
     }
-    for (int k0 = 0; k0 < K; k0 += 16) {
+    // the next 16-row slab is fetched into registers while the tensor cores work on the current one
+    float fa[4], fb[4];
+    auto fetch = [&](int k0) {
         const int k = k0 + skk;
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
             const int ca = ti * CG40 + sc + q, cb = tj * CG40 + sc + q;
-            double va = 0.0, vb = 0.0;
-            if (k < K) {
-                if (ca < D) va = ((double)__ldg(Xa + (size_t)k * ld + ca) - mua[q]) * scale;
-                if (cb < D) vb = ((double)__ldg(Xa + (size_t)k * ld + cb) - mub[q]) * scale;
-            }
-            sA[skk][sc + q] = va;
-            sB[skk][sc + q] = vb;
+            fa[q] = (k < K && ca < D) ? __ldg(Xa + (size_t)k * ld + ca) : 0.f;
+            fb[q] = (k < K && cb < D) ? __ldg(Xa + (size_t)k * ld + cb) : 0.f;
+        }
+    };
+    fetch(0);
+    for (int k0 = 0; k0 < K; k0 += 16) {
+        const bool kin = k0 + skk < K;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int ca = ti * CG40 + sc + q, cb = tj * CG40 + sc + q;
+            sA[skk][sc + q] = (kin && ca < D) ? ((double)fa[q] - mua[q]) * scale : 0.0;
+            sB[skk][sc + q] = (kin && cb < D) ? ((double)fb[q] - mub[q]) * scale : 0.0;
         }
         __syncthreads();
+        if (k0 + 16 < K) fetch(k0 + 16);
 #pragma unroll
         for (int k4 = 0; k4 < 16; k4 += 4) {
             const double af = sA[k4 + fk][i0 + fr];
