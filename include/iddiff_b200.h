@@ -314,8 +314,9 @@ int idb_spectrum_large_variant(double* G, int n, int n_out, float* sv, void* wor
  * where cudaMalloc is not (under CUDA graph capture, in tight serving loops, in harnesses that forbid it).  It has no
  * counterpart in the reference.  Limit: n <= 4096
  * (idb_spectrum_large_static_max_n()); a larger n is rejected with an error, use idb_spectrum_large there.  Same
- * arguments, output and kernels as idb_spectrum_large otherwise (G [n][n] fp64 is overwritten; sv [n_out] fp32
- * descending).  Every call on a device shares the one array: calls that overlap on the GPU race -- serialise them.  Nothing
+ * arguments and output as idb_spectrum_large otherwise (G [n][n] fp64 is overwritten; sv [n_out] fp32 descending); it
+ * always runs the one-class fused tridiagonalisation kernel (idb_spectrum_large_variant 1), whose workspace is 8 n
+ * doubles -- the panel kernel idb_spectrum_large prefers from n = 3584 keeps megabytes of per-CTA partial sums.  Every call on a device shares the one array: calls that overlap on the GPU race -- serialise them.  Nothing
  * needs clearing between calls (every workspace word is written before it is read). */
 #define IDB_SPECTRUM_STATIC_MAX_N 4096
 int idb_spectrum_large_static_max_n(void);
