@@ -173,6 +173,15 @@ __device__ __forceinline__ double tf_block_sum(double v, double* red) {
     return t;
 }
 
+#ifdef TF_PROFILE   // phase timers of CTA 0 (tools/tridiag_small_profile.cu)
+__device__ double tf_prof[8];
+#define TF_TICK_START() long long tf_t = clock64()
+#define TF_TICK(i) do { long long tf_n = clock64(); tf_acc[i] += tf_n - tf_t; tf_t = tf_n; } while (0)
+#else
+#define TF_TICK_START() do {} while (0)
+#define TF_TICK(i) do {} while (0)
+#endif
+
 template <int T, bool CACHE, bool SMEM_A>
 __global__ void __launch_bounds__(TF_THREADS, 1) tridiag_fused_small_kernel(const double* __restrict__ G, int n,
                                                                             uint8_t* __restrict__ workspace) {
@@ -202,6 +211,11 @@ __global__ void __launch_bounds__(TF_THREADS, 1) tridiag_fused_small_kernel(cons
     }
     __syncthreads();
 
+#ifdef TF_PROFILE
+    long long tf_acc[4] = {0, 0, 0, 0};
+#endif
+    TF_TICK_START();
+    TF_TICK(3);
     bool pend = false;
     for (int k = 0; k + 2 < n; ++k) {
         const int r0 = k + 1;
@@ -233,6 +247,7 @@ __global__ void __launch_bounds__(TF_THREADS, 1) tridiag_fused_small_kernel(cons
             e_out[k] = beta;
         }
         __syncthreads();
+        TF_TICK(0);
         // (2) one pass over the trailing block
         if (pend || tau != 0.0) {
             double cacc[T], uj[CACHE ? T : 1], wj[CACHE ? T : 1], vj[CACHE ? T : 1];
@@ -304,6 +319,7 @@ __global__ void __launch_bounds__(TF_THREADS, 1) tridiag_fused_small_kernel(cons
             }
         }
         __syncthreads();
+        TF_TICK(1);
         // (3) p = tau A u,  w_new = p - (tau/2)(p.u) u,  (v, w) <- (u, w_new)
         if (tau != 0.0) {
             double pv = 0.0;
@@ -326,7 +342,12 @@ __global__ void __launch_bounds__(TF_THREADS, 1) tridiag_fused_small_kernel(cons
             pend = false;
         }
         __syncthreads();
+        TF_TICK(2);
     }
+#ifdef TF_PROFILE
+    if (blockIdx.x == 0 && tid == 0)
+        for (int i = 0; i < 4; ++i) tf_prof[i] = (double)tf_acc[i];
+#endif
     if (tid == 0) {
         const int ia = n - 2, ib = n - 1;
         double va = 0.0, vb = 0.0, wa = 0.0, wb = 0.0;
