@@ -188,7 +188,10 @@ __global__ void __launch_bounds__(TF_THREADS, 1) tridiag_fused_small_kernel(cons
     extern __shared__ __align__(16) uint8_t tri_smem[];
     __shared__ double red[TF_WARPS];
     const int a = blockIdx.x;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31;
+    // warp-uniform by construction AND known to be so to the compiler: the shuffles of the pass below then need no
+    // re-convergence sequences (WARPSYNC.COLLECTIVE / ENDCOLLECTIVE)
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
     const size_t per_anchor = tri_packed_bytes(n) + 2 * (size_t)n * sizeof(double);
     uint8_t* ws = workspace + (size_t)a * per_anchor;
     const int nv = (n + 1) & ~1;
@@ -212,7 +215,7 @@ __global__ void __launch_bounds__(TF_THREADS, 1) tridiag_fused_small_kernel(cons
     __syncthreads();
 
 #ifdef TF_PROFILE
-    long long tf_acc[4] = {0, 0, 0, 0};
+    long long tf_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 #endif
     TF_TICK_START();
     TF_TICK(3);
@@ -249,7 +252,7 @@ __global__ void __launch_bounds__(TF_THREADS, 1) tridiag_fused_small_kernel(cons
         __syncthreads();
         TF_TICK(0);
         // (2) one pass over the trailing block
-        if (pend || tau != 0.0) {
+        if (__any_sync(0xffffffffu, pend || tau != 0.0)) {      // (uniform over the CTA; the vote tells the compiler)
             double cacc[T], uj[CACHE ? T : 1], wj[CACHE ? T : 1], vj[CACHE ? T : 1];
 #pragma unroll
             for (int t = 0; t < T; ++t) {
@@ -262,6 +265,7 @@ __global__ void __launch_bounds__(TF_THREADS, 1) tridiag_fused_small_kernel(cons
                     vj[t] = in && pend ? v[j] : 0.0;
                 }
             }
+            TF_TICK(4);
             // TF_RB rows of this warp in flight together: independent dependency chains and interleaved reductions
             for (int ib = r0 + warp; ib < n; ib += TF_WARPS * TF_RB) {
                 double* Ai[TF_RB];
@@ -293,16 +297,17 @@ __global__ void __launch_bounds__(TF_THREADS, 1) tridiag_fused_small_kernel(cons
                     for (int b = 0; b < TF_RB; ++b) x[b] = Ai[b][j <= ir[b] ? j : r0];
 #pragma unroll
                     for (int b = 0; b < TF_RB; ++b) {
-                        // warp-uniform skip: fp64 issue is the scarce resource here, a fully masked row costs nothing
-                        if (r0 + 32 * t <= ir[b]) {
-                            const bool in = j <= ir[b];
-                            const double xn = x[b] - vi[b] * wjt - wi[b] * vjt;      // vi = wi = 0 unless pending
-                            if (in && pend) Ai[b][j] = xn;
-                            sr[b] = fma(xn, in ? ujt : 0.0, sr[b]);
-                            cacc[t] = fma(xn, j < ir[b] ? ui[b] : 0.0, cacc[t]);
-                        }
+                        // no branch per row: the pass is bound by the latency of its dependent fp64 chains (phase timers,
+                        // tools/tridiag_small_profile.cu), and straight-line code lets the four rows' chains interleave;
+                        // a group beyond the row is all-masked (loads from a safe address, contributes zeros)
+                        const bool in = j <= ir[b];
+                        const double xn = x[b] - vi[b] * wjt - wi[b] * vjt;      // vi = wi = 0 unless pending
+                        if (in && pend) Ai[b][j] = xn;
+                        sr[b] = fma(xn, in ? ujt : 0.0, sr[b]);
+                        cacc[t] = fma(xn, j < ir[b] ? ui[b] : 0.0, cacc[t]);
                     }
                 }
+                TF_TICK(5);
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1)
 #pragma unroll
@@ -311,12 +316,14 @@ __global__ void __launch_bounds__(TF_THREADS, 1) tridiag_fused_small_kernel(cons
 #pragma unroll
                     for (int b = 0; b < TF_RB; ++b)
                         if (ir[b] >= 0) rowp[ir[b]] = sr[b];
+                TF_TICK(6);
             }
 #pragma unroll
             for (int t = 0; t < T; ++t) {
                 const int j = r0 + lane + 32 * t;
                 if (j < n) cpart[warp * nv + j] = cacc[t];
             }
+            TF_TICK(7);
         }
         __syncthreads();
         TF_TICK(1);
@@ -346,7 +353,7 @@ __global__ void __launch_bounds__(TF_THREADS, 1) tridiag_fused_small_kernel(cons
     }
 #ifdef TF_PROFILE
     if (blockIdx.x == 0 && tid == 0)
-        for (int i = 0; i < 4; ++i) tf_prof[i] = (double)tf_acc[i];
+        for (int i = 0; i < 8; ++i) tf_prof[i] = (double)tf_acc[i];
 #endif
     if (tid == 0) {
         const int ia = n - 2, ib = n - 1;

@@ -33,8 +33,8 @@ int main(int argc, char** argv) {
     }
     double acc[8];
     cudaMemcpyFromSymbol(acc, idb::tf_prof, sizeof(acc));
-    const char* names[4] = {"(1) column + reflector", "(2) fused pass", "(3) p, w", "load"};
-    double tot = 0; for (int i = 0; i < 4; ++i) tot += acc[i];
-    for (int i = 0; i < 4; ++i) printf("  %-24s %6.1f %%  %9.0f cycles / column\n", names[i], 100 * acc[i] / tot, acc[i] / n);
+    const char* names[8] = {"(1) column + reflector", "(2) wait at the barrier after the pass", "(3) p, w", "load", "(2a) column-side registers", "(2b) batch: loads + fma", "(2c) batch: row reduction", "(2d) column partials out"};
+    double tot = 0; for (int i = 0; i < 8; ++i) tot += acc[i];
+    for (int i = 0; i < 8; ++i) printf("  %-40s %6.1f %%  %9.0f cycles / column\n", names[i], 100 * acc[i] / tot, acc[i] / n);
     return 0;
 }
