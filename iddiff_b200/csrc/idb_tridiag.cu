@@ -150,7 +150,7 @@ __global__ void __launch_bounds__(TRI_THREADS, 1) tridiag_kernel(const double* _
 }
 
 // Fused variant (default): the rank-2 update of step k-1 and the symmetric matrix-vector product of step k in ONE pass
-// over the packed trailing block.  A warp owns rows i = r0 + warp, r0 + warp + #warps, ... and walks each along its
+// over the packed trailing block.  A warp owns batches of four consecutive rows (r0 + 4 warp + 64 q ...) and walks each along its
 // contiguous columns (conflict-free); an element A[i][j] is read once, gets the pending pair (v, w) applied, is
 // written back, and feeds BOTH halves of the symmetric product: the row sum p_i (a warp reduction) and the column sum
 // p_j, which a lane accumulates in registers for its own columns j = r0 + lane + 32 t over all rows of the warp.  The
@@ -267,13 +267,15 @@ __global__ void __launch_bounds__(TF_THREADS, 1) tridiag_fused_small_kernel(cons
             }
             TF_TICK(4);
             // TF_RB rows of this warp in flight together: independent dependency chains and interleaved reductions
-            for (int ib = r0 + warp; ib < n; ib += TF_WARPS * TF_RB) {
+            // a batch = TF_RB CONSECUTIVE rows (lengths differ by at most TF_RB - 1: no column group is walked for a row
+            // that does not reach it; with rows dealt one by one over the warps a batch spanned 48 rows of length)
+            for (int ib = r0 + warp * TF_RB; ib < n; ib += TF_WARPS * TF_RB) {
                 double* Ai[TF_RB];
                 double vi[TF_RB], wi[TF_RB], ui[TF_RB], sr[TF_RB];
                 int ir[TF_RB];
 #pragma unroll
                 for (int b = 0; b < TF_RB; ++b) {
-                    const int i = ib + b * TF_WARPS;
+                    const int i = ib + b;
                     const bool on = i < n;
                     ir[b] = on ? i : -1;                       // -1: no column satisfies j <= i
                     const int ic = on ? i : r0;
@@ -283,7 +285,7 @@ __global__ void __launch_bounds__(TF_THREADS, 1) tridiag_fused_small_kernel(cons
                     ui[b] = on ? u[ic] : 0.0;
                     sr[b] = 0.0;
                 }
-                const int imax = min(ib + (TF_RB - 1) * TF_WARPS, n - 1);
+                const int imax = min(ib + TF_RB - 1, n - 1);
 #pragma unroll
                 for (int t = 0; t < T; ++t) {
                     if (r0 + 32 * t > imax) break;             // warp-uniform: no row of this batch reaches these columns
@@ -308,14 +310,23 @@ __global__ void __launch_bounds__(TF_THREADS, 1) tridiag_fused_small_kernel(cons
                     }
                 }
                 TF_TICK(5);
+                {   // transposing butterfly: the four row sums over 32 lanes in 2 + 1 + 3 shuffles; lane 8 g ends with row g
+                    static_assert(TF_RB == 4, "butterfly written for four rows");
+                    const bool h16 = lane & 16, h8 = lane & 8;
+                    double t2[2];
 #pragma unroll
-                for (int o = 16; o > 0; o >>= 1)
-#pragma unroll
-                    for (int b = 0; b < TF_RB; ++b) sr[b] += __shfl_xor_sync(0xffffffffu, sr[b], o);
-                if (lane == 0)
-#pragma unroll
-                    for (int b = 0; b < TF_RB; ++b)
-                        if (ir[b] >= 0) rowp[ir[b]] = sr[b];
+                    for (int e2 = 0; e2 < 2; ++e2) {
+                        const double keep = h16 ? sr[e2 + 2] : sr[e2], send = h16 ? sr[e2] : sr[e2 + 2];
+                        t2[e2] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+                    }
+                    const double keep = h8 ? t2[1] : t2[0], send = h8 ? t2[0] : t2[1];
+                    double t1 = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+                    t1 += __shfl_xor_sync(0xffffffffu, t1, 4);
+                    t1 += __shfl_xor_sync(0xffffffffu, t1, 2);
+                    t1 += __shfl_xor_sync(0xffffffffu, t1, 1);
+                    const int irg = h16 ? (h8 ? ir[3] : ir[2]) : (h8 ? ir[1] : ir[0]);
+                    if ((lane & 7) == 0 && irg >= 0) rowp[irg] = t1;
+                }
                 TF_TICK(6);
             }
 #pragma unroll
