@@ -156,9 +156,17 @@ __global__ void __launch_bounds__(TRI_THREADS, 1) tridiag_kernel(const double* _
 // p_j, which a lane accumulates in registers for its own columns j = r0 + lane + 32 t over all rows of the warp.  The
 // per-warp column sums meet in shared memory.  2 accesses of the matrix per eliminated column instead of 4, and 5
 // block-wide synchronisations instead of 10 -- the stage is latency-bound (one anchor per SM), so that is its time.
-constexpr int TF_THREADS = 512;
+#ifdef TF_EXP_THREADS
+constexpr int TF_THREADS = TF_EXP_THREADS;
+#else
+constexpr int TF_THREADS = 256;   // measured (tools/tridiag_small_profile.cu, 512 anchors of n = 200, tridiag + bisect): 512 threads x 4-row
+#endif                              // batches 5.07 ms (128-register cap: spills), 384 x 4 3.92, 256 x 4 3.87, 256 x 8 3.79, 192 x 8 4.14, 128 x 8 4.23
 constexpr int TF_WARPS = TF_THREADS / 32;
-constexpr int TF_RB = 4;
+#ifdef TF_EXP_RB
+constexpr int TF_RB = TF_EXP_RB;
+#else
+constexpr int TF_RB = 8;
+#endif
 
 __host__ __device__ inline size_t tf_vec_bytes(int n) { return (size_t)(4 + TF_WARPS) * ((n + 1) & ~1) * sizeof(double); }
 
@@ -310,8 +318,7 @@ __global__ void __launch_bounds__(TF_THREADS, 1) tridiag_fused_small_kernel(cons
                     }
                 }
                 TF_TICK(5);
-                {   // transposing butterfly: the four row sums over 32 lanes in 2 + 1 + 3 shuffles; lane 8 g ends with row g
-                    static_assert(TF_RB == 4, "butterfly written for four rows");
+                if constexpr (TF_RB == 4) {   // transposing butterfly: four row sums over 32 lanes in 2 + 1 + 3 shuffles; lane 8 g ends with row g
                     const bool h16 = lane & 16, h8 = lane & 8;
                     double t2[2];
 #pragma unroll
@@ -326,6 +333,29 @@ __global__ void __launch_bounds__(TF_THREADS, 1) tridiag_fused_small_kernel(cons
                     t1 += __shfl_xor_sync(0xffffffffu, t1, 1);
                     const int irg = h16 ? (h8 ? ir[3] : ir[2]) : (h8 ? ir[1] : ir[0]);
                     if ((lane & 7) == 0 && irg >= 0) rowp[irg] = t1;
+                } else {                      // eight rows: 4 + 2 + 1 + 2 shuffles; lane 4 g ends with row g
+                    static_assert(TF_RB == 4 || TF_RB == 8, "butterfly written for four or eight rows");
+                    const bool h16 = lane & 16, h8 = lane & 8, h4 = lane & 4;
+                    double t4[4], t2[2];
+#pragma unroll
+                    for (int e2 = 0; e2 < 4; ++e2) {
+                        const double keep = h16 ? sr[(e2 + 4) % TF_RB] : sr[e2], send = h16 ? sr[e2] : sr[(e2 + 4) % TF_RB];
+                        t4[e2] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+                    }
+#pragma unroll
+                    for (int e2 = 0; e2 < 2; ++e2) {
+                        const double keep = h8 ? t4[e2 + 2] : t4[e2], send = h8 ? t4[e2] : t4[e2 + 2];
+                        t2[e2] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+                    }
+                    const double keep = h4 ? t2[1] : t2[0], send = h4 ? t2[0] : t2[1];
+                    double t1 = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+                    t1 += __shfl_xor_sync(0xffffffffu, t1, 2);
+                    t1 += __shfl_xor_sync(0xffffffffu, t1, 1);
+                    const int rg = (h16 ? 4 : 0) + (h8 ? 2 : 0) + (h4 ? 1 : 0);
+                    int irg = ir[0];
+#pragma unroll
+                    for (int e2 = 1; e2 < TF_RB; ++e2) irg = rg == e2 ? ir[e2] : irg;
+                    if ((lane & 3) == 0 && irg >= 0) rowp[irg] = t1;
                 }
                 TF_TICK(6);
             }
