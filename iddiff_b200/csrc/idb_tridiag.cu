@@ -226,7 +226,6 @@ __global__ void __launch_bounds__(TF_THREADS, 1) tridiag_fused_small_kernel(cons
     long long tf_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 #endif
     TF_TICK_START();
-    TF_TICK(3);
     bool pend = false;
     for (int k = 0; k + 2 < n; ++k) {
         const int r0 = k + 1;
@@ -294,6 +293,7 @@ __global__ void __launch_bounds__(TF_THREADS, 1) tridiag_fused_small_kernel(cons
                     sr[b] = 0.0;
                 }
                 const int imax = min(ib + TF_RB - 1, n - 1);
+                TF_TICK(3);
 #pragma unroll
                 for (int t = 0; t < T; ++t) {
                     if (r0 + 32 * t > imax) break;             // warp-uniform: no row of this batch reaches these columns
@@ -301,20 +301,32 @@ __global__ void __launch_bounds__(TF_THREADS, 1) tridiag_fused_small_kernel(cons
                     const double ujt = CACHE ? uj[t] : (j < n ? u[j] : 0.0);
                     const double wjt = CACHE ? wj[t] : (pend && j < n ? w[j] : 0.0);
                     const double vjt = CACHE ? vj[t] : (pend && j < n ? v[j] : 0.0);
-                    // branch-free: every load is issued up front from a safe address, masked lanes contribute zeros
                     double x[TF_RB];
+                    if (r0 + 32 * t + 31 < ib && ib + TF_RB <= n) {
+                        // warp-uniform: the column group lies strictly inside EVERY row of the batch (consecutive rows) --
+                        // no masks, no address selects; most of the elements of the block go through here
 #pragma unroll
-                    for (int b = 0; b < TF_RB; ++b) x[b] = Ai[b][j <= ir[b] ? j : r0];
+                        for (int b = 0; b < TF_RB; ++b) x[b] = Ai[b][j];
 #pragma unroll
-                    for (int b = 0; b < TF_RB; ++b) {
-                        // no branch per row: the pass is bound by the latency of its dependent fp64 chains (phase timers,
-                        // tools/tridiag_small_profile.cu), and straight-line code lets the four rows' chains interleave;
-                        // a group beyond the row is all-masked (loads from a safe address, contributes zeros)
-                        const bool in = j <= ir[b];
-                        const double xn = x[b] - vi[b] * wjt - wi[b] * vjt;      // vi = wi = 0 unless pending
-                        if (in && pend) Ai[b][j] = xn;
-                        sr[b] = fma(xn, in ? ujt : 0.0, sr[b]);
-                        cacc[t] = fma(xn, j < ir[b] ? ui[b] : 0.0, cacc[t]);
+                        for (int b = 0; b < TF_RB; ++b) {
+                            const double xn = x[b] - vi[b] * wjt - wi[b] * vjt;  // vi = wi = 0 unless pending
+                            if (pend) Ai[b][j] = xn;
+                            sr[b] = fma(xn, ujt, sr[b]);
+                            cacc[t] = fma(xn, ui[b], cacc[t]);
+                        }
+                    } else {
+                        // the groups holding the diagonal: every load is issued up front from a safe address, masked lanes
+                        // contribute zeros; straight-line per-row code so that the rows' fp64 chains interleave
+#pragma unroll
+                        for (int b = 0; b < TF_RB; ++b) x[b] = Ai[b][j <= ir[b] ? j : r0];
+#pragma unroll
+                        for (int b = 0; b < TF_RB; ++b) {
+                            const bool in = j <= ir[b];
+                            const double xn = x[b] - vi[b] * wjt - wi[b] * vjt;
+                            if (in && pend) Ai[b][j] = xn;
+                            sr[b] = fma(xn, in ? ujt : 0.0, sr[b]);
+                            cacc[t] = fma(xn, j < ir[b] ? ui[b] : 0.0, cacc[t]);
+                        }
                     }
                 }
                 TF_TICK(5);

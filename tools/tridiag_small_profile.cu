@@ -6,7 +6,12 @@
 #include <vector>
 #include <cuda_runtime.h>
 #include "idb_kernels.h"
-namespace idb { extern __device__ double tf_prof[8]; size_t tridiag_workspace_bytes(int n_anchors, int n); }
+namespace idb {
+#ifdef TF_PROFILE
+extern __device__ double tf_prof[8];
+#endif
+size_t tridiag_workspace_bytes(int n_anchors, int n);
+}
 __global__ void fill_spd(double* G, int n, int A) {
     const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= (size_t)A * n * n) return;
@@ -31,10 +36,12 @@ int main(int argc, char** argv) {
         float ms = 0; cudaEventElapsedTime(&ms, a, b);
         printf("n %d anchors %d rep %d: tridiag + bisect %.3f ms (%s / %s)\n", n, A, rep, ms, cudaGetErrorString(e), cudaGetErrorString(e2));
     }
+#ifdef TF_PROFILE
     double acc[8];
     cudaMemcpyFromSymbol(acc, idb::tf_prof, sizeof(acc));
-    const char* names[8] = {"(1) column + reflector", "(2) wait at the barrier after the pass", "(3) p, w", "load", "(2a) column-side registers", "(2b) batch: loads + fma", "(2c) batch: row reduction", "(2d) column partials out"};
+    const char* names[8] = {"(1) column + reflector", "(2) wait at the barrier after the pass", "(3) p, w", "(2b0) batch set-up (row sides, pointers)", "(2a) column-side registers", "(2b) batch: loads + fma", "(2c) batch: row reduction", "(2d) column partials out"};
     double tot = 0; for (int i = 0; i < 8; ++i) tot += acc[i];
     for (int i = 0; i < 8; ++i) printf("  %-40s %6.1f %%  %9.0f cycles / column\n", names[i], 100 * acc[i] / tot, acc[i] / n);
+#endif
     return 0;
 }
