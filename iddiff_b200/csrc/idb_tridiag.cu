@@ -456,19 +456,18 @@ __device__ __forceinline__ int sturm_count(const double* __restrict__ d, const d
     double p0 = 1.0, p1 = d[0] - x;
     if (p1 == 0.0) p1 = -1e-300;
     int cnt = __double2hiint(p1) < 0;
+    // branch-free step, as in idb_eig_large.cu: the rare events (an exact zero, a rescale) are selects and exponent arithmetic
+#pragma unroll 4
     for (int i = 1; i < n; ++i) {
         double p2 = fma(d[i] - x, p1, -(e2[i - 1] * p0));
-        int hi = __double2hiint(p2);
-        if (((hi & 0x7ff00000) == 0) && p2 == 0.0) {       // exact zero: takes the sign opposite to p1 (a sign change)
-            p2 = -p1 * 0x1p-60;
-            hi = __double2hiint(p2);
-        }
-        cnt += (hi ^ __double2hiint(p1)) < 0;
+        const int h1 = __double2hiint(p1);
+        p2 = (p2 == 0.0) ? __hiloint2double((h1 ^ 0x80000000) - (60 << 20), __double2loint(p1)) : p2;   // -p1 2^-60: a sign change
+        const int hi = __double2hiint(p2);
+        cnt += (unsigned)(hi ^ h1) >> 31;
         const int ex = (hi >> 20) & 0x7ff;                   // biased exponent
-        if (ex > 1023 + 400) { p2 *= 0x1p-400; p1 *= 0x1p-400; }
-        else if (ex < 1023 - 400) { p2 *= 0x1p400; p1 *= 0x1p400; }
-        p0 = p1;
-        p1 = p2;
+        const int adj = ex > 1023 + 400 ? -(400 << 20) : (ex < 1023 - 400 ? (400 << 20) : 0);   // exact power-of-two rescale of the pair
+        p0 = __hiloint2double(h1 + adj, __double2loint(p1));
+        p1 = __hiloint2double(hi + adj, __double2loint(p2));
     }
     return cnt;
 }
