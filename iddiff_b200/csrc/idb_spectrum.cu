@@ -131,8 +131,8 @@ constexpr int CG40_LD = 52;   // row stride = 4 (mod 16) doubles: the 4 k-rows o
 __global__ void __launch_bounds__(160) center_gram40_kernel(const float* __restrict__ X, long long anchor_stride, int ld,
                                                             int K, int D, double scale,
                                                             const double* __restrict__ colmean, double* __restrict__ G) {
-    __shared__ double sA[16][CG40_LD];
-    __shared__ double sB[16][CG40_LD];
+    __shared__ __align__(16) double sA[16][CG40_LD];
+    __shared__ __align__(16) double sB[16][CG40_LD];
     const int T = (D + CG40 - 1) / CG40;
     int ti = 0, rem = blockIdx.x;
     while (rem >= T - ti) { rem -= T - ti; ++ti; }
@@ -146,33 +146,49 @@ __global__ void __launch_bounds__(160) center_gram40_kernel(const float* __restr
     double acc[5][2];
 #pragma unroll
     for (int n = 0; n < 5; ++n) acc[n][0] = acc[n][1] = 0.0;
-    const int skk = threadIdx.x / 10, sc = (threadIdx.x % 10) << 2;   // 16 k-rows x 10 groups of 4 columns
-    double mua[4], mub[4];
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        const int ca = ti * CG40 + sc + q, cb = tj * CG40 + sc + q;
-        mua[q] = ca < D ? mu[ca] : 0.0;
-        mub[q] = cb < D ? mu[cb] : 0.0;
-    }
+    // staging: 20 threads per k-row, two columns each (one conflict-free 16-byte shared store per operand), 8 rows per pass,
+    // two passes per 16-row slab.  ncu: the kernel is bound by shared-memory wavefronts (LSU data pipe 96 % busy), and the
+    // former mapping (4 scalar stores per thread, 32 bytes apart across lanes) spent 41 % of them on bank-conflicted stores.
+    const int skk = threadIdx.x / 20, sc = (threadIdx.x % 20) << 1;
+    const int ca = ti * CG40 + sc, cb = tj * CG40 + sc;
+    const double mua0 = ca < D ? mu[ca] : 0.0, mua1 = ca + 1 < D ? mu[ca + 1] : 0.0;
+    const double mub0 = cb < D ? mu[cb] : 0.0, mub1 = cb + 1 < D ? mu[cb + 1] : 0.0;
+    const bool vec2 = ((ld & 1) == 0) && ((reinterpret_cast<uintptr_t>(Xa) & 7) == 0) && ((D & 1) == 0);
     // the next 16-row slab is fetched into registers while the tensor cores work on the current one
-    float fa[4], fb[4];
+    float2 fa[2], fb[2];
     auto fetch = [&](int k0) {
-        const int k = k0 + skk;
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            const int ca = ti * CG40 + sc + q, cb = tj * CG40 + sc + q;
-            fa[q] = (k < K && ca < D) ? __ldg(Xa + (size_t)k * ld + ca) : 0.f;
-            fb[q] = (k < K && cb < D) ? __ldg(Xa + (size_t)k * ld + cb) : 0.f;
+        for (int ps = 0; ps < 2; ++ps) {
+            const int k = k0 + ps * 8 + skk;
+            fa[ps] = make_float2(0.f, 0.f);
+            fb[ps] = make_float2(0.f, 0.f);
+            if (k < K) {
+                const float* row = Xa + (size_t)k * ld;
+                if (vec2) {
+                    if (ca < D) fa[ps] = __ldg(reinterpret_cast<const float2*>(row + ca));
+                    if (cb < D) fb[ps] = __ldg(reinterpret_cast<const float2*>(row + cb));
+                } else {
+                    if (ca < D) fa[ps].x = __ldg(row + ca);
+                    if (ca + 1 < D) fa[ps].y = __ldg(row + ca + 1);
+                    if (cb < D) fb[ps].x = __ldg(row + cb);
+                    if (cb + 1 < D) fb[ps].y = __ldg(row + cb + 1);
+                }
+            }
         }
     };
     fetch(0);
     for (int k0 = 0; k0 < K; k0 += 16) {
-        const bool kin = k0 + skk < K;
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            const int ca = ti * CG40 + sc + q, cb = tj * CG40 + sc + q;
-            sA[skk][sc + q] = (kin && ca < D) ? ((double)fa[q] - mua[q]) * scale : 0.0;
-            sB[skk][sc + q] = (kin && cb < D) ? ((double)fb[q] - mub[q]) * scale : 0.0;
+        for (int ps = 0; ps < 2; ++ps) {
+            const int kr = ps * 8 + skk;
+            const bool kin = k0 + kr < K;
+            double2 va, vb;
+            va.x = (kin && ca < D) ? ((double)fa[ps].x - mua0) * scale : 0.0;
+            va.y = (kin && ca + 1 < D) ? ((double)fa[ps].y - mua1) * scale : 0.0;
+            vb.x = (kin && cb < D) ? ((double)fb[ps].x - mub0) * scale : 0.0;
+            vb.y = (kin && cb + 1 < D) ? ((double)fb[ps].y - mub1) * scale : 0.0;
+            *reinterpret_cast<double2*>(&sA[kr][sc]) = va;
+            *reinterpret_cast<double2*>(&sB[kr][sc]) = vb;
         }
         __syncthreads();
         if (k0 + 16 < K) fetch(k0 + 16);
