@@ -286,7 +286,7 @@ __global__ void __launch_bounds__(TF_THREADS, 1) tridiag_fused_small_kernel(cons
                     const bool on = i < n;
                     ir[b] = on ? i : -1;                       // -1: no column satisfies j <= i
                     const int ic = on ? i : r0;
-                    Ai[b] = A + (size_t)ic * (ic + 1) / 2;
+                    Ai[b] = A + ((ic * (ic + 1)) >> 1);        // 32-bit: n <= 225 on this path
                     vi[b] = on && pend ? v[ic] : 0.0;
                     wi[b] = on && pend ? w[ic] : 0.0;
                     ui[b] = on ? u[ic] : 0.0;
